@@ -1,0 +1,210 @@
+/*
+ * ptb.h — C ABI of the B200-native path-tracing integrator.
+ *
+ * Drop-in boundary for the trace / scatter / resolve dispatch of
+ * samukallio/path-tracer (`src/integrator`).  Each entry point names the
+ * reference interface it replaces (file:line relative to the reference root).
+ * The scene data model is unchanged: `ptb_scene_view` is a set of
+ * {pointer,count} pairs over the arrays `PackSceneData()` produces
+ * (src/scene/scene.hpp:347-356), byte-identical to src/scene/scene.hpp:82-173.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative PTB_E_* code;
+ *     ptb_last_error() returns a thread-local description of the last failure;
+ *   - handles are opaque and caller-owned; a renderer borrows its scene and
+ *     film (they must outlive it), exactly like basic_renderer borrows
+ *     vulkan_scene / vulkan_sample_buffer (src/integrator/basic.cpp:177-178);
+ *   - work is enqueued on the context's CUDA stream and returns immediately;
+ *     ptb_renderer_sync / downloads / host resolves synchronise;
+ *   - there is NO CPU fallback: every call fails with PTB_E_CUDA when no
+ *     sm_100 device is usable.
+ */
+#ifndef PTB_H
+#define PTB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PTB_OK            0
+#define PTB_E_INVALID    -1   /* bad argument / inconsistent scene arrays */
+#define PTB_E_CUDA       -2   /* CUDA runtime error (message in ptb_last_error) */
+#define PTB_E_NOMEM      -3
+#define PTB_E_UNSUPPORTED -4
+
+/* ---- packed scene records: src/scene/scene.hpp:82-173 (std430) ------------ */
+typedef struct { float To[16]; float From[16]; } ptb_packed_transform;               /* :82-86  col-major */
+typedef struct { float AtlasPlacementMinimum[2]; float AtlasPlacementMaximum[2];
+                 uint32_t AtlasImageIndex, Type, Flags, Unused0; } ptb_packed_texture; /* :90-98  */
+typedef struct { int32_t Type; uint32_t MaterialIndex, MeshRootNodeIndex, Pad0;
+                 ptb_packed_transform Transform; } ptb_packed_shape;                 /* :102-108 */
+typedef struct { float Minimum[3]; uint32_t ChildNodeIndices;
+                 float Maximum[3]; uint32_t ShapeIndex; } ptb_packed_shape_node;     /* :112-118 */
+typedef struct { float Position0[3]; uint32_t VertexIndex0;
+                 float Position1[3]; uint32_t VertexIndex1;
+                 float Position2[3]; uint32_t VertexIndex2; } ptb_packed_mesh_face;  /* :122-130 */
+typedef struct { uint32_t PackedNormal, PackedUV; } ptb_packed_mesh_vertex;          /* :134-138 */
+typedef struct { float Minimum[3]; uint32_t FaceBeginOrNodeIndex;
+                 float Maximum[3]; uint32_t FaceEndIndex; } ptb_packed_mesh_node;    /* :142-148 */
+typedef struct { float SkyboxMeanDirection[3]; float SkyboxConcentration;
+                 float SkyboxSamplingProbability, SkyboxBrightness;
+                 uint32_t SkyboxTextureIndex, ShapeCount;
+                 float SceneScatterRate; uint32_t Pad[3]; } ptb_packed_scene_globals; /* :152-161 */
+typedef struct { uint32_t Model; float FocalLength, ApertureRadius, SensorDistance;
+                 float SensorSize[2]; uint32_t Pad[2];
+                 ptb_packed_transform Transform; } ptb_packed_camera;                /* :165-173 */
+
+/* scene_dirty_flag: src/scene/scene.hpp:323-333 (same bit values) */
+#define PTB_SCENE_DIRTY_GLOBALS        (1u << 0)
+#define PTB_SCENE_DIRTY_TEXTURES       (1u << 1)
+#define PTB_SCENE_DIRTY_MATERIALS      (1u << 2)
+#define PTB_SCENE_DIRTY_SHAPES         (1u << 3)
+#define PTB_SCENE_DIRTY_MESHES         (1u << 4)
+#define PTB_SCENE_DIRTY_CAMERAS        (1u << 5)
+#define PTB_SCENE_DIRTY_SKYBOX_TEXTURE (1u << 6)
+#define PTB_SCENE_DIRTY_ALL            0xFFFFFFFFu
+
+/* The host arrays of `scene` after PackSceneData (src/scene/scene.hpp:347-356).
+ * Every pointer is HOST memory; ptb_scene_update copies what the dirty flags
+ * select, so the arrays may be freed on return. */
+typedef struct {
+    const ptb_packed_texture*     Textures;      uint32_t TextureCount;      uint32_t _r0;
+    const uint32_t*               MaterialData;  uint32_t MaterialWordCount; uint32_t _r1;  /* 32 words / slot */
+    const ptb_packed_shape*       Shapes;        uint32_t ShapeCount;        uint32_t _r2;
+    const ptb_packed_shape_node*  ShapeNodes;    uint32_t ShapeNodeCount;    uint32_t _r3;
+    const ptb_packed_mesh_face*   MeshFaces;     uint32_t MeshFaceCount;     uint32_t _r4;
+    const ptb_packed_mesh_vertex* MeshVertices;  uint32_t MeshVertexCount;   uint32_t _r5;
+    const ptb_packed_mesh_node*   MeshNodes;     uint32_t MeshNodeCount;     uint32_t _r6;
+    const ptb_packed_camera*      Cameras;       uint32_t CameraCount;       uint32_t _r7;
+    const float* const*           AtlasLayers;   uint32_t AtlasLayerCount;   /* scene::Images, RGBA32F */
+    uint32_t                      AtlasWidth;                                /* 4096 in the reference (scene.cpp:1122) */
+    uint32_t                      AtlasHeight;   uint32_t _r8;
+    const ptb_packed_scene_globals* Globals;
+} ptb_scene_view;
+
+/* render_flag: src/integrator/integrator.hpp:6-10 */
+#define PTB_RENDER_FLAG_ACCUMULATE    (1u << 0)
+#define PTB_RENDER_FLAG_SAMPLE_JITTER (1u << 1)
+
+/* tone_mapping_mode: src/integrator/integrator.hpp:12-19 */
+#define PTB_TONE_MAPPING_MODE_CLAMP    0u
+#define PTB_TONE_MAPPING_MODE_REINHARD 1u
+#define PTB_TONE_MAPPING_MODE_HABLE    2u
+#define PTB_TONE_MAPPING_MODE_ACES     3u
+
+/* resolve_parameters: src/integrator/integrator.hpp:43-48 */
+typedef struct { float Brightness; uint32_t ToneMappingMode; float ToneMappingWhiteLevel; } ptb_resolve_params;
+
+/* Integrator structure (north_star: both are implemented). */
+#define PTB_INTEGRATOR_WAVEFRONT  0u   /* trace kernel + scatter kernel per round, SoA state in HBM */
+#define PTB_INTEGRATOR_MEGAKERNEL 1u   /* one persistent kernel, path state in registers across rounds */
+
+/* Traversal backend for the trace step. */
+#define PTB_TRAVERSAL_BVH2_REFERENCE 0u /* the packed two-level BVH2 as-is, reference visiting order */
+#define PTB_TRAVERSAL_WIDE           1u /* compressed BVH8 re-flattened at ptb_scene_update */
+
+/* Tie rule for equal hit times. */
+#define PTB_TIE_FAITHFUL  0u  /* reference rules; needs PTB_TRAVERSAL_BVH2_REFERENCE */
+#define PTB_TIE_CANONICAL 1u  /* lowest (t, ShapeIndex, PrimitiveIndex) */
+
+/* The public tunables of basic_renderer (src/integrator/basic.hpp:19-25) that
+ * the application pokes before Reset/Run (src/application/application.cpp:104-107),
+ * plus the build's own knobs. */
+typedef struct {
+    uint32_t CameraIndex;
+    uint32_t RenderFlags;
+    uint32_t PathLengthLimit;            /* 0 = unlimited (reference behaviour: value is never read) */
+    float    PathTerminationProbability;
+    uint32_t Integrator;                 /* PTB_INTEGRATOR_* */
+    uint32_t Traversal;                  /* PTB_TRAVERSAL_*  */
+    uint32_t TieMode;                    /* PTB_TIE_*        */
+    uint32_t Reserved;
+} ptb_render_params;
+
+typedef struct {
+    uint64_t rays_traced;      /* trace invocations on live slots  (Mrays/s numerator)  */
+    uint64_t paths_finished;   /* accumulator alpha increments     (Mpaths/s numerator) */
+    uint64_t kernel_launches;  /* kernels launched by this renderer since creation      */
+    uint64_t frame_index;      /* basic_renderer::FrameIndex */
+} ptb_stats;
+
+/* Test / preview ray cast record (K1 on caller rays; preview_render.glsl:96-109). */
+typedef struct { float ox, oy, oz, dx, dy, dz, duration; } ptb_ray;
+typedef struct {
+    float    t;
+    uint32_t shape, prim, material, shape_type;   /* shape == 0xFFFFFFFF: miss */
+    float    nx, ny, nz, tx, ty, tz, u, v;
+    float    bx, by, bz;
+} ptb_hit;
+
+typedef struct ptb_context  ptb_context;
+typedef struct ptb_scene    ptb_scene;
+typedef struct ptb_film     ptb_film;
+typedef struct ptb_renderer ptb_renderer;
+
+const char* ptb_last_error(void);
+const char* ptb_version(void);
+
+/* Replaces CreateVulkan/DestroyVulkan as far as the integrator needs a device
+ * (src/core/vulkan.cpp:1816): binds one CUDA device (one process per GPU). */
+int  ptb_context_create(int cuda_device, ptb_context** out);
+void ptb_context_destroy(ptb_context* ctx);
+int  ptb_context_sync(ptb_context* ctx);
+/* cudaStream_t of the context, for callers that share buffers with it. */
+void* ptb_context_stream(ptb_context* ctx);
+
+/* CreateVulkanScene / UpdateVulkanScene / DestroyVulkanScene
+ * (src/scene/scene.hpp:440-442, scene.cpp:1643-2006).  Update synchronises the
+ * stream first (the reference does vkDeviceWaitIdle, scene.cpp:1704), copies the
+ * arrays selected by dirty_flags and re-flattens the wide BVH when meshes change. */
+int  ptb_scene_create(ptb_context* ctx, ptb_scene** out);
+int  ptb_scene_update(ptb_scene* scene, const ptb_scene_view* view, uint32_t dirty_flags);
+void ptb_scene_destroy(ptb_scene* scene);
+
+/* CreateSampleBuffer / DestroySampleBuffer (src/integrator/integrator.hpp:51-53):
+ * the RGBA32F accumulator (rgb = sum of CIE XYZ, a = sample count).
+ * `external_device_rgba` (may be NULL) lets the caller own the device buffer,
+ * e.g. a tensor that a collective reduces. */
+int  ptb_film_create(ptb_context* ctx, uint32_t width, uint32_t height, void* external_device_rgba, ptb_film** out);
+void ptb_film_destroy(ptb_film* film);
+void* ptb_film_device_accum(ptb_film* film);
+int  ptb_film_download_accum(ptb_film* film, float* host_rgba, size_t count_floats);
+int  ptb_film_upload_accum(ptb_film* film, const float* host_rgba, size_t count_floats);
+/* RenderSampleBuffer (src/integrator/integrator.hpp:55-60, resolve.glsl:112-130):
+ * normalise by alpha, XYZ->sRGB, Brightness, tone-map; then the sRGB OETF the
+ * reference gets from its _SRGB swapchain.  Either output may be NULL.
+ * host_srgb8 is W*H*4 bytes (RGBA), host_linear_rgb is W*H*3 floats (pre-OETF). */
+int  ptb_film_resolve(ptb_film* film, const ptb_resolve_params* params, uint8_t* host_srgb8, float* host_linear_rgb);
+/* Same, output left in device memory (W*H*4 bytes), no synchronisation. */
+int  ptb_film_resolve_device(ptb_film* film, const ptb_resolve_params* params, void* device_srgb8);
+
+/* CreateBasicRenderer / DestroyBasicRenderer (src/integrator/basic.hpp:28-29). */
+int  ptb_renderer_create(ptb_context* ctx, ptb_scene* scene, ptb_film* film, ptb_renderer** out);
+void ptb_renderer_destroy(ptb_renderer* r);
+/* The caller-poked public fields of basic_renderer (basic.hpp:19-25). */
+int  ptb_renderer_set_params(ptb_renderer* r, const ptb_render_params* params);
+int  ptb_renderer_set_frame_index(ptb_renderer* r, uint32_t frame_index);
+/* ResetBasicRenderer (basic.cpp:285-304): clear the film, start one path per pixel. */
+int  ptb_renderer_reset(ptb_renderer* r);
+/* RunBasicRenderer (basic.cpp:306-332): FrameIndex += 1, then `rounds` x {trace, scatter}
+ * sharing that seed. */
+int  ptb_renderer_run(ptb_renderer* r, uint32_t rounds);
+/* `frames` consecutive RunBasicRenderer(…, 1) calls — what Update() issues in
+ * steady state, one per displayed frame (application.cpp:114) — as one call. */
+int  ptb_renderer_run_frames(ptb_renderer* r, uint32_t frames);
+int  ptb_renderer_sync(ptb_renderer* r);
+int  ptb_renderer_stats(ptb_renderer* r, ptb_stats* out);
+/* Debug/test: download one named SoA state array (names of basic.glsl.inc:23-59). */
+int  ptb_renderer_download_state(ptb_renderer* r, const char* name, void* host, size_t bytes);
+uint32_t ptb_renderer_slot_count(ptb_renderer* r);
+
+/* Trace() on caller-supplied host rays (K1/K5; the ray-cast parity harness). */
+int  ptb_raycast(ptb_scene* scene, const ptb_ray* host_rays, size_t n, uint32_t traversal, uint32_t tie_mode, ptb_hit* host_hits);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTB_H */

@@ -1,0 +1,65 @@
+"""In-tree builds of the native libraries.
+
+* ``libptb.so``        CUDA C ABI (include/ptb.h), sm_100a only      -> build_cuda()
+* ``libptb_scene.so``  host scene layer (CPU, mirrors scene.hpp API)  -> build_scene()
+
+The built files are git-ignored but travel to the GPU box with gpurun.
+"""
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+REPO = os.path.dirname(ROOT)
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+
+HOST_SOURCES = ["scene.cpp", "pack.cpp", "spectrum.cpp", "procedural.cpp", "capi.cpp"]
+CUDA_SOURCES = ["ptb_api.cu"]
+
+SPECTRUM_TABLE = os.path.join(ROOT, "data", "sRGBSpectrumTable.dat")
+
+
+def _newer(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def _run(cmd, cwd):
+    r = subprocess.run(cmd, cwd=cwd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout)
+        raise RuntimeError("build failed: " + " ".join(cmd))
+    return r.stdout
+
+
+def build_scene(force=False):
+    d = os.path.join(ROOT, "host")
+    out = os.path.join(ROOT, "libptb_scene.so")
+    deps = [os.path.join(d, f) for f in os.listdir(d)] + [os.path.join(REPO, "include", "ptb.h")]
+    if force or _newer(out, deps):
+        _run(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-pthread", "-shared", "-o", out] + HOST_SOURCES, d)
+    return out
+
+
+def cuda_flags():
+    return ["-std=c++17", "-O3", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a",
+            "--fmad=false",            # numerical contract with the oracle: no implicit contraction
+            "-Xcompiler", "-fPIC", "-shared", "-cudart", "static"]
+
+
+def build_cuda(force=False, verbose=False):
+    d = os.path.join(ROOT, "csrc")
+    out = os.path.join(ROOT, "libptb.so")
+    deps = [os.path.join(d, f) for f in os.listdir(d)] + [os.path.join(REPO, "include", "ptb.h")]
+    if force or _newer(out, deps):
+        cmd = [NVCC] + cuda_flags() + (["-Xptxas", "-v"] if verbose else []) + ["-I", os.path.join(REPO, "include"), "-o", out] + CUDA_SOURCES
+        log = _run(cmd, d)
+        if verbose:
+            print(log)
+    return out
+
+
+def build_all(force=False):
+    return build_scene(force), build_cuda(force)

@@ -1,0 +1,392 @@
+// Host scene layer, part 2: PackSceneData — flattening of the source
+// description into the packed arrays the integrator consumes.
+// Follows /root/reference/src/scene/scene.cpp:1031-1093 (ShapeBounds) and
+// :1115-1621 (PackSceneData); material packers follow basic_diffuse.hpp:17-28,
+// basic_metal.hpp:26-52, basic_translucent.hpp:26-61.
+#include "scene.hpp"
+#include <cassert>
+#include <functional>
+
+namespace ptb { namespace host {
+
+namespace {
+
+inline uint32_t f2u(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
+inline uint32_t tex_index(texture const* T) { return T ? T->PackedTextureIndex : TEXTURE_INDEX_NONE; }   // scene.hpp:391-395
+inline uint32_t mat_index(material const* M) { return M ? M->PackedMaterialIndex : 0u; }                 // scene.hpp:397-401
+
+void store_mat4(float* dst, mat4 const& m) { std::memcpy(dst, &m, 64); }
+ptb_packed_transform pack_transform(mat4 const& m) {     // scene.hpp:403-406
+    ptb_packed_transform t;
+    store_mat4(t.To, m);
+    store_mat4(t.From, inverse(m));
+    return t;
+}
+
+// Post-order walk with accumulated transforms; inactive entities prune their
+// subtree (scene.cpp:127-149).
+void walk(entity* E, mat4 const& Outer, std::function<void(entity*, mat4 const&)> const& Fn) {
+    if (!E->Active) return;
+    mat4 M = mul(Outer, make_transform(E->Transform.Position, E->Transform.Rotation, E->Transform.Scale));
+    for (entity* C : E->Children) walk(C, M, Fn);
+    Fn(E, M);
+}
+
+void put_spectrum(scene* S, uint32_t* A, uint32_t at, vec3 color) {
+    vec3 b = GetParametricSpectrumCoefficients(S->RGBSpectrumTable, color);
+    A[at + 0] = f2u(b.x); A[at + 1] = f2u(b.y); A[at + 2] = f2u(b.z);
+}
+
+// Word offsets are the `const uint` tables at the top of each material's
+// .glsl.inc / .hpp pair.
+void pack_material(scene* S, material const* M, uint32_t* A) {
+    switch (M->Type) {
+    case MATERIAL_TYPE_BASIC_DIFFUSE:
+        put_spectrum(S, A, 1, M->BaseColor);
+        A[4] = tex_index(M->BaseTexture);
+        break;
+    case MATERIAL_TYPE_BASIC_METAL:
+        put_spectrum(S, A, 1, M->BaseColor);       A[4] = tex_index(M->BaseTexture);
+        put_spectrum(S, A, 5, M->SpecularColor);   A[8] = tex_index(M->SpecularTexture);
+        A[9] = f2u(M->Roughness);                  A[10] = tex_index(M->RoughnessTexture);
+        A[11] = f2u(M->RoughnessAnisotropy);       A[12] = tex_index(M->RoughnessAnisotropyTexture);
+        break;
+    case MATERIAL_TYPE_BASIC_TRANSLUCENT:
+        A[1] = f2u(M->IOR);
+        A[2] = f2u(M->AbbeNumber);
+        A[3] = f2u(M->Roughness);                  A[4] = tex_index(M->RoughnessTexture);
+        A[5] = f2u(M->RoughnessAnisotropy);        A[6] = tex_index(M->RoughnessAnisotropyTexture);
+        put_spectrum(S, A, 7, M->TransmissionColor);
+        A[10] = f2u(M->TransmissionDepth);
+        put_spectrum(S, A, 11, M->ScatteringColor);
+        A[14] = f2u(M->ScatteringAnisotropy);
+        break;
+    case MATERIAL_TYPE_OPENPBR:
+        // Shader include disabled in the reference (scene.glsl.inc:685): the record only
+        // has to occupy its two slots so that slot numbering is unchanged.
+        break;
+    }
+}
+inline uint32_t material_words(material_type T) { return T == MATERIAL_TYPE_OPENPBR ? 64u : 32u; }   // scene.hpp:468-483
+
+// ---- texture atlas (scene.cpp:1120-1233) ----
+// The reference places rectangles with stb_rect_pack's skyline heuristic; any
+// non-overlapping placement is equivalent for rendering, so a simple shelf
+// packer is used here (placements are therefore not byte-comparable).
+struct shelf_packer {
+    uint32_t W, H, x = 0, y = 0, row_h = 0;
+    bool place(uint32_t w, uint32_t h, uint32_t& ox, uint32_t& oy) {
+        if (w > W || h > H) return false;
+        if (x + w > W) { y += row_h; x = 0; row_h = 0; }
+        if (y + h > H) return false;
+        ox = x; oy = y; x += w; row_h = std::max(row_h, h);
+        return true;
+    }
+};
+
+void pack_textures(scene* S) {
+    S->Images.clear();
+    S->TexturePack.clear();
+    std::vector<texture*> Pending(S->Textures.begin(), S->Textures.end());
+    const uint32_t AW = S->AtlasWidth, AH = S->AtlasHeight;
+    while (!Pending.empty()) {
+        shelf_packer P{AW, AH};
+        std::vector<float> Layer((size_t)AW * AH * 4, 0.0f);
+        const uint32_t ImageIndex = (uint32_t)S->Images.size();
+        std::vector<texture*> Left;
+        bool any = false;
+        for (texture* T : Pending) {
+            uint32_t rx, ry;
+            if (!P.place(T->Width, T->Height, rx, ry)) { Left.push_back(T); continue; }
+            any = true;
+            T->PackedTextureIndex = (uint32_t)S->TexturePack.size();
+            ptb_packed_texture K{};
+            K.AtlasImageIndex = ImageIndex;
+            // half-texel inset, V flipped: scene.cpp:1168-1177
+            K.AtlasPlacementMinimum[0] = (rx + 0.5f) / float(AW);
+            K.AtlasPlacementMinimum[1] = (ry + T->Height - 0.5f) / float(AH);
+            K.AtlasPlacementMaximum[0] = (rx + T->Width - 0.5f) / float(AW);
+            K.AtlasPlacementMaximum[1] = (ry + 0.5f) / float(AH);
+            K.Type = (uint32_t)T->Type;       // (left uninitialised by the reference)
+            K.Flags = T->EnableNearestFiltering ? (uint32_t)TEXTURE_FLAG_FILTER_NEAREST : 0u;
+            for (uint32_t Y = 0; Y < T->Height; Y++) {
+                vec4 const* Src = T->Pixels.data() + (size_t)Y * T->Width;
+                float* Dst = Layer.data() + ((size_t)(ry + Y) * AW + rx) * 4;
+                for (uint32_t X = 0; X < T->Width; X++, Dst += 4) {
+                    vec4 V = Src[X];
+                    if (T->Type == TEXTURE_TYPE_RAW) {
+                        Dst[0] = V.x; Dst[1] = V.y; Dst[2] = V.z; Dst[3] = V.w;
+                    } else if (T->Type == TEXTURE_TYPE_REFLECTANCE_WITH_ALPHA) {       // scene.cpp:1187-1195
+                        vec3 B = GetParametricSpectrumCoefficients(S->RGBSpectrumTable, {V.x, V.y, V.z});
+                        Dst[0] = B.x; Dst[1] = B.y; Dst[2] = B.z; Dst[3] = V.w;
+                    } else {                                                            // RADIANCE, scene.cpp:1196-1211
+                        float I = 2 * std::max(std::max(V.x, V.y), V.z);
+                        if (I > 1e-6f) {
+                            vec3 B = GetParametricSpectrumCoefficients(S->RGBSpectrumTable, {V.x / I, V.y / I, V.z / I});
+                            Dst[0] = B.x; Dst[1] = B.y; Dst[2] = B.z; Dst[3] = I;
+                        } else { Dst[0] = Dst[1] = Dst[2] = Dst[3] = 0.0f; }
+                    }
+                }
+            }
+            S->TexturePack.push_back(K);
+        }
+        if (!any) break;   // a texture larger than the atlas: dropped (the reference would loop forever)
+        S->Images.push_back(std::move(Layer));
+        Pending.swap(Left);
+    }
+}
+
+// scene.cpp:1031-1093
+bounds shape_bounds(scene const* S, ptb_packed_shape const& O) {
+    vec3 lo, hi;
+    switch (O.Type) {
+    case SHAPE_TYPE_MESH_INSTANCE: {
+        auto const& N = S->MeshNodePack[O.MeshRootNodeIndex];
+        lo = {N.Minimum[0], N.Minimum[1], N.Minimum[2]}; hi = {N.Maximum[0], N.Maximum[1], N.Maximum[2]};
+        break; }
+    case SHAPE_TYPE_PLANE: lo = {-1e9f, -1e9f, -1e-9f}; hi = {+1e9f, +1e9f, +1e-9f}; break;    // Q11
+    default: lo = {-1, -1, -1}; hi = {+1, +1, +1}; break;
+    }
+    mat4 To; std::memcpy(&To, O.Transform.To, 64);
+    bounds B;
+    for (int k = 0; k < 8; k++) {
+        vec4 C{(k & 1) ? hi.x : lo.x, (k & 2) ? hi.y : lo.y, (k & 4) ? hi.z : lo.z, 1.0f};
+        vec4 Wc = mul(To, C);
+        B.Minimum = min3(B.Minimum, {Wc.x, Wc.y, Wc.z});
+        B.Maximum = max3(B.Maximum, {Wc.x, Wc.y, Wc.z});
+    }
+    return B;
+}
+
+// Top-level BVH over shapes: greedy nearest-neighbour agglomeration with 16-bit
+// child indices, root swapped into slot 0 (scene.cpp:1402-1492, quirk Q9 incl. the
+// `Size.z*Size.z` area term at :1437).
+void build_shape_nodes(scene* S) {
+    auto& Nodes = S->ShapeNodePack;
+    Nodes.resize(1);
+    std::memset(&Nodes[0], 0, sizeof(Nodes[0]));
+    std::vector<uint16_t> Map;
+    for (uint32_t s = 0; s < S->ShapePack.size(); s++) {
+        bounds B = shape_bounds(S, S->ShapePack[s]);
+        Map.push_back((uint16_t)Nodes.size());
+        ptb_packed_shape_node N{};
+        N.Minimum[0] = B.Minimum.x; N.Minimum[1] = B.Minimum.y; N.Minimum[2] = B.Minimum.z;
+        N.Maximum[0] = B.Maximum.x; N.Maximum[1] = B.Maximum.y; N.Maximum[2] = B.Maximum.z;
+        N.ChildNodeIndices = 0; N.ShapeIndex = s;
+        Nodes.push_back(N);
+    }
+    if (S->ShapePack.empty()) return;
+
+    auto best_match = [&](uint16_t A) -> uint16_t {
+        auto const& NA = Nodes[Map[A]];
+        float BestArea = INFINITY;
+        uint16_t Best = 0xFFFF;
+        for (uint16_t B = 0; B < Map.size(); B++) {
+            if (A == B) continue;
+            auto const& NB = Nodes[Map[B]];
+            float sx = std::max(NA.Maximum[0], NB.Maximum[0]) - std::min(NA.Minimum[0], NB.Minimum[0]);
+            float sy = std::max(NA.Maximum[1], NB.Maximum[1]) - std::min(NA.Minimum[1], NB.Minimum[1]);
+            float sz = std::max(NA.Maximum[2], NB.Maximum[2]) - std::min(NA.Minimum[2], NB.Minimum[2]);
+            float Area = (sx * sy + sy * sz) + sz * sz;
+            if (Area <= BestArea) { BestArea = Area; Best = B; }
+        }
+        return Best;
+    };
+
+    uint16_t A = 0, B = best_match(A);
+    while (Map.size() > 1) {
+        uint16_t C = best_match(B);
+        if (A == C) {
+            uint16_t IA = Map[A], IB = Map[B];
+            ptb_packed_shape_node N{};
+            for (int k = 0; k < 3; k++) {
+                N.Minimum[k] = std::min(Nodes[IA].Minimum[k], Nodes[IB].Minimum[k]);
+                N.Maximum[k] = std::max(Nodes[IA].Maximum[k], Nodes[IB].Maximum[k]);
+            }
+            N.ChildNodeIndices = uint32_t(IA) | (uint32_t(IB) << 16);
+            N.ShapeIndex = SHAPE_INDEX_NONE;
+            Map[A] = (uint16_t)Nodes.size();
+            Map[B] = Map.back();
+            Map.pop_back();
+            if (A == Map.size()) A = B;
+            Nodes.push_back(N);
+            B = best_match(A);
+        } else {
+            A = B; B = C;
+        }
+    }
+    Nodes[0] = Nodes[Map[A]];
+    Nodes[Map[A]] = Nodes.back();
+    Nodes.pop_back();
+}
+
+}  // namespace
+
+uint32_t PackSceneData(scene* Scene) {
+    uint32_t Dirty = Scene->DirtyFlags;
+
+    if (Dirty & SCENE_DIRTY_TEXTURES) {
+        pack_textures(Scene);
+        Dirty |= SCENE_DIRTY_MATERIALS;
+    }
+
+    // Materials (scene.cpp:1236-1263): slots 0-1 = fallback OpenPBR; slot = word offset / 32.
+    if (Dirty & SCENE_DIRTY_MATERIALS) {
+        auto& P = Scene->MaterialAttributePack;
+        P.clear();
+        P.resize(64, 0u);
+        P[0] = MATERIAL_TYPE_OPENPBR;
+        for (material* M : Scene->Materials) {
+            size_t Off = P.size();
+            P.resize(Off + material_words(M->Type), 0u);
+            P[Off] = (uint32_t)M->Type;
+            pack_material(Scene, M, &P[Off]);
+            M->PackedMaterialIndex = (uint32_t)Off / 32;
+        }
+        Dirty |= SCENE_DIRTY_SHAPES;
+    }
+
+    // Meshes (scene.cpp:1266-1343): global vertex / face / node index bases.
+    if (Dirty & SCENE_DIRTY_MESHES) {
+        auto& VP = Scene->MeshVertexPack; auto& FP = Scene->MeshFacePack; auto& NP = Scene->MeshNodePack;
+        size_t nv = 0, nf = 0, nn = 0;
+        for (mesh* M : Scene->Meshes) { nv += M->Vertices.size(); nf += M->Faces.size(); nn += M->Nodes.size(); }
+        VP.clear(); VP.reserve(nv); FP.clear(); FP.reserve(nf); NP.clear(); NP.reserve(nn);
+        for (mesh* M : Scene->Meshes) {
+            const uint32_t VB = (uint32_t)VP.size(), FB = (uint32_t)FP.size(), NB = (uint32_t)NP.size();
+            for (mesh_vertex const& V : M->Vertices)
+                VP.push_back({pack_unit_vector(V.Normal), pack_half2x16(V.UV.x, V.UV.y)});
+            for (mesh_face const& F : M->Faces) {
+                ptb_packed_mesh_face K;
+                vec3 const& p0 = M->Vertices[F.VertexIndex[0]].Position;
+                vec3 const& p1 = M->Vertices[F.VertexIndex[1]].Position;
+                vec3 const& p2 = M->Vertices[F.VertexIndex[2]].Position;
+                K.Position0[0] = p0.x; K.Position0[1] = p0.y; K.Position0[2] = p0.z; K.VertexIndex0 = VB + F.VertexIndex[0];
+                K.Position1[0] = p1.x; K.Position1[1] = p1.y; K.Position1[2] = p1.z; K.VertexIndex1 = VB + F.VertexIndex[1];
+                K.Position2[0] = p2.x; K.Position2[1] = p2.y; K.Position2[2] = p2.z; K.VertexIndex2 = VB + F.VertexIndex[2];
+                FP.push_back(K);
+            }
+            for (mesh_node const& N : M->Nodes) {
+                ptb_packed_mesh_node K;
+                K.Minimum[0] = N.Bounds.Minimum.x; K.Minimum[1] = N.Bounds.Minimum.y; K.Minimum[2] = N.Bounds.Minimum.z;
+                K.Maximum[0] = N.Bounds.Maximum.x; K.Maximum[1] = N.Bounds.Maximum.y; K.Maximum[2] = N.Bounds.Maximum.z;
+                if (N.ChildNodeIndex > 0) { K.FaceBeginOrNodeIndex = NB + N.ChildNodeIndex; K.FaceEndIndex = 0; }
+                else { K.FaceBeginOrNodeIndex = FB + N.FaceBeginIndex; K.FaceEndIndex = FB + N.FaceEndIndex; }
+                NP.push_back(K);
+            }
+            M->PackedRootNodeIndex = NB;
+        }
+        Dirty |= SCENE_DIRTY_SHAPES;
+    }
+
+    // Shapes + top-level BVH (scene.cpp:1346-1498).
+    if (Dirty & SCENE_DIRTY_SHAPES) {
+        Scene->ShapePack.clear();
+        walk(&Scene->Root, mat4::identity(), [Scene](entity* E, mat4 const& M) {
+            ptb_packed_shape K{};
+            switch (E->Type) {
+            case ENTITY_TYPE_MESH_INSTANCE:
+                if (!E->Mesh) return;
+                K.Type = SHAPE_TYPE_MESH_INSTANCE; K.MeshRootNodeIndex = E->Mesh->PackedRootNodeIndex; break;
+            case ENTITY_TYPE_PLANE: K.Type = SHAPE_TYPE_PLANE; break;
+            case ENTITY_TYPE_SPHERE: K.Type = SHAPE_TYPE_SPHERE; break;
+            case ENTITY_TYPE_CUBE: K.Type = SHAPE_TYPE_CUBE; break;
+            default: return;
+            }
+            K.MaterialIndex = mat_index(E->Material);
+            K.Transform = pack_transform(M);
+            E->PackedShapeIndex = (uint32_t)Scene->ShapePack.size();
+            Scene->ShapePack.push_back(K);
+        });
+        build_shape_nodes(Scene);
+        Dirty |= SCENE_DIRTY_GLOBALS;
+    }
+
+    // Cameras (scene.cpp:1501-1539).  Pinhole sensor aspect is fixed at 2.0 (Q12).
+    if (Dirty & SCENE_DIRTY_CAMERAS) {
+        Scene->CameraPack.clear();
+        walk(&Scene->Root, mat4::identity(), [Scene](entity* E, mat4 const& M) {
+            if (E->Type != ENTITY_TYPE_CAMERA) return;
+            ptb_packed_camera K{};
+            K.Model = (uint32_t)E->CameraModel;
+            if (E->CameraModel == CAMERA_MODEL_PINHOLE) {
+                const float AspectRatio = 2.0f;
+                K.ApertureRadius = E->Pinhole.ApertureDiameterInMM / 2000.0f;
+                K.SensorSize[0] = 2 * std::tan((E->Pinhole.FieldOfViewInDegrees / 2) * 0.01745329251994329576923690768489f);
+                K.SensorSize[1] = K.SensorSize[0] / AspectRatio;
+                K.SensorDistance = 1.0f;
+            }
+            if (E->CameraModel == CAMERA_MODEL_THIN_LENS) {
+                K.FocalLength = E->ThinLens.FocalLengthInMM / 1000.0f;
+                K.ApertureRadius = E->ThinLens.ApertureDiameterInMM / 2000.0f;
+                K.SensorDistance = 1.0f / (1000.0f / E->ThinLens.FocalLengthInMM - 1.0f / E->ThinLens.FocusDistance);
+                K.SensorSize[0] = E->ThinLens.SensorSizeInMM.x / 1000.0f;
+                K.SensorSize[1] = E->ThinLens.SensorSizeInMM.y / 1000.0f;
+            }
+            K.Transform = pack_transform(M);
+            E->PackedCameraIndex = (uint32_t)Scene->CameraPack.size();
+            Scene->CameraPack.push_back(K);
+        });
+    }
+
+    // Skybox vMF lobe (scene.cpp:1542-1604, quirk Q23): luminance^2 * cos(theta) weights on raw RGB.
+    if (Dirty & SCENE_DIRTY_SKYBOX_TEXTURE) {
+        ptb_packed_scene_globals* G = &Scene->Globals;
+        texture* Sky = Scene->Root.SkyboxTexture;
+        G->SkyboxTextureIndex = tex_index(Sky);
+        if (Sky) {
+            const float PI_ = 3.141592653f, TAU_ = 6.283185306f;
+            vec3 Mean{0, 0, 0};
+            float WeightSum = 0.0f;
+            for (uint32_t Y = 0; Y < Sky->Height; Y++) {
+                float Theta = (0.5f - (Y + 0.5f) / Sky->Height) * PI_;
+                for (uint32_t X = 0; X < Sky->Width; X++) {
+                    float Phi = ((X + 0.5f) / Sky->Width - 0.5f) * TAU_;
+                    vec4 C = Sky->Pixels[(size_t)Y * Sky->Width + X];
+                    float Lum = dot3({0.2126f, 0.7152f, 0.0722f}, {C.x, C.y, C.z});
+                    float Weight = std::cos(Theta) * Lum * Lum;
+                    vec3 Dir{std::cos(Theta) * std::cos(Phi), std::cos(Theta) * std::sin(Phi), std::sin(Theta)};
+                    Mean = Mean + Weight * Dir;
+                    WeightSum += Weight;
+                }
+            }
+            Mean = Mean / WeightSum;
+            float R = length3(Mean);
+            vec3 D = Mean / R;
+            G->SkyboxMeanDirection[0] = D.x; G->SkyboxMeanDirection[1] = D.y; G->SkyboxMeanDirection[2] = D.z;
+            G->SkyboxConcentration = R * (3.0f - R * R) / (1 - R * R);
+        }
+        Dirty |= SCENE_DIRTY_GLOBALS;
+    }
+
+    if (Dirty & SCENE_DIRTY_GLOBALS) {           // scene.cpp:1607-1616
+        ptb_packed_scene_globals* G = &Scene->Globals;
+        G->SkyboxSamplingProbability = Scene->Root.SkyboxSamplingProbability;
+        G->SkyboxBrightness = Scene->Root.SkyboxBrightness;
+        G->SceneScatterRate = Scene->Root.ScatterRate;
+        G->ShapeCount = (uint32_t)Scene->ShapePack.size();
+    }
+
+    Scene->DirtyFlags = 0;
+    return Dirty;
+}
+
+ptb_scene_view scene::View() {
+    ImagePointers.clear();
+    for (auto const& L : Images) ImagePointers.push_back(L.data());
+    ptb_scene_view V{};
+    V.Textures = TexturePack.data();           V.TextureCount = (uint32_t)TexturePack.size();
+    V.MaterialData = MaterialAttributePack.data(); V.MaterialWordCount = (uint32_t)MaterialAttributePack.size();
+    V.Shapes = ShapePack.data();               V.ShapeCount = (uint32_t)ShapePack.size();
+    V.ShapeNodes = ShapeNodePack.data();       V.ShapeNodeCount = (uint32_t)ShapeNodePack.size();
+    V.MeshFaces = MeshFacePack.data();         V.MeshFaceCount = (uint32_t)MeshFacePack.size();
+    V.MeshVertices = MeshVertexPack.data();    V.MeshVertexCount = (uint32_t)MeshVertexPack.size();
+    V.MeshNodes = MeshNodePack.data();         V.MeshNodeCount = (uint32_t)MeshNodePack.size();
+    V.Cameras = CameraPack.data();             V.CameraCount = (uint32_t)CameraPack.size();
+    V.AtlasLayers = ImagePointers.data();      V.AtlasLayerCount = (uint32_t)ImagePointers.size();
+    V.AtlasWidth = AtlasWidth;                 V.AtlasHeight = AtlasHeight;
+    V.Globals = &Globals;
+    return V;
+}
+
+}}  // namespace ptb::host

@@ -1,0 +1,256 @@
+// Host scene layer, part 1: source-description API and the mesh BVH2 builder.
+// See scene.hpp.  Citations are to /root/reference/src/scene/scene.cpp.
+#include "scene.hpp"
+#include <cassert>
+#include <cstdio>
+#include <mutex>
+
+namespace ptb { namespace host {
+
+// ---- process-wide RGB->spectrum table (scene.cpp:918-927) ------------------
+namespace {
+std::mutex g_table_mutex;
+parametric_spectrum_table* g_table = nullptr;
+std::string g_table_path = "sRGBSpectrumTable.dat";
+}
+
+void SetSpectrumTablePath(char const* Path) { std::lock_guard<std::mutex> l(g_table_mutex); g_table_path = Path; }
+
+parametric_spectrum_table const* SharedSpectrumTable(char const* Path) {
+    std::lock_guard<std::mutex> l(g_table_mutex);
+    if (g_table) return g_table;
+    if (Path) g_table_path = Path;
+    g_table = new parametric_spectrum_table;
+    if (!LoadParametricSpectrumTable(g_table, g_table_path.c_str())) {
+        std::fprintf(stderr, "[ptb-host] %s not found, generating it (all host threads)...\n", g_table_path.c_str());
+        BuildParametricSpectrumTableForSRGB(g_table, 0);
+        if (!SaveParametricSpectrumTable(g_table, g_table_path.c_str()))
+            std::fprintf(stderr, "[ptb-host] warning: could not save %s\n", g_table_path.c_str());
+    }
+    return g_table;
+}
+
+// ---- entities (scene.cpp:161-268) -------------------------------------------
+entity* CreateEntity(scene* Scene, entity_type Type, entity* Parent) {
+    entity* E = new entity;
+    E->Type = Type;
+    if (!Parent) Parent = &Scene->Root;
+    E->Parent = Parent;
+    Parent->Children.push_back(E);
+    if (Type == ENTITY_TYPE_CAMERA) Scene->DirtyFlags |= SCENE_DIRTY_CAMERAS;
+    else Scene->DirtyFlags |= SCENE_DIRTY_SHAPES;
+    return E;
+}
+
+void DestroyEntity(scene* Scene, entity* Entity) {
+    if (entity* P = Entity->Parent) {
+        auto& C = P->Children;
+        C.erase(std::remove(C.begin(), C.end(), Entity), C.end());
+    }
+    std::vector<entity*> Kids = Entity->Children;
+    for (entity* K : Kids) { K->Parent = nullptr; DestroyEntity(Scene, K); }
+    Scene->DirtyFlags |= SCENE_DIRTY_SHAPES | SCENE_DIRTY_CAMERAS;
+    delete Entity;
+}
+
+// scene.cpp:380-410
+material* CreateMaterial(scene* Scene, material_type Type, char const* Name) {
+    material* M = new material;
+    M->Type = Type;
+    M->Name = Name ? Name : "New Material";
+    Scene->Materials.push_back(M);
+    Scene->DirtyFlags |= SCENE_DIRTY_MATERIALS;
+    return M;
+}
+
+// scene.cpp:270-292: 2x2 checker A B / B A.
+texture* CreateCheckerTexture(scene* Scene, char const* Name, texture_type Type, vec4 const& A, vec4 const& B) {
+    vec4 Px[4] = {A, B, B, A};
+    return CreateTexture(Scene, Name, Type, 2, 2, Px);
+}
+
+texture* CreateTexture(scene* Scene, char const* Name, texture_type Type, uint32_t Width, uint32_t Height, vec4 const* Pixels) {
+    texture* T = new texture;
+    T->Name = Name ? Name : "New Texture";
+    T->Type = Type;
+    T->Width = Width; T->Height = Height;
+    T->Pixels.assign(Pixels, Pixels + (size_t)Width * Height);
+    Scene->Textures.push_back(T);
+    Scene->DirtyFlags |= SCENE_DIRTY_TEXTURES;
+    return T;
+}
+
+// ---- mesh BVH2 (scene.cpp:424-599) -------------------------------------------
+namespace {
+
+inline void grow(bounds& B, vec3 P) { B.Minimum = min3(B.Minimum, P); B.Maximum = max3(B.Maximum, P); }
+inline void grow(bounds& B, bounds const& O) { B.Minimum = min3(B.Minimum, O.Minimum); B.Maximum = max3(B.Maximum, O.Maximum); }
+// scene.cpp:53-57
+inline float half_area(bounds const& B) {
+    vec3 E = B.Maximum - B.Minimum;
+    return (E.x * E.y + E.y * E.z) + E.z * E.x;
+}
+
+// Per-face cache kept in lock-step with Mesh->Faces while partitioning; holds
+// exactly the values the reference recomputes on the fly (scene.cpp:424-433,443-450).
+struct face_cache { vec3 Centroid; bounds Box; };
+
+struct builder {
+    mesh* Mesh;
+    std::vector<face_cache> Cache;
+
+    explicit builder(mesh* M) : Mesh(M), Cache(M->Faces.size()) {
+        for (size_t f = 0; f < M->Faces.size(); f++) {
+            face_cache& C = Cache[f];
+            for (int a = 0; a < 3; a++) {
+                float Sum = 0.0f;
+                for (int k = 0; k < 3; k++) Sum += M->Vertices[M->Faces[f].VertexIndex[k]].Position[a];
+                C.Centroid[a] = Sum / 3.0f;
+            }
+            for (int k = 0; k < 3; k++) grow(C.Box, M->Vertices[M->Faces[f].VertexIndex[k]].Position);
+        }
+    }
+
+    // BuildMeshNode (scene.cpp:435-599): top-down binned SAH, 32 bins per axis,
+    // cost N_L*A_L + N_R*A_R against N*A, children allocated adjacently.
+    void build(uint32_t NodeIndex, uint32_t Depth) {
+        constexpr uint32_t BINS = 32;
+        const uint32_t Begin = Mesh->Nodes[NodeIndex].FaceBeginIndex;
+        const uint32_t End = Mesh->Nodes[NodeIndex].FaceEndIndex;
+        const uint32_t FaceCount = End - Begin;
+
+        bounds NodeBounds;
+        for (uint32_t f = Begin; f < End; f++) grow(NodeBounds, Cache[f].Box);
+        Mesh->Nodes[NodeIndex].Bounds = NodeBounds;
+
+        int SplitAxis = 0;
+        float SplitPosition = 0.0f;
+        float SplitCost = +INFINITY;
+
+        for (int Axis = 0; Axis < 3; Axis++) {
+            float Lo = +INFINITY, Hi = -INFINITY;
+            for (uint32_t f = Begin; f < End; f++) {
+                Lo = std::min(Lo, Cache[f].Centroid[Axis]);
+                Hi = std::max(Hi, Cache[f].Centroid[Axis]);
+            }
+            if (Lo == Hi) continue;
+
+            bounds BinBox[BINS];
+            uint32_t BinCount[BINS] = {};
+            const float BinsPerUnit = float(BINS) / (Hi - Lo);
+            for (uint32_t f = Begin; f < End; f++) {
+                uint32_t b = std::min(static_cast<uint32_t>(BinsPerUnit * (Cache[f].Centroid[Axis] - Lo)), BINS - 1);
+                grow(BinBox[b], Cache[f].Box);
+                BinCount[b]++;
+            }
+
+            // Prefix (left) and suffix (right) sweeps: scene.cpp:506-532.
+            float LeftArea[BINS - 1], RightArea[BINS - 1];
+            uint32_t LeftCount[BINS - 1], RightCount[BINS - 1];
+            bounds LB, RB;
+            uint32_t LN = 0, RN = 0;
+            for (uint32_t i = 0; i < BINS - 1; i++) {
+                uint32_t j = BINS - 2 - i;
+                if (BinCount[i] > 0) { LN += BinCount[i]; grow(LB, BinBox[i]); }
+                LeftCount[i] = LN; LeftArea[i] = half_area(LB);
+                if (BinCount[j + 1] > 0) { RN += BinCount[j + 1]; grow(RB, BinBox[j + 1]); }
+                RightCount[j] = RN; RightArea[j] = half_area(RB);
+            }
+
+            const float Interval = (Hi - Lo) / float(BINS);
+            float Position = Lo + Interval;
+            for (uint32_t i = 0; i < BINS - 1; i++) {
+                float Cost = LeftCount[i] * LeftArea[i] + RightCount[i] * RightArea[i];
+                if (Cost < SplitCost) { SplitCost = Cost; SplitAxis = Axis; SplitPosition = Position; }
+                Position += Interval;
+            }
+        }
+
+        // Leaf if splitting does not pay (scene.cpp:552-554); no leaf-size clamp (Q20).
+        if (SplitCost >= FaceCount * half_area(NodeBounds)) return;
+
+        // In-place partition, scene.cpp:556-573 (the last candidate is never tested).
+        uint32_t Split = Begin, Swap = End - 1;
+        while (Split < Swap) {
+            if (Cache[Split].Centroid[SplitAxis] < SplitPosition) {
+                Split++;
+            } else {
+                std::swap(Mesh->Faces[Split], Mesh->Faces[Swap]);
+                std::swap(Cache[Split], Cache[Swap]);
+                Swap--;
+            }
+        }
+        if (Split == Begin || Split == End) return;
+
+        const uint32_t Left = static_cast<uint32_t>(Mesh->Nodes.size());
+        Mesh->Nodes[NodeIndex].ChildNodeIndex = Left;
+        mesh_node L; L.FaceBeginIndex = Begin; L.FaceEndIndex = Split;
+        mesh_node R; R.FaceBeginIndex = Split; R.FaceEndIndex = End;
+        Mesh->Nodes.push_back(L);
+        Mesh->Nodes.push_back(R);
+        Mesh->Depth = std::max(Mesh->Depth, Depth + 1);
+        build(Left, Depth + 1);
+        build(Left + 1, Depth + 1);
+    }
+};
+
+}  // namespace
+
+mesh* CreateMesh(scene* Scene, char const* Name, std::vector<mesh_vertex>&& Vertices, std::vector<mesh_face>&& Faces) {
+    mesh* M = new mesh;
+    M->Name = Name ? Name : "Mesh";
+    M->Vertices = std::move(Vertices);
+    M->Faces = std::move(Faces);
+    M->Nodes.reserve(2 * M->Faces.size());          // scene.cpp:853
+    mesh_node Root; Root.FaceBeginIndex = 0; Root.FaceEndIndex = static_cast<uint32_t>(M->Faces.size());
+    M->Nodes.push_back(Root);
+    builder B(M);
+    B.build(0, 0);
+    Scene->Meshes.push_back(M);
+    Scene->DirtyFlags |= SCENE_DIRTY_MATERIALS | SCENE_DIRTY_MESHES;   // scene.cpp:868-869
+    return M;
+}
+
+// scene.cpp:912-943
+scene* CreateScene(bool WithDefaults) {
+    scene* S = new scene;
+    S->Root.Name = "Scene";
+    S->Root.Type = ENTITY_TYPE_ROOT;
+    S->RGBSpectrumTable = SharedSpectrumTable();
+    std::memset(&S->Globals, 0, sizeof(S->Globals));
+    S->Globals.SkyboxConcentration = 1.0f;           // scene.hpp:152-161 defaults
+    S->Globals.SkyboxBrightness = 1.0f;
+    S->Globals.SkyboxTextureIndex = TEXTURE_INDEX_NONE;
+    if (WithDefaults) {
+        material* PlaneMaterial = CreateMaterial(S, MATERIAL_TYPE_BASIC_DIFFUSE, "Plane Material");
+        PlaneMaterial->BaseTexture = CreateCheckerTexture(S, "Plane Texture", TEXTURE_TYPE_REFLECTANCE_WITH_ALPHA, {1, 1, 1, 1}, {0.5f, 0.5f, 0.5f, 1});
+        PlaneMaterial->BaseTexture->EnableNearestFiltering = true;
+        entity* Plane = CreateEntity(S, ENTITY_TYPE_PLANE);
+        Plane->Name = "Plane";
+        Plane->Material = PlaneMaterial;
+        entity* Camera = CreateEntity(S, ENTITY_TYPE_CAMERA);
+        Camera->Name = "Camera";
+        Camera->Transform.Position = {0, 0, 1};
+    }
+    S->DirtyFlags = SCENE_DIRTY_ALL;
+    return S;
+}
+
+// scene.cpp:945-959
+void DestroyScene(scene* Scene) {
+    while (!Scene->Root.Children.empty()) DestroyEntity(Scene, Scene->Root.Children[0]);
+    for (mesh* M : Scene->Meshes) delete M;
+    for (material* M : Scene->Materials) delete M;
+    for (texture* T : Scene->Textures) delete T;
+    delete Scene;
+}
+
+static entity* find_shape(entity* E, uint32_t Index) {   // scene.cpp:1623-1640
+    if (!E->Active) return nullptr;
+    if (E->PackedShapeIndex == Index) return E;
+    for (entity* C : E->Children) if (entity* R = find_shape(C, Index)) return R;
+    return nullptr;
+}
+entity* FindEntityByPackedShapeIndex(scene* Scene, uint32_t PackedShapeIndex) { return find_shape(&Scene->Root, PackedShapeIndex); }
+
+}}  // namespace ptb::host
