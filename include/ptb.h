@@ -163,6 +163,16 @@ void* ptb_context_stream(ptb_context* ctx);
 int  ptb_scene_create(ptb_context* ctx, ptb_scene** out);
 int  ptb_scene_update(ptb_scene* scene, const ptb_scene_view* view, uint32_t dirty_flags);
 void ptb_scene_destroy(ptb_scene* scene);
+/* Result of the scene flattening done inside ptb_scene_update: the compressed
+ * 8-wide BVH that replaces the reference's nested BVH2 walks on the hot path
+ * (scene.glsl.inc:336-399,468-520).  status != 0: only the reference-layout
+ * traversal (PTB_TRAVERSAL_BVH2_REFERENCE) is usable for this scene. */
+typedef struct {
+    int32_t  status;
+    uint32_t node_count, prim_count, plane_count, depth, bvh2_depth;
+    double   sah_cost, build_seconds;
+} ptb_wide_info;
+int  ptb_scene_wide_info(ptb_scene* scene, ptb_wide_info* out);
 
 /* CreateSampleBuffer / DestroySampleBuffer (src/integrator/integrator.hpp:51-53):
  * the RGBA32F accumulator (rgb = sum of CIE XYZ, a = sample count).
@@ -196,6 +206,14 @@ int  ptb_renderer_run(ptb_renderer* r, uint32_t rounds);
  * steady state, one per displayed frame (application.cpp:114) — as one call. */
 int  ptb_renderer_run_frames(ptb_renderer* r, uint32_t frames);
 int  ptb_renderer_sync(ptb_renderer* r);
+/* Measurement aid (no reference counterpart: the reference has no timers):
+ * same work as ptb_renderer_run_frames, with CUDA events around every kernel launch
+ * on the context stream; returns the summed device time per kernel. */
+typedef struct {
+    float    trace_ms, scatter_ms, mega_ms;
+    uint32_t trace_launches, scatter_launches, mega_launches;
+} ptb_kernel_times;
+int  ptb_renderer_profile_frames(ptb_renderer* r, uint32_t frames, ptb_kernel_times* out);
 int  ptb_renderer_stats(ptb_renderer* r, ptb_stats* out);
 /* Debug/test: download one named SoA state array (names of basic.glsl.inc:23-59). */
 int  ptb_renderer_download_state(ptb_renderer* r, const char* name, void* host, size_t bytes);
@@ -203,6 +221,8 @@ uint32_t ptb_renderer_slot_count(ptb_renderer* r);
 
 /* Trace() on caller-supplied host rays (K1/K5; the ray-cast parity harness). */
 int  ptb_raycast(ptb_scene* scene, const ptb_ray* host_rays, size_t n, uint32_t traversal, uint32_t tie_mode, ptb_hit* host_hits);
+/* Same with both buffers already in device memory; enqueued on the context stream, no synchronisation. */
+int  ptb_raycast_device(ptb_scene* scene, const ptb_ray* device_rays, size_t n, uint32_t traversal, uint32_t tie_mode, ptb_hit* device_hits);
 
 #ifdef __cplusplus
 }

@@ -14,7 +14,7 @@ REPO = os.path.dirname(ROOT)
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
 HOST_SOURCES = ["scene.cpp", "pack.cpp", "spectrum.cpp", "procedural.cpp", "capi.cpp"]
-CUDA_SOURCES = ["ptb_api.cu"]
+CUDA_SOURCES = ["ptb_api.cu", "ptb_kernels.cu", "ptb_wide_build.cpp"]
 
 SPECTRUM_TABLE = os.path.join(ROOT, "data", "sRGBSpectrumTable.dat")
 
@@ -54,7 +54,7 @@ def build_cuda(force=False, verbose=False):
     out = os.path.join(ROOT, "libptb.so")
     deps = [os.path.join(d, f) for f in os.listdir(d)] + [os.path.join(REPO, "include", "ptb.h")]
     if force or _newer(out, deps):
-        cmd = [NVCC] + cuda_flags() + (["-Xptxas", "-v"] if verbose else []) + ["-I", os.path.join(REPO, "include"), "-o", out] + CUDA_SOURCES
+        cmd = [NVCC] + cuda_flags() + (["-Xptxas", "-v"] if verbose else []) + ["-I", os.path.join(REPO, "include"), "-I", d, "-o", out] + CUDA_SOURCES
         log = _run(cmd, d)
         if verbose:
             print(log)

@@ -1,0 +1,543 @@
+// C ABI of the integrator (include/ptb.h): contexts, scene upload + wide-BVH
+// flattening, film, renderer (reset / run / resolve) and the ray-cast harness.
+// Replaces the host side of src/integrator/{basic,integrator}.cpp and the
+// device-upload half of src/scene/scene.cpp:1643-2006.  There is no CPU
+// execution path: without a usable CUDA device every entry point fails.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "ptb.h"
+#include "ptb_kernels.h"
+#include "ptb_wide_build.h"
+
+using namespace ptb;
+
+namespace {
+
+thread_local std::string g_error;
+
+int fail(int code, const std::string& msg) { g_error = msg; return code; }
+int cuda_fail(cudaError_t e, const char* what) {
+    g_error = std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
+    return PTB_E_CUDA;
+}
+#define CU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return cuda_fail(e_, #x); } while (0)
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr; size_t n = 0;
+    cudaError_t upload(const T* host, size_t count, cudaStream_t st) {
+        if (count != n || !p) {
+            if (p) cudaFree(p);
+            p = nullptr; n = 0;
+            if (count) { cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T)); if (e != cudaSuccess) return e; }
+            n = count;
+        }
+        if (count) return cudaMemcpyAsync(p, host, count * sizeof(T), cudaMemcpyHostToDevice, st);
+        return cudaSuccess;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+};
+
+}  // namespace
+
+struct ptb_context { int device; cudaStream_t stream; };
+
+struct ptb_scene {
+    ptb_context* ctx;
+    DevBuf<ptb_packed_texture> textures;
+    DevBuf<uint32_t> materials;
+    DevBuf<ptb_packed_shape> shapes;
+    DevBuf<ptb_packed_shape_node> shape_nodes;
+    DevBuf<ptb_packed_mesh_face> faces;
+    DevBuf<ptb_packed_mesh_vertex> vertices;
+    DevBuf<ptb_packed_mesh_node> mesh_nodes;
+    DevBuf<ptb_packed_camera> cameras;
+    std::vector<DevBuf<float>> layers;
+    DevBuf<const float*> layer_table;
+    DevBuf<uint32_t> wide_nodes;
+    DevBuf<float> wide_prims;
+    DevBuf<uint32_t> wide_planes;
+    DeviceScene ds;
+    ptb_wide_info wide_info;
+};
+
+struct ptb_film {
+    ptb_context* ctx;
+    uint32_t width, height;
+    float4* accum; bool external;
+    uchar4* srgb; float* linear;
+};
+
+struct ptb_renderer {
+    ptb_context* ctx; ptb_scene* scene; ptb_film* film;
+    ptb_render_params params;
+    uint32_t frame_index;
+    RenderConsts pc;
+    WavefrontState st;
+    void* state_block;
+    uint64_t rays_traced, kernel_launches;
+};
+
+extern "C" {
+
+const char* ptb_last_error(void) { return g_error.c_str(); }
+const char* ptb_version(void) { return "path_tracer_b200 0.1 (sm_100a)"; }
+
+int ptb_context_create(int cuda_device, ptb_context** out) {
+    if (!out) return fail(PTB_E_INVALID, "ptb_context_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+    if (cuda_device < 0 || cuda_device >= count) return fail(PTB_E_CUDA, "ptb_context_create: no such CUDA device (there is no CPU fallback)");
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, cuda_device));
+    if (prop.major != 10) return fail(PTB_E_UNSUPPORTED, std::string("ptb_context_create: kernels are built for sm_100a only, device is ") + prop.name);
+    CU(cudaSetDevice(cuda_device));
+    ptb_context* c = new ptb_context();
+    c->device = cuda_device;
+    e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { delete c; return cuda_fail(e, "cudaStreamCreate"); }
+    *out = c;
+    return PTB_OK;
+}
+void ptb_context_destroy(ptb_context* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+int ptb_context_sync(ptb_context* ctx) {
+    if (!ctx) return fail(PTB_E_INVALID, "ptb_context_sync: NULL context");
+    CU(cudaStreamSynchronize(ctx->stream));
+    return PTB_OK;
+}
+void* ptb_context_stream(ptb_context* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+// ---- scene ----
+int ptb_scene_create(ptb_context* ctx, ptb_scene** out) {
+    if (!ctx || !out) return fail(PTB_E_INVALID, "ptb_scene_create: NULL argument");
+    ptb_scene* s = new ptb_scene();
+    s->ctx = ctx;
+    std::memset(&s->ds, 0, sizeof s->ds);
+    std::memset(&s->wide_info, 0, sizeof s->wide_info);
+    s->ds.wide_tlas_root = 0xFFFFFFFFu;
+    s->ds.globals.SkyboxTextureIndex = 0xFFFFFFFFu;
+    *out = s;
+    return PTB_OK;
+}
+
+int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
+    if (!s || !v) return fail(PTB_E_INVALID, "ptb_scene_update: NULL argument");
+    cudaStream_t st = s->ctx->stream;
+    CU(cudaSetDevice(s->ctx->device));
+    CU(cudaStreamSynchronize(st));      // the reference does vkDeviceWaitIdle here (scene.cpp:1704)
+    if (dirty & PTB_SCENE_DIRTY_TEXTURES) {
+        CU(s->textures.upload(v->Textures, v->TextureCount, st));
+        for (auto& l : s->layers) l.release();
+        s->layers.assign(v->AtlasLayerCount, DevBuf<float>());
+        std::vector<const float*> table(v->AtlasLayerCount);
+        const size_t texels = (size_t)v->AtlasWidth * v->AtlasHeight * 4;
+        for (uint32_t i = 0; i < v->AtlasLayerCount; i++) {
+            CU(s->layers[i].upload(v->AtlasLayers[i], texels, st));
+            table[i] = s->layers[i].p;
+        }
+        CU(s->layer_table.upload(table.data(), table.size(), st));
+        CU(cudaStreamSynchronize(st));   // `table` is a stack object
+        s->ds.textures = s->textures.p; s->ds.texture_count = v->TextureCount;
+        s->ds.atlas_layers = s->layer_table.p; s->ds.atlas_width = v->AtlasWidth; s->ds.atlas_height = v->AtlasHeight;
+    }
+    if (dirty & PTB_SCENE_DIRTY_MATERIALS) {
+        CU(s->materials.upload(v->MaterialData, v->MaterialWordCount, st));
+        s->ds.material_data = s->materials.p; s->ds.material_word_count = v->MaterialWordCount;
+    }
+    if (dirty & PTB_SCENE_DIRTY_SHAPES) {
+        CU(s->shapes.upload(v->Shapes, v->ShapeCount, st));
+        CU(s->shape_nodes.upload(v->ShapeNodes, v->ShapeNodeCount, st));
+        s->ds.shapes = s->shapes.p; s->ds.shape_count = v->ShapeCount;
+        s->ds.shape_nodes = s->shape_nodes.p; s->ds.shape_node_count = v->ShapeNodeCount;
+    }
+    if (dirty & PTB_SCENE_DIRTY_MESHES) {
+        CU(s->faces.upload(v->MeshFaces, v->MeshFaceCount, st));
+        CU(s->vertices.upload(v->MeshVertices, v->MeshVertexCount, st));
+        CU(s->mesh_nodes.upload(v->MeshNodes, v->MeshNodeCount, st));
+        s->ds.mesh_faces = s->faces.p; s->ds.mesh_face_count = v->MeshFaceCount;
+        s->ds.mesh_vertices = s->vertices.p;
+        s->ds.mesh_nodes = s->mesh_nodes.p; s->ds.mesh_node_count = v->MeshNodeCount;
+    }
+    if (dirty & PTB_SCENE_DIRTY_CAMERAS) {
+        CU(s->cameras.upload(v->Cameras, v->CameraCount, st));
+        s->ds.cameras = s->cameras.p; s->ds.camera_count = v->CameraCount;
+    }
+    if ((dirty & (PTB_SCENE_DIRTY_GLOBALS | PTB_SCENE_DIRTY_SHAPES | PTB_SCENE_DIRTY_SKYBOX_TEXTURE)) && v->Globals) s->ds.globals = *v->Globals;
+    if (dirty & (PTB_SCENE_DIRTY_SHAPES | PTB_SCENE_DIRTY_MESHES)) {
+        // scene flattening: packed two-level BVH2 scene -> one compressed BVH8
+        WideBuild wb;
+        std::string err;
+        int rc = build_wide_bvh(v, &wb, &err);
+        s->wide_info.status = rc;
+        if (rc == PTB_OK) {
+            CU(s->wide_nodes.upload(wb.nodes.data(), wb.nodes.size(), st));
+            CU(s->wide_prims.upload(wb.prims.data(), wb.prims.size(), st));
+            CU(s->wide_planes.upload(wb.planes.data(), wb.planes.size(), st));
+            CU(cudaStreamSynchronize(st));
+            s->ds.wide_nodes = (const uint4*)s->wide_nodes.p;
+            s->ds.wide_tris = (const float4*)s->wide_prims.p;
+            s->ds.wide_planes = s->wide_planes.p;
+            s->ds.wide_plane_count = (uint32_t)wb.planes.size();
+            s->ds.wide_tlas_root = wb.node_count ? 0u : 0xFFFFFFFFu;
+            s->wide_info.node_count = wb.node_count; s->wide_info.prim_count = wb.prim_count;
+            s->wide_info.plane_count = (uint32_t)wb.planes.size();
+            s->wide_info.depth = wb.depth; s->wide_info.bvh2_depth = wb.bvh2_depth;
+            s->wide_info.sah_cost = wb.sah_cost; s->wide_info.build_seconds = wb.build_seconds;
+        } else {
+            // The reference-layout traversal stays usable; the wide backend reports the reason.
+            s->ds.wide_nodes = nullptr; s->ds.wide_tlas_root = 0xFFFFFFFFu; s->ds.wide_plane_count = 0;
+            g_error = "wide BVH build failed: " + err;
+        }
+    }
+    CU(cudaStreamSynchronize(st));
+    return PTB_OK;
+}
+
+void ptb_scene_destroy(ptb_scene* s) {
+    if (!s) return;
+    cudaSetDevice(s->ctx->device);
+    cudaStreamSynchronize(s->ctx->stream);
+    s->textures.release(); s->materials.release(); s->shapes.release(); s->shape_nodes.release();
+    s->faces.release(); s->vertices.release(); s->mesh_nodes.release(); s->cameras.release();
+    for (auto& l : s->layers) l.release();
+    s->layer_table.release(); s->wide_nodes.release(); s->wide_prims.release(); s->wide_planes.release();
+    delete s;
+}
+
+int ptb_scene_wide_info(ptb_scene* s, ptb_wide_info* out) {
+    if (!s || !out) return fail(PTB_E_INVALID, "ptb_scene_wide_info: NULL argument");
+    *out = s->wide_info;
+    return PTB_OK;
+}
+
+// ---- film ----
+int ptb_film_create(ptb_context* ctx, uint32_t width, uint32_t height, void* external, ptb_film** out) {
+    if (!ctx || !out || width == 0 || height == 0) return fail(PTB_E_INVALID, "ptb_film_create: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    ptb_film* f = new ptb_film();
+    f->ctx = ctx; f->width = width; f->height = height; f->external = external != nullptr;
+    f->accum = (float4*)external; f->srgb = nullptr; f->linear = nullptr;
+    const size_t n = (size_t)width * height;
+    if (!external) {
+        cudaError_t e = cudaMalloc((void**)&f->accum, n * sizeof(float4));
+        if (e != cudaSuccess) { delete f; return cuda_fail(e, "cudaMalloc(film)"); }
+        cudaMemsetAsync(f->accum, 0, n * sizeof(float4), ctx->stream);
+    }
+    *out = f;
+    return PTB_OK;
+}
+void ptb_film_destroy(ptb_film* f) {
+    if (!f) return;
+    cudaSetDevice(f->ctx->device);
+    cudaStreamSynchronize(f->ctx->stream);
+    if (!f->external && f->accum) cudaFree(f->accum);
+    if (f->srgb) cudaFree(f->srgb);
+    if (f->linear) cudaFree(f->linear);
+    delete f;
+}
+void* ptb_film_device_accum(ptb_film* f) { return f ? (void*)f->accum : nullptr; }
+int ptb_film_download_accum(ptb_film* f, float* host, size_t count) {
+    if (!f || !host || count != (size_t)f->width * f->height * 4) return fail(PTB_E_INVALID, "ptb_film_download_accum: bad argument");
+    CU(cudaMemcpyAsync(host, f->accum, count * sizeof(float), cudaMemcpyDeviceToHost, f->ctx->stream));
+    CU(cudaStreamSynchronize(f->ctx->stream));
+    return PTB_OK;
+}
+int ptb_film_upload_accum(ptb_film* f, const float* host, size_t count) {
+    if (!f || !host || count != (size_t)f->width * f->height * 4) return fail(PTB_E_INVALID, "ptb_film_upload_accum: bad argument");
+    CU(cudaMemcpyAsync(f->accum, host, count * sizeof(float), cudaMemcpyHostToDevice, f->ctx->stream));
+    CU(cudaStreamSynchronize(f->ctx->stream));
+    return PTB_OK;
+}
+int ptb_film_resolve_device(ptb_film* f, const ptb_resolve_params* p, void* device_srgb8) {
+    if (!f || !p || !device_srgb8) return fail(PTB_E_INVALID, "ptb_film_resolve_device: NULL argument");
+    if (p->ToneMappingMode > PTB_TONE_MAPPING_MODE_ACES) return fail(PTB_E_INVALID, "ptb_film_resolve: unknown tone mapping mode");
+    CU(launch_resolve(f->accum, f->width, f->height, *p, (uchar4*)device_srgb8, nullptr, f->ctx->stream));
+    return PTB_OK;
+}
+int ptb_film_resolve(ptb_film* f, const ptb_resolve_params* p, uint8_t* host_srgb8, float* host_linear) {
+    if (!f || !p) return fail(PTB_E_INVALID, "ptb_film_resolve: NULL argument");
+    if (p->ToneMappingMode > PTB_TONE_MAPPING_MODE_ACES) return fail(PTB_E_INVALID, "ptb_film_resolve: unknown tone mapping mode");
+    CU(cudaSetDevice(f->ctx->device));
+    const size_t n = (size_t)f->width * f->height;
+    if (host_srgb8 && !f->srgb) CU(cudaMalloc((void**)&f->srgb, n * sizeof(uchar4)));
+    if (host_linear && !f->linear) CU(cudaMalloc((void**)&f->linear, n * 3 * sizeof(float)));
+    CU(launch_resolve(f->accum, f->width, f->height, *p, host_srgb8 ? f->srgb : nullptr, host_linear ? f->linear : nullptr, f->ctx->stream));
+    if (host_srgb8) CU(cudaMemcpyAsync(host_srgb8, f->srgb, n * 4, cudaMemcpyDeviceToHost, f->ctx->stream));
+    if (host_linear) CU(cudaMemcpyAsync(host_linear, f->linear, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, f->ctx->stream));
+    CU(cudaStreamSynchronize(f->ctx->stream));
+    return PTB_OK;
+}
+
+// ---- renderer ----
+int ptb_renderer_create(ptb_context* ctx, ptb_scene* scene, ptb_film* film, ptb_renderer** out) {
+    if (!ctx || !scene || !film || !out) return fail(PTB_E_INVALID, "ptb_renderer_create: NULL argument");
+    CU(cudaSetDevice(ctx->device));
+    ptb_renderer* r = new ptb_renderer();
+    r->ctx = ctx; r->scene = scene; r->film = film;
+    std::memset(&r->params, 0, sizeof r->params);
+    r->params.RenderFlags = PTB_RENDER_FLAG_ACCUMULATE | PTB_RENDER_FLAG_SAMPLE_JITTER;   // application.cpp:106
+    r->params.Traversal = PTB_TRAVERSAL_WIDE;
+    r->params.TieMode = PTB_TIE_CANONICAL;
+    r->frame_index = 0; r->rays_traced = 0; r->kernel_launches = 0;
+    RenderConsts& pc = r->pc;
+    std::memset(&pc, 0, sizeof pc);
+    pc.width = film->width; pc.height = film->height;
+    pc.tiles_x = (film->width + 15) / 16;
+    const uint32_t tiles = pc.tiles_x * ((film->height + 15) / 16);
+    pc.slot_count = tiles * 256u;
+    const size_t S = pc.slot_count;
+    const size_t bytes = S * (7 * 16) + (size_t)tiles * sizeof(unsigned);
+    cudaError_t e = cudaMalloc(&r->state_block, bytes);
+    if (e != cudaSuccess) { delete r; return cuda_fail(e, "cudaMalloc(wavefront state)"); }
+    cudaMemsetAsync(r->state_block, 0, bytes, ctx->stream);
+    char* b = (char*)r->state_block;
+    r->st.ray = (float4*)b; b += S * 16;
+    r->st.hit0 = (uint4*)b; b += S * 16;
+    r->st.hit1 = (uint4*)b; b += S * 16;
+    r->st.path0 = (uint4*)b; b += S * 16;
+    r->st.path1 = (float4*)b; b += S * 16;
+    r->st.path2 = (float4*)b; b += S * 16;
+    r->st.path3 = (float4*)b; b += S * 16;
+    r->st.tile_paths = (unsigned*)b;
+    *out = r;
+    return PTB_OK;
+}
+void ptb_renderer_destroy(ptb_renderer* r) {
+    if (!r) return;
+    cudaSetDevice(r->ctx->device);
+    cudaStreamSynchronize(r->ctx->stream);
+    cudaFree(r->state_block);
+    delete r;
+}
+int ptb_renderer_set_params(ptb_renderer* r, const ptb_render_params* p) {
+    if (!r || !p) return fail(PTB_E_INVALID, "ptb_renderer_set_params: NULL argument");
+    if (p->Integrator > PTB_INTEGRATOR_MEGAKERNEL || p->Traversal > PTB_TRAVERSAL_WIDE || p->TieMode > PTB_TIE_CANONICAL)
+        return fail(PTB_E_INVALID, "ptb_renderer_set_params: unknown enum value");
+    if (p->Traversal == PTB_TRAVERSAL_WIDE && p->TieMode != PTB_TIE_CANONICAL)
+        return fail(PTB_E_INVALID, "ptb_renderer_set_params: the wide traversal is order-free and needs PTB_TIE_CANONICAL");
+    r->params = *p;
+    return PTB_OK;
+}
+int ptb_renderer_set_frame_index(ptb_renderer* r, uint32_t f) {
+    if (!r) return fail(PTB_E_INVALID, "NULL renderer");
+    r->frame_index = f;
+    return PTB_OK;
+}
+
+static int prepare(ptb_renderer* r) {
+    const DeviceScene& ds = r->scene->ds;
+    if (r->params.CameraIndex >= ds.camera_count) return fail(PTB_E_INVALID, "renderer: CameraIndex out of range");
+    if (r->params.Traversal == PTB_TRAVERSAL_WIDE && ds.shape_count > 0 && r->scene->wide_info.status != PTB_OK)
+        return fail(PTB_E_UNSUPPORTED, "renderer: wide BVH unavailable for this scene (" + g_error + ")");
+    r->pc.camera_index = r->params.CameraIndex;
+    r->pc.render_flags = r->params.RenderFlags;
+    r->pc.path_length_limit = r->params.PathLengthLimit;
+    r->pc.termination_probability = r->params.PathTerminationProbability;
+    return PTB_OK;
+}
+
+int ptb_renderer_reset(ptb_renderer* r) {
+    if (!r) return fail(PTB_E_INVALID, "NULL renderer");
+    int rc = prepare(r);
+    if (rc) return rc;
+    CU(cudaSetDevice(r->ctx->device));
+    r->pc.random_seed = r->frame_index;      // basic.cpp:285-304: seed = FrameIndex, Restart = 1
+    CU(launch_restart(r->scene->ds, r->pc, r->st, r->film->accum, r->ctx->stream));
+    r->kernel_launches += 1;
+    return PTB_OK;
+}
+
+static int run_rounds(ptb_renderer* r, uint32_t rounds, uint32_t seed_stride) {
+    const DeviceScene& ds = r->scene->ds;
+    cudaStream_t st = r->ctx->stream;
+    const uint64_t live = (uint64_t)r->film->width * r->film->height;
+    if (r->params.Integrator == PTB_INTEGRATOR_MEGAKERNEL) {
+        CU(launch_megakernel(ds, r->pc, r->st, r->film->accum, r->params.Traversal, r->params.TieMode, rounds, seed_stride, st));
+        r->kernel_launches += 1;
+    } else {
+        RenderConsts pc = r->pc;
+        for (uint32_t k = 0; k < rounds; k++) {
+            CU(launch_trace(ds, pc, r->st, r->params.Traversal, r->params.TieMode, st));
+            CU(launch_scatter(ds, pc, r->st, r->film->accum, st));
+            pc.random_seed += seed_stride;
+        }
+        r->kernel_launches += 2ull * rounds;
+    }
+    r->rays_traced += live * rounds;
+    return PTB_OK;
+}
+
+int ptb_renderer_run(ptb_renderer* r, uint32_t rounds) {
+    if (!r) return fail(PTB_E_INVALID, "NULL renderer");
+    int rc = prepare(r);
+    if (rc) return rc;
+    CU(cudaSetDevice(r->ctx->device));
+    r->frame_index += 1;                      // basic.cpp:315
+    r->pc.random_seed = r->frame_index;
+    return run_rounds(r, rounds, 0u);         // all rounds of one call share the seed (basic.cpp:323-331)
+}
+
+int ptb_renderer_run_frames(ptb_renderer* r, uint32_t frames) {
+    if (!r) return fail(PTB_E_INVALID, "NULL renderer");
+    if (frames == 0) return PTB_OK;
+    int rc = prepare(r);
+    if (rc) return rc;
+    CU(cudaSetDevice(r->ctx->device));
+    r->pc.random_seed = r->frame_index + 1;   // frame k of this call runs with seed FrameIndex + k
+    rc = run_rounds(r, frames, 1u);
+    r->frame_index += frames;
+    return rc;
+}
+
+int ptb_renderer_profile_frames(ptb_renderer* r, uint32_t frames, ptb_kernel_times* out) {
+    if (!r || !out) return fail(PTB_E_INVALID, "ptb_renderer_profile_frames: NULL argument");
+    std::memset(out, 0, sizeof *out);
+    if (frames == 0) return PTB_OK;
+    if (frames > 4096) return fail(PTB_E_INVALID, "ptb_renderer_profile_frames: at most 4096 frames per call");
+    int rc = prepare(r);
+    if (rc) return rc;
+    CU(cudaSetDevice(r->ctx->device));
+    cudaStream_t st = r->ctx->stream;
+    const DeviceScene& ds = r->scene->ds;
+    const bool mega = r->params.Integrator == PTB_INTEGRATOR_MEGAKERNEL;
+    const uint32_t per = mega ? 2u : 3u;
+    std::vector<cudaEvent_t> ev((size_t)frames * per);
+    for (auto& e : ev) CU(cudaEventCreate(&e));
+    RenderConsts pc = r->pc;
+    pc.random_seed = r->frame_index + 1;
+    for (uint32_t k = 0; k < frames; k++) {
+        cudaEvent_t* e = &ev[(size_t)k * per];
+        CU(cudaEventRecord(e[0], st));
+        if (mega) {
+            CU(launch_megakernel(ds, pc, r->st, r->film->accum, r->params.Traversal, r->params.TieMode, 1u, 1u, st));
+            CU(cudaEventRecord(e[1], st));
+        } else {
+            CU(launch_trace(ds, pc, r->st, r->params.Traversal, r->params.TieMode, st));
+            CU(cudaEventRecord(e[1], st));
+            CU(launch_scatter(ds, pc, r->st, r->film->accum, st));
+            CU(cudaEventRecord(e[2], st));
+        }
+        pc.random_seed += 1;
+    }
+    CU(cudaStreamSynchronize(st));
+    for (uint32_t k = 0; k < frames; k++) {
+        cudaEvent_t* e = &ev[(size_t)k * per];
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, e[0], e[1]));
+        if (mega) { out->mega_ms += ms; out->mega_launches++; }
+        else {
+            out->trace_ms += ms; out->trace_launches++;
+            CU(cudaEventElapsedTime(&ms, e[1], e[2]));
+            out->scatter_ms += ms; out->scatter_launches++;
+        }
+    }
+    for (auto& e : ev) cudaEventDestroy(e);
+    r->frame_index += frames;
+    r->rays_traced += (uint64_t)r->film->width * r->film->height * frames;
+    r->kernel_launches += (uint64_t)frames * (mega ? 1u : 2u);
+    return PTB_OK;
+}
+
+int ptb_renderer_sync(ptb_renderer* r) {
+    if (!r) return fail(PTB_E_INVALID, "NULL renderer");
+    CU(cudaStreamSynchronize(r->ctx->stream));
+    return PTB_OK;
+}
+
+int ptb_renderer_stats(ptb_renderer* r, ptb_stats* out) {
+    if (!r || !out) return fail(PTB_E_INVALID, "ptb_renderer_stats: NULL argument");
+    const uint32_t tiles = r->pc.slot_count / 256u;
+    std::vector<unsigned> host(tiles);
+    CU(cudaMemcpyAsync(host.data(), r->st.tile_paths, tiles * sizeof(unsigned), cudaMemcpyDeviceToHost, r->ctx->stream));
+    CU(cudaStreamSynchronize(r->ctx->stream));
+    uint64_t paths = 0;
+    for (unsigned c : host) paths += c;
+    out->rays_traced = r->rays_traced;
+    out->paths_finished = paths;
+    out->kernel_launches = r->kernel_launches;
+    out->frame_index = r->frame_index;
+    return PTB_OK;
+}
+
+uint32_t ptb_renderer_slot_count(ptb_renderer* r) { return r ? r->pc.slot_count : 0; }
+
+// Named SoA arrays of the reference's state (basic.glsl.inc:23-59), gathered from the 16-byte records.
+int ptb_renderer_download_state(ptb_renderer* r, const char* name, void* host, size_t bytes) {
+    if (!r || !name || !host) return fail(PTB_E_INVALID, "ptb_renderer_download_state: NULL argument");
+    const size_t S = r->pc.slot_count;
+    if (bytes != S * 4) return fail(PTB_E_INVALID, "ptb_renderer_download_state: expected slot_count*4 bytes");
+    struct Field { const char* name; int record; int word; };
+    static const Field fields[] = {
+        {"OriginX", 0, 0}, {"OriginY", 0, 1}, {"OriginZ", 0, 2}, {"PackedVelocity", 0, 3},
+        {"Time", 1, 0}, {"ShapeAndMaterialIndex", 1, 1}, {"PackedNormal", 1, 2}, {"PackedTangentX", 1, 3},
+        {"TextureU", 2, 0}, {"TextureV", 2, 1}, {"PrimitiveIndex", 2, 2}, {"ShapeType", 2, 3},
+        {"ImagePosition", 3, 0}, {"NormalizedLambda0", 3, 1}, {"ActiveShapeIndex01", 3, 2}, {"ActiveShapeIndex23", 3, 3},
+        {"Throughput0", 4, 0}, {"Throughput1", 4, 1}, {"Throughput2", 4, 2}, {"Throughput3", 4, 3},
+        // the reference stores Probability.w in array 2 and .z in array 3 (basic.glsl.inc:176-177,208-209)
+        {"Probability0", 5, 0}, {"Probability1", 5, 1}, {"Probability2", 5, 3}, {"Probability3", 5, 2},
+        {"SampleR", 6, 0}, {"SampleG", 6, 1}, {"SampleB", 6, 2}, {"PathLength", 6, 3},
+    };
+    for (const Field& f : fields) {
+        if (std::strcmp(f.name, name)) continue;
+        std::vector<uint32_t> rec(S * 4);
+        const char* base = (const char*)r->state_block + (size_t)f.record * S * 16;
+        CU(cudaMemcpyAsync(rec.data(), base, S * 16, cudaMemcpyDeviceToHost, r->ctx->stream));
+        CU(cudaStreamSynchronize(r->ctx->stream));
+        uint32_t* o = (uint32_t*)host;
+        for (size_t i = 0; i < S; i++) o[i] = rec[4 * i + f.word];
+        return PTB_OK;
+    }
+    if (!std::strcmp(name, "Duration")) {
+        float* o = (float*)host;
+        for (size_t i = 0; i < S; i++) o[i] = PTB_HIT_TIME_LIMIT;
+        return PTB_OK;
+    }
+    return fail(PTB_E_INVALID, std::string("ptb_renderer_download_state: unknown array ") + name);
+}
+
+// ---- ray cast harness ----
+int ptb_raycast(ptb_scene* s, const ptb_ray* host_rays, size_t n, uint32_t traversal, uint32_t tie, ptb_hit* host_hits) {
+    if (!s || (n && (!host_rays || !host_hits))) return fail(PTB_E_INVALID, "ptb_raycast: NULL argument");
+    if (traversal > PTB_TRAVERSAL_WIDE || tie > PTB_TIE_CANONICAL) return fail(PTB_E_INVALID, "ptb_raycast: unknown enum value");
+    if (traversal == PTB_TRAVERSAL_WIDE && tie != PTB_TIE_CANONICAL) return fail(PTB_E_INVALID, "ptb_raycast: the wide traversal needs PTB_TIE_CANONICAL");
+    if (traversal == PTB_TRAVERSAL_WIDE && s->ds.shape_count > 0 && s->wide_info.status != PTB_OK) return fail(PTB_E_UNSUPPORTED, "ptb_raycast: wide BVH unavailable");
+    if (n == 0) return PTB_OK;
+    CU(cudaSetDevice(s->ctx->device));
+    cudaStream_t st = s->ctx->stream;
+    ptb_ray* d_rays = nullptr; ptb_hit* d_hits = nullptr;
+    CU(cudaMalloc((void**)&d_rays, n * sizeof(ptb_ray)));
+    cudaError_t e = cudaMalloc((void**)&d_hits, n * sizeof(ptb_hit));
+    if (e != cudaSuccess) { cudaFree(d_rays); return cuda_fail(e, "cudaMalloc(hits)"); }
+    e = cudaMemcpyAsync(d_rays, host_rays, n * sizeof(ptb_ray), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = launch_raycast(s->ds, d_rays, n, traversal, tie, d_hits, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(host_hits, d_hits, n * sizeof(ptb_hit), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(d_rays); cudaFree(d_hits);
+    if (e != cudaSuccess) return cuda_fail(e, "ptb_raycast");
+    return PTB_OK;
+}
+
+int ptb_raycast_device(ptb_scene* s, const ptb_ray* d_rays, size_t n, uint32_t traversal, uint32_t tie, ptb_hit* d_hits) {
+    if (!s || (n && (!d_rays || !d_hits))) return fail(PTB_E_INVALID, "ptb_raycast_device: NULL argument");
+    if (traversal > PTB_TRAVERSAL_WIDE || tie > PTB_TIE_CANONICAL) return fail(PTB_E_INVALID, "ptb_raycast_device: unknown enum value");
+    if (traversal == PTB_TRAVERSAL_WIDE && tie != PTB_TIE_CANONICAL) return fail(PTB_E_INVALID, "ptb_raycast_device: the wide traversal needs PTB_TIE_CANONICAL");
+    if (traversal == PTB_TRAVERSAL_WIDE && s->ds.shape_count > 0 && s->wide_info.status != PTB_OK) return fail(PTB_E_UNSUPPORTED, "ptb_raycast_device: wide BVH unavailable");
+    CU(cudaSetDevice(s->ctx->device));
+    CU(launch_raycast(s->ds, d_rays, n, traversal, tie, d_hits, s->ctx->stream));
+    return PTB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,38 @@
+// Host-visible launch interface of the sm_100a kernels (ptb_kernels.cu).
+// Called only by the C ABI implementation (ptb_api.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include "ptb_scatter.cuh"
+
+namespace ptb {
+
+// Wavefront state, one record group per path slot (slot = 16x16-tile-major pixel
+// order, basic_scatter.glsl:324-328 with tiles_x = ceil(W/16)).  The reference
+// keeps 26 separate 4-byte arrays (basic.glsl.inc:23-59); here the same fields
+// are grouped into 16-byte records so every access is one coalesced LDG.128 /
+// STG.128 per thread.  Ray.Duration is not stored: every stored ray has
+// HIT_TIME_LIMIT (basic_scatter.glsl:307, scene.glsl.inc:617).
+struct WavefrontState {
+    float4* ray;      // origin.xyz, oct-packed direction (bits)
+    uint4*  hit0;     // t (bits), shape<<16|material, packed normal, packed tangent
+    uint4*  hit1;     // u (bits), v (bits), primitive index, shape type
+    uint4*  path0;    // pixel index, lambda0 (bits), active shapes 0|1, active shapes 2|3
+    float4* path1;    // throughput at the 4 wavelengths
+    float4* path2;    // probability at the 4 wavelengths
+    float4* path3;    // sample XYZ, path length (bits)
+    unsigned int* tile_paths;   // per 256-slot tile: paths finished since reset (u32 wraps are summed by the host in u64 deltas)
+};
+
+struct LaunchStats { unsigned int launches; };
+
+cudaError_t launch_restart(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, cudaStream_t stream);
+cudaError_t launch_trace(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, unsigned traversal, unsigned tie, cudaStream_t stream);
+cudaError_t launch_scatter(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, cudaStream_t stream);
+// `rounds` x {trace, scatter} with the path state in registers; seed = pc.random_seed + k * seed_stride for round k.
+cudaError_t launch_megakernel(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum,
+                              unsigned traversal, unsigned tie, unsigned rounds, unsigned seed_stride, cudaStream_t stream);
+cudaError_t launch_resolve(const float4* accum, unsigned width, unsigned height, ptb_resolve_params params,
+                           uchar4* out_srgb8, float* out_linear_rgb, cudaStream_t stream);
+cudaError_t launch_raycast(const DeviceScene& s, const ptb_ray* rays, size_t n, unsigned traversal, unsigned tie, ptb_hit* out, cudaStream_t stream);
+
+}  // namespace ptb

@@ -1,0 +1,316 @@
+"""Host-side mirror of the reference's integrator interface over the C ABI.
+
+The reference drives its path tracer through seven free functions and a struct
+of public tunables (src/integrator/integrator.hpp:51-60, src/integrator/basic.hpp
+:6-32, called from src/application/application.cpp:100-124).  This module keeps
+those names and argument meanings — CreateSampleBuffer, CreateBasicRenderer,
+ResetBasicRenderer, RunBasicRenderer, RenderSampleBuffer, and a BasicRenderer
+whose CameraIndex / RenderFlags / PathLengthLimit / PathTerminationProbability
+fields the caller pokes before Reset/Run — and forwards them to libptb.so
+(include/ptb.h), the hand-written sm_100a CUDA implementation.
+
+There is no CPU fallback: if libptb.so cannot be built/loaded, or no B200 is
+visible, the calls raise.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _build
+from .types import (KernelTimes, RenderParams, ResolveParams, SceneView, Stats, WideInfo, HIT_DTYPE, RAY_DTYPE,
+                    RENDER_FLAG_ACCUMULATE, RENDER_FLAG_SAMPLE_JITTER, INTEGRATOR_WAVEFRONT, INTEGRATOR_MEGAKERNEL,
+                    TRAVERSAL_BVH2_REFERENCE, TRAVERSAL_WIDE, TIE_FAITHFUL, TIE_CANONICAL, SCENE_DIRTY_ALL,
+                    TONE_CLAMP, TONE_REINHARD, TONE_HABLE, TONE_ACES)
+
+# every symbol include/ptb.h declares (checked by tests/test_abi.py)
+ABI_SYMBOLS = [
+    "ptb_last_error", "ptb_version",
+    "ptb_context_create", "ptb_context_destroy", "ptb_context_sync", "ptb_context_stream",
+    "ptb_scene_create", "ptb_scene_update", "ptb_scene_destroy", "ptb_scene_wide_info",
+    "ptb_film_create", "ptb_film_destroy", "ptb_film_device_accum", "ptb_film_download_accum", "ptb_film_upload_accum",
+    "ptb_film_resolve", "ptb_film_resolve_device",
+    "ptb_renderer_create", "ptb_renderer_destroy", "ptb_renderer_set_params", "ptb_renderer_set_frame_index",
+    "ptb_renderer_reset", "ptb_renderer_run", "ptb_renderer_run_frames", "ptb_renderer_profile_frames", "ptb_renderer_sync", "ptb_renderer_stats",
+    "ptb_renderer_download_state", "ptb_renderer_slot_count", "ptb_raycast", "ptb_raycast_device",
+]
+
+STATE_ARRAYS = {
+    "OriginX": "f4", "OriginY": "f4", "OriginZ": "f4", "Duration": "f4", "PackedVelocity": "u4",
+    "Time": "f4", "TextureU": "f4", "TextureV": "f4", "ShapeAndMaterialIndex": "u4", "PackedNormal": "u4", "PackedTangentX": "u4",
+    "ImagePosition": "i4", "NormalizedLambda0": "f4", "Throughput0": "f4", "Throughput1": "f4", "Throughput2": "f4", "Throughput3": "f4",
+    "Probability0": "f4", "Probability1": "f4", "Probability2": "f4", "Probability3": "f4", "SampleR": "f4", "SampleG": "f4", "SampleB": "f4",
+    "ActiveShapeIndex01": "u4", "ActiveShapeIndex23": "u4", "PathLength": "u4", "PrimitiveIndex": "u4", "ShapeType": "u4",
+}
+
+_lib = None
+
+
+class PtbError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__("ptb error %d: %s" % (code, message))
+        self.code = code
+
+
+def lib():
+    """Loads libptb.so (building it in-tree with nvcc when missing or stale)."""
+    global _lib
+    if _lib is None:
+        L = C.CDLL(_build.build_cuda())
+        vp, u32, sz = C.c_void_p, C.c_uint32, C.c_size_t
+        L.ptb_last_error.restype = C.c_char_p
+        L.ptb_version.restype = C.c_char_p
+        L.ptb_context_create.argtypes = [C.c_int, C.POINTER(vp)]
+        L.ptb_context_destroy.argtypes = [vp]
+        L.ptb_context_destroy.restype = None
+        L.ptb_context_sync.argtypes = [vp]
+        L.ptb_context_stream.argtypes = [vp]
+        L.ptb_context_stream.restype = vp
+        L.ptb_scene_create.argtypes = [vp, C.POINTER(vp)]
+        L.ptb_scene_update.argtypes = [vp, C.POINTER(SceneView), u32]
+        L.ptb_scene_destroy.argtypes = [vp]
+        L.ptb_scene_destroy.restype = None
+        L.ptb_scene_wide_info.argtypes = [vp, C.POINTER(WideInfo)]
+        L.ptb_film_create.argtypes = [vp, u32, u32, vp, C.POINTER(vp)]
+        L.ptb_film_destroy.argtypes = [vp]
+        L.ptb_film_destroy.restype = None
+        L.ptb_film_device_accum.argtypes = [vp]
+        L.ptb_film_device_accum.restype = vp
+        L.ptb_film_download_accum.argtypes = [vp, vp, sz]
+        L.ptb_film_upload_accum.argtypes = [vp, vp, sz]
+        L.ptb_film_resolve.argtypes = [vp, C.POINTER(ResolveParams), vp, vp]
+        L.ptb_film_resolve_device.argtypes = [vp, C.POINTER(ResolveParams), vp]
+        L.ptb_renderer_create.argtypes = [vp, vp, vp, C.POINTER(vp)]
+        L.ptb_renderer_destroy.argtypes = [vp]
+        L.ptb_renderer_destroy.restype = None
+        L.ptb_renderer_set_params.argtypes = [vp, C.POINTER(RenderParams)]
+        L.ptb_renderer_set_frame_index.argtypes = [vp, u32]
+        L.ptb_renderer_reset.argtypes = [vp]
+        L.ptb_renderer_run.argtypes = [vp, u32]
+        L.ptb_renderer_run_frames.argtypes = [vp, u32]
+        L.ptb_renderer_profile_frames.argtypes = [vp, u32, C.POINTER(KernelTimes)]
+        L.ptb_renderer_sync.argtypes = [vp]
+        L.ptb_renderer_stats.argtypes = [vp, C.POINTER(Stats)]
+        L.ptb_renderer_download_state.argtypes = [vp, C.c_char_p, vp, sz]
+        L.ptb_renderer_slot_count.argtypes = [vp]
+        L.ptb_renderer_slot_count.restype = u32
+        L.ptb_raycast.argtypes = [vp, vp, sz, u32, u32, vp]
+        L.ptb_raycast_device.argtypes = [vp, vp, sz, u32, u32, vp]
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise PtbError(rc, lib().ptb_last_error().decode(errors="replace"))
+
+
+class Context:
+    """One CUDA device + stream (stands in for the `vulkan*` every reference call takes)."""
+
+    def __init__(self, device=0):
+        self.h = C.c_void_p()
+        _check(lib().ptb_context_create(device, C.byref(self.h)))
+        self.device = device
+
+    def sync(self):
+        _check(lib().ptb_context_sync(self.h))
+
+    @property
+    def stream(self):
+        return lib().ptb_context_stream(self.h)
+
+    def close(self):
+        if self.h:
+            lib().ptb_context_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class DeviceScene:
+    """CreateVulkanScene / UpdateVulkanScene / DestroyVulkanScene (scene.hpp:440-442)."""
+
+    def __init__(self, ctx, host_scene=None):
+        self.ctx = ctx
+        self.h = C.c_void_p()
+        _check(lib().ptb_scene_create(ctx.h, C.byref(self.h)))
+        if host_scene is not None:
+            self.update(host_scene, SCENE_DIRTY_ALL)
+
+    def update(self, host_scene, dirty_flags=SCENE_DIRTY_ALL):
+        """host_scene: path_tracer_b200.scene.Scene (packed) or a raw SceneView."""
+        view = host_scene if isinstance(host_scene, SceneView) else host_scene.view
+        _check(lib().ptb_scene_update(self.h, C.byref(view), dirty_flags))
+
+    def wide_info(self):
+        w = WideInfo()
+        _check(lib().ptb_scene_wide_info(self.h, C.byref(w)))
+        return {n: getattr(w, n) for n, _ in WideInfo._fields_}
+
+    def raycast(self, rays, traversal=TRAVERSAL_WIDE, tie=TIE_CANONICAL):
+        """Trace() on caller rays (host arrays in, host hits out)."""
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        out = np.zeros(len(rays), dtype=HIT_DTYPE)
+        _check(lib().ptb_raycast(self.h, rays.ctypes.data, len(rays), traversal, tie, out.ctypes.data))
+        return out
+
+    def raycast_device(self, d_rays, n, d_hits, traversal=TRAVERSAL_WIDE, tie=TIE_CANONICAL):
+        """Same on device-resident buffers (raw pointers); asynchronous on the context stream."""
+        _check(lib().ptb_raycast_device(self.h, d_rays, n, traversal, tie, d_hits))
+
+    def close(self):
+        if self.h:
+            lib().ptb_scene_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class SampleBuffer:
+    """vulkan_sample_buffer (integrator.hpp:21-41): the RGBA32F accumulator, headless."""
+
+    def __init__(self, ctx, width, height, external_device_ptr=None):
+        self.ctx, self.Width, self.Height = ctx, width, height
+        self.h = C.c_void_p()
+        _check(lib().ptb_film_create(ctx.h, width, height, external_device_ptr, C.byref(self.h)))
+
+    @property
+    def device_ptr(self):
+        return lib().ptb_film_device_accum(self.h)
+
+    def download(self):
+        a = np.empty((self.Height, self.Width, 4), dtype=np.float32)
+        _check(lib().ptb_film_download_accum(self.h, a.ctypes.data, a.size))
+        return a
+
+    def upload(self, accum):
+        a = np.ascontiguousarray(accum, dtype=np.float32)
+        _check(lib().ptb_film_upload_accum(self.h, a.ctypes.data, a.size))
+
+    def resolve(self, Brightness=1.0, ToneMappingMode=TONE_CLAMP, ToneMappingWhiteLevel=1.0, want_linear=True, want_srgb8=True):
+        p = ResolveParams(Brightness, ToneMappingMode, ToneMappingWhiteLevel)
+        lin = np.empty((self.Height, self.Width, 3), dtype=np.float32) if want_linear else None
+        srgb = np.empty((self.Height, self.Width, 4), dtype=np.uint8) if want_srgb8 else None
+        _check(lib().ptb_film_resolve(self.h, C.byref(p), srgb.ctypes.data if want_srgb8 else None, lin.ctypes.data if want_linear else None))
+        return lin, srgb
+
+    def close(self):
+        if self.h:
+            lib().ptb_film_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class BasicRenderer:
+    """basic_renderer (basic.hpp:6-26).  The five public fields are poked by the
+    caller before Reset/Run, as the reference application does (application.cpp:104-107)."""
+
+    def __init__(self, ctx, scene, sample_buffer):
+        self.ctx, self.Scene, self.SampleBuffer = ctx, scene, sample_buffer
+        self.CameraIndex = 0
+        self.RenderFlags = RENDER_FLAG_ACCUMULATE | RENDER_FLAG_SAMPLE_JITTER
+        self.PathLengthLimit = 0
+        self.PathTerminationProbability = 0.0
+        # the build's own knobs
+        self.Integrator = INTEGRATOR_WAVEFRONT
+        self.Traversal = TRAVERSAL_WIDE
+        self.TieMode = TIE_CANONICAL
+        self.h = C.c_void_p()
+        _check(lib().ptb_renderer_create(ctx.h, scene.h, sample_buffer.h, C.byref(self.h)))
+
+    def _push(self):
+        p = RenderParams(self.CameraIndex, self.RenderFlags, self.PathLengthLimit, self.PathTerminationProbability,
+                         self.Integrator, self.Traversal, self.TieMode, 0)
+        _check(lib().ptb_renderer_set_params(self.h, C.byref(p)))
+
+    def set_frame_index(self, f):
+        _check(lib().ptb_renderer_set_frame_index(self.h, f))
+
+    def reset(self):
+        self._push()
+        _check(lib().ptb_renderer_reset(self.h))
+
+    def run(self, rounds=1):
+        self._push()
+        _check(lib().ptb_renderer_run(self.h, rounds))
+
+    def run_frames(self, frames):
+        self._push()
+        _check(lib().ptb_renderer_run_frames(self.h, frames))
+
+    def profile_frames(self, frames):
+        """run_frames with CUDA events around every kernel: summed device ms per kernel."""
+        self._push()
+        t = KernelTimes()
+        _check(lib().ptb_renderer_profile_frames(self.h, frames, C.byref(t)))
+        return {n: getattr(t, n) for n, _ in KernelTimes._fields_}
+
+    def sync(self):
+        _check(lib().ptb_renderer_sync(self.h))
+
+    def stats(self):
+        s = Stats()
+        _check(lib().ptb_renderer_stats(self.h, C.byref(s)))
+        return {n: getattr(s, n) for n, _ in Stats._fields_}
+
+    @property
+    def slot_count(self):
+        return lib().ptb_renderer_slot_count(self.h)
+
+    def state(self, name):
+        out = np.empty(self.slot_count, dtype=np.dtype("<" + STATE_ARRAYS[name]))
+        _check(lib().ptb_renderer_download_state(self.h, name.encode(), out.ctypes.data, out.nbytes))
+        return out
+
+    def close(self):
+        if self.h:
+            lib().ptb_renderer_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+# ---- the reference's free functions (same names, `vulkan*` -> Context) ----
+def CreateSampleBuffer(ctx, Width, Height):              # integrator.hpp:51
+    return SampleBuffer(ctx, Width, Height)
+
+
+def DestroySampleBuffer(ctx, SampleBuffer_):             # integrator.hpp:53
+    SampleBuffer_.close()
+
+
+def RenderSampleBuffer(ctx, SampleBuffer_, Parameters):  # integrator.hpp:55-60; Parameters = (Brightness, ToneMappingMode, ToneMappingWhiteLevel)
+    return SampleBuffer_.resolve(*Parameters)
+
+
+def CreateBasicRenderer(ctx, Scene, SampleBuffer_):      # basic.hpp:28
+    return BasicRenderer(ctx, Scene, SampleBuffer_)
+
+
+def DestroyBasicRenderer(ctx, Renderer):                 # basic.hpp:29
+    Renderer.close()
+
+
+def ResetBasicRenderer(ctx, Renderer):                   # basic.hpp:31
+    Renderer.reset()
+
+
+def RunBasicRenderer(ctx, Renderer, Rounds):             # basic.hpp:32
+    Renderer.run(Rounds)

@@ -41,6 +41,16 @@ class Stats(C.Structure):
                 ("kernel_launches", C.c_uint64), ("frame_index", C.c_uint64)]
 
 
+class KernelTimes(C.Structure):
+    _fields_ = [("trace_ms", C.c_float), ("scatter_ms", C.c_float), ("mega_ms", C.c_float),
+                ("trace_launches", u32), ("scatter_launches", u32), ("mega_launches", u32)]
+
+
+class WideInfo(C.Structure):
+    _fields_ = [("status", C.c_int32), ("node_count", u32), ("prim_count", u32), ("plane_count", u32), ("depth", u32),
+                ("bvh2_depth", u32), ("sah_cost", C.c_double), ("build_seconds", C.c_double)]
+
+
 # numpy record layouts of the packed arrays (src/scene/scene.hpp:82-173)
 RAY_DTYPE = np.dtype([("o", "<f4", 3), ("d", "<f4", 3), ("duration", "<f4")])
 HIT_DTYPE = np.dtype([("t", "<f4"), ("shape", "<u4"), ("prim", "<u4"), ("material", "<u4"), ("shape_type", "<u4"),

@@ -1,0 +1,342 @@
+"""Parity of the CUDA path (through the C ABI) with the oracle, on a real B200.
+
+Levels (BASELINE.json north_star): ray casts — hit IDs bit-exact, t within 1e-5
+relative (here: bit-exact); primary + first-bounce radiance within 1e-4;
+converged images within 1 % mean per-channel relative error.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from util import bits, ids_equal, random_rays
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+MISS = 0xFFFFFFFF
+
+SCENES = [("cornell", ()), ("terrain", (64,)), ("room", (1, 512)), ("spherefield", (12, 2, 2))]
+
+
+@pytest.fixture(scope="module")
+def I():
+    from path_tracer_b200 import integrator
+    return integrator
+
+
+@pytest.fixture(scope="module")
+def dev(I, gpu, scenes):
+    cache = {}
+
+    def get(name, *params):
+        key = (name,) + params
+        if key not in cache:
+            cache[key] = I.DeviceScene(gpu, scenes(name, *params))
+        return cache[key]
+    return get
+
+
+def render_pair(I, gpu, dev, oracle, scenes, name, params, w, h, frames, camera=0, flags=3, limit=0, term=0.0, tie=None,
+                traversal=None, integrator=None, restart_rounds=2):
+    """Reset + RunBasicRenderer(2) + `frames` steady-state frames on both sides (application.cpp:104-114)."""
+    sc = scenes(name, *params)
+    tie = oracle.TIE_FAITHFUL if tie is None else tie
+    o = oracle.Renderer(sc.view, w, h, camera_index=camera, render_flags=flags, path_length_limit=limit,
+                        path_termination_probability=term, tie=tie)
+    o.set_frame_index(0)
+    o.reset()
+    o.run(restart_rounds)
+    o.run_frames(frames)
+    film = I.SampleBuffer(gpu, w, h)
+    r = I.BasicRenderer(gpu, dev(name, *params), film)
+    r.CameraIndex, r.RenderFlags, r.PathLengthLimit, r.PathTerminationProbability = camera, flags, limit, term
+    r.TieMode = I.TIE_CANONICAL if tie == oracle.TIE_CANONICAL else I.TIE_FAITHFUL
+    r.Traversal = I.TRAVERSAL_BVH2_REFERENCE if traversal is None else traversal
+    r.Integrator = I.INTEGRATOR_WAVEFRONT if integrator is None else integrator
+    r.set_frame_index(0)
+    r.reset()
+    r.run(restart_rounds)
+    r.run_frames(frames)
+    r.sync()
+    return o, r, film
+
+
+# ---------------------------------------------------------------- ray casts
+@pytest.mark.parametrize("name,params", SCENES)
+def test_raycast_reference_layout_is_bit_exact(I, dev, oracle, scenes, name, params):
+    sc = scenes(name, *params)
+    rays = random_rays(sc, 100000, 5, oracle)
+    for trav_tie, otie in ((I.TIE_FAITHFUL, oracle.TIE_FAITHFUL), (I.TIE_CANONICAL, oracle.TIE_CANONICAL)):
+        ref = oracle.raycast(sc.view, rays, tie=otie)
+        out = dev(name, *params).raycast(rays, I.TRAVERSAL_BVH2_REFERENCE, trav_tie)
+        assert ids_equal(out, ref).all()
+        assert (bits(out["t"]) == bits(ref["t"])).all()
+        hit = ref["shape"] != MISS
+        assert (out["material"][hit] == ref["material"][hit]).all() and (out["shape_type"][hit] == ref["shape_type"][hit]).all()
+        assert np.array_equal(out["bary"][hit], ref["bary"][hit])
+        # normals/tangents: sqrt and divide are IEEE on both sides; sphere UV goes through atan2 (libdevice vs glibc)
+        assert np.abs(out["n"][hit] - ref["n"][hit]).max() <= 1e-6
+        assert np.abs(out["tan"][hit] - ref["tan"][hit]).max() <= 1e-6
+        assert np.abs(out["uv"][hit] - ref["uv"][hit]).max() <= 1e-6
+
+
+@pytest.mark.parametrize("name,params", SCENES)
+def test_raycast_wide_bvh(I, dev, oracle, scenes, name, params):
+    """IDs and t against the reference traversal; where they differ the CUDA hit must be the
+    brute-force closest hit (the reference BVH2 culled its own closest primitive: NaN slab
+    tests on axis-parallel rays, Q19, or entry-time rounding)."""
+    sc = scenes(name, *params)
+    n = 200000
+    rays = random_rays(sc, n, 6, oracle)
+    ref = oracle.raycast(sc.view, rays, tie=oracle.TIE_CANONICAL)
+    out = dev(name, *params).raycast(rays, I.TRAVERSAL_WIDE, I.TIE_CANONICAL)
+    same = ids_equal(out, ref) & (bits(out["t"]) == bits(ref["t"]))
+    bad = np.nonzero(~same)[0]
+    assert len(bad) <= n * 1e-4
+    if len(bad):
+        bf = oracle.raycast_bruteforce(sc.view, rays[bad])
+        assert ids_equal(out[bad], bf).all() and (bits(out["t"][bad]) == bits(bf["t"])).all()
+    sample = np.arange(0, n, 97)
+    bf = oracle.raycast_bruteforce(sc.view, rays[sample])
+    assert ids_equal(out[sample], bf).all() and (bits(out["t"][sample]) == bits(bf["t"])).all()
+
+
+@pytest.mark.parametrize("tag", ["cornell_raycast", "terrain32_raycast"])
+def test_raycast_golden_files(I, dev, tag):
+    g = np.load(os.path.join(GOLD, tag + ".npz"))
+    from path_tracer_b200.types import RAY_DTYPE
+    rays = np.ascontiguousarray(g["rays"]).view(RAY_DTYPE).reshape(-1)
+    d = dev(str(g["scene"][0]), *[int(x) for x in g["scene_params"]])
+    for trav, tie, key in ((I.TRAVERSAL_BVH2_REFERENCE, I.TIE_FAITHFUL, "faithful"), (I.TRAVERSAL_BVH2_REFERENCE, I.TIE_CANONICAL, "canonical"),
+                           (I.TRAVERSAL_WIDE, I.TIE_CANONICAL, "brute")):
+        out = d.raycast(rays, trav, tie)
+        assert (out["shape"] == g[key + "_shape"]).all() and (out["prim"] == g[key + "_prim"]).all()
+        assert (bits(out["t"]) == bits(g[key + "_t"])).all()
+
+
+def test_raycast_axis_parallel_and_empty(I, gpu, dev, oracle, scenes):
+    sc = scenes("cornell")
+    rays = random_rays(sc, 3000, 8, oracle)
+    rays["d"] = np.eye(3, dtype=np.float32)[np.arange(3000) % 3] * np.where(np.arange(3000) % 2, -1.0, 1.0)[:, None].astype(np.float32)
+    out = dev("cornell").raycast(rays, I.TRAVERSAL_WIDE, I.TIE_CANONICAL)
+    bf = oracle.raycast_bruteforce(sc.view, rays)
+    assert ids_equal(out, bf).all() and (bits(out["t"]) == bits(bf["t"])).all()
+    assert len(dev("cornell").raycast(rays[:0])) == 0              # empty batch
+    one = dev("cornell").raycast(rays[:1], I.TRAVERSAL_BVH2_REFERENCE, I.TIE_FAITHFUL)   # ragged: single ray
+    assert one["shape"][0] == oracle.raycast(sc.view, rays[:1])["shape"][0]
+
+
+# ---------------------------------------------------------------- radiance
+def assert_radiance_close(a, b, tol=1e-4, max_outlier_fraction=2e-3):
+    """|a-b| <= tol * max(|b|, 1) per channel; a path whose random branch flips on an ulp
+    (libdevice vs glibc transcendentals) changes a whole sample, so a small fraction of
+    pixels may deviate — counted and bounded, never ignored silently."""
+    assert a.shape == b.shape
+    err = np.abs(a - b) / np.maximum(np.abs(b), 1.0)
+    bad = (err.max(axis=-1) > tol)
+    assert bad.mean() <= max_outlier_fraction, "outliers %d of %d" % (bad.sum(), bad.size)
+    return int(bad.sum())
+
+
+@pytest.mark.parametrize("name,params,w,h", [("cornell", (), 160, 96), ("terrain", (64,), 160, 96), ("room", (1, 512), 128, 64),
+                                             ("spherefield", (12, 2, 2), 128, 64)])
+def test_primary_and_first_bounce_radiance(I, gpu, dev, oracle, scenes, name, params, w, h):
+    """Restart + RunBasicRenderer(Rounds=2) (application.cpp:104-110): identical seeding, accumulators within 1e-4."""
+    o, r, film = render_pair(I, gpu, dev, oracle, scenes, name, params, w, h, frames=0)
+    a, b = film.download(), o.accum()
+    assert np.array_equal(a[..., 3], b[..., 3])                    # same paths finished per pixel
+    assert_radiance_close(a[..., :3], b[..., :3])
+    # wavefront state after the second round: origins bit-equal wherever the path history is equal
+    for arr in ("PackedVelocity", "OriginX", "ImagePosition", "NormalizedLambda0", "ShapeAndMaterialIndex"):
+        ga, oa = r.state(arr), o.state(arr)
+        live = r.state("ImagePosition") == o.state("ImagePosition")
+        assert (bits(ga)[live] == bits(oa)[live]).mean() > 0.995, arr
+    st = r.stats()
+    assert st["rays_traced"] == 2 * w * h and st["paths_finished"] == int(b[..., 3].sum()) == o.stats()["paths"]
+
+
+def test_first_bounce_golden(I, gpu, dev, scenes):
+    g = np.load(os.path.join(GOLD, "cornell_first_bounce.npz"))
+    w, h = int(g["size"][0]), int(g["size"][1])
+    film = I.SampleBuffer(gpu, w, h)
+    r = I.BasicRenderer(gpu, dev("cornell"), film)
+    r.Traversal, r.TieMode = I.TRAVERSAL_BVH2_REFERENCE, I.TIE_FAITHFUL
+    r.set_frame_index(0)
+    r.reset()
+    r.run(2)
+    a = film.download()
+    assert np.array_equal(a[..., 3], g["accum"][..., 3])
+    assert_radiance_close(a[..., :3], g["accum"][..., :3])
+
+
+@pytest.mark.parametrize("w,h", [(50, 30), (17, 33), (16, 16)])
+def test_ragged_film_sizes(I, gpu, dev, oracle, scenes, w, h):
+    """Widths/heights that are not multiples of the 16x16 tile (generalisation of Q5)."""
+    o, r, film = render_pair(I, gpu, dev, oracle, scenes, "cornell", (), w, h, frames=3)
+    a, b = film.download(), o.accum()
+    assert np.array_equal(a[..., 3], b[..., 3])
+    assert_radiance_close(a[..., :3], b[..., :3], max_outlier_fraction=5e-3)
+
+
+def test_flags_limit_and_termination(I, gpu, dev, oracle, scenes):
+    # no jitter, no accumulate, PathLengthLimit as a real limit (D5), Russian roulette 0.25
+    for flags, limit, term in ((0, 0, 0.0), (1, 3, 0.0), (3, 0, 0.25), (2, 1, 0.0)):
+        o, r, film = render_pair(I, gpu, dev, oracle, scenes, "cornell", (), 64, 48, frames=4, flags=flags, limit=limit, term=term)
+        a, b = film.download(), o.accum()
+        assert np.array_equal(a[..., 3], b[..., 3]), (flags, limit, term)
+        assert_radiance_close(a[..., :3], b[..., :3], max_outlier_fraction=5e-3)
+
+
+def test_cameras_thin_lens_and_360(I, gpu, dev, oracle, scenes):
+    o, r, film = render_pair(I, gpu, dev, oracle, scenes, "room", (1, 512), 96, 48, frames=2)            # thin lens + textures + sky lobe
+    assert_radiance_close(film.download()[..., :3], o.accum()[..., :3], max_outlier_fraction=5e-3)
+    o, r, film = render_pair(I, gpu, dev, oracle, scenes, "spherefield", (12, 2, 2), 128, 64, frames=2)  # 360 camera, mixed materials
+    assert_radiance_close(film.download()[..., :3], o.accum()[..., :3], max_outlier_fraction=5e-3)
+
+
+def test_megakernel_equals_wavefront(I, gpu, dev, scenes):
+    """Same device functions, state in registers vs in HBM: films must be bit-identical."""
+    for name, params in (("cornell", ()), ("spherefield", (12, 2, 2))):
+        films = []
+        for integ in (I.INTEGRATOR_WAVEFRONT, I.INTEGRATOR_MEGAKERNEL):
+            film = I.SampleBuffer(gpu, 96, 64)
+            r = I.BasicRenderer(gpu, dev(name, *params), film)
+            r.Integrator = integ
+            r.set_frame_index(3)
+            r.reset()
+            r.run(2)
+            r.run_frames(7)
+            r.run(3)
+            films.append((film.download(), r.stats(), r.state("PackedVelocity"), r.state("Throughput1")))
+        assert np.array_equal(films[0][0], films[1][0])
+        assert films[0][1]["paths_finished"] == films[1][1]["paths_finished"] and films[0][1]["rays_traced"] == films[1][1]["rays_traced"]
+        assert np.array_equal(films[0][2], films[1][2]) and np.array_equal(bits(films[0][3]), bits(films[1][3]))
+
+
+@pytest.mark.parametrize("name,params", [("cornell", ()), ("terrain", (64,))])
+def test_converged_image_within_one_percent(I, gpu, dev, oracle, scenes, name, params):
+    """Wide BVH + megakernel on the GPU against the reference-order oracle at equal sample counts."""
+    w, h, frames = 96, 64, 400
+    o, r, film = render_pair(I, gpu, dev, oracle, scenes, name, params, w, h, frames=frames, tie=oracle.TIE_CANONICAL,
+                             traversal=I.TRAVERSAL_WIDE, integrator=I.INTEGRATOR_MEGAKERNEL)
+    a, b = film.download(), o.accum()
+    ia = a[..., :3] / np.maximum(a[..., 3:], 1)
+    ib = b[..., :3] / np.maximum(b[..., 3:], 1)
+    rel = np.abs(ia.mean(axis=(0, 1)) - ib.mean(axis=(0, 1))) / ib.mean(axis=(0, 1))
+    assert (rel <= 0.01).all(), rel
+    assert abs(a[..., 3].sum() - b[..., 3].sum()) / b[..., 3].sum() < 0.01
+    per_pixel = np.abs(ia - ib).mean() / ib.mean()
+    assert per_pixel <= 0.01, per_pixel
+
+
+# ---------------------------------------------------------------- resolve
+@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+def test_resolve_tone_mapping(I, gpu, oracle, mode):
+    rng = np.random.default_rng(9)
+    w, h = 64, 32
+    accum = np.zeros((h, w, 4), np.float32)
+    accum[..., 3] = rng.integers(0, 50, size=(h, w))
+    accum[..., :3] = rng.uniform(0, 3, size=(h, w, 3)) * accum[..., 3:]
+    accum[0, :8] = 0                                             # untouched pixels: alpha 0
+    film = I.SampleBuffer(gpu, w, h)
+    film.upload(accum)
+    assert np.array_equal(film.download(), accum)
+    lin, srgb = film.resolve(1.7, mode, 2.5)
+    rl, rs = oracle.resolve(accum, 1.7, mode, 2.5)
+    ok = np.isfinite(rl)
+    assert (np.isfinite(lin) == ok).all()                        # Reinhard 0/0 -> NaN on both sides (Q15)
+    assert np.allclose(lin[ok], rl[ok], rtol=1e-5, atol=1e-6)
+    assert np.abs(srgb.astype(int) - rs.astype(int)).max() <= 1  # powf differs by an ulp at rounding boundaries
+    assert (srgb[..., 3] == 255).all()
+
+
+# ---------------------------------------------------------------- API behaviour
+def test_error_behaviour(I, gpu, dev):
+    film = I.SampleBuffer(gpu, 32, 32)
+    r = I.BasicRenderer(gpu, dev("cornell"), film)
+    r.CameraIndex = 99
+    with pytest.raises(I.PtbError):
+        r.reset()
+    r.CameraIndex = 0
+    r.Traversal, r.TieMode = I.TRAVERSAL_WIDE, I.TIE_FAITHFUL     # order-free traversal cannot honour order-dependent ties
+    with pytest.raises(I.PtbError):
+        r.reset()
+    with pytest.raises(I.PtbError):
+        I.SampleBuffer(gpu, 0, 10)
+    with pytest.raises(I.PtbError):
+        film.upload(np.zeros((3, 3, 4), np.float32))
+    with pytest.raises(I.PtbError):
+        film.resolve(1.0, 7, 1.0)
+
+
+def test_empty_scene_renders_sky(I, gpu, oracle):
+    from path_tracer_b200 import scene as S
+    sc = S.Scene()
+    sc.create_camera((0, -5, 1), (0, 0, 1))
+    sc.pack()
+    d = I.DeviceScene(gpu, sc)
+    for trav, tie in ((I.TRAVERSAL_WIDE, I.TIE_CANONICAL), (I.TRAVERSAL_BVH2_REFERENCE, I.TIE_FAITHFUL)):
+        film = I.SampleBuffer(gpu, 32, 16)
+        r = I.BasicRenderer(gpu, d, film)
+        r.Traversal, r.TieMode = trav, tie
+        r.reset()
+        r.run(2)
+        a = film.download()
+        assert (a[..., 3] == 2).all()                            # every path escapes on its first segment
+        o = oracle.Renderer(sc.view, 32, 16)
+        o.reset()
+        o.run(2)
+        assert_radiance_close(a[..., :3], o.accum()[..., :3])
+
+
+def test_scene_update_dirty_flags(I, gpu, oracle):
+    """UpdateVulkanScene semantics: only the flagged arrays are re-uploaded; moving a shape re-flattens."""
+    from path_tracer_b200 import scene as S
+    sc = S.Scene()
+    m = sc.create_material(S.MATERIAL_BASIC_DIFFUSE, "m", BaseColor=(0.5, 0.5, 0.5))
+    e = sc.create_entity(S.ENTITY_SPHERE, position=(0, 0, 0), material=m)
+    sc.create_camera((0, -5, 0), (0, 0, 0))
+    sc.pack()
+    d = I.DeviceScene(gpu, sc)
+    ray = oracle.make_rays(np.array([[0, -5, 0]], np.float32), np.array([[0, 1, 0]], np.float32))
+    assert d.raycast(ray)["t"][0] == 4.0
+    sc.set_transform(e, position=(0, 2, 0))
+    flags = sc.pack()
+    assert flags & 8                                             # SCENE_DIRTY_SHAPES
+    d.update(sc, flags)
+    assert d.raycast(ray)["t"][0] == 6.0
+    assert d.raycast(ray, I.TRAVERSAL_BVH2_REFERENCE, I.TIE_FAITHFUL)["t"][0] == 6.0
+
+
+# ---------------------------------------------------------------- BASELINE.json full sizes (size-independent properties)
+def test_full_size_c2_properties(I, gpu, oracle):
+    """C2: 1,002,528 triangles, 1920x1080.  Properties that need no full-size oracle run:
+    alpha sum == paths finished == stats; film non-negative and finite; wide ray casts equal the
+    reference traversal on a 100k-ray sample and brute force on a small one."""
+    from path_tracer_b200 import scene as S
+    sc = S.Scene.make("terrain", 708)
+    assert sc.view.MeshFaceCount == 1002528
+    d = I.DeviceScene(gpu, sc)
+    info = d.wide_info()
+    assert info["status"] == 0 and info["prim_count"] == 1002528 and info["depth"] <= 30
+    w, h = 1920, 1080
+    film = I.SampleBuffer(gpu, w, h)
+    r = I.BasicRenderer(gpu, d, film)
+    r.reset()
+    r.run(2)
+    r.run_frames(14)
+    st = r.stats()
+    a = film.download()
+    assert st["rays_traced"] == 16 * w * h
+    assert int(a[..., 3].sum()) == st["paths_finished"] > w * h
+    assert np.isfinite(a).all() and (a[..., 3] >= 0).all() and (a[..., 1] >= 0).all()
+    lin, srgb = film.resolve(1.0, I.TONE_ACES, 1.0)
+    assert np.isfinite(lin).all() and srgb[..., :3].std() > 5      # an actual picture
+    rays = random_rays(sc, 100000, 31, oracle)
+    out = d.raycast(rays)
+    ref = oracle.raycast(sc.view, rays, tie=oracle.TIE_CANONICAL)
+    bad = np.nonzero(~(ids_equal(out, ref) & (bits(out["t"]) == bits(ref["t"]))))[0]
+    assert len(bad) <= 20
+    sample = np.concatenate([bad, np.arange(0, 100000, 500)]).astype(np.int64)
+    bf = oracle.raycast_bruteforce(sc.view, rays[sample])
+    assert ids_equal(out[sample], bf).all() and (bits(out["t"][sample]) == bits(bf["t"])).all()

@@ -1,0 +1,122 @@
+"""Host logic on CPU: packed layouts, the reference-order mesh BVH2, and the wide-BVH
+flattening (checked through tests/host_emu, a g++ build of the product's per-thread
+device functions — test infrastructure, see tests/host_emu/emu.cpp)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from util import ids_equal, random_rays
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EMU_DIR = os.path.join(ROOT, "tests", "host_emu")
+
+
+@pytest.fixture(scope="module")
+def emu():
+    out = os.path.join(EMU_DIR, "_build", "libemu.so")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    csrc = os.path.join(ROOT, "path_tracer_b200", "csrc")
+    srcs = [os.path.join(EMU_DIR, "emu.cpp"), os.path.join(csrc, "ptb_wide_build.cpp")]
+    deps = srcs + [os.path.join(csrc, f) for f in os.listdir(csrc)]
+    if not os.path.exists(out) or any(os.path.getmtime(d) > os.path.getmtime(out) for d in deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-pthread", "-I", csrc,
+                               "-I", os.path.join(ROOT, "include"), "-I", "/usr/local/cuda/include", "-o", out] + srcs)
+    L = C.CDLL(out)
+    L.emu_create.restype = C.c_void_p
+    L.emu_create.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
+    L.emu_destroy.argtypes = [C.c_void_p]
+    L.emu_raycast.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
+    L.emu_wide_info.argtypes = [C.c_void_p, C.c_void_p]
+    L.emu_set.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float, C.c_uint32]
+    L.emu_reset.argtypes = [C.c_void_p]
+    L.emu_run.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_int]
+    L.emu_accum.restype = C.c_void_p
+    L.emu_accum.argtypes = [C.c_void_p]
+    return L
+
+
+def test_packed_layouts(scenes):
+    sc = scenes("terrain", 32)
+    v = sc.view
+    assert v.MeshFaceCount == 2 * 32 * 32 and v.ShapeCount == 2
+    assert sc.shapes.dtype.itemsize == 144 and sc.mesh_nodes.dtype.itemsize == 32 and sc.mesh_faces.dtype.itemsize == 48
+    assert v.MaterialWordCount % 32 == 0
+    # material slots 0-1 are the fallback OpenPBR record (scene.cpp:1241-1250): first user slot is 2
+    assert int(sc.shapes["MaterialIndex"].min()) >= 2
+    g = sc.globals
+    assert g["ShapeCount"] == v.ShapeCount and g["SkyboxTextureIndex"] == 0xFFFFFFFF
+
+
+def test_mesh_bvh2_invariants(scenes):
+    """Children adjacent, leaves partition the face range, boxes contain their faces (scene.cpp:435-599)."""
+    sc = scenes("terrain", 32)
+    nodes, faces = sc.mesh_nodes, sc.mesh_faces
+    root = int(sc.shapes[sc.shapes["Type"] == 0]["MeshRootNodeIndex"][0])
+    seen = np.zeros(len(faces), dtype=np.int32)
+    stack = [root]
+    while stack:
+        n = nodes[stack.pop()]
+        if n["FaceEndIndex"] > 0:
+            b, e = int(n["FaceBeginOrNodeIndex"]), int(n["FaceEndIndex"])
+            seen[b:e] += 1
+            for k in ("Position0", "Position1", "Position2"):
+                p = faces[k][b:e]
+                assert (p >= n["Minimum"] - 1e-6).all() and (p <= n["Maximum"] + 1e-6).all()
+        else:
+            c = int(n["FaceBeginOrNodeIndex"])
+            stack += [c, c + 1]
+    assert (seen == 1).all()
+
+
+@pytest.mark.parametrize("name,params", [("cornell", ()), ("terrain", (48,)), ("room", (1, 256)), ("spherefield", (10, 2, 2))])
+def test_wide_flattening_equals_brute_force(emu, oracle, scenes, name, params):
+    """The wide BVH is only a culling structure: its closest hit must be the brute-force
+    closest hit of the reference's primitive tests (canonical ties), bit for bit."""
+    sc = scenes(name, *params)
+    e = emu.emu_create(C.addressof(sc.view), 16, 16)
+    assert e
+    info = (C.c_uint32 * 5)()
+    emu.emu_wide_info(e, info)
+    assert info[2] <= 30                                    # depth fits the traversal stack
+    n = 6000
+    rays = random_rays(sc, n, 21, oracle)
+    # axis-parallel and signed-zero directions are the classic slab-test traps
+    rays["d"][:64] = np.eye(3, dtype=np.float32)[np.arange(64) % 3] * np.where(np.arange(64) % 2, -1, 1)[:, None]
+    rays["d"][64:96, 0] = -0.0
+    rays["d"][64:96] /= np.linalg.norm(rays["d"][64:96], axis=1, keepdims=True)
+    from path_tracer_b200.types import HIT_DTYPE
+    out = np.zeros(n, dtype=HIT_DTYPE)
+    emu.emu_raycast(e, rays.ctypes.data, n, 2, out.ctypes.data)
+    bf = oracle.raycast_bruteforce(sc.view, rays)
+    assert ids_equal(out, bf).all()
+    assert (out["t"].view(np.uint32) == bf["t"].view(np.uint32)).all()
+    # the reference-layout traversal compiled from the same headers is bit-identical to the oracle's
+    for mode, tie in ((0, oracle.TIE_FAITHFUL), (1, oracle.TIE_CANONICAL)):
+        ref = oracle.raycast(sc.view, rays, tie=tie)
+        emu.emu_raycast(e, rays.ctypes.data, n, mode, out.ctypes.data)
+        assert ids_equal(out, ref).all() and (out["t"].view(np.uint32) == ref["t"].view(np.uint32)).all()
+        hit = ref["shape"] != 0xFFFFFFFF
+        assert np.array_equal(out["n"][hit], ref["n"][hit]) and np.array_equal(out["uv"][hit], ref["uv"][hit])
+    emu.emu_destroy(e)
+
+
+def test_device_functions_render_like_the_oracle(emu, oracle, scenes):
+    """Scatter/regenerate logic of the product headers (g++ build) against the oracle, same libm: exact."""
+    sc = scenes("cornell")
+    w, h = 48, 32
+    e = emu.emu_create(C.addressof(sc.view), w, h)
+    r = oracle.Renderer(sc.view, w, h, tie=oracle.TIE_FAITHFUL)
+    r.set_frame_index(0)
+    r.reset()
+    r.run(2)
+    r.run_frames(5)
+    emu.emu_set(e, 0, 3, 0, 0.0, 0)
+    emu.emu_reset(e)
+    emu.emu_run(e, 2, 0, 0)
+    emu.emu_run(e, 5, 0, 1)
+    b = np.frombuffer((C.c_float * (w * h * 4)).from_address(emu.emu_accum(e)), dtype=np.float32).reshape(h, w, 4)
+    assert np.array_equal(r.accum(), b)
+    emu.emu_destroy(e)
