@@ -149,15 +149,16 @@ def run_reference(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=16, help="steady-state frames (rounds) per step")
     ap.add_argument("--integrator", default="wavefront", choices=["wavefront", "megakernel"])
     ap.add_argument("--traversal", default="wide", choices=["wide", "bvh2"])
     ap.add_argument("--grid", type=int, default=GRID)
-    ap.add_argument("--ref-frames", type=int, default=4)
-    ap.add_argument("--ref-tile-stride", type=int, default=16)
+    ap.add_argument("--ref-frames", type=int, default=8, help="frames per step of the CPU reference arm")
+    ap.add_argument("--ref-tile-stride", type=int, default=4, help="CPU arms process every n-th 16x16 tile (bounded sample)")
+    ap.add_argument("--cpu-frames", type=int, default=96, help="frames of the cpu_baseline sample (about 10-30 s of CPU work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
 
@@ -264,11 +265,11 @@ def main():
     seg_bytes, trace_bytes = None, None
     if not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1
-        c = oracle_sample(scene, args.ref_frames, args.ref_tile_stride, threads)
+        c = oracle_sample(scene, args.cpu_frames, args.ref_tile_stride, threads)
         seg_bytes, trace_bytes = bytes_per_segment(c)
         cpu = {"value": c["rays"] / c["seconds"] / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
                "sample": "every %d-th 16x16 tile of the same 1920x1080 film, %d frames, %d rays in %.1f s"
-                         % (args.ref_tile_stride, args.ref_frames, c["rays"], c["seconds"]),
+                         % (args.ref_tile_stride, args.cpu_frames, c["rays"], c["seconds"]),
                "mpaths_per_s": c["paths"] / c["seconds"] / 1e6,
                "per_ray": {"node_fetches": c["node_fetches"] / c["rays"], "face_tests": c["face_tests"] / c["rays"],
                            "shape_visits": c["shape_visits"] / c["rays"], "mesh_hit_fraction": c["mesh_hits"] / c["rays"]}}
