@@ -155,6 +155,7 @@ def main():
     ap.add_argument("--frames", type=int, default=16, help="steady-state frames (rounds) per step")
     ap.add_argument("--integrator", default="wavefront", choices=["wavefront", "megakernel"])
     ap.add_argument("--traversal", default="wide", choices=["wide", "bvh2"])
+    ap.add_argument("--trace-variant", type=int, default=-1, help="PTB_TRACE_VARIANT_* (default: the library's)")
     ap.add_argument("--grid", type=int, default=GRID)
     ap.add_argument("--ref-frames", type=int, default=8, help="frames per step of the CPU reference arm")
     ap.add_argument("--ref-tile-stride", type=int, default=4, help="CPU arms process every n-th 16x16 tile (bounded sample)")
@@ -192,6 +193,8 @@ def main():
     r.Integrator = I.INTEGRATOR_MEGAKERNEL if args.integrator == "megakernel" else I.INTEGRATOR_WAVEFRONT
     r.Traversal = I.TRAVERSAL_WIDE if args.traversal == "wide" else I.TRAVERSAL_BVH2_REFERENCE
     r.TieMode = I.TIE_CANONICAL
+    if args.trace_variant >= 0:
+        r.TraceVariant = args.trace_variant
     F = args.frames
     total_frames = F * (args.warmup + 2 * args.steps + 8)
     r.set_frame_index(D.frame_schedule(rank, world, total_frames))                      # disjoint seed block per rank
@@ -288,7 +291,7 @@ def main():
         "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_max / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "frames_per_step": F, "rays_per_step_per_gpu": WIDTH * HEIGHT * F,
-                   "integrator": args.integrator, "traversal": args.traversal, "parallelism": "sample-split x%d" % world,
+                   "integrator": args.integrator, "traversal": args.traversal, "trace_variant": r.TraceVariant, "parallelism": "sample-split x%d" % world,
                    "l2": "per-round working set (232 MB wavefront state + ~170 MB scene) exceeds the 126 MB L2; no explicit flush",
                    "wide_bvh": {k: wide[k] for k in ("node_count", "prim_count", "depth", "build_seconds")}},
         "mpaths_per_s": paths_all / (ms_max * 1e-3) / 1e6,

@@ -106,6 +106,12 @@ typedef struct { float Brightness; uint32_t ToneMappingMode; float ToneMappingWh
 #define PTB_TRAVERSAL_BVH2_REFERENCE 0u /* the packed two-level BVH2 as-is, reference visiting order */
 #define PTB_TRAVERSAL_WIDE           1u /* compressed BVH8 re-flattened at ptb_scene_update */
 
+/* Trace-step kernel for PTB_TRAVERSAL_WIDE.  0 = one thread per slot; 1..MAX = persistent
+ * warps with dynamic ray fetch, numbered tuning points (see ptb_kernels.cu). */
+#define PTB_TRACE_VARIANT_SIMPLE  0u
+#define PTB_TRACE_VARIANT_DEFAULT 2u
+#define PTB_TRACE_VARIANT_MAX     10u
+
 /* Tie rule for equal hit times. */
 #define PTB_TIE_FAITHFUL  0u  /* reference rules; needs PTB_TRAVERSAL_BVH2_REFERENCE */
 #define PTB_TIE_CANONICAL 1u  /* lowest (t, ShapeIndex, PrimitiveIndex) */
@@ -121,7 +127,7 @@ typedef struct {
     uint32_t Integrator;                 /* PTB_INTEGRATOR_* */
     uint32_t Traversal;                  /* PTB_TRAVERSAL_*  */
     uint32_t TieMode;                    /* PTB_TIE_*        */
-    uint32_t Reserved;
+    uint32_t TraceVariant;               /* PTB_TRACE_VARIANT_*: kernel shape of the wide-BVH trace step */
 } ptb_render_params;
 
 typedef struct {

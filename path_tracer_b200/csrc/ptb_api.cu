@@ -45,7 +45,7 @@ struct DevBuf {
 
 }  // namespace
 
-struct ptb_context { int device; cudaStream_t stream; };
+struct ptb_context { int device; cudaStream_t stream; unsigned* counter; };
 
 struct ptb_scene {
     ptb_context* ctx;
@@ -64,6 +64,7 @@ struct ptb_scene {
     DevBuf<uint32_t> wide_planes;
     DeviceScene ds;
     ptb_wide_info wide_info;
+    unsigned raycast_variant;
 };
 
 struct ptb_film {
@@ -103,6 +104,8 @@ int ptb_context_create(int cuda_device, ptb_context** out) {
     c->device = cuda_device;
     e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) { delete c; return cuda_fail(e, "cudaStreamCreate"); }
+    e = cudaMalloc((void**)&c->counter, 64);
+    if (e != cudaSuccess) { cudaStreamDestroy(c->stream); delete c; return cuda_fail(e, "cudaMalloc(counter)"); }
     *out = c;
     return PTB_OK;
 }
@@ -111,6 +114,7 @@ void ptb_context_destroy(ptb_context* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     cudaStreamDestroy(ctx->stream);
+    cudaFree(ctx->counter);
     delete ctx;
 }
 int ptb_context_sync(ptb_context* ctx) {
@@ -129,6 +133,7 @@ int ptb_scene_create(ptb_context* ctx, ptb_scene** out) {
     std::memset(&s->wide_info, 0, sizeof s->wide_info);
     s->ds.wide_tlas_root = 0xFFFFFFFFu;
     s->ds.globals.SkyboxTextureIndex = 0xFFFFFFFFu;
+    s->raycast_variant = PTB_TRACE_VARIANT_DEFAULT;
     *out = s;
     return PTB_OK;
 }
@@ -291,6 +296,7 @@ int ptb_renderer_create(ptb_context* ctx, ptb_scene* scene, ptb_film* film, ptb_
     r->params.RenderFlags = PTB_RENDER_FLAG_ACCUMULATE | PTB_RENDER_FLAG_SAMPLE_JITTER;   // application.cpp:106
     r->params.Traversal = PTB_TRAVERSAL_WIDE;
     r->params.TieMode = PTB_TIE_CANONICAL;
+    r->params.TraceVariant = PTB_TRACE_VARIANT_DEFAULT;
     r->frame_index = 0; r->rays_traced = 0; r->kernel_launches = 0;
     RenderConsts& pc = r->pc;
     std::memset(&pc, 0, sizeof pc);
@@ -299,7 +305,7 @@ int ptb_renderer_create(ptb_context* ctx, ptb_scene* scene, ptb_film* film, ptb_
     const uint32_t tiles = pc.tiles_x * ((film->height + 15) / 16);
     pc.slot_count = tiles * 256u;
     const size_t S = pc.slot_count;
-    const size_t bytes = S * (7 * 16) + (size_t)tiles * sizeof(unsigned);
+    const size_t bytes = S * (7 * 16) + (size_t)(tiles + 16) * sizeof(unsigned);
     cudaError_t e = cudaMalloc(&r->state_block, bytes);
     if (e != cudaSuccess) { delete r; return cuda_fail(e, "cudaMalloc(wavefront state)"); }
     cudaMemsetAsync(r->state_block, 0, bytes, ctx->stream);
@@ -311,7 +317,8 @@ int ptb_renderer_create(ptb_context* ctx, ptb_scene* scene, ptb_film* film, ptb_
     r->st.path1 = (float4*)b; b += S * 16;
     r->st.path2 = (float4*)b; b += S * 16;
     r->st.path3 = (float4*)b; b += S * 16;
-    r->st.tile_paths = (unsigned*)b;
+    r->st.tile_paths = (unsigned*)b; b += (size_t)tiles * sizeof(unsigned);
+    r->st.ray_counter = (unsigned*)b;
     *out = r;
     return PTB_OK;
 }
@@ -324,7 +331,7 @@ void ptb_renderer_destroy(ptb_renderer* r) {
 }
 int ptb_renderer_set_params(ptb_renderer* r, const ptb_render_params* p) {
     if (!r || !p) return fail(PTB_E_INVALID, "ptb_renderer_set_params: NULL argument");
-    if (p->Integrator > PTB_INTEGRATOR_MEGAKERNEL || p->Traversal > PTB_TRAVERSAL_WIDE || p->TieMode > PTB_TIE_CANONICAL)
+    if (p->Integrator > PTB_INTEGRATOR_MEGAKERNEL || p->Traversal > PTB_TRAVERSAL_WIDE || p->TieMode > PTB_TIE_CANONICAL || p->TraceVariant > PTB_TRACE_VARIANT_MAX)
         return fail(PTB_E_INVALID, "ptb_renderer_set_params: unknown enum value");
     if (p->Traversal == PTB_TRAVERSAL_WIDE && p->TieMode != PTB_TIE_CANONICAL)
         return fail(PTB_E_INVALID, "ptb_renderer_set_params: the wide traversal is order-free and needs PTB_TIE_CANONICAL");
@@ -370,7 +377,7 @@ static int run_rounds(ptb_renderer* r, uint32_t rounds, uint32_t seed_stride) {
     } else {
         RenderConsts pc = r->pc;
         for (uint32_t k = 0; k < rounds; k++) {
-            CU(launch_trace(ds, pc, r->st, r->params.Traversal, r->params.TieMode, st));
+            CU(launch_trace(ds, pc, r->st, r->params.Traversal, r->params.TieMode, r->params.TraceVariant, st));
             CU(launch_scatter(ds, pc, r->st, r->film->accum, st));
             pc.random_seed += seed_stride;
         }
@@ -425,7 +432,7 @@ int ptb_renderer_profile_frames(ptb_renderer* r, uint32_t frames, ptb_kernel_tim
             CU(launch_megakernel(ds, pc, r->st, r->film->accum, r->params.Traversal, r->params.TieMode, 1u, 1u, st));
             CU(cudaEventRecord(e[1], st));
         } else {
-            CU(launch_trace(ds, pc, r->st, r->params.Traversal, r->params.TieMode, st));
+            CU(launch_trace(ds, pc, r->st, r->params.Traversal, r->params.TieMode, r->params.TraceVariant, st));
             CU(cudaEventRecord(e[1], st));
             CU(launch_scatter(ds, pc, r->st, r->film->accum, st));
             CU(cudaEventRecord(e[2], st));
@@ -482,8 +489,8 @@ int ptb_renderer_download_state(ptb_renderer* r, const char* name, void* host, s
     struct Field { const char* name; int record; int word; };
     static const Field fields[] = {
         {"OriginX", 0, 0}, {"OriginY", 0, 1}, {"OriginZ", 0, 2}, {"PackedVelocity", 0, 3},
-        {"Time", 1, 0}, {"ShapeAndMaterialIndex", 1, 1}, {"PackedNormal", 1, 2}, {"PackedTangentX", 1, 3},
-        {"TextureU", 2, 0}, {"TextureV", 2, 1}, {"PrimitiveIndex", 2, 2}, {"ShapeType", 2, 3},
+        {"Time", 1, 0}, {"ShapeAndMaterialIndex", 1, 1}, {"PrimitiveIndex", 1, 2}, {"ShapeType", 1, 3},
+        {"PrimitiveCoordinateX", 2, 0}, {"PrimitiveCoordinateY", 2, 1}, {"PrimitiveCoordinateZ", 2, 2},
         {"ImagePosition", 3, 0}, {"NormalizedLambda0", 3, 1}, {"ActiveShapeIndex01", 3, 2}, {"ActiveShapeIndex23", 3, 3},
         {"Throughput0", 4, 0}, {"Throughput1", 4, 1}, {"Throughput2", 4, 2}, {"Throughput3", 4, 3},
         // the reference stores Probability.w in array 2 and .z in array 3 (basic.glsl.inc:176-177,208-209)
@@ -498,6 +505,23 @@ int ptb_renderer_download_state(ptb_renderer* r, const char* name, void* host, s
         CU(cudaStreamSynchronize(r->ctx->stream));
         uint32_t* o = (uint32_t*)host;
         for (size_t i = 0; i < S; i++) o[i] = rec[4 * i + f.word];
+        return PTB_OK;
+    }
+    // derived from the stored hit on demand (the scatter kernel derives them the same way)
+    static const char* derived[] = {"PackedNormal", "PackedTangentX", "TextureU", "TextureV"};
+    for (int k = 0; k < 4; k++) {
+        if (std::strcmp(derived[k], name)) continue;
+        uint4* tmp = nullptr;
+        CU(cudaMalloc((void**)&tmp, S * 16));
+        cudaError_t e = cudaMemsetAsync(tmp, 0, S * 16, r->ctx->stream);
+        if (e == cudaSuccess) e = launch_hit_attributes(r->scene->ds, r->pc, r->st, tmp, r->ctx->stream);
+        std::vector<uint32_t> rec(S * 4);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(rec.data(), tmp, S * 16, cudaMemcpyDeviceToHost, r->ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(r->ctx->stream);
+        cudaFree(tmp);
+        if (e != cudaSuccess) return cuda_fail(e, "ptb_renderer_download_state");
+        uint32_t* o = (uint32_t*)host;
+        for (size_t i = 0; i < S; i++) o[i] = rec[4 * i + k];
         return PTB_OK;
     }
     if (!std::strcmp(name, "Duration")) {
@@ -522,7 +546,7 @@ int ptb_raycast(ptb_scene* s, const ptb_ray* host_rays, size_t n, uint32_t trave
     cudaError_t e = cudaMalloc((void**)&d_hits, n * sizeof(ptb_hit));
     if (e != cudaSuccess) { cudaFree(d_rays); return cuda_fail(e, "cudaMalloc(hits)"); }
     e = cudaMemcpyAsync(d_rays, host_rays, n * sizeof(ptb_ray), cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) e = launch_raycast(s->ds, d_rays, n, traversal, tie, d_hits, st);
+    if (e == cudaSuccess) e = launch_raycast(s->ds, d_rays, n, traversal, tie, s->raycast_variant, s->ctx->counter, d_hits, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(host_hits, d_hits, n * sizeof(ptb_hit), cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     cudaFree(d_rays); cudaFree(d_hits);
@@ -536,7 +560,7 @@ int ptb_raycast_device(ptb_scene* s, const ptb_ray* d_rays, size_t n, uint32_t t
     if (traversal == PTB_TRAVERSAL_WIDE && tie != PTB_TIE_CANONICAL) return fail(PTB_E_INVALID, "ptb_raycast_device: the wide traversal needs PTB_TIE_CANONICAL");
     if (traversal == PTB_TRAVERSAL_WIDE && s->ds.shape_count > 0 && s->wide_info.status != PTB_OK) return fail(PTB_E_UNSUPPORTED, "ptb_raycast_device: wide BVH unavailable");
     CU(cudaSetDevice(s->ctx->device));
-    CU(launch_raycast(s->ds, d_rays, n, traversal, tie, d_hits, s->ctx->stream));
+    CU(launch_raycast(s->ds, d_rays, n, traversal, tie, s->raycast_variant, s->ctx->counter, d_hits, s->ctx->stream));
     return PTB_OK;
 }
 

@@ -70,6 +70,29 @@ __device__ __forceinline__ void store_path(const WavefrontState& st, u32 slot, c
     st.path3[slot] = make_float4(path.sample.x, path.sample.y, path.sample.z, __uint_as_float(path.length));
 }
 
+// Compact closest-hit record written by the trace kernels.
+__device__ __forceinline__ void store_hit(const DeviceScene& s, const WavefrontState& st, u32 slot, const HitId& h) {
+    if (h.shape == PTB_SHAPE_NONE) {
+        st.hit0[slot] = make_uint4(__float_as_uint(PTB_HIT_TIME_LIMIT), 0xFFFFFFFFu, 0xFFFFFFFFu, 0u);
+        return;
+    }
+    const u32 material = __ldg(&s.shapes[h.shape].MaterialIndex);
+    st.hit0[slot] = make_uint4(__float_as_uint(h.t), (h.shape << 16) | material, h.prim, h.shape_type);   // 16-bit ids: basic.glsl.inc:150
+    st.hit1[slot] = make_uint4(__float_as_uint(h.coords.x), __float_as_uint(h.coords.y), __float_as_uint(h.coords.z), 0u);
+}
+// The wavefront hit as scatter sees it (basic.glsl.inc:99-131): attributes are derived here and
+// pass through the reference's 24-byte quantisation (oct-encoded normal/tangent).
+__device__ __forceinline__ PackedHit load_packed_hit(const DeviceScene& s, const WavefrontState& st, u32 slot) {
+    const uint4 h0 = st.hit0[slot];
+    if (h0.y == 0xFFFFFFFFu) return packed_miss();
+    const uint4 h1 = st.hit1[slot];
+    HitId h;
+    h.t = __uint_as_float(h0.x); h.shape = h0.y >> 16; h.prim = h0.z; h.shape_type = h0.w;
+    h.coords = mk3(__uint_as_float(h1.x), __uint_as_float(h1.y), __uint_as_float(h1.z));
+    const Surface sf = finish_hit(s, h);
+    return pack_hit(h, sf);
+}
+
 // ---- K3: restart ----
 __global__ void __launch_bounds__(256) k_restart(const DeviceScene s, const RenderConsts pc, const WavefrontState st, float4* __restrict__ accum) {
     const u32 slot = blockIdx.x * 256u + threadIdx.x;
@@ -83,6 +106,7 @@ __global__ void __launch_bounds__(256) k_restart(const DeviceScene s, const Rend
     store_path(st, slot, path);
     accum[y * pc.width + x] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (threadIdx.x == 0) st.tile_paths[blockIdx.x] = 0u;
+    if (slot == 0) *st.ray_counter = 0u;
 }
 
 // ---- K1: trace ----
@@ -93,29 +117,153 @@ __global__ void __launch_bounds__(128) k_trace(const DeviceScene s, const Render
     if (!slot_pixel(pc, slot, x, y)) return;
     const Ray ray = load_ray(st, slot);
     const HitId h = closest_hit<MODE>(s, ray);
-    if (h.shape == PTB_SHAPE_NONE) {
-        st.hit0[slot] = make_uint4(__float_as_uint(PTB_HIT_TIME_LIMIT), 0xFFFFFFFFu, 0u, 0u);
-        st.hit1[slot] = make_uint4(0u, 0u, 0xFFFFFFFFu, 0u);
-        return;
+    store_hit(s, st, slot, h);
+}
+
+
+// ---- K1, persistent warp-cooperative variant -----------------------------------------------
+// B200 has no RT cores: closest-hit queries are software traversal on the SMs, and their cost is
+// dominated by SIMT divergence (rays of a warp finish after very different numbers of steps;
+// v1 above runs at ~8 of 32 lanes, profiles/r01_v1_k_trace_wide.txt).  Here the grid is sized
+// to the machine (resident warps only) and every warp loops
+//     refill  : lanes whose ray is done fetch new rays from a global counter (ballot + prefix rank),
+//     node    : every active lane visits one node (all active lanes have node work here),
+//     prims   : lanes with leaf primitives test them; when only a few lanes have any, lanes that
+//               still have node work park the primitive group on their stack (vote-driven postponing),
+//     pop     : lanes out of node work pop their stack or retire and store their hit.
+// The first entries of each lane's stack live in shared memory, lane-interleaved (bank = lane, so
+// any mix of stack depths is conflict-free); deeper entries spill to local memory.
+#define PTB_SMEM_STACK 10
+#define PTB_TRACE_WARPS 4
+
+struct WarpStack {
+    uint2* smem;                                   // entry k of this lane at smem[k * 32]
+    uint2 spill[PTB_WIDE_STACK - PTB_SMEM_STACK];
+    int sp;
+    __device__ __forceinline__ void push(uint2 v) {
+        if (sp < PTB_SMEM_STACK) smem[sp * 32] = v;
+        else if (sp < PTB_WIDE_STACK) spill[sp - PTB_SMEM_STACK] = v;
+        else return;
+        sp++;
     }
-    const Surface sf = finish_hit(s, h);
-    const PackedHit p = pack_hit(h, sf);
-    st.hit0[slot] = make_uint4(__float_as_uint(p.t), p.shape_material, p.normal, p.tangent);
-    st.hit1[slot] = make_uint4(__float_as_uint(p.u), __float_as_uint(p.v), h.prim, h.shape_type);
+    __device__ __forceinline__ uint2 pop() {
+        --sp;
+        return sp < PTB_SMEM_STACK ? smem[sp * 32] : spill[sp - PTB_SMEM_STACK];
+    }
+    __device__ __forceinline__ bool empty() const { return sp == 0; }
+};
+
+// Ray source / hit sink of the integrator: the wavefront state, slot order.
+struct WavefrontJob {
+    DeviceScene s; RenderConsts pc; WavefrontState st;
+    __device__ __forceinline__ u32 total() const { return pc.slot_count; }
+    __device__ __forceinline__ unsigned* counter() const { return st.ray_counter; }
+    __device__ __forceinline__ bool load(u32 i, Ray& r) const { u32 x, y; if (!slot_pixel(pc, i, x, y)) return false; r = load_ray(st, i); return true; }
+    __device__ __forceinline__ void store(u32 i, const HitId& h) const { store_hit(s, st, i, h); }
+};
+// Caller rays (parity harness).
+struct RaycastJob {
+    DeviceScene s; const ptb_ray* rays; ptb_hit* out; u32 n; unsigned* ctr;
+    __device__ __forceinline__ u32 total() const { return n; }
+    __device__ __forceinline__ unsigned* counter() const { return ctr; }
+    __device__ __forceinline__ bool load(u32 i, Ray& r) const {
+        const ptb_ray in = rays[i];
+        r.origin = mk3(in.ox, in.oy, in.oz); r.velocity = mk3(in.dx, in.dy, in.dz); r.duration = in.duration;
+        return true;
+    }
+    __device__ __forceinline__ void store(u32 i, const HitId& h) const;
+};
+
+template <class Job, int REFILL, int POSTPONE>
+__global__ void __launch_bounds__(32 * PTB_TRACE_WARPS) k_trace_persistent(const Job job) {
+    __shared__ uint2 stack_mem[PTB_TRACE_WARPS][PTB_SMEM_STACK][32];
+    const DeviceScene& s = job.s;
+    const u32 lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const u32 lt_mask = (1u << lane) - 1u;
+    const u32 total = job.total();
+
+    bool active = false, exhausted = false;
+    u32 index = 0, cur_shape = PTB_SHAPE_NONE;
+    Ray ray, obj;
+    WideCtx c;
+    HitId h;
+    uint2 ng = make_uint2(0u, 0u);
+    WarpStack stack;
+    stack.smem = &stack_mem[warp][0][lane];
+    stack.sp = 0;
+    ray.origin = ray.velocity = mk3(0, 0, 0); ray.duration = 0; obj = ray; c = wide_ctx(ray);
+    h.t = 0; h.shape = PTB_SHAPE_NONE; h.prim = 0; h.shape_type = 0; h.coords = mk3(0, 0, 0);
+
+    for (;;) {
+        // ---- refill ----
+        const u32 idle = __ballot_sync(0xFFFFFFFFu, !active);
+        if (!exhausted && (__popc(idle) >= REFILL || idle == 0xFFFFFFFFu)) {
+            const u32 want = __popc(idle);
+            u32 base = 0;
+            if (lane == 0) base = atomicAdd(job.counter(), want);
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            if (base + want >= total) exhausted = true;
+            if (!active) {
+                index = base + __popc(idle & lt_mask);
+                if (index < total && job.load(index, ray)) {
+                    h = wide_begin(s, ray);
+                    if (s.wide_tlas_root == 0xFFFFFFFFu) {
+                        job.store(index, h);
+                    } else {
+                        c = wide_ctx(ray);
+                        ng = make_uint2(0u, 0x80000000u);
+                        stack.sp = 0;
+                        cur_shape = PTB_SHAPE_NONE;
+                        active = true;
+                    }
+                }
+            }
+        }
+        if (!__any_sync(0xFFFFFFFFu, active)) {
+            if (exhausted) break;
+            continue;
+        }
+
+        // ---- node ----
+        uint2 tg = make_uint2(0u, 0u);
+        if (active) {
+            if (ng.y > 0x00FFFFFFu) wide_node_step(s, c, h.t, ng, tg, stack);
+            else { tg = ng; ng = make_uint2(0u, 0u); }          // a parked primitive group came off the stack
+        }
+
+        // ---- leaf primitives ----
+        u32 busy = __ballot_sync(0xFFFFFFFFu, tg.y != 0u);
+        while (busy) {
+            if (tg.y != 0u) {
+                if (POSTPONE > 0 && __popc(busy) < POSTPONE && ng.y > 0x00FFFFFFu && stack.sp < 16) {
+                    stack.push(tg);                             // few lanes have leaf work: park it, keep descending
+                    tg.y = 0u;
+                } else {
+                    const u32 j = highest_bit(tg.y);
+                    tg.y &= ~(1u << j);
+                    wide_prim_test(s, ray, tg.x + j, cur_shape, obj, h);
+                }
+            }
+            busy = __ballot_sync(0xFFFFFFFFu, tg.y != 0u);
+        }
+
+        // ---- pop / retire ----
+        if (active && ng.y <= 0x00FFFFFFu) {
+            if (stack.empty()) { job.store(index, h); active = false; }
+            else ng = stack.pop();
+        }
+    }
 }
 
 // ---- K2: scatter ----
-__global__ void __launch_bounds__(256) k_scatter(const DeviceScene s, const RenderConsts pc, const WavefrontState st, float4* __restrict__ accum) {
+__global__ void __launch_bounds__(256, 3) k_scatter(const DeviceScene s, const RenderConsts pc, const WavefrontState st, float4* __restrict__ accum) {
     const u32 slot = blockIdx.x * 256u + threadIdx.x;
     u32 x, y;
     bool finished = false;
     if (slot_pixel(pc, slot, x, y)) {
         PathState path = load_path(st, slot);
         Ray ray = load_ray(st, slot);
-        const uint4 h0 = st.hit0[slot];
-        PackedHit p;
-        p.t = __uint_as_float(h0.x); p.shape_material = h0.y; p.normal = h0.z; p.tangent = h0.w; p.u = p.v = 0.0f;
-        if (h0.y != 0xFFFFFFFFu) { const uint4 h1 = st.hit1[slot]; p.u = __uint_as_float(h1.x); p.v = __uint_as_float(h1.y); }
+        const PackedHit p = load_packed_hit(s, st, slot);
         const SurfaceHit hit = unpack_hit(p, ray);
         finished = scatter_invocation(s, pc, x, y, path, ray, hit, accum);
         store_ray(st, slot, ray);
@@ -123,6 +271,7 @@ __global__ void __launch_bounds__(256) k_scatter(const DeviceScene s, const Rend
     }
     const int c = __syncthreads_count(finished ? 1 : 0);
     if (threadIdx.x == 0 && c) st.tile_paths[blockIdx.x] += (unsigned)c;
+    if (slot == 0) *st.ray_counter = 0u;       // re-arm the dynamic ray fetch of the next trace launch
 }
 
 // ---- megakernel: rounds x {trace, scatter}, state in registers ----
@@ -168,14 +317,7 @@ __global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ accu
 }
 
 // ---- ray cast on caller rays ----
-template <int MODE>
-__global__ void __launch_bounds__(128) k_raycast(const DeviceScene s, const ptb_ray* __restrict__ rays, size_t n, ptb_hit* __restrict__ out) {
-    const size_t i = (size_t)blockIdx.x * 128u + threadIdx.x;
-    if (i >= n) return;
-    const ptb_ray in = rays[i];
-    Ray r;
-    r.origin = mk3(in.ox, in.oy, in.oz); r.velocity = mk3(in.dx, in.dy, in.dz); r.duration = in.duration;
-    const HitId h = closest_hit<MODE>(s, r);
+__device__ __forceinline__ void write_ray_hit(const DeviceScene& s, const HitId& h, ptb_hit* __restrict__ out, size_t i) {
     ptb_hit o;
     memset(&o, 0, sizeof o);
     o.t = h.t; o.shape = h.shape; o.prim = 0xFFFFFFFFu;
@@ -189,6 +331,26 @@ __global__ void __launch_bounds__(128) k_raycast(const DeviceScene s, const ptb_
     }
     out[i] = o;
 }
+__device__ __forceinline__ void RaycastJob::store(u32 i, const HitId& h) const { write_ray_hit(s, h, out, i); }
+
+template <int MODE>
+__global__ void __launch_bounds__(128) k_raycast(const DeviceScene s, const ptb_ray* __restrict__ rays, size_t n, ptb_hit* __restrict__ out) {
+    const size_t i = (size_t)blockIdx.x * 128u + threadIdx.x;
+    if (i >= n) return;
+    const ptb_ray in = rays[i];
+    Ray r;
+    r.origin = mk3(in.ox, in.oy, in.oz); r.velocity = mk3(in.dx, in.dy, in.dz); r.duration = in.duration;
+    write_ray_hit(s, closest_hit<MODE>(s, r), out, i);
+}
+
+// Debug/test: the attributes scatter derives from the stored hits, in the reference's packed form.
+__global__ void __launch_bounds__(256) k_hit_attributes(const DeviceScene s, const RenderConsts pc, const WavefrontState st, uint4* __restrict__ out) {
+    const u32 slot = blockIdx.x * 256u + threadIdx.x;
+    u32 x, y;
+    if (!slot_pixel(pc, slot, x, y)) return;
+    const PackedHit p = load_packed_hit(s, st, slot);
+    out[slot] = make_uint4(p.normal, p.tangent, __float_as_uint(p.u), __float_as_uint(p.v));
+}
 
 // ---- launchers ----
 cudaError_t launch_restart(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, cudaStream_t stream) {
@@ -196,13 +358,51 @@ cudaError_t launch_restart(const DeviceScene& s, const RenderConsts& pc, const W
     return cudaGetLastError();
 }
 
-cudaError_t launch_trace(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, unsigned traversal, unsigned tie, cudaStream_t stream) {
+// Persistent grid: exactly the warps that are resident at once (148 SMs x occupancy).
+template <class K>
+static unsigned persistent_grid(K kernel) {
+    int dev = 0, sms = 148, per_sm = 1;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 32 * PTB_TRACE_WARPS, 0);
+    if (per_sm < 1) per_sm = 1;
+    return (unsigned)(sms * per_sm);
+}
+
+// Tuning points of the persistent kernel: {refill threshold (idle lanes), postpone threshold (lanes with leaf work)}.
+#define PTB_PERSISTENT_VARIANTS(X) X(1, 8, 0) X(2, 8, 8) X(3, 16, 8) X(4, 4, 8) X(5, 8, 16) X(6, 16, 16) X(7, 12, 4) X(8, 32, 0) X(9, 16, 0) X(10, 24, 8)
+
+template <class Job>
+static cudaError_t launch_persistent(const Job& job, unsigned variant, cudaStream_t stream) {
+    switch (variant) {
+#define X(ID, R, P) case ID: { static unsigned grid = 0; if (!grid) grid = persistent_grid(k_trace_persistent<Job, R, P>); \
+                               k_trace_persistent<Job, R, P><<<grid, 32 * PTB_TRACE_WARPS, 0, stream>>>(job); break; }
+        PTB_PERSISTENT_VARIANTS(X)
+#undef X
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_trace(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, unsigned traversal, unsigned tie,
+                         unsigned variant, cudaStream_t stream) {
+    const int mode = mode_of(traversal, tie);
+    if (mode == MODE_WIDE && variant != 0) {
+        WavefrontJob job;
+        job.s = s; job.pc = pc; job.st = st;
+        return launch_persistent(job, variant, stream);
+    }
     const unsigned grid = pc.slot_count / 128u;
-    switch (mode_of(traversal, tie)) {
+    switch (mode) {
         case MODE_BVH2_FAITHFUL: k_trace<MODE_BVH2_FAITHFUL><<<grid, 128, 0, stream>>>(s, pc, st); break;
         case MODE_BVH2_CANONICAL: k_trace<MODE_BVH2_CANONICAL><<<grid, 128, 0, stream>>>(s, pc, st); break;
         default: k_trace<MODE_WIDE><<<grid, 128, 0, stream>>>(s, pc, st); break;
     }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_hit_attributes(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, uint4* out, cudaStream_t stream) {
+    k_hit_attributes<<<pc.slot_count / 256u, 256, 0, stream>>>(s, pc, st, out);
     return cudaGetLastError();
 }
 
@@ -229,10 +429,19 @@ cudaError_t launch_resolve(const float4* accum, unsigned width, unsigned height,
     return cudaGetLastError();
 }
 
-cudaError_t launch_raycast(const DeviceScene& s, const ptb_ray* rays, size_t n, unsigned traversal, unsigned tie, ptb_hit* out, cudaStream_t stream) {
+cudaError_t launch_raycast(const DeviceScene& s, const ptb_ray* rays, size_t n, unsigned traversal, unsigned tie, unsigned variant,
+                           unsigned* counter, ptb_hit* out, cudaStream_t stream) {
     if (n == 0) return cudaSuccess;
+    const int mode = mode_of(traversal, tie);
+    if (mode == MODE_WIDE && variant != 0 && counter && n < 0xFFFFFFFFull) {
+        cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(unsigned), stream);
+        if (e != cudaSuccess) return e;
+        RaycastJob job;
+        job.s = s; job.rays = rays; job.out = out; job.n = (u32)n; job.ctr = counter;
+        return launch_persistent(job, variant, stream);
+    }
     const unsigned grid = (unsigned)((n + 127) / 128);
-    switch (mode_of(traversal, tie)) {
+    switch (mode) {
         case MODE_BVH2_FAITHFUL: k_raycast<MODE_BVH2_FAITHFUL><<<grid, 128, 0, stream>>>(s, rays, n, out); break;
         case MODE_BVH2_CANONICAL: k_raycast<MODE_BVH2_CANONICAL><<<grid, 128, 0, stream>>>(s, rays, n, out); break;
         default: k_raycast<MODE_WIDE><<<grid, 128, 0, stream>>>(s, rays, n, out); break;

@@ -14,25 +14,35 @@ namespace ptb {
 // HIT_TIME_LIMIT (basic_scatter.glsl:307, scene.glsl.inc:617).
 struct WavefrontState {
     float4* ray;      // origin.xyz, oct-packed direction (bits)
-    uint4*  hit0;     // t (bits), shape<<16|material, packed normal, packed tangent
-    uint4*  hit1;     // u (bits), v (bits), primitive index, shape type
+    uint4*  hit0;     // t (bits), shape<<16|material (0xFFFFFFFF = miss), primitive index, shape type
+    uint4*  hit1;     // primitive coordinates xyz (barycentrics / object-space point), unused
+                      // (normal, tangent and UV are derived from these in the scatter kernel, where all
+                      //  lanes of a warp do it together, instead of by whichever lane finishes traversal)
     uint4*  path0;    // pixel index, lambda0 (bits), active shapes 0|1, active shapes 2|3
     float4* path1;    // throughput at the 4 wavelengths
     float4* path2;    // probability at the 4 wavelengths
     float4* path3;    // sample XYZ, path length (bits)
+    unsigned int* ray_counter;  // dynamic ray fetch of the persistent trace kernel; zeroed by restart/scatter
     unsigned int* tile_paths;   // per 256-slot tile: paths finished since reset (u32 wraps are summed by the host in u64 deltas)
 };
 
 struct LaunchStats { unsigned int launches; };
 
 cudaError_t launch_restart(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, cudaStream_t stream);
-cudaError_t launch_trace(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, unsigned traversal, unsigned tie, cudaStream_t stream);
+// variant 0: one thread per slot; variant >= 1: persistent warps with dynamic ray fetch (wide traversal only),
+// tuning point (refill threshold, postpone threshold) selected by the variant number.
+cudaError_t launch_trace(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, unsigned traversal, unsigned tie,
+                         unsigned variant, cudaStream_t stream);
+// Debug/test: closest-hit attributes of the stored hits as {packed normal, packed tangent, u, v} per slot.
+cudaError_t launch_hit_attributes(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, uint4* out, cudaStream_t stream);
 cudaError_t launch_scatter(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, cudaStream_t stream);
 // `rounds` x {trace, scatter} with the path state in registers; seed = pc.random_seed + k * seed_stride for round k.
 cudaError_t launch_megakernel(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum,
                               unsigned traversal, unsigned tie, unsigned rounds, unsigned seed_stride, cudaStream_t stream);
 cudaError_t launch_resolve(const float4* accum, unsigned width, unsigned height, ptb_resolve_params params,
                            uchar4* out_srgb8, float* out_linear_rgb, cudaStream_t stream);
-cudaError_t launch_raycast(const DeviceScene& s, const ptb_ray* rays, size_t n, unsigned traversal, unsigned tie, ptb_hit* out, cudaStream_t stream);
+// counter: device u32 (zeroed by the launcher) for the persistent variant; may be null for variant 0.
+cudaError_t launch_raycast(const DeviceScene& s, const ptb_ray* rays, size_t n, unsigned traversal, unsigned tie, unsigned variant,
+                           unsigned* counter, ptb_hit* out, cudaStream_t stream);
 
 }  // namespace ptb

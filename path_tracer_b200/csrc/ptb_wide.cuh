@@ -19,12 +19,16 @@
 //   w6-7  meta[8]      0 = empty; inner: 0b001_11sss (sss = slot); leaf: unary(count)<<5 | offset
 //   w8-13 qlo x,y,z    8 bytes each
 //   w14-19 qhi x,y,z
+//
+// The building blocks (ray context, node step, primitive test) are shared by the
+// per-thread query closest_hit_wide() — used by the megakernel and the ray-cast
+// harness — and by the persistent warp-cooperative trace kernel in ptb_kernels.cu.
 #pragma once
 #include "ptb_trace.cuh"
 
 namespace ptb {
 
-#define PTB_WIDE_STACK 32
+#define PTB_WIDE_STACK 48      // tree depth <= 30 (checked by the builder) + up to 16 parked primitive groups
 
 PTB_HD u32 bytes_sign_extend(u32 x) {     // per byte: 0xFF if its top bit is set, else 0
 #if defined(__CUDA_ARCH__)
@@ -51,107 +55,163 @@ PTB_HD u32 popcount(u32 x) {
     return (u32)__builtin_popcount(x);
 #endif
 }
-PTB_HD float byte_to_float(u32 w, int j) { return (float)((w >> (8 * j)) & 0xFFu); }
+// Byte j of w as the float 1 + q * 2^-15, built with one byte permute (ALU pipe)
+// instead of an int->float conversion (XU pipe, quarter rate): bytes = 3F 80 qq 00.
+template <int J>
+PTB_HD float byte_as_unit_float(u32 w) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(__byte_perm(w, 0x3F800000u, 0x7604u | (J << 4)));
+#else
+    return u2f(0x3F800000u | (((w >> (8 * J)) & 0xFFu) << 8));
+#endif
+}
+
+// Per-ray constants of the traversal.
+struct WideCtx {
+    f3 origin;
+    f3 inv_dir;          // 1/d with |d| clamped away from zero (sign kept, -0 counts as negative)
+    bool nx, ny, nz;
+    u32 octinv, octinv4;
+};
+
+PTB_HD WideCtx wide_ctx(const Ray& r) {
+    // The tree is a culling structure: it only has to be conservative (the reference's own
+    // slab test divides by zero instead, common.glsl.inc:157-158).
+    const float tiny = 8.271806e-25f;   // 2^-80
+    const f3 d = r.velocity;
+    WideCtx c;
+    c.origin = r.origin;
+    c.inv_dir = mk3(1.0f / (fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x)),
+                    1.0f / (fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y)),
+                    1.0f / (fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z)));
+    c.nx = c.inv_dir.x < 0.0f; c.ny = c.inv_dir.y < 0.0f; c.nz = c.inv_dir.z < 0.0f;
+    c.octinv = 7u - ((c.nx ? 1u : 0u) | (c.ny ? 2u : 0u) | (c.nz ? 4u : 0u));
+    c.octinv4 = c.octinv * 0x01010101u;
+    return c;
+}
+
+// Slab test of four quantised child boxes (one meta word + six plane words).
+// Plane distance along the ray: t = q*a + b with a = 2^e/d, b = (p - o)/d, evaluated as
+// fma(1 + q*2^-15, A, B) with A = 32768 a, B = b - A.  `lo`/`hi` biases carry the
+// rounding-error bound of that evaluation, so the test can only err towards "hit".
+template <int J>
+PTB_HD void wide_test_child(u32 nearx, u32 farx, u32 neary, u32 fary, u32 nearz, u32 farz,
+                            float Ax, float Ay, float Az, float Bxl, float Bxh, float Byl, float Byh, float Bzl, float Bzh,
+                            float reach, u32 child_bits4, u32 bit_index4, u32& hitmask) {
+    const float t0x = fmaf(byte_as_unit_float<J>(nearx), Ax, Bxl), t1x = fmaf(byte_as_unit_float<J>(farx), Ax, Bxh);
+    const float t0y = fmaf(byte_as_unit_float<J>(neary), Ay, Byl), t1y = fmaf(byte_as_unit_float<J>(fary), Ay, Byh);
+    const float t0z = fmaf(byte_as_unit_float<J>(nearz), Az, Bzl), t1z = fmaf(byte_as_unit_float<J>(farz), Az, Bzh);
+    const float tmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.0f));
+    const float tmax = fminf(fminf(t1x, t1y), fminf(t1z, reach));
+    const u32 bits = ((child_bits4 >> (8 * J)) & 0xFFu) << ((bit_index4 >> (8 * J)) & 0xFFu);
+    if (tmin <= tmax) hitmask |= bits;
+}
+
+// Visits the nearest pending child of node group `ng`: pushes the remainder of the group,
+// loads the child node, tests its 8 children against [0, reach], and returns the child's own
+// node group (in ng) and primitive group (in tg).
+template <class Stack>
+PTB_HD void wide_node_step(const DeviceScene& s, const WideCtx& c, float reach, uint2& ng, uint2& tg, Stack& stack) {
+    const u32 hits = ng.y;
+    const u32 bit = highest_bit(hits);
+    ng.y &= ~(1u << bit);
+    if (ng.y > 0x00FFFFFFu) stack.push(ng);
+    const u32 slot = (bit - 24u) ^ c.octinv;
+    const u32 rel = popcount(hits & ~(0xFFFFFFFFu << slot));
+    const uint4* np = s.wide_nodes + 5 * (size_t)(ng.x + rel);
+    const uint4 n0 = PTB_LDG(&np[0]), n1 = PTB_LDG(&np[1]), n2 = PTB_LDG(&np[2]), n3 = PTB_LDG(&np[3]), n4 = PTB_LDG(&np[4]);
+
+    // A = 2^(e+15) / d ;  B = (p - o)/d - A ;  error bound 2^-21 (|b| + |A|)
+    const float Ax = u2f(((n0.w & 0xFFu) + 15u) << 23) * c.inv_dir.x;
+    const float Ay = u2f((((n0.w >> 8) & 0xFFu) + 15u) << 23) * c.inv_dir.y;
+    const float Az = u2f((((n0.w >> 16) & 0xFFu) + 15u) << 23) * c.inv_dir.z;
+    const float bx = (u2f(n0.x) - c.origin.x) * c.inv_dir.x;
+    const float by = (u2f(n0.y) - c.origin.y) * c.inv_dir.y;
+    const float bz = (u2f(n0.z) - c.origin.z) * c.inv_dir.z;
+    const float ex = (fabsf(bx) + fabsf(Ax)) * 4.7683716e-7f;
+    const float ey = (fabsf(by) + fabsf(Ay)) * 4.7683716e-7f;
+    const float ez = (fabsf(bz) + fabsf(Az)) * 4.7683716e-7f;
+    const float Bx = bx - Ax, By = by - Ay, Bz = bz - Az;
+    const float Bxl = Bx - ex, Bxh = Bx + ex, Byl = By - ey, Byh = By + ey, Bzl = Bz - ez, Bzh = Bz + ez;
+
+    u32 hitmask = 0;
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+        const u32 meta4 = half ? n1.w : n1.z;
+        const u32 is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const u32 inner_mask4 = bytes_sign_extend(is_inner4 << 3);
+        const u32 bit_index4 = (meta4 ^ (c.octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
+        const u32 child_bits4 = (meta4 >> 5) & 0x07070707u;
+        const u32 qlx = half ? n2.y : n2.x, qly = half ? n2.w : n2.z, qlz = half ? n3.y : n3.x;
+        const u32 qhx = half ? n3.w : n3.z, qhy = half ? n4.y : n4.x, qhz = half ? n4.w : n4.z;
+        const u32 nearx = c.nx ? qhx : qlx, farx = c.nx ? qlx : qhx;
+        const u32 neary = c.ny ? qhy : qly, fary = c.ny ? qly : qhy;
+        const u32 nearz = c.nz ? qhz : qlz, farz = c.nz ? qlz : qhz;
+        wide_test_child<0>(nearx, farx, neary, fary, nearz, farz, Ax, Ay, Az, Bxl, Bxh, Byl, Byh, Bzl, Bzh, reach, child_bits4, bit_index4, hitmask);
+        wide_test_child<1>(nearx, farx, neary, fary, nearz, farz, Ax, Ay, Az, Bxl, Bxh, Byl, Byh, Bzl, Bzh, reach, child_bits4, bit_index4, hitmask);
+        wide_test_child<2>(nearx, farx, neary, fary, nearz, farz, Ax, Ay, Az, Bxl, Bxh, Byl, Byh, Bzl, Bzh, reach, child_bits4, bit_index4, hitmask);
+        wide_test_child<3>(nearx, farx, neary, fary, nearz, farz, Ax, Ay, Az, Bxl, Bxh, Byl, Byh, Bzl, Bzh, reach, child_bits4, bit_index4, hitmask);
+    }
+    ng.x = n1.x;
+    ng.y = (hitmask & 0xFF000000u) | (n0.w >> 24);
+    tg.x = n1.y;
+    tg.y = hitmask & 0x00FFFFFFu;
+}
+
+// One leaf primitive: exact reference test on the object-space ray of its shape.  The
+// object-space ray is cached across consecutive primitives of the same shape.
+PTB_HD void wide_prim_test(const DeviceScene& s, const Ray& world, u32 prim_index, u32& cur_shape, Ray& obj, HitId& h) {
+    const float4* tp = s.wide_tris + 3 * (size_t)prim_index;
+    const float4 v0 = PTB_LDG(&tp[0]), v1 = PTB_LDG(&tp[1]), v2 = PTB_LDG(&tp[2]);
+    const u32 face = f2u(v0.w), shape = f2u(v1.w), kind = f2u(v2.w);
+    if (shape != cur_shape) { obj = object_ray(s, world, shape); cur_shape = shape; }
+    if (kind == 0u) test_triangle<true>(obj, mk3(v0.x, v0.y, v0.z), mk3(v1.x, v1.y, v1.z), mk3(v2.x, v2.y, v2.z), shape, face, h);
+    else test_analytic<true>(obj, kind, shape, h);
+}
+
+// Unbounded shapes (planes) are not in the tree: tested first, which also shortens the reach.
+PTB_HD HitId wide_begin(const DeviceScene& s, const Ray& r) {
+    HitId h;
+    h.t = r.duration; h.shape = PTB_SHAPE_NONE; h.prim = 0xFFFFFFFFu; h.shape_type = 0; h.coords = mk3(0, 0, 0);
+    for (u32 i = 0; i < s.wide_plane_count; i++) {
+        const u32 shape = PTB_LDG(&s.wide_planes[i]);
+        const Ray o = object_ray(s, r, shape);
+        test_analytic<true>(o, PTB_SHAPE_PLANE, shape, h);
+    }
+    return h;
+}
+
+// Per-thread stack in local memory (megakernel, ray-cast harness, host emulation).
+struct LocalStack {
+    uint2 e[PTB_WIDE_STACK];
+    int sp;
+    PTB_HD void push(uint2 v) { if (sp < PTB_WIDE_STACK) e[sp++] = v; }
+    PTB_HD uint2 pop() { return e[--sp]; }
+    PTB_HD bool empty() const { return sp == 0; }
+};
 
 // Canonical closest hit: lexicographically lowest (t, shape, face) among all
 // primitives the reference tests would accept with t <= ray.duration.
 PTB_HD HitId closest_hit_wide(const DeviceScene& s, const Ray& r) {
-    HitId h;
-    h.t = r.duration; h.shape = PTB_SHAPE_NONE; h.prim = 0xFFFFFFFFu; h.shape_type = 0; h.coords = mk3(0, 0, 0);
-
-    // unbounded shapes first: cheap, and they shorten the reach before traversal
-    for (u32 i = 0; i < s.wide_plane_count; i++) {
-        u32 shape = PTB_LDG(&s.wide_planes[i]);
-        Ray o = object_ray(s, r, shape);
-        test_analytic<true>(o, PTB_SHAPE_PLANE, shape, h);
-    }
+    HitId h = wide_begin(s, r);
     if (s.wide_tlas_root == 0xFFFFFFFFu) return h;
-
-    // Reciprocal direction with |d| clamped away from zero: the tree is a culling
-    // structure, it only has to be conservative (the reference's own slab test
-    // divides by zero instead, common.glsl.inc:157-158).
-    const float tiny = 8.271806e-25f;   // 2^-80
-    f3 d = r.velocity;
-    f3 id = mk3(1.0f / (fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x)),
-                1.0f / (fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y)),
-                1.0f / (fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z)));
-    const bool nx = id.x < 0.0f, ny = id.y < 0.0f, nz = id.z < 0.0f;   // sign of the clamped reciprocal: -0 counts as negative
-    const u32 octinv = 7u - ((nx ? 1u : 0u) | (ny ? 2u : 0u) | (nz ? 4u : 0u));
-    const u32 octinv4 = octinv * 0x01010101u;
-
-    uint2 stack[PTB_WIDE_STACK];
-    int sp = 0;
+    const WideCtx c = wide_ctx(r);
+    LocalStack stack;
+    stack.sp = 0;
     uint2 ng = make_uint2(0u, 0x80000000u);     // root pseudo-group: one hit, slot 7^octinv, no inner mask
     u32 cur_shape = PTB_SHAPE_NONE;
     Ray obj = r;
-
     while (true) {
-        // ---- pop the nearest pending child of the current node group ----
-        const u32 hits = ng.y;
-        const u32 bit = highest_bit(hits);
-        ng.y &= ~(1u << bit);
-        if (ng.y > 0x00FFFFFFu && sp < PTB_WIDE_STACK) stack[sp++] = ng;
-        const u32 slot = (bit - 24u) ^ octinv;
-        const u32 rel = popcount(hits & ~(0xFFFFFFFFu << slot));
-        const uint4* np = s.wide_nodes + 5 * (size_t)(ng.x + rel);
-        const uint4 n0 = PTB_LDG(&np[0]), n1 = PTB_LDG(&np[1]), n2 = PTB_LDG(&np[2]), n3 = PTB_LDG(&np[3]), n4 = PTB_LDG(&np[4]);
-
-        // ---- slab test of the 8 quantised child boxes ----
-        const float ax = u2f((n0.w & 0xFFu) << 23) * id.x;
-        const float ay = u2f(((n0.w >> 8) & 0xFFu) << 23) * id.y;
-        const float az = u2f(((n0.w >> 16) & 0xFFu) << 23) * id.z;
-        const float bx = (u2f(n0.x) - r.origin.x) * id.x;
-        const float by = (u2f(n0.y) - r.origin.y) * id.y;
-        const float bz = (u2f(n0.z) - r.origin.z) * id.z;
-        // rounding-error bound of q*a+b against the exact plane distance: 2^-22 (|b| + 256 |a|)
-        const float ex = (fabsf(bx) + 256.0f * fabsf(ax)) * 2.3841858e-7f;
-        const float ey = (fabsf(by) + 256.0f * fabsf(ay)) * 2.3841858e-7f;
-        const float ez = (fabsf(bz) + 256.0f * fabsf(az)) * 2.3841858e-7f;
-        const float bxl = bx - ex, bxh = bx + ex, byl = by - ey, byh = by + ey, bzl = bz - ez, bzh = bz + ez;
-
-        u32 hitmask = 0;
-#pragma unroll
-        for (int half = 0; half < 2; half++) {
-            const u32 meta4 = half ? n1.w : n1.z;
-            const u32 is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-            const u32 inner_mask4 = bytes_sign_extend(is_inner4 << 3);
-            const u32 bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
-            const u32 child_bits4 = (meta4 >> 5) & 0x07070707u;
-            const u32 qlx = half ? n2.y : n2.x, qly = half ? n2.w : n2.z, qlz = half ? n3.y : n3.x;
-            const u32 qhx = half ? n3.w : n3.z, qhy = half ? n4.y : n4.x, qhz = half ? n4.w : n4.z;
-            const u32 nearx = nx ? qhx : qlx, farx = nx ? qlx : qhx;
-            const u32 neary = ny ? qhy : qly, fary = ny ? qly : qhy;
-            const u32 nearz = nz ? qhz : qlz, farz = nz ? qlz : qhz;
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const float t0x = fmaf(byte_to_float(nearx, j), ax, bxl), t1x = fmaf(byte_to_float(farx, j), ax, bxh);
-                const float t0y = fmaf(byte_to_float(neary, j), ay, byl), t1y = fmaf(byte_to_float(fary, j), ay, byh);
-                const float t0z = fmaf(byte_to_float(nearz, j), az, bzl), t1z = fmaf(byte_to_float(farz, j), az, bzh);
-                const float tmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.0f));
-                const float tmax = fminf(fminf(t1x, t1y), fminf(t1z, h.t));
-                if (tmin <= tmax) hitmask |= ((child_bits4 >> (8 * j)) & 0xFFu) << ((bit_index4 >> (8 * j)) & 0xFFu);
-            }
+        uint2 tg;
+        wide_node_step(s, c, h.t, ng, tg, stack);
+        while (tg.y) {
+            const u32 j = highest_bit(tg.y);
+            tg.y &= ~(1u << j);
+            wide_prim_test(s, r, tg.x + j, cur_shape, obj, h);
         }
-        ng.x = n1.x;
-        ng.y = (hitmask & 0xFF000000u) | (n0.w >> 24);
-        u32 tri_bits = hitmask & 0x00FFFFFFu;
-        const u32 tri_base = n1.y;
-
-        // ---- leaf primitives of this node ----
-        while (tri_bits) {
-            const u32 j = highest_bit(tri_bits);
-            tri_bits &= ~(1u << j);
-            const float4* tp = s.wide_tris + 3 * (size_t)(tri_base + j);
-            const float4 v0 = PTB_LDG(&tp[0]), v1 = PTB_LDG(&tp[1]), v2 = PTB_LDG(&tp[2]);
-            const u32 face = f2u(v0.w), shape = f2u(v1.w), kind = f2u(v2.w);
-            if (shape != cur_shape) { obj = object_ray(s, r, shape); cur_shape = shape; }
-            if (kind == 0u) test_triangle<true>(obj, mk3(v0.x, v0.y, v0.z), mk3(v1.x, v1.y, v1.z), mk3(v2.x, v2.y, v2.z), shape, face, h);
-            else test_analytic<true>(obj, kind, shape, h);
-        }
-
         if (ng.y <= 0x00FFFFFFu) {
-            if (sp == 0) break;
-            ng = stack[--sp];
+            if (stack.empty()) break;
+            ng = stack.pop();
         }
     }
     return h;

@@ -1,6 +1,8 @@
 // See ptb_wide_build.h.  Host-only C++ (no CUDA): binned-SAH BVH2 over world-space
-// primitive bounds -> greedy surface-area collapse to 8-wide -> octant slot
-// assignment -> 8-bit quantisation (outward rounded).
+// primitive bounds -> SAH-optimal collapse to 8-wide by dynamic programming (the
+// forest-cost recurrence of Ylitie, Karras, Laine, "Efficient Incoherent Ray
+// Traversal on GPUs Through Compressed Wide BVHs", HPG 2017, section 3.1) -> octant
+// slot assignment -> 8-bit quantisation (outward rounded).
 #include "ptb_wide_build.h"
 
 #include <algorithm>
@@ -219,7 +221,44 @@ int build_wide_bvh(const ptb_scene_view* v, WideBuild* out, std::string* err) {
     B.build(0, 0, (uint32_t)N, 1);
     out->bvh2_depth = B.max_depth.load();
 
-    // ---- collapse to 8-wide, assign slots, quantise, emit breadth-first ----
+    // ---- SAH-optimal collapse: C(n,i) = cheapest way to put the subtree of n into at most i child slots ----
+    //   leaf n:            C(n,i)   = A(n) * P(n) * c_prim
+    //   D(n,j)            = min_{0<k<j} C(left,k) + C(right,j-k)
+    //   C(n,1)            = A(n) * c_node + D(n,8)            (n becomes a wide node of its own)
+    //   C(n,i), i = 2..7  = min(D(n,i), C(n,i-1))
+    // Children are allocated after their parent, so a descending index sweep is bottom-up.
+    struct Dp { float c[7]; uint8_t split[8]; };      // c[i-1] = C(n,i); split[j-1] = k chosen for D(n,j) (0: inherit C(n,j-1))
+    const uint32_t n_b2 = B.node_alloc.load();
+    std::vector<Dp> dp(n_b2);
+    {
+        const double c_node = 1.0, c_prim = 0.4;
+        for (uint32_t ni = n_b2; ni-- > 0;) {
+            const B2& n = B.nodes[ni];
+            Dp& d = dp[ni];
+            std::memset(&d, 0, sizeof d);
+            const double area = n.b.area();
+            if (n.count > 0) { for (int i = 0; i < 7; i++) d.c[i] = (float)(area * n.count * c_prim); continue; }
+            if (ni != 0 && n.left == 0) continue;     // unused slot of the pair allocator
+            const Dp& l = dp[n.left]; const Dp& r = dp[n.right];
+            double D[9]; int K[9];
+            for (int j = 2; j <= 8; j++) {
+                D[j] = INFINITY; K[j] = 1;
+                for (int k = 1; k < j; k++) {
+                    if (k > 7 || j - k > 7) continue;
+                    const double v = (double)l.c[k - 1] + (double)r.c[j - k - 1];
+                    if (v < D[j]) { D[j] = v; K[j] = k; }
+                }
+            }
+            d.c[0] = (float)(area * c_node + D[8]);
+            d.split[7] = (uint8_t)K[8];
+            for (int i = 2; i <= 7; i++) {
+                if (D[i] < d.c[i - 2]) { d.c[i - 1] = (float)D[i]; d.split[i - 1] = (uint8_t)K[i]; }
+                else { d.c[i - 1] = d.c[i - 2]; d.split[i - 1] = 0; }
+            }
+        }
+    }
+
+    // ---- assign slots, quantise, emit breadth-first ----
     struct Task { uint32_t b2, index, depth; };
     std::vector<Task> queue;
     queue.push_back({0u, 0u, 1u});
@@ -237,13 +276,22 @@ int build_wide_bvh(const ptb_scene_view* v, WideBuild* out, std::string* err) {
         uint32_t ch[8]; int nch = 0;
         if (self.count > 0) { ch[nch++] = t.b2; }
         else {
-            ch[nch++] = self.left; ch[nch++] = self.right;
-            while (nch < 8) {
-                int pick = -1; double pa = -1.0;
-                for (int k = 0; k < nch; k++) if (B.nodes[ch[k]].count == 0) { double a = B.nodes[ch[k]].b.area(); if (a > pa) { pa = a; pick = k; } }
-                if (pick < 0) break;
-                uint32_t n = ch[pick];
-                ch[pick] = B.nodes[n].left; ch[nch++] = B.nodes[n].right;
+            // children of this wide node = the optimal 8-slot forest below the BVH2 node
+            struct Item { uint32_t n; int slots; };
+            Item work[16]; int nw = 0;
+            const int k8 = dp[t.b2].split[7];
+            work[nw++] = {self.right, 8 - k8};
+            work[nw++] = {self.left, k8};
+            while (nw > 0) {
+                Item it = work[--nw];
+                const B2& node = B.nodes[it.n];
+                int i = it.slots;
+                if (node.count > 0 || i == 1) { ch[nch++] = it.n; continue; }
+                while (i > 1 && dp[it.n].split[i - 1] == 0) i--;          // C(n,i) inherited from C(n,i-1)
+                if (i == 1) { ch[nch++] = it.n; continue; }
+                const int k = dp[it.n].split[i - 1];
+                work[nw++] = {node.right, i - k};
+                work[nw++] = {node.left, k};
             }
         }
         sah += self.b.area() / root_area;

@@ -20,6 +20,7 @@ from . import _build
 from .types import (KernelTimes, RenderParams, ResolveParams, SceneView, Stats, WideInfo, HIT_DTYPE, RAY_DTYPE,
                     RENDER_FLAG_ACCUMULATE, RENDER_FLAG_SAMPLE_JITTER, INTEGRATOR_WAVEFRONT, INTEGRATOR_MEGAKERNEL,
                     TRAVERSAL_BVH2_REFERENCE, TRAVERSAL_WIDE, TIE_FAITHFUL, TIE_CANONICAL, SCENE_DIRTY_ALL,
+                    TRACE_VARIANT_SIMPLE, TRACE_VARIANT_DEFAULT, TRACE_VARIANT_MAX,
                     TONE_CLAMP, TONE_REINHARD, TONE_HABLE, TONE_ACES)
 
 # every symbol include/ptb.h declares (checked by tests/test_abi.py)
@@ -40,6 +41,7 @@ STATE_ARRAYS = {
     "ImagePosition": "i4", "NormalizedLambda0": "f4", "Throughput0": "f4", "Throughput1": "f4", "Throughput2": "f4", "Throughput3": "f4",
     "Probability0": "f4", "Probability1": "f4", "Probability2": "f4", "Probability3": "f4", "SampleR": "f4", "SampleG": "f4", "SampleB": "f4",
     "ActiveShapeIndex01": "u4", "ActiveShapeIndex23": "u4", "PathLength": "u4", "PrimitiveIndex": "u4", "ShapeType": "u4",
+    "PrimitiveCoordinateX": "f4", "PrimitiveCoordinateY": "f4", "PrimitiveCoordinateZ": "f4",
 }
 
 _lib = None
@@ -228,12 +230,13 @@ class BasicRenderer:
         self.Integrator = INTEGRATOR_WAVEFRONT
         self.Traversal = TRAVERSAL_WIDE
         self.TieMode = TIE_CANONICAL
+        self.TraceVariant = TRACE_VARIANT_DEFAULT
         self.h = C.c_void_p()
         _check(lib().ptb_renderer_create(ctx.h, scene.h, sample_buffer.h, C.byref(self.h)))
 
     def _push(self):
         p = RenderParams(self.CameraIndex, self.RenderFlags, self.PathLengthLimit, self.PathTerminationProbability,
-                         self.Integrator, self.Traversal, self.TieMode, 0)
+                         self.Integrator, self.Traversal, self.TieMode, self.TraceVariant)
         _check(lib().ptb_renderer_set_params(self.h, C.byref(p)))
 
     def set_frame_index(self, f):

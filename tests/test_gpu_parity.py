@@ -213,6 +213,31 @@ def test_megakernel_equals_wavefront(I, gpu, dev, scenes):
         assert np.array_equal(films[0][2], films[1][2]) and np.array_equal(bits(films[0][3]), bits(films[1][3]))
 
 
+def test_trace_kernel_variants_are_equivalent(I, gpu, dev, oracle, scenes):
+    """Persistent/dynamic-fetch trace kernels visit nodes in another order than the one-thread-per-slot
+    kernel; with canonical ties the closest hit — and so the whole film and state — must be identical."""
+    for name, params in (("terrain", (64,)), ("spherefield", (12, 2, 2)), ("room", (1, 512))):
+        ref = None
+        for variant in range(0, I.TRACE_VARIANT_MAX + 1):
+            film = I.SampleBuffer(gpu, 112, 80)
+            r = I.BasicRenderer(gpu, dev(name, *params), film)
+            r.TraceVariant = variant
+            r.set_frame_index(1)
+            r.reset()
+            r.run(2)
+            r.run_frames(6)
+            out = (film.download(), r.state("PrimitiveIndex"), r.state("Time"), r.state("PackedNormal"), r.stats()["paths_finished"])
+            if ref is None:
+                ref = out
+                continue
+            assert np.array_equal(out[0], ref[0]), (name, variant)
+            assert np.array_equal(out[1], ref[1]) and np.array_equal(bits(out[2]), bits(ref[2])) and np.array_equal(out[3], ref[3])
+            assert out[4] == ref[4]
+    r.TraceVariant = 99
+    with pytest.raises(I.PtbError):
+        r.reset()
+
+
 @pytest.mark.parametrize("name,params", [("cornell", ()), ("terrain", (64,))])
 def test_converged_image_within_one_percent(I, gpu, dev, oracle, scenes, name, params):
     """Wide BVH + megakernel on the GPU against the reference-order oracle at equal sample counts."""
