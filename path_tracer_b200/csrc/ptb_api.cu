@@ -195,10 +195,10 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
             s->ds.wide_nodes = (const uint4*)s->wide_nodes.p;
             s->ds.wide_tris = (const float4*)s->wide_prims.p;
             s->ds.wide_planes = s->wide_planes.p;
-            s->ds.wide_plane_count = (uint32_t)wb.planes.size();
+            s->ds.wide_plane_count = (uint32_t)(wb.planes.size() / 2);
             s->ds.wide_tlas_root = wb.node_count ? 0u : 0xFFFFFFFFu;
             s->wide_info.node_count = wb.node_count; s->wide_info.prim_count = wb.prim_count;
-            s->wide_info.plane_count = (uint32_t)wb.planes.size();
+            s->wide_info.plane_count = (uint32_t)(wb.planes.size() / 2);
             s->wide_info.depth = wb.depth; s->wide_info.bvh2_depth = wb.bvh2_depth;
             s->wide_info.sah_cost = wb.sah_cost; s->wide_info.build_seconds = wb.build_seconds;
         } else {

@@ -128,13 +128,15 @@ __global__ void __launch_bounds__(128) k_trace(const DeviceScene s, const Render
 // to the machine (resident warps only) and every warp loops
 //     refill  : lanes whose ray is done fetch new rays from a global counter (ballot + prefix rank),
 //     node    : every active lane visits one node (all active lanes have node work here),
-//     prims   : lanes with leaf primitives test them; when only a few lanes have any, lanes that
-//               still have node work park the primitive group on their stack (vote-driven postponing),
+//     prims   : lanes with leaf primitives test them (vote-driven loop),
 //     pop     : lanes out of node work pop their stack or retire and store their hit.
 // The first entries of each lane's stack live in shared memory, lane-interleaved (bank = lane, so
 // any mix of stack depths is conflict-free); deeper entries spill to local memory.
 #define PTB_SMEM_STACK 10
 #define PTB_TRACE_WARPS 4
+#ifndef PTB_TRACE_MIN_BLOCKS
+#define PTB_TRACE_MIN_BLOCKS 6
+#endif
 
 struct WarpStack {
     uint2* smem;                                   // entry k of this lane at smem[k * 32]
@@ -174,8 +176,8 @@ struct RaycastJob {
     __device__ __forceinline__ void store(u32 i, const HitId& h) const;
 };
 
-template <class Job, int REFILL, int POSTPONE>
-__global__ void __launch_bounds__(32 * PTB_TRACE_WARPS) k_trace_persistent(const Job job) {
+template <class Job, int REFILL>
+__global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_TRACE_MIN_BLOCKS) k_trace_persistent(const Job job) {
     __shared__ uint2 stack_mem[PTB_TRACE_WARPS][PTB_SMEM_STACK][32];
     const DeviceScene& s = job.s;
     const u32 lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
@@ -224,27 +226,14 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS) k_trace_persistent(const
             continue;
         }
 
-        // ---- node ----
-        uint2 tg = make_uint2(0u, 0u);
-        if (active) {
-            if (ng.y > 0x00FFFFFFu) wide_node_step(s, c, h.t, ng, tg, stack);
-            else { tg = ng; ng = make_uint2(0u, 0u); }          // a parked primitive group came off the stack
-        }
+        // ---- node: every active lane has node work here ----
+        PrimGroup pg;
+        pg.base = pg.bits = pg.valid = 0u;
+        if (active) wide_node_step(s, c, h.t, ng, pg, stack);
 
         // ---- leaf primitives ----
-        u32 busy = __ballot_sync(0xFFFFFFFFu, tg.y != 0u);
-        while (busy) {
-            if (tg.y != 0u) {
-                if (POSTPONE > 0 && __popc(busy) < POSTPONE && ng.y > 0x00FFFFFFu && stack.sp < 16) {
-                    stack.push(tg);                             // few lanes have leaf work: park it, keep descending
-                    tg.y = 0u;
-                } else {
-                    const u32 j = highest_bit(tg.y);
-                    tg.y &= ~(1u << j);
-                    wide_prim_test(s, ray, tg.x + j, cur_shape, obj, h);
-                }
-            }
-            busy = __ballot_sync(0xFFFFFFFFu, tg.y != 0u);
+        while (__any_sync(0xFFFFFFFFu, pg.bits != 0u)) {
+            if (pg.bits != 0u) wide_prim_step(s, ray, pg, cur_shape, obj, h);
         }
 
         // ---- pop / retire ----
@@ -369,14 +358,16 @@ static unsigned persistent_grid(K kernel) {
     return (unsigned)(sms * per_sm);
 }
 
-// Tuning points of the persistent kernel: {refill threshold (idle lanes), postpone threshold (lanes with leaf work)}.
-#define PTB_PERSISTENT_VARIANTS(X) X(1, 8, 0) X(2, 8, 8) X(3, 16, 8) X(4, 4, 8) X(5, 8, 16) X(6, 16, 16) X(7, 12, 4) X(8, 32, 0) X(9, 16, 0) X(10, 24, 8)
+// Tuning points of the persistent kernel: refill threshold (idle lanes that trigger a fetch).
+// Parking leaf work on the stack when few lanes have any (vote-driven postponing) was measured in
+// round 1 and did not pay on B200 (profiles/r01_v2_variant_sweep.txt); it was removed.
+#define PTB_PERSISTENT_VARIANTS(X) X(1, 8) X(2, 4) X(3, 12) X(4, 16) X(5, 24) X(6, 32) X(7, 2) X(8, 1)
 
 template <class Job>
 static cudaError_t launch_persistent(const Job& job, unsigned variant, cudaStream_t stream) {
     switch (variant) {
-#define X(ID, R, P) case ID: { static unsigned grid = 0; if (!grid) grid = persistent_grid(k_trace_persistent<Job, R, P>); \
-                               k_trace_persistent<Job, R, P><<<grid, 32 * PTB_TRACE_WARPS, 0, stream>>>(job); break; }
+#define X(ID, R) case ID: { static unsigned grid = 0; if (!grid) grid = persistent_grid(k_trace_persistent<Job, R>); \
+                            k_trace_persistent<Job, R><<<grid, 32 * PTB_TRACE_WARPS, 0, stream>>>(job); break; }
         PTB_PERSISTENT_VARIANTS(X)
 #undef X
         default: return cudaErrorInvalidValue;

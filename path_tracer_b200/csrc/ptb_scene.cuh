@@ -31,8 +31,8 @@ struct DeviceScene {
     ptb_packed_scene_globals       globals;           // by value: lives in the kernel parameter bank
     // wide BVH (ptb_wide.cuh); null until built
     const uint4*  wide_nodes;        // 80-byte nodes as 5 x uint4
-    const float4* wide_tris;         // 3 x float4 per leaf primitive: object-space vertices; .w = face index, shape index, kind
-    const u32*    wide_planes;       // shape indices of unbounded shapes (planes), tested linearly
+    const float4* wide_tris;         // 3 x float4 per leaf primitive: object-space vertices; .w = face index, shape index, tag (rank<<3 | identity<<2 | kind)
+    const u32*    wide_planes;       // {shape index, tag} of unbounded shapes (planes), tested linearly
     u32 wide_plane_count;
     u32 wide_tlas_root;              // 0 when the tree exists, 0xFFFFFFFF when the scene has no bounded primitive
 };

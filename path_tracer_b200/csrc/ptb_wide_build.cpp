@@ -9,6 +9,7 @@
 #include <atomic>
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 
@@ -27,12 +28,12 @@ struct Box {
     }
 };
 
-struct Prim { uint32_t shape, face, kind; };   // kind: 0 triangle, 2 sphere, 3 cube (shape types)
+struct Prim { uint32_t shape, face, kind, tag; };   // kind: 0 triangle, 2 sphere, 3 cube (shape types); tag: see ptb_wide.cuh
 
 struct B2 { Box b; uint32_t left, right, first, count; };   // leaf when count > 0
 
 constexpr int BINS = 16;
-constexpr uint32_t MAX_LEAF = 3;        // a wide-node child slot encodes 1..3 primitives in unary
+static uint32_t MAX_LEAF = 3;           // a wide-node child slot holds 1..3 primitives
 
 inline void xform_point(const float* m, const float* p, double* out) {   // column-major To * (p,1), in double
     for (int r = 0; r < 3; r++) out[r] = (double)m[r] * p[0] + (double)m[4 + r] * p[1] + (double)m[8 + r] * p[2] + (double)m[12 + r];
@@ -155,6 +156,7 @@ inline uint32_t exponent_byte(double extent) {
 int build_wide_bvh(const ptb_scene_view* v, WideBuild* out, std::string* err) {
     auto t0 = std::chrono::steady_clock::now();
     *out = WideBuild();
+    if (std::getenv("PTB_WIDE_MAXLEAF")) MAX_LEAF = (uint32_t)std::atoi(std::getenv("PTB_WIDE_MAXLEAF"));
     Builder B;
 
     // ---- gather bounded primitives in world space ----
@@ -171,7 +173,7 @@ int build_wide_bvh(const ptb_scene_view* v, WideBuild* out, std::string* err) {
                 b.grow(wf);
             }
             pad_box(b);
-            B.pbox.push_back(b); B.prims.push_back({s, 0u, (uint32_t)sh.Type});
+            B.pbox.push_back(b); B.prims.push_back({s, 0u, (uint32_t)sh.Type, 0u});
             continue;
         }
         if (sh.Type != 0) continue;
@@ -195,7 +197,7 @@ int build_wide_bvh(const ptb_scene_view* v, WideBuild* out, std::string* err) {
                     if (!(std::isfinite(b.lo[0]) && std::isfinite(b.lo[1]) && std::isfinite(b.lo[2]) &&
                           std::isfinite(b.hi[0]) && std::isfinite(b.hi[1]) && std::isfinite(b.hi[2]))) continue;
                     pad_box(b);
-                    B.pbox.push_back(b); B.prims.push_back({s, f, 0u});
+                    B.pbox.push_back(b); B.prims.push_back({s, f, 0u, 0u});
                 }
             } else {
                 stack.push_back(n.FaceBeginOrNodeIndex + 1);
@@ -205,6 +207,30 @@ int build_wide_bvh(const ptb_scene_view* v, WideBuild* out, std::string* err) {
     }
     const size_t N = B.prims.size();
     out->prim_count = (uint32_t)N;
+    if (N + out->planes.size() >= (1ull << 27)) { *err = "more than 2^27 primitives"; return PTB_E_UNSUPPORTED; }
+    {
+        // tag = rank << 3 | identity << 2 | kind.  rank = position in the canonical (shape, face) order, so a
+        // 64-bit key {hit time bits, tag} orders hits exactly like the canonical tie rule; identity = the shape's
+        // transform is the identity matrix (object ray = world ray + 0.0f, no matrix fetch); kind = shape type & 3.
+        std::vector<std::pair<uint64_t, uint32_t>> order;
+        order.reserve(N + out->planes.size());
+        for (size_t i = 0; i < N; i++) order.push_back({((uint64_t)B.prims[i].shape << 32) | B.prims[i].face, (uint32_t)i});
+        for (size_t i = 0; i < out->planes.size(); i++) order.push_back({(uint64_t)out->planes[i] << 32, (uint32_t)(N + i)});
+        std::sort(order.begin(), order.end());
+        auto is_identity = [&](uint32_t shape) {
+            static const float I[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+            return !std::memcmp(v->Shapes[shape].Transform.From, I, 64) && !std::memcmp(v->Shapes[shape].Transform.To, I, 64);
+        };
+        std::vector<uint32_t> plane_tags(out->planes.size());
+        for (size_t r = 0; r < order.size(); r++) {
+            const uint32_t i = order[r].second;
+            if (i < N) B.prims[i].tag = ((uint32_t)r << 3) | (is_identity(B.prims[i].shape) ? 4u : 0u) | (B.prims[i].kind & 3u);
+            else plane_tags[i - N] = ((uint32_t)r << 3) | 1u;
+        }
+        std::vector<uint32_t> pl;
+        for (size_t i = 0; i < out->planes.size(); i++) { pl.push_back(out->planes[i]); pl.push_back(plane_tags[i]); }
+        out->planes.swap(pl);      // {shape, tag} pairs
+    }
     if (N == 0) { out->node_count = 0; return PTB_OK; }
     if (N > 0x7FFFFFFFull) { *err = "too many primitives for the wide BVH"; return PTB_E_UNSUPPORTED; }
 
@@ -231,7 +257,8 @@ int build_wide_bvh(const ptb_scene_view* v, WideBuild* out, std::string* err) {
     const uint32_t n_b2 = B.node_alloc.load();
     std::vector<Dp> dp(n_b2);
     {
-        const double c_node = 1.0, c_prim = 0.4;
+        const double c_node = 1.0;
+        const double c_prim = std::getenv("PTB_WIDE_CPRIM") ? std::atof(std::getenv("PTB_WIDE_CPRIM")) : 0.4;
         for (uint32_t ni = n_b2; ni-- > 0;) {
             const B2& n = B.nodes[ni];
             Dp& d = dp[ni];
@@ -324,10 +351,9 @@ int build_wide_bvh(const ptb_scene_view* v, WideBuild* out, std::string* err) {
             std::memcpy(&w[a], &self.b.lo[a], 4);
         }
         uint32_t imask = 0;
-        uint8_t meta[8] = {0}, q[6][8];
+        uint32_t valid24 = 0; uint8_t q[6][8];
         std::memset(q, 0, sizeof q);
         const uint32_t child_base = next_node, prim_base = (uint32_t)(out->prims.size() / 12);
-        uint32_t prim_off = 0;
         for (int s = 0; s < 8; s++) {
             int c = child_in_slot[s];
             if (c < 0) continue;
@@ -340,10 +366,9 @@ int build_wide_bvh(const ptb_scene_view* v, WideBuild* out, std::string* err) {
             }
             if (cn.count == 0) {
                 imask |= 1u << s;
-                meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
                 queue.push_back({ch[c], next_node++, t.depth + 1});
             } else {
-                meta[s] = (uint8_t)((((1u << cn.count) - 1u) << 5) | prim_off);
+                valid24 |= ((1u << cn.count) - 1u) << (3 * s);     // slot s owns bits 3s..3s+2; primitives are stored compacted in bit order
                 for (uint32_t k = 0; k < cn.count; k++) {
                     const Prim& p = B.prims[B.idx[cn.first + k]];
                     float rec[12];
@@ -352,16 +377,15 @@ int build_wide_bvh(const ptb_scene_view* v, WideBuild* out, std::string* err) {
                         const ptb_packed_mesh_face& F = v->MeshFaces[p.face];
                         std::memcpy(&rec[0], F.Position0, 12); std::memcpy(&rec[4], F.Position1, 12); std::memcpy(&rec[8], F.Position2, 12);
                     }
-                    std::memcpy(&rec[3], &p.face, 4); std::memcpy(&rec[7], &p.shape, 4); std::memcpy(&rec[11], &p.kind, 4);
+                    std::memcpy(&rec[3], &p.face, 4); std::memcpy(&rec[7], &p.shape, 4); std::memcpy(&rec[11], &p.tag, 4);
                     out->prims.insert(out->prims.end(), rec, rec + 12);
                 }
-                prim_off += cn.count;
                 sah += cn.b.area() / root_area * cn.count;
             }
         }
         w[3] = ebyte[0] | (ebyte[1] << 8) | (ebyte[2] << 16) | (imask << 24);
         w[4] = child_base; w[5] = prim_base;
-        std::memcpy(&w[6], meta, 8);
+        w[6] = valid24; w[7] = 0;
         for (int a = 0; a < 6; a++) std::memcpy(&w[8 + 2 * a], q[a], 8);   // qlo x,y,z then qhi x,y,z
         if (out->nodes.size() < ((size_t)next_node) * 20) out->nodes.resize((size_t)next_node * 20);
         std::memcpy(&out->nodes[(size_t)t.index * 20], w, sizeof w);

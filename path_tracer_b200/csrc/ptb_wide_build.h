@@ -22,7 +22,7 @@ namespace ptb {
 struct WideBuild {
     std::vector<uint32_t> nodes;     // 20 words (80 B) per node; node 0 is the root
     std::vector<float>    prims;     // 12 floats (48 B) per leaf primitive
-    std::vector<uint32_t> planes;    // shape indices of unbounded shapes
+    std::vector<uint32_t> planes;    // {shape index, tag} per unbounded shape
     uint32_t node_count = 0, prim_count = 0, depth = 0, bvh2_depth = 0;
     double   sah_cost = 0.0;         // SAH cost of the wide tree (node area-weighted), for diagnostics
     double   build_seconds = 0.0;

@@ -58,7 +58,7 @@ void* emu_create(const ptb_scene_view* v, u32 w, u32 h) {
     int rc = build_wide_bvh(v, &e->wb, &err);
     if (rc != 0) { fprintf(stderr, "emu: wide build failed: %s\n", err.c_str()); delete e; return nullptr; }
     e->ds.wide_nodes = (const uint4*)e->wb.nodes.data(); e->ds.wide_tris = (const float4*)e->wb.prims.data();
-    e->ds.wide_planes = e->wb.planes.data(); e->ds.wide_plane_count = (u32)e->wb.planes.size();
+    e->ds.wide_planes = e->wb.planes.data(); e->ds.wide_plane_count = (u32)(e->wb.planes.size() / 2);
     e->ds.wide_tlas_root = e->wb.node_count ? 0u : 0xFFFFFFFFu;
     memset(&e->pc, 0, sizeof e->pc);
     e->pc.width = w; e->pc.height = h; e->pc.tiles_x = (w + 15) / 16; e->pc.slot_count = w * h;
@@ -87,6 +87,35 @@ void emu_raycast(void* p, const ptb_ray* rays, uint64_t n, int mode, ptb_hit* ou
             out[i] = o;
         }
     });
+}
+
+// Traversal statistics of the wide BVH on caller rays: node steps and primitive tests per ray
+// (builder tuning aid: lets BVH quality be compared on the CPU).
+void emu_wide_stats(void* p, const ptb_ray* rays, uint64_t n, uint64_t* out3) {
+    Emu* e = (Emu*)p;
+    std::atomic<uint64_t> nodes(0), prims(0), maxsp(0);
+    parallel_for(n, 1024, [&](uint64_t b, uint64_t en) {
+        uint64_t ln = 0, lp = 0, ms = 0;
+        for (uint64_t i = b; i < en; i++) {
+            Ray r; r.origin = mk3(rays[i].ox, rays[i].oy, rays[i].oz); r.velocity = mk3(rays[i].dx, rays[i].dy, rays[i].dz); r.duration = rays[i].duration;
+            HitId h = wide_begin(e->ds, r);
+            if (e->ds.wide_tlas_root == 0xFFFFFFFFu) continue;
+            const WideCtx c = wide_ctx(r);
+            LocalStack stack; stack.sp = 0;
+            uint2 ng = make_uint2(0u, 0x80000000u);
+            u32 cur = PTB_SHAPE_NONE; Ray obj = r;
+            while (true) {
+                PrimGroup pg;
+                wide_node_step(e->ds, c, h.t, ng, pg, stack); ln++;
+                if ((uint64_t)stack.sp > ms) ms = stack.sp;
+                while (pg.bits) { wide_prim_step(e->ds, r, pg, cur, obj, h); lp++; }
+                if (ng.y <= 0x00FFFFFFu) { if (stack.empty()) break; ng = stack.pop(); }
+            }
+        }
+        nodes += ln; prims += lp;
+        uint64_t m = maxsp.load(); while (ms > m && !maxsp.compare_exchange_weak(m, ms)) {}
+    });
+    out3[0] = nodes; out3[1] = prims; out3[2] = maxsp;
 }
 
 void emu_set(void* p, u32 camera, u32 flags, u32 limit, float term, u32 frame_index) {
