@@ -276,13 +276,19 @@ def main():
                "mpaths_per_s": c["paths"] / c["seconds"] / 1e6,
                "per_ray": {"node_fetches": c["node_fetches"] / c["rays"], "face_tests": c["face_tests"] / c["rays"],
                            "shape_visits": c["shape_visits"] / c["rays"], "mesh_hit_fraction": c["mesh_hits"] / c["rays"]}}
+    bytes_source = "oracle traversal counters of this run's CPU sample"
+    if trace_bytes is None:
+        # no CPU sample in this run (N>1 or --no-cpu-baseline): the per-ray figure the oracle counted for this
+        # workload in the committed full run (profiles/r01_v1_bench.json: 82.5 nodes, 7.05 faces, 1.92 shapes per ray)
+        seg_bytes, trace_bytes = 3522.405, 3314.405
+        bytes_source = "oracle traversal counters recorded in profiles/r01_v1_bench.json (same workload)"
     roofline = None
     if trace_bytes is not None:
         live = WIDTH * HEIGHT
         achieved = live * trace_bytes / (trace_ms * 1e-3) / 1e9
         roofline = {"bound": "hbm", "kernel": "k_trace" if kt["trace_launches"] else "k_mega", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                     "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
-                    "algorithmic_bytes_per_ray": trace_bytes, "rays_per_launch": live, "kernel_ms": trace_ms,
+                    "algorithmic_bytes_per_ray": trace_bytes, "bytes_source": bytes_source, "rays_per_launch": live, "kernel_ms": trace_ms,
                     "segment_bytes_model": seg_bytes, "whole_segment_achieved_gbs": value * 1e6 * seg_bytes / 1e9,
                     "whole_segment_frac": value * 1e6 * seg_bytes / 1e9 / hbm_peak,
                     "note": "geometry (~60 MB wide BVH + prims) is L2-resident: the kernel is SM-issue/latency bound, see profiles/"}

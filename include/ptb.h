@@ -109,8 +109,8 @@ typedef struct { float Brightness; uint32_t ToneMappingMode; float ToneMappingWh
 /* Trace-step kernel for PTB_TRAVERSAL_WIDE.  0 = one thread per slot; 1..MAX = persistent
  * warps with dynamic ray fetch, numbered tuning points (see ptb_kernels.cu). */
 #define PTB_TRACE_VARIANT_SIMPLE  0u
-#define PTB_TRACE_VARIANT_DEFAULT 1u
-#define PTB_TRACE_VARIANT_MAX     8u
+#define PTB_TRACE_VARIANT_DEFAULT 10u
+#define PTB_TRACE_VARIANT_MAX     15u
 
 /* Tie rule for equal hit times. */
 #define PTB_TIE_FAITHFUL  0u  /* reference rules; needs PTB_TRAVERSAL_BVH2_REFERENCE */

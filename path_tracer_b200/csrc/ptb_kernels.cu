@@ -244,6 +244,223 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_TRACE_MIN_BLOCKS) k_
     }
 }
 
+// ---- K1, cooperative leaf tests ------------------------------------------------------------
+// In k_trace_persistent the leaf-primitive loop runs at ~5 of 32 lanes and takes half of the kernel's
+// time (profiles/r01_v2_k_trace_persistent.txt): per node step only a few lanes have primitives to
+// test, and the rest of the warp waits for them.  Here primitive tests are decoupled from the ray that
+// asked for them.  After a node step a lane appends its hit leaf primitives as ONE group record
+// {owner lane, primitive base, hit bits, valid bits} to a per-warp queue in shared memory and goes on;
+// whenever the queue holds 32 primitives the whole warp tests one each: the group sizes are scanned,
+// lane i finds the group that owns the i-th primitive (bit mask of group starts + find-leading-one),
+// reads the owner's ray and current reach from shared memory, runs the exact reference test, and
+// publishes an accepted hit with a 64-bit atomicMin on the owner's key {t bits, canonical rank}.  That
+// key order IS the canonical tie rule (lowest t, then shape, then face: the builder ranks primitives
+// in that order), so the result does not depend on which lane tested what, or when.
+//   SPEC    a lane keeps traversing while its primitives wait in the queue (its reach is stale until
+//           the flush: more node steps, full lanes) or stalls until they have been tested;
+//   WAIT_T  a partial flush happens when this many lanes cannot go on without one.
+// Rays are fetched from the global counter in chunks of PTB_COOP_CHUNK consecutive slots per warp.
+#define PTB_COOP_QUEUE 64           // groups; >= 31 (left by a flush) + 32 (one per lane and round), power of two
+#define PTB_COOP_CHUNK 64
+#ifndef PTB_COOP_MIN_BLOCKS
+#define PTB_COOP_MIN_BLOCKS 6
+#endif
+
+struct CoopWarp {
+    uint2 stack[PTB_SMEM_STACK][32];
+    unsigned long long key[32];       // closest hit so far: {t bits (+0 canonical), tag}; tag 0xFFFFFFFF = none
+    float ray[6][32];                 // world-space origin, velocity of each lane's ray
+    u32 detail[7][32];                // t, shape, face, shape type, coords of the hit `key` names
+    uint4 group[PTB_COOP_QUEUE];      // {owner lane << 27 | primitive base, pending bits, valid bits, -}
+    u32 starts[32];                   // flush scratch: queue position (relative to the head) of the group starting at primitive i
+};
+
+// Tests the first min(32, queued) primitives of the group queue, one per lane.  ghead / qprims are updated.
+__device__ __forceinline__ void coop_flush(const DeviceScene& s, CoopWarp& W, u32 lane, u32& ghead, u32 gtail, u32& qprims) {
+    __syncwarp();
+    const u32 groups = min(gtail - ghead, 32u);
+    uint4 g = make_uint4(0u, 0u, 0u, 0u);
+    if (lane < groups) g = W.group[(ghead + lane) & (PTB_COOP_QUEUE - 1)];
+    const u32 n = (u32)__popc(g.y);
+    u32 incl = n;
+#pragma unroll
+    for (int d = 1; d < 32; d *= 2) { const u32 t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= (u32)d) incl += t; }
+    const u32 excl = incl - n;
+    const bool starts_here = n != 0u && excl < 32u;
+    const u32 start_mask = __reduce_or_sync(0xFFFFFFFFu, starts_here ? 1u << excl : 0u);
+    if (starts_here) W.starts[excl] = lane;
+    const u32 take = min(qprims, 32u);
+    __syncwarp();
+
+    bool won = false;
+    u32 owner = 0;
+    unsigned long long key = 0;
+    HitId h;
+    h.t = 0; h.shape = PTB_SHAPE_NONE; h.prim = 0xFFFFFFFFu; h.shape_type = 0; h.coords = mk3(0, 0, 0);
+    if (lane < take) {
+        const u32 start = highest_bit(start_mask & (0xFFFFFFFFu >> (31u - lane)));
+        const uint4 gg = W.group[(ghead + W.starts[start]) & (PTB_COOP_QUEUE - 1)];
+        u32 bits = gg.y;
+        for (u32 k = lane - start; k != 0u; k--) bits &= bits - 1u;          // this lane takes the k-th lowest pending bit
+        const u32 b = (u32)__ffs((int)bits) - 1u;
+        owner = gg.x >> 27;
+        const float4* tp = s.wide_tris + 3 * (size_t)((gg.x & 0x07FFFFFFu) + (u32)__popc(gg.z & ((1u << b) - 1u)));
+        const float4 v0 = PTB_LDG(&tp[0]), v1 = PTB_LDG(&tp[1]), v2 = PTB_LDG(&tp[2]);
+        const u32 face = f2u(v0.w), shape = f2u(v1.w), tag = f2u(v2.w);
+        Ray w;
+        w.origin = mk3(W.ray[0][owner], W.ray[1][owner], W.ray[2][owner]);
+        w.velocity = mk3(W.ray[3][owner], W.ray[4][owner], W.ray[5][owner]);
+        h.t = w.duration = u2f((u32)(W.key[owner] >> 32));
+        Ray o;
+        if (tag & 4u) {        // identity transform: the same arithmetic on constants, no matrix fetch
+            const float I[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+            o.origin = mat_mul_point(I, w.origin); o.velocity = mat_mul_vector(I, w.velocity); o.duration = w.duration;
+        } else {
+            o = object_ray(s, w, shape);
+        }
+        if ((tag & 3u) == 0u) test_triangle<true>(o, mk3(v0.x, v0.y, v0.z), mk3(v1.x, v1.y, v1.z), mk3(v2.x, v2.y, v2.z), shape, face, h);
+        else test_analytic<true>(o, tag & 3u, shape, h);
+        if (h.shape != PTB_SHAPE_NONE) {
+            u32 tb = f2u(h.t);
+            if (tb == 0x80000000u) tb = 0u;         // -0 == +0 in the reference's comparisons
+            key = ((unsigned long long)tb << 32) | tag;
+            atomicMin(&W.key[owner], key);
+            won = true;
+        }
+    }
+    __syncwarp();
+    if (won && W.key[owner] == key) {
+        W.detail[0][owner] = f2u(h.t); W.detail[1][owner] = h.shape; W.detail[2][owner] = h.prim; W.detail[3][owner] = h.shape_type;
+        W.detail[4][owner] = f2u(h.coords.x); W.detail[5][owner] = f2u(h.coords.y); W.detail[6][owner] = f2u(h.coords.z);
+    }
+    // consumed groups leave the queue (they are a prefix of it); at most one group is consumed in part
+    const u32 used = excl >= take ? 0u : min(n, take - excl);
+    if (used != 0u && used != n) {
+        u32 bits = g.y;
+        for (u32 k = used; k != 0u; k--) bits &= bits - 1u;
+        W.group[(ghead + lane) & (PTB_COOP_QUEUE - 1)].y = bits;
+    }
+    ghead += (u32)__popc(__ballot_sync(0xFFFFFFFFu, n != 0u && used == n));
+    qprims -= take;
+    __syncwarp();
+}
+
+template <class Job, int REFILL, bool SPEC, int WAIT_T>
+__global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_trace_coop(const Job job) {
+    __shared__ CoopWarp warp_mem[PTB_TRACE_WARPS];
+    const DeviceScene& s = job.s;
+    const u32 lane = threadIdx.x & 31u;
+    CoopWarp& W = warp_mem[threadIdx.x >> 5];
+    const u32 lt_mask = (1u << lane) - 1u;
+    const u32 total = job.total();
+
+    bool active = false, drained = false;      // drained: the global counter has passed `total`
+    u32 pool_next = 0, pool_end = 0;           // this warp's chunk of ray indices (warp-uniform)
+    u32 index = 0;
+    u32 ghead = 0, gtail = 0, qprims = 0;      // group queue sequence numbers and queued primitive count (warp-uniform)
+    u32 last_seq = 0;                          // one past this lane's newest group: its tests are pending while last_seq > ghead
+    WideCtx c;
+    uint2 ng = make_uint2(0u, 0u);
+    WarpStack stack;
+    stack.smem = &W.stack[0][lane];
+    stack.sp = 0;
+    { Ray z; z.origin = z.velocity = mk3(0, 0, 0); z.duration = 0; c = wide_ctx(z); }
+
+    for (;;) {
+        // ---- refill ----
+        const u32 idle = __ballot_sync(0xFFFFFFFFu, !active);
+        if (__popc(idle) >= REFILL || idle == 0xFFFFFFFFu) {
+            if (pool_next == pool_end && !drained) {
+                u32 base = 0;
+                if (lane == 0) base = atomicAdd(job.counter(), (unsigned)PTB_COOP_CHUNK);
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                pool_next = min(base, total);
+                pool_end = min(base + PTB_COOP_CHUNK, total);
+                if (base + PTB_COOP_CHUNK >= total) drained = true;
+            }
+            const u32 avail = pool_end - pool_next;
+            const u32 rank = (u32)__popc(idle & lt_mask);
+            if (!active && rank < avail) {
+                index = pool_next + rank;
+                Ray ray;
+                if (job.load(index, ray)) {
+                    // unbounded shapes (planes) are tested by the owner, up front
+                    HitId h;
+                    h.t = ray.duration; h.shape = PTB_SHAPE_NONE; h.prim = 0xFFFFFFFFu; h.shape_type = 0; h.coords = mk3(0, 0, 0);
+                    u32 tag = 0xFFFFFFFFu;
+                    for (u32 i = 0; i < s.wide_plane_count; i++) {
+                        const uint2 pl = PTB_LDG((const uint2*)s.wide_planes + i);
+                        const u32 before = h.shape;
+                        test_analytic<true>(object_ray(s, ray, pl.x), PTB_SHAPE_PLANE, pl.x, h);
+                        if (h.shape != before) tag = pl.y;
+                    }
+                    if (s.wide_tlas_root == 0xFFFFFFFFu) {
+                        job.store(index, h);
+                    } else {
+                        c = wide_ctx(ray);
+                        ng = make_uint2(0u, 0x80000000u);
+                        stack.sp = 0;
+                        last_seq = ghead;
+                        active = true;
+                        W.ray[0][lane] = ray.origin.x; W.ray[1][lane] = ray.origin.y; W.ray[2][lane] = ray.origin.z;
+                        W.ray[3][lane] = ray.velocity.x; W.ray[4][lane] = ray.velocity.y; W.ray[5][lane] = ray.velocity.z;
+                        u32 tb = f2u(h.t);
+                        if (tb == 0x80000000u) tb = 0u;
+                        W.key[lane] = ((unsigned long long)tb << 32) | tag;
+                        W.detail[0][lane] = f2u(h.t); W.detail[1][lane] = h.shape; W.detail[2][lane] = h.prim; W.detail[3][lane] = h.shape_type;
+                        W.detail[4][lane] = f2u(h.coords.x); W.detail[5][lane] = f2u(h.coords.y); W.detail[6][lane] = f2u(h.coords.z);
+                    }
+                }
+            }
+            pool_next += min((u32)__popc(idle), avail);
+            __syncwarp();
+        }
+        if (!__any_sync(0xFFFFFFFFu, active)) {
+            if (drained && pool_next == pool_end) break;
+            continue;
+        }
+
+        // ---- node ----
+        PrimGroup pg;
+        pg.base = pg.bits = pg.valid = 0u;
+        if (active && ng.y > 0x00FFFFFFu && (SPEC || (int)(last_seq - ghead) <= 0)) {
+            const float reach = u2f((u32)(W.key[lane] >> 32));
+            wide_node_step(s, c, reach, ng, pg, stack);
+            if (ng.y <= 0x00FFFFFFu && !stack.empty()) ng = stack.pop();
+        }
+
+        // ---- queue the hit leaf primitives, one group per lane; 32 queued primitives are tested at once ----
+        const u32 has = __ballot_sync(0xFFFFFFFFu, pg.bits != 0u);
+        if (has != 0u) {
+            if (pg.bits != 0u) {
+                const u32 q = gtail + (u32)__popc(has & lt_mask);
+                W.group[q & (PTB_COOP_QUEUE - 1)] = make_uint4((lane << 27) | pg.base, pg.bits, pg.valid, 0u);
+                last_seq = q + 1u;
+            }
+            gtail += (u32)__popc(has);
+            qprims += __reduce_add_sync(0xFFFFFFFFu, (u32)__popc(pg.bits));
+            while (qprims >= 32u) coop_flush(s, W, lane, ghead, gtail, qprims);
+        }
+
+        // ---- partial flush when too many lanes wait for their tests ----
+        if (qprims != 0u) {
+            const bool pending = (int)(last_seq - ghead) > 0;
+            const bool stepper = active && ng.y > 0x00FFFFFFu && (SPEC || !pending);
+            const u32 waiting = __ballot_sync(0xFFFFFFFFu, active && pending && !stepper);
+            if (__popc(waiting) >= WAIT_T || !__any_sync(0xFFFFFFFFu, stepper)) coop_flush(s, W, lane, ghead, gtail, qprims);
+        }
+
+        // ---- retire ----
+        if (active && ng.y <= 0x00FFFFFFu && (int)(last_seq - ghead) <= 0) {
+            HitId h;
+            h.t = u2f(W.detail[0][lane]); h.shape = W.detail[1][lane]; h.prim = W.detail[2][lane]; h.shape_type = W.detail[3][lane];
+            h.coords = mk3(u2f(W.detail[4][lane]), u2f(W.detail[5][lane]), u2f(W.detail[6][lane]));
+            job.store(index, h);
+            active = false;
+        }
+    }
+}
+
 // ---- K2: scatter ----
 __global__ void __launch_bounds__(256, 3) k_scatter(const DeviceScene s, const RenderConsts pc, const WavefrontState st, float4* __restrict__ accum) {
     const u32 slot = blockIdx.x * 256u + threadIdx.x;
@@ -358,10 +575,14 @@ static unsigned persistent_grid(K kernel) {
     return (unsigned)(sms * per_sm);
 }
 
-// Tuning points of the persistent kernel: refill threshold (idle lanes that trigger a fetch).
+// Variants of the wide trace kernel (TraceVariant of the render parameters; 0 = one thread per slot):
+//   1-4   k_trace_persistent, refill threshold (idle lanes that trigger a fetch) 8 / 4 / 16 / 32
+//   5-    k_trace_coop {refill, speculate, waiting lanes that force a partial flush}
 // Parking leaf work on the stack when few lanes have any (vote-driven postponing) was measured in
-// round 1 and did not pay on B200 (profiles/r01_v2_variant_sweep.txt); it was removed.
-#define PTB_PERSISTENT_VARIANTS(X) X(1, 8) X(2, 4) X(3, 12) X(4, 16) X(5, 24) X(6, 32) X(7, 2) X(8, 1)
+// round 1 and did not pay on B200; it was removed.  Sweep: profiles/r01_v3_variant_sweep.txt.
+#define PTB_PERSISTENT_VARIANTS(X) X(1, 8) X(2, 4) X(3, 16) X(4, 32)
+#define PTB_COOP_VARIANTS(X) X(5, 8, false, 8) X(6, 8, false, 16) X(7, 8, false, 24) X(8, 8, false, 32) X(9, 8, false, 4) \
+                             X(10, 8, true, 8) X(11, 8, true, 16) X(12, 8, true, 32) X(13, 8, true, 4) X(14, 16, false, 16) X(15, 4, false, 16)
 
 template <class Job>
 static cudaError_t launch_persistent(const Job& job, unsigned variant, cudaStream_t stream) {
@@ -369,6 +590,10 @@ static cudaError_t launch_persistent(const Job& job, unsigned variant, cudaStrea
 #define X(ID, R) case ID: { static unsigned grid = 0; if (!grid) grid = persistent_grid(k_trace_persistent<Job, R>); \
                             k_trace_persistent<Job, R><<<grid, 32 * PTB_TRACE_WARPS, 0, stream>>>(job); break; }
         PTB_PERSISTENT_VARIANTS(X)
+#undef X
+#define X(ID, R, S, W) case ID: { static unsigned grid = 0; if (!grid) grid = persistent_grid(k_trace_coop<Job, R, S, W>); \
+                                  k_trace_coop<Job, R, S, W><<<grid, 32 * PTB_TRACE_WARPS, 0, stream>>>(job); break; }
+        PTB_COOP_VARIANTS(X)
 #undef X
         default: return cudaErrorInvalidValue;
     }
@@ -424,7 +649,7 @@ cudaError_t launch_raycast(const DeviceScene& s, const ptb_ray* rays, size_t n, 
                            unsigned* counter, ptb_hit* out, cudaStream_t stream) {
     if (n == 0) return cudaSuccess;
     const int mode = mode_of(traversal, tie);
-    if (mode == MODE_WIDE && variant != 0 && counter && n < 0xFFFFFFFFull) {
+    if (mode == MODE_WIDE && variant != 0 && counter && n < 0xF0000000ull) {
         cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(unsigned), stream);
         if (e != cudaSuccess) return e;
         RaycastJob job;
