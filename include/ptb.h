@@ -106,8 +106,9 @@ typedef struct { float Brightness; uint32_t ToneMappingMode; float ToneMappingWh
 #define PTB_TRAVERSAL_BVH2_REFERENCE 0u /* the packed two-level BVH2 as-is, reference visiting order */
 #define PTB_TRAVERSAL_WIDE           1u /* compressed BVH8 re-flattened at ptb_scene_update */
 
-/* Trace-step kernel for PTB_TRAVERSAL_WIDE.  0 = one thread per slot; 1..MAX = persistent
- * warps with dynamic ray fetch, numbered tuning points (see ptb_kernels.cu). */
+/* Trace-step kernel for PTB_TRAVERSAL_WIDE.  0 = one thread per slot; 1..4 = persistent warps
+ * with dynamic ray fetch; 5..MAX = the same with cooperative leaf tests (numbered tuning points,
+ * see ptb_kernels.cu).  All variants produce identical hit records. */
 #define PTB_TRACE_VARIANT_SIMPLE  0u
 #define PTB_TRACE_VARIANT_DEFAULT 10u
 #define PTB_TRACE_VARIANT_MAX     15u
