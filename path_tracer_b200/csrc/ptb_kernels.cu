@@ -132,7 +132,9 @@ __global__ void __launch_bounds__(128) k_trace(const DeviceScene s, const Render
 //     pop     : lanes out of node work pop their stack or retire and store their hit.
 // The first entries of each lane's stack live in shared memory, lane-interleaved (bank = lane, so
 // any mix of stack depths is conflict-free); deeper entries spill to local memory.
+#ifndef PTB_SMEM_STACK
 #define PTB_SMEM_STACK 10
+#endif
 #define PTB_TRACE_WARPS 4
 #ifndef PTB_TRACE_MIN_BLOCKS
 #define PTB_TRACE_MIN_BLOCKS 6
@@ -259,9 +261,12 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_TRACE_MIN_BLOCKS) k_
 //   SPEC    a lane keeps traversing while its primitives wait in the queue (its reach is stale until
 //           the flush: more node steps, full lanes) or stalls until they have been tested;
 //   WAIT_T  a partial flush happens when this many lanes cannot go on without one.
-// Rays are fetched from the global counter in chunks of PTB_COOP_CHUNK consecutive slots per warp.
+// Rays are fetched from the global counter in chunks of PTB_COOP_CHUNK consecutive slots per warp
+// (32: measured best on B200; 128 costs 8 % to tail imbalance, profiles/r01_v3_ab_builds.txt).
 #define PTB_COOP_QUEUE 64           // groups; >= 31 (left by a flush) + 32 (one per lane and round), power of two
-#define PTB_COOP_CHUNK 64
+#ifndef PTB_COOP_CHUNK
+#define PTB_COOP_CHUNK 32
+#endif
 #ifndef PTB_COOP_MIN_BLOCKS
 #define PTB_COOP_MIN_BLOCKS 6
 #endif

@@ -13,6 +13,7 @@ There is no CPU fallback: if libptb.so cannot be built/loaded, or no B200 is
 visible, the calls raise.
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -57,7 +58,8 @@ def lib():
     """Loads libptb.so (building it in-tree with nvcc when missing or stale)."""
     global _lib
     if _lib is None:
-        L = C.CDLL(_build.build_cuda())
+        # PTB_LIB: load another in-tree build of the same sources (A/B experiments with -D tuning macros)
+        L = C.CDLL(os.environ.get("PTB_LIB") or _build.build_cuda())
         vp, u32, sz = C.c_void_p, C.c_uint32, C.c_size_t
         L.ptb_last_error.restype = C.c_char_p
         L.ptb_version.restype = C.c_char_p
