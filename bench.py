@@ -259,6 +259,7 @@ def main():
     kt = r.profile_frames(F)
     trace_ms = (kt["trace_ms"] / max(1, kt["trace_launches"])) if kt["trace_launches"] else (kt["mega_ms"] / max(1, kt["mega_launches"]))
 
+    D.shutdown()
     if rank != 0:
         return
 

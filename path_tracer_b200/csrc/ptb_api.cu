@@ -65,6 +65,7 @@ struct ptb_scene {
     DeviceScene ds;
     ptb_wide_info wide_info;
     unsigned raycast_variant;
+    uint32_t material_features;      // PTB_FEAT_DIFFUSE/METAL/TRANSLUCENT bits of the uploaded material slots
 };
 
 struct ptb_film {
@@ -134,6 +135,7 @@ int ptb_scene_create(ptb_context* ctx, ptb_scene** out) {
     s->ds.wide_tlas_root = 0xFFFFFFFFu;
     s->ds.globals.SkyboxTextureIndex = 0xFFFFFFFFu;
     s->raycast_variant = PTB_TRACE_VARIANT_DEFAULT;
+    s->material_features = 0;
     *out = s;
     return PTB_OK;
 }
@@ -161,6 +163,11 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
     if (dirty & PTB_SCENE_DIRTY_MATERIALS) {
         CU(s->materials.upload(v->MaterialData, v->MaterialWordCount, st));
         s->ds.material_data = s->materials.p; s->ds.material_word_count = v->MaterialWordCount;
+        s->material_features = 0;
+        for (uint32_t slot = 0; slot + 1 <= v->MaterialWordCount / 32u; slot++) {
+            const uint32_t type = v->MaterialData[32u * slot];          // word 0 = material type (scene.glsl.inc:687-762)
+            s->material_features |= type == 0u ? PTB_FEAT_DIFFUSE : type == 1u ? PTB_FEAT_METAL : type == 2u ? PTB_FEAT_TRANSLUCENT : 0u;
+        }
     }
     if (dirty & PTB_SCENE_DIRTY_SHAPES) {
         CU(s->shapes.upload(v->Shapes, v->ShapeCount, st));
@@ -181,6 +188,10 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
         s->ds.cameras = s->cameras.p; s->ds.camera_count = v->CameraCount;
     }
     if ((dirty & (PTB_SCENE_DIRTY_GLOBALS | PTB_SCENE_DIRTY_SHAPES | PTB_SCENE_DIRTY_SKYBOX_TEXTURE)) && v->Globals) s->ds.globals = *v->Globals;
+    // what scatter can meet in this scene: selects the k_scatter instantiation (ptb_kernels.cu)
+    s->ds.features = s->material_features | (s->ds.texture_count ? PTB_FEAT_TEXTURES : 0u)
+                   | (s->ds.globals.SkyboxTextureIndex != 0xFFFFFFFFu ? PTB_FEAT_SKY_TEXTURE : 0u)
+                   | (s->ds.globals.SceneScatterRate > 0.0f ? PTB_FEAT_SCENE_SCATTER : 0u);
     if (dirty & (PTB_SCENE_DIRTY_SHAPES | PTB_SCENE_DIRTY_MESHES)) {
         // scene flattening: packed two-level BVH2 scene -> one compressed BVH8
         WideBuild wb;

@@ -33,13 +33,13 @@ struct Medium { u32 priority; f4 ior, absorption, scattering; float anisotropy; 
 
 // ---- BasicDiffuse (basic_diffuse.glsl.inc:19-50) ----
 // The pdf is wi.z/pi of the GIVEN direction (reference quirk Q7), kept as is.
-PTB_HD bool diffuse_eval(const DeviceScene& s, const BsdfParams& p, f3 wi, f4& throughput, f4& pdf) {
+PTB_HDN bool diffuse_eval(const DeviceScene& s, const BsdfParams& p, f3 wi, f4& throughput, f4& pdf) {
     f4 reflectance = material_reflectance(s, p.material, PTB_DIFFUSE_BASE, p.lambda, p.uv);
     pdf = mk4(wi.z / PTB_PI);
     throughput = pdf * reflectance;
     return true;
 }
-PTB_HD bool diffuse_sample(const DeviceScene& s, const BsdfParams& p, f3 wi, Rng& g, f3& wo, f4& throughput, f4& pdf) {
+PTB_HDN bool diffuse_sample(const DeviceScene& s, const BsdfParams& p, f3 wi, Rng& g, f3& wo, f4& throughput, f4& pdf) {
     f3 d = random_direction(g);
     wo = safe_normalize(d + mk3(0, 0, 1));
     return diffuse_eval(s, p, wi, throughput, pdf);
@@ -57,7 +57,7 @@ PTB_HD MetalParams metal_params(const DeviceScene& s, const BsdfParams& p) {    
     m.rough = m.alpha.x * m.alpha.y > PTB_EPSILON;
     return m;
 }
-PTB_HD bool metal_eval(const DeviceScene& s, const BsdfParams& p, f3 wi, f3 wo, f4& throughput, f4& pdf) {   // :46-84
+PTB_HDN bool metal_eval(const DeviceScene& s, const BsdfParams& p, f3 wi, f3 wo, f4& throughput, f4& pdf) {   // :46-84
     MetalParams m = metal_params(s, p);
     if (wi.z <= 0.0f || wo.z <= 0.0f || !m.rough) return false;
     f3 half = safe_normalize(wi + wo);
@@ -69,7 +69,7 @@ PTB_HD bool metal_eval(const DeviceScene& s, const BsdfParams& p, f3 wi, f3 wo, 
     throughput = (pdf * gs) * f;
     return true;
 }
-PTB_HD bool metal_sample(const DeviceScene& s, const BsdfParams& p, f3 wi, Rng& g, f3& wo, f4& throughput, f4& pdf) {   // :87-141
+PTB_HDN bool metal_sample(const DeviceScene& s, const BsdfParams& p, f3 wi, Rng& g, f3& wo, f4& throughput, f4& pdf) {   // :87-141
     MetalParams m = metal_params(s, p);
     if (wi.z <= 0.0f) return false;
     float u1 = g.uniform();
@@ -102,7 +102,7 @@ PTB_HD TransParams trans_params(const DeviceScene& s, const BsdfParams& p, f3 wi
     t.rough = t.alpha.x * t.alpha.y > PTB_EPSILON;
     return t;
 }
-PTB_HD void trans_load_medium(const DeviceScene& s, u32 material, f4 lambda, Medium& m) {   // :55-82
+PTB_HDN void trans_load_medium(const DeviceScene& s, u32 material, f4 lambda, Medium& m) {   // :55-82
     m.ior = cauchy_ior(material_f32(s, material, PTB_TRANS_IOR), material_f32(s, material, PTB_TRANS_ABBE), lambda);
     float depth = material_f32(s, material, PTB_TRANS_DEPTH);
     if (depth > 0.0f) {
@@ -133,7 +133,7 @@ PTB_HD f4 trans_refraction_pdf(f3 wi, f3 wo, const TransParams& t, f3 h1, f4 ci,
     f4 jac = abs4(co) / (q * q);
     return (((d * (1.0f - f)) * gm) * jac) * abs4(ci / wi.z);
 }
-PTB_HD bool trans_eval(const DeviceScene& s, const BsdfParams& p, f3 wi, f3 wo, f4& throughput, f4& pdf) {   // :90-169
+PTB_HDN bool trans_eval(const DeviceScene& s, const BsdfParams& p, f3 wi, f3 wo, f4& throughput, f4& pdf) {   // :90-169
     TransParams t = trans_params(s, p, wi);
     if (!t.rough) { pdf = mk4(0.0f); throughput = mk4(0.0f); return true; }
     if (wi.z * wo.z > 0.0f) {
@@ -152,7 +152,7 @@ PTB_HD bool trans_eval(const DeviceScene& s, const BsdfParams& p, f3 wi, f3 wo, 
     throughput = pdf * gs;
     return true;
 }
-PTB_HD bool trans_sample(const DeviceScene& s, const BsdfParams& p, f3 wi, Rng& g, f3& wo, f4& throughput, f4& pdf) {   // :172-339
+PTB_HDN bool trans_sample(const DeviceScene& s, const BsdfParams& p, f3 wi, Rng& g, f3& wo, f4& throughput, f4& pdf) {   // :172-339
     TransParams t = trans_params(s, p, wi);
     float u1 = g.uniform();
     float u2 = g.uniform();
@@ -189,27 +189,27 @@ PTB_HD bool trans_sample(const DeviceScene& s, const BsdfParams& p, f3 wi, Rng& 
 PTB_HD u32 material_type(const DeviceScene& s, u32 slot) { return material_u32(s, slot, 0); }
 
 PTB_HD bool material_load_medium(const DeviceScene& s, u32 material, f4 lambda, Medium& m) {
-    if (material_type(s, material) == 2u) { trans_load_medium(s, material, lambda, m); return true; }
+    if ((s.features & PTB_FEAT_TRANSLUCENT) && material_type(s, material) == 2u) { trans_load_medium(s, material, lambda, m); return true; }
     return false;
 }
 PTB_HD bool material_has_dirac(const DeviceScene& s, const BsdfParams& p) {
     u32 type = material_type(s, p.material);
-    if (type == 1u) return material_value(s, p.material, PTB_METAL_ROUGHNESS, p.uv) < 1e-3f;
-    if (type == 2u) return material_value(s, p.material, PTB_TRANS_ROUGHNESS, p.uv) < 1e-3f;
+    if ((s.features & PTB_FEAT_METAL) && type == 1u) return material_value(s, p.material, PTB_METAL_ROUGHNESS, p.uv) < 1e-3f;
+    if ((s.features & PTB_FEAT_TRANSLUCENT) && type == 2u) return material_value(s, p.material, PTB_TRANS_ROUGHNESS, p.uv) < 1e-3f;
     return false;
 }
 PTB_HD bool material_eval(const DeviceScene& s, const BsdfParams& p, f3 wi, f3 wo, f4& throughput, f4& pdf) {
     u32 type = material_type(s, p.material);
-    if (type == 0u) return diffuse_eval(s, p, wi, throughput, pdf);
-    if (type == 1u) return metal_eval(s, p, wi, wo, throughput, pdf);
-    if (type == 2u) return trans_eval(s, p, wi, wo, throughput, pdf);
+    if ((s.features & PTB_FEAT_DIFFUSE) && type == 0u) return diffuse_eval(s, p, wi, throughput, pdf);
+    if ((s.features & PTB_FEAT_METAL) && type == 1u) return metal_eval(s, p, wi, wo, throughput, pdf);
+    if ((s.features & PTB_FEAT_TRANSLUCENT) && type == 2u) return trans_eval(s, p, wi, wo, throughput, pdf);
     return false;
 }
 PTB_HD bool material_sample(const DeviceScene& s, const BsdfParams& p, f3 wi, Rng& g, f3& wo, f4& throughput, f4& pdf) {
     u32 type = material_type(s, p.material);
-    if (type == 0u) return diffuse_sample(s, p, wi, g, wo, throughput, pdf);
-    if (type == 1u) return metal_sample(s, p, wi, g, wo, throughput, pdf);
-    if (type == 2u) return trans_sample(s, p, wi, g, wo, throughput, pdf);
+    if ((s.features & PTB_FEAT_DIFFUSE) && type == 0u) return diffuse_sample(s, p, wi, g, wo, throughput, pdf);
+    if ((s.features & PTB_FEAT_METAL) && type == 1u) return metal_sample(s, p, wi, g, wo, throughput, pdf);
+    if ((s.features & PTB_FEAT_TRANSLUCENT) && type == 2u) return trans_sample(s, p, wi, g, wo, throughput, pdf);
     return false;
 }
 

@@ -467,8 +467,20 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
 }
 
 // ---- K2: scatter ----
-__global__ void __launch_bounds__(256, 3) k_scatter(const DeviceScene s, const RenderConsts pc, const WavefrontState st, float4* __restrict__ accum) {
-    const u32 slot = blockIdx.x * 256u + threadIdx.x;
+#ifndef PTB_SCATTER_THREADS
+#define PTB_SCATTER_THREADS 128
+#endif
+#ifndef PTB_SCATTER_MIN_BLOCKS
+#define PTB_SCATTER_MIN_BLOCKS (1024 / PTB_SCATTER_THREADS)
+#endif
+// FEATURES: compile-time scene-feature mask (PTB_FEAT_*); the launcher picks the smallest instantiation
+// that covers the scene.  The fully general kernel is ~300 KB of SASS and stalls on instruction fetch.
+template <u32 FEATURES>
+__global__ void __launch_bounds__(PTB_SCATTER_THREADS, PTB_SCATTER_MIN_BLOCKS)
+k_scatter(const DeviceScene scene, const RenderConsts pc, const WavefrontState st, float4* __restrict__ accum) {
+    DeviceScene s = scene;
+    s.features = FEATURES;               // a constant from here on: absent features fold away
+    const u32 slot = blockIdx.x * (u32)PTB_SCATTER_THREADS + threadIdx.x;
     u32 x, y;
     bool finished = false;
     if (slot_pixel(pc, slot, x, y)) {
@@ -480,8 +492,9 @@ __global__ void __launch_bounds__(256, 3) k_scatter(const DeviceScene s, const R
         store_ray(st, slot, ray);
         store_path(st, slot, path);
     }
-    const int c = __syncthreads_count(finished ? 1 : 0);
-    if (threadIdx.x == 0 && c) st.tile_paths[blockIdx.x] += (unsigned)c;
+    // finished-path counters per 256-slot tile; no block barrier, so warps retire as they finish
+    const u32 c = (u32)__popc(__ballot_sync(0xFFFFFFFFu, finished));
+    if ((threadIdx.x & 31u) == 0u && c != 0u) atomicAdd(&st.tile_paths[slot >> 8], c);
     if (slot == 0) *st.ray_counter = 0u;       // re-arm the dynamic ray fetch of the next trace launch
 }
 
@@ -628,7 +641,11 @@ cudaError_t launch_hit_attributes(const DeviceScene& s, const RenderConsts& pc, 
 }
 
 cudaError_t launch_scatter(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, cudaStream_t stream) {
-    k_scatter<<<pc.slot_count / 256u, 256, 0, stream>>>(s, pc, st, accum);
+    const unsigned grid = pc.slot_count / (unsigned)PTB_SCATTER_THREADS;
+    const u32 opaque = PTB_FEAT_DIFFUSE | PTB_FEAT_METAL | PTB_FEAT_TEXTURES | PTB_FEAT_SKY_TEXTURE;
+    if ((s.features & ~PTB_FEAT_DIFFUSE) == 0u) k_scatter<PTB_FEAT_DIFFUSE><<<grid, PTB_SCATTER_THREADS, 0, stream>>>(s, pc, st, accum);
+    else if ((s.features & ~opaque) == 0u) k_scatter<opaque><<<grid, PTB_SCATTER_THREADS, 0, stream>>>(s, pc, st, accum);
+    else k_scatter<PTB_FEAT_ALL><<<grid, PTB_SCATTER_THREADS, 0, stream>>>(s, pc, st, accum);
     return cudaGetLastError();
 }
 

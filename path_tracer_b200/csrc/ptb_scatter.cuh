@@ -107,12 +107,12 @@ PTB_HD void generate_new_path(const DeviceScene& s, const RenderConsts& pc, Rng&
 
 // basic_scatter.glsl:44-64.  A shape whose material defines no medium leaves
 // the reference's struct uninitialised; pinned to vacuum here (same as the oracle).
-PTB_HD Medium resolve_medium(const DeviceScene& s, u32 shape, f4 lambda) {
+PTB_HDN Medium resolve_medium(const DeviceScene& s, u32 shape, f4 lambda) {
     Medium m;
     m.ior = mk4(1.0f); m.absorption = mk4(0.0f); m.scattering = mk4(0.0f); m.anisotropy = 0.0f;
     if (shape == PTB_SHAPE_NONE) {
         m.priority = 0xFFFFFFFFu;
-        m.scattering = mk4(s.globals.SceneScatterRate);
+        if (s.features & PTB_FEAT_SCENE_SCATTER) m.scattering = mk4(s.globals.SceneScatterRate);
     } else {
         material_load_medium(s, PTB_LDG(&s.shapes[shape].MaterialIndex), lambda, m);
         m.priority = shape;
@@ -152,10 +152,12 @@ PTB_HD bool scatter_vertex(const DeviceScene& s, const RenderConsts& pc, Rng& g,
 
     const Medium medium = resolve_medium(s, active, lambda);
 
-    path.throughput = path.throughput * exp4((-medium.absorption) * hit.t);
+    // without media, absorption = scattering = 0: exp(-0 * t) = 1 exactly and no scattering event is drawn
+    const bool media = (s.features & (PTB_FEAT_TRANSLUCENT | PTB_FEAT_SCENE_SCATTER)) != 0u;
+    if (media) path.throughput = path.throughput * exp4((-medium.absorption) * hit.t);
 
     float scatter_t = PTB_HIT_TIME_LIMIT;
-    if (medium.scattering.x > 0.0f) scatter_t = (-logf(g.uniform())) / medium.scattering.x;
+    if (media && medium.scattering.x > 0.0f) scatter_t = (-logf(g.uniform())) / medium.scattering.x;
 
     if (hit.t >= scatter_t) {
         if (scatter_t < PTB_HIT_TIME_LIMIT) {

@@ -35,13 +35,25 @@ struct DeviceScene {
     const u32*    wide_planes;       // {shape index, tag} of unbounded shapes (planes), tested linearly
     u32 wide_plane_count;
     u32 wide_tlas_root;              // 0 when the tree exists, 0xFFFFFFFF when the scene has no bounded primitive
+    u32 features;                    // PTB_FEAT_*: what the scene can make scatter do (set at ptb_scene_update)
 };
+
+// Scene features.  k_scatter is instantiated for a few masks: the kernel overwrites `features` of its
+// by-value scene with the compile-time mask, so every test below folds and the code of absent
+// features is never emitted.  The host picks the smallest instantiation that covers the scene.
+#define PTB_FEAT_DIFFUSE       1u     // BasicDiffuse materials
+#define PTB_FEAT_METAL         2u     // BasicMetal
+#define PTB_FEAT_TRANSLUCENT   4u     // BasicTranslucent (dielectric + interior medium)
+#define PTB_FEAT_TEXTURES      8u     // any texture in the scene
+#define PTB_FEAT_SKY_TEXTURE  16u     // skybox texture set
+#define PTB_FEAT_SCENE_SCATTER 32u    // SceneScatterRate > 0
+#define PTB_FEAT_ALL          63u
 
 struct Ray { f3 origin; f3 velocity; float duration; };
 
 // ---- spectrum.glsl.inc ----
 // :10-34  Wyman-Sloan-Shirley multi-lobe fit of the CIE 1931 observer.
-PTB_HD f3 standard_observer(float l) {
+PTB_HDN f3 standard_observer(float l) {
     f3 r;
     {
         float t1 = (l - 442.0f) * (l < 442.0f ? 0.0624f : 0.0374f);
@@ -79,7 +91,7 @@ PTB_HD float parametric_spectrum(f3 beta, float l) {
     float x = (beta.x * l + beta.y) * l + beta.z;
     return 0.5f + x / (2.0f * sqrtf(1.0f + x * x));
 }
-PTB_HD f4 parametric_spectrum(f3 beta, f4 l) {
+PTB_HDN f4 parametric_spectrum(f3 beta, f4 l) {
     return mk4(parametric_spectrum(beta, l.x), parametric_spectrum(beta, l.y), parametric_spectrum(beta, l.z), parametric_spectrum(beta, l.w));
 }
 PTB_HD f4 parametric_spectrum(f4 beta_and_intensity, f4 l) { return beta_and_intensity.w * parametric_spectrum(xyz(beta_and_intensity), l); }
@@ -87,37 +99,40 @@ PTB_HD f4 parametric_spectrum(f4 beta_and_intensity, f4 l) { return beta_and_int
 // ---- textures (scene.glsl.inc:181-205) ----
 // Vulkan REPEAT addressing at LOD 0 on the atlas layer: nearest = floor(u),
 // linear = texels floor(u-0.5), +1 with fp32 weights frac(u-0.5).
-PTB_HD int wrap_repeat(int i, int n) { int m = i % n; return m < 0 ? m + n : m; }
+PTB_HDN int wrap_repeat(int i, int n) { int m = i % n; return m < 0 ? m + n : m; }
 
+// x, y already wrapped into the layer
 PTB_HD f4 fetch_texel(const DeviceScene& s, u32 layer, int x, int y) {
     const float4* base = (const float4*)s.atlas_layers[layer];
-    size_t o = (size_t)wrap_repeat(y, (int)s.atlas_height) * s.atlas_width + (size_t)wrap_repeat(x, (int)s.atlas_width);
+    size_t o = (size_t)y * s.atlas_width + (size_t)x;
     float4 t = PTB_LDG(&base[o]);
     return mk4(t.x, t.y, t.z, t.w);
 }
 
-PTB_HD f4 sample_texture(const DeviceScene& s, u32 index, f2 uv) {
+PTB_HDN f4 sample_texture(const DeviceScene& s, u32 index, f2 uv) {
     const uint4* rec = (const uint4*)&s.textures[index];
     uint4 r0 = PTB_LDG(&rec[0]);     // placement min.xy, max.xy
     uint4 r1 = PTB_LDG(&rec[1]);     // layer, type, flags, pad
     float u = gmix(u2f(r0.x), u2f(r0.z), gfract(uv.x)) * (float)s.atlas_width;
     float v = gmix(u2f(r0.y), u2f(r0.w), gfract(uv.y)) * (float)s.atlas_height;
-    if (r1.z & 1u) return fetch_texel(s, r1.x, (int)floorf(u), (int)floorf(v));
+    const int W = (int)s.atlas_width, H = (int)s.atlas_height;
+    if (r1.z & 1u) return fetch_texel(s, r1.x, wrap_repeat((int)floorf(u), W), wrap_repeat((int)floorf(v), H));
     float ub = u - 0.5f, vb = v - 0.5f;
     float fu = floorf(ub), fv = floorf(vb);
     float a = ub - fu, b = vb - fv;
-    int i0 = (int)fu, j0 = (int)fv;
-    f4 t00 = fetch_texel(s, r1.x, i0, j0), t10 = fetch_texel(s, r1.x, i0 + 1, j0);
-    f4 t01 = fetch_texel(s, r1.x, i0, j0 + 1), t11 = fetch_texel(s, r1.x, i0 + 1, j0 + 1);
+    const int i0 = wrap_repeat((int)fu, W), j0 = wrap_repeat((int)fv, H);
+    const int i1 = i0 + 1 == W ? 0 : i0 + 1, j1 = j0 + 1 == H ? 0 : j0 + 1;
+    f4 t00 = fetch_texel(s, r1.x, i0, j0), t10 = fetch_texel(s, r1.x, i1, j0);
+    f4 t01 = fetch_texel(s, r1.x, i0, j1), t11 = fetch_texel(s, r1.x, i1, j1);
     f4 row0 = t00 * (1.0f - a) + t10 * a;
     f4 row1 = t01 * (1.0f - a) + t11 * a;
     return row0 * (1.0f - b) + row1 * b;
 }
 
 // scene.glsl.inc:209-229 — equirectangular sky; z-up world.
-PTB_HD f4 skybox_radiance(const DeviceScene& s, f3 dir, f4 lambda) {
+PTB_HDN f4 skybox_radiance(const DeviceScene& s, f3 dir, f4 lambda) {
     f4 spectrum;
-    if (s.globals.SkyboxTextureIndex == 0xFFFFFFFFu) {
+    if (!(s.features & PTB_FEAT_SKY_TEXTURE) || s.globals.SkyboxTextureIndex == 0xFFFFFFFFu) {
         spectrum = mk4(0, 0, 100, 1);
     } else {
         float phi = atan2f(dir.y, dir.x);
@@ -134,24 +149,24 @@ PTB_HD f3 material_f3(const DeviceScene& s, u32 slot, u32 attr) {
     return mk3(material_f32(s, slot, attr), material_f32(s, slot, attr + 1), material_f32(s, slot, attr + 2));
 }
 // reflectance = sigmoid-poly(beta) [* sigmoid-poly(texel.xyz)]
-PTB_HD f4 material_reflectance(const DeviceScene& s, u32 slot, u32 attr, f4 lambda, f2 uv) {
+PTB_HDN f4 material_reflectance(const DeviceScene& s, u32 slot, u32 attr, f4 lambda, f2 uv) {
     f4 value = parametric_spectrum(material_f3(s, slot, attr), lambda);
     u32 tex = material_u32(s, slot, attr + 3);
-    if (tex != 0xFFFFFFFFu) value = value * parametric_spectrum(xyz(sample_texture(s, tex, uv)), lambda);
+    if ((s.features & PTB_FEAT_TEXTURES) && tex != 0xFFFFFFFFu) value = value * parametric_spectrum(xyz(sample_texture(s, tex, uv)), lambda);
     return value;
 }
 // scalar [* texel.r]
-PTB_HD float material_value(const DeviceScene& s, u32 slot, u32 attr, f2 uv) {
+PTB_HDN float material_value(const DeviceScene& s, u32 slot, u32 attr, f2 uv) {
     float value = material_f32(s, slot, attr);
     u32 tex = material_u32(s, slot, attr + 1);
-    if (tex != 0xFFFFFFFFu) value *= sample_texture(s, tex, uv).x;
+    if ((s.features & PTB_FEAT_TEXTURES) && tex != 0xFFFFFFFFu) value *= sample_texture(s, tex, uv).x;
     return value;
 }
 
 // ---- cameras (scene.glsl.inc:613-655) ----
 // Pinhole and thin lens both draw two randoms for the aperture disk even at
 // radius 0; the 360 camera draws none.  Output is in world space.
-PTB_HD Ray generate_camera_ray(const DeviceScene& s, u32 camera_index, f2 nsp, Rng& g) {
+PTB_HDN Ray generate_camera_ray(const DeviceScene& s, u32 camera_index, f2 nsp, Rng& g) {
     const ptb_packed_camera* cam = &s.cameras[camera_index];
     const uint4 head = PTB_LDG((const uint4*)cam);            // model, focal, aperture, sensor distance
     const float2 sensor = PTB_LDG((const float2*)&cam->SensorSize[0]);

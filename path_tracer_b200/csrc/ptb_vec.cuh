@@ -18,9 +18,19 @@
 #if defined(__CUDACC__)
 #define PTB_HD __host__ __device__ __forceinline__
 #define PTB_D __device__ __forceinline__
+// Large helpers with many call sites.  Fully inlined, k_scatter is ~300 KB of SASS and stalls on
+// instruction fetch (profiles/r01_v3b_ncu_summary.txt, no_instruction); making them real functions
+// (-DPTB_NOINLINE_HELPERS) was measured and is worse (ABI spills: scatter 0.30 -> 0.43 ms,
+// profiles/r01_v3_ab_builds.txt), so the code size is cut by scene-feature specialisation instead.
+#if defined(PTB_NOINLINE_HELPERS)
+#define PTB_HDN static __host__ __device__ __noinline__
+#else
+#define PTB_HDN PTB_HD
+#endif
 #else
 #define PTB_HD inline
 #define PTB_D inline
+#define PTB_HDN inline
 #endif
 
 #if defined(__CUDA_ARCH__)

@@ -60,6 +60,7 @@ void* emu_create(const ptb_scene_view* v, u32 w, u32 h) {
     e->ds.wide_nodes = (const uint4*)e->wb.nodes.data(); e->ds.wide_tris = (const float4*)e->wb.prims.data();
     e->ds.wide_planes = e->wb.planes.data(); e->ds.wide_plane_count = (u32)(e->wb.planes.size() / 2);
     e->ds.wide_tlas_root = e->wb.node_count ? 0u : 0xFFFFFFFFu;
+    e->ds.features = PTB_FEAT_ALL;
     memset(&e->pc, 0, sizeof e->pc);
     e->pc.width = w; e->pc.height = h; e->pc.tiles_x = (w + 15) / 16; e->pc.slot_count = w * h;
     e->pc.render_flags = 3;
