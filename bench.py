@@ -30,8 +30,28 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-WIDTH, HEIGHT, GRID = 1920, 1080, 708
-WORKLOAD = "C2: procedural 1,002,528-triangle terrain + ground plane, diffuse, pinhole, 1920x1080"
+# BASELINE.json configs.  C2 is the configuration the metric is quoted on and
+# the default; the others are parity-test cases that can also be timed with --workload.
+#   key: (description, scene name, scene params, width, height, tone map, path length limit, CPU tile stride)
+WORKLOADS = {
+    "C1": ("C1: Cornell box of planes/spheres/cubes, diffuse+mirror+glass, pinhole, 640x480", "cornell", (), 640, 480, "aces", 0, 1),
+    "C2": ("C2: procedural 1,002,528-triangle terrain + ground plane, diffuse, pinhole, 1920x1080", "terrain", (708,), 1920, 1080, "aces", 0, 4),
+    "C3": ("C3: textured 76,800-triangle room + 3 refractive spheres, thin lens, HDR sky texture, Hable, 1920x1080", "room", (1, 4096), 1920, 1080, "hable", 0, 4),
+    "C4": ("C4: 9,994,240-triangle sphere field, mixed materials, 360 camera, ACES, 8-bounce, 4096x2048", "spherefield", (488, 5, 2), 4096, 2048, "aces", 8, 16),
+    "C5": ("C5: 9,994,240-triangle sphere field, mixed materials, pinhole, 3840x2160", "spherefield", (488, 5, 0), 3840, 2160, "aces", 0, 16),
+}
+WORKLOAD, SCENE_NAME, SCENE_PARAMS, WIDTH, HEIGHT, TONE, PATH_LIMIT, CPU_STRIDE = WORKLOADS["C2"]
+GRID = 708
+
+
+def select_workload(args):
+    global WORKLOAD, SCENE_NAME, SCENE_PARAMS, WIDTH, HEIGHT, TONE, PATH_LIMIT, CPU_STRIDE
+    WORKLOAD, SCENE_NAME, SCENE_PARAMS, WIDTH, HEIGHT, TONE, PATH_LIMIT, CPU_STRIDE = WORKLOADS[args.workload]
+    if args.workload == "C2" and args.grid != GRID:
+        SCENE_PARAMS = (args.grid,)
+        WORKLOAD += " (grid %d)" % args.grid
+    if args.ref_tile_stride <= 0:
+        args.ref_tile_stride = CPU_STRIDE
 
 
 def load_peaks():
@@ -88,7 +108,7 @@ class ClockSampler:
 def oracle_sample(scene, frames, tile_stride, threads):
     """The oracle on every `tile_stride`-th 16x16 tile of the full-size film: restart + `frames` frames."""
     from oracle import binding as O
-    r = O.Renderer(scene.view, WIDTH, HEIGHT, tie=O.TIE_FAITHFUL, threads=threads, tile_stride=tile_stride)
+    r = O.Renderer(scene.view, WIDTH, HEIGHT, tie=O.TIE_FAITHFUL, threads=threads, tile_stride=tile_stride, path_length_limit=PATH_LIMIT)
     r.set_frame_index(0)
     r.reset()
     r.run(2)                                  # warm-up: restart rounds
@@ -115,11 +135,11 @@ def run_reference(args, rank, world):
         return
     from path_tracer_b200 import scene as S
     S.ensure_spectrum_table()
-    sc = S.Scene.make("terrain", GRID)
+    sc = S.Scene.make(SCENE_NAME, *SCENE_PARAMS)
     from oracle import binding as O
     threads = os.cpu_count() or 1
     stride = args.ref_tile_stride
-    r = O.Renderer(sc.view, WIDTH, HEIGHT, tie=O.TIE_FAITHFUL, threads=threads, tile_stride=stride)
+    r = O.Renderer(sc.view, WIDTH, HEIGHT, tie=O.TIE_FAITHFUL, threads=threads, tile_stride=stride, path_length_limit=PATH_LIMIT)
     r.set_frame_index(0)
     r.reset()
     r.run(2)
@@ -133,7 +153,7 @@ def run_reference(args, rank, world):
     s1 = r.stats()
     rays, paths = s1["rays"] - s0["rays"], s1["paths"] - s0["paths"]
     mrays = rays / dt / 1e6
-    sample = "every %d-th 16x16 tile of the 1920x1080 film (%d rays/frame), %d frames/step" % (stride, rays // max(1, args.steps * args.ref_frames), args.ref_frames)
+    sample = "every %d-th 16x16 tile of the %dx%d film (%d rays/frame), %d frames/step" % (stride, WIDTH, HEIGHT, rays // max(1, args.steps * args.ref_frames), args.ref_frames)
     print(json.dumps({
         "impl": "reference", "metric": "Mrays/s (ray segments traced, whole job)", "value": mrays, "unit": "Mrays/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
@@ -157,11 +177,14 @@ def main():
     ap.add_argument("--traversal", default="wide", choices=["wide", "bvh2"])
     ap.add_argument("--trace-variant", type=int, default=-1, help="PTB_TRACE_VARIANT_* (default: the library's)")
     ap.add_argument("--grid", type=int, default=GRID)
+    ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS), help="BASELINE.json config (default C2, the one the metric is quoted on)")
     ap.add_argument("--ref-frames", type=int, default=8, help="frames per step of the CPU reference arm")
-    ap.add_argument("--ref-tile-stride", type=int, default=4, help="CPU arms process every n-th 16x16 tile (bounded sample)")
+    ap.add_argument("--ref-tile-stride", type=int, default=0, help="CPU arms process every n-th 16x16 tile (bounded sample)")
     ap.add_argument("--cpu-frames", type=int, default=96, help="frames of the cpu_baseline sample (about 10-30 s of CPU work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--spp-target", type=int, default=0, help="also measure the seconds from reset until every pixel holds this many samples")
     args = ap.parse_args()
+    select_workload(args)
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -182,7 +205,7 @@ def main():
     rank, world = D.init_process_group()
 
     S.ensure_spectrum_table()
-    scene = S.Scene.make("terrain", args.grid)
+    scene = S.Scene.make(SCENE_NAME, *SCENE_PARAMS)
     ctx = I.Context(local_rank)
     dscene = I.DeviceScene(ctx, scene)
     wide = dscene.wide_info()
@@ -193,6 +216,7 @@ def main():
     r.Integrator = I.INTEGRATOR_MEGAKERNEL if args.integrator == "megakernel" else I.INTEGRATOR_WAVEFRONT
     r.Traversal = I.TRAVERSAL_WIDE if args.traversal == "wide" else I.TRAVERSAL_BVH2_REFERENCE
     r.TieMode = I.TIE_CANONICAL
+    r.PathLengthLimit = PATH_LIMIT
     if args.trace_variant >= 0:
         r.TraceVariant = args.trace_variant
     F = args.frames
@@ -248,7 +272,7 @@ def main():
     for _ in range(args.steps):
         dscene.update(scene, 1 | 32)              # SCENE_DIRTY_GLOBALS | SCENE_DIRTY_CAMERAS (synchronises, like the reference)
         r.run_frames(F)
-        lin_unused, srgb = film.resolve(1.0, I.TONE_ACES, 1.0, want_linear=False)
+        lin_unused, srgb = film.resolve(1.0, I.TONE_HABLE if TONE == "hable" else I.TONE_ACES, 1.0, want_linear=False)
         s3 = r.stats()
     e2e_s = time.perf_counter() - t0
     e2e_s = D.max_over_ranks(e2e_s, device)
@@ -258,6 +282,22 @@ def main():
     # ---- per-kernel device time (events around every launch) for the roofline of the trace kernel ----
     kt = r.profile_frames(F)
     trace_ms = (kt["trace_ms"] / max(1, kt["trace_launches"])) if kt["trace_launches"] else (kt["mega_ms"] / max(1, kt["mega_launches"]))
+
+    # ---- optional: wall time from reset until min-over-pixels alpha >= target ----
+    spp = None
+    if args.spp_target > 0 and world == 1:
+        r.reset()
+        r.sync()
+        t0 = time.perf_counter()
+        frames_done = 0
+        while True:
+            r.run_frames(64)
+            r.sync()
+            frames_done += 64
+            if float(film_t[..., 3].min()) >= args.spp_target or frames_done > 64 * 4096:
+                break
+        spp = {"target": args.spp_target, "seconds": time.perf_counter() - t0, "frames": frames_done,
+               "min_alpha": float(film_t[..., 3].min()), "mean_alpha": float(film_t[..., 3].mean())}
 
     D.shutdown()
     if rank != 0:
@@ -273,12 +313,12 @@ def main():
         seg_bytes, trace_bytes = bytes_per_segment(c)
         cpu = {"value": c["rays"] / c["seconds"] / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
                "sample": "every %d-th 16x16 tile of the same 1920x1080 film, %d frames, %d rays in %.1f s"
-                         % (args.ref_tile_stride, args.cpu_frames, c["rays"], c["seconds"]),
+                         .replace("1920x1080", "%dx%d" % (WIDTH, HEIGHT)) % (args.ref_tile_stride, args.cpu_frames, c["rays"], c["seconds"]),
                "mpaths_per_s": c["paths"] / c["seconds"] / 1e6,
                "per_ray": {"node_fetches": c["node_fetches"] / c["rays"], "face_tests": c["face_tests"] / c["rays"],
                            "shape_visits": c["shape_visits"] / c["rays"], "mesh_hit_fraction": c["mesh_hits"] / c["rays"]}}
     bytes_source = "oracle traversal counters of this run's CPU sample"
-    if trace_bytes is None:
+    if trace_bytes is None and args.workload == "C2" and args.grid == GRID:
         # no CPU sample in this run (N>1 or --no-cpu-baseline): the per-ray figure the oracle counted for this
         # workload in the committed full run (profiles/r01_v1_bench.json: 82.5 nodes, 7.05 faces, 1.92 shapes per ray)
         seg_bytes, trace_bytes = 3522.405, 3314.405
@@ -304,6 +344,7 @@ def main():
         "mpaths_per_s": paths_all / (ms_max * 1e-3) / 1e6,
         "grays_per_s_per_gpu": value / world / 1e3,
         "seconds_to_1024_paths_per_pixel_1080p": 1024.0 * WIDTH * HEIGHT / (paths_all / world / (ms_max * 1e-3)) if paths_all else None,
+        "time_to_spp": spp,
         "gpu_launches": int(launches),
         "kernel_ms": {"trace": kt["trace_ms"] / max(1, kt["trace_launches"]), "scatter": kt["scatter_ms"] / max(1, kt["scatter_launches"]),
                       "mega": kt["mega_ms"] / max(1, kt["mega_launches"])},

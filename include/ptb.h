@@ -113,6 +113,11 @@ typedef struct { float Brightness; uint32_t ToneMappingMode; float ToneMappingWh
 #define PTB_TRACE_VARIANT_DEFAULT 10u
 #define PTB_TRACE_VARIANT_MAX     15u
 
+/* Scatter-step structure of the wavefront integrator. */
+#define PTB_SCATTER_AUTO   0u  /* queues when the scene mixes material types or has media, else direct */
+#define PTB_SCATTER_DIRECT 1u  /* one kernel over all slots in slot order */
+#define PTB_SCATTER_QUEUES 2u  /* per-round material queues {miss, diffuse, metal, other} + one specialised kernel each */
+
 /* Tie rule for equal hit times. */
 #define PTB_TIE_FAITHFUL  0u  /* reference rules; needs PTB_TRAVERSAL_BVH2_REFERENCE */
 #define PTB_TIE_CANONICAL 1u  /* lowest (t, ShapeIndex, PrimitiveIndex) */
@@ -129,6 +134,8 @@ typedef struct {
     uint32_t Traversal;                  /* PTB_TRAVERSAL_*  */
     uint32_t TieMode;                    /* PTB_TIE_*        */
     uint32_t TraceVariant;               /* PTB_TRACE_VARIANT_*: kernel shape of the wide-BVH trace step */
+    uint32_t ScatterMode;                /* PTB_SCATTER_* */
+    uint32_t Reserved[3];                /* must be 0 */
 } ptb_render_params;
 
 typedef struct {

@@ -82,8 +82,28 @@ struct ptb_renderer {
     RenderConsts pc;
     WavefrontState st;
     void* state_block;
+    unsigned* queue;              // material queues of the scatter step (allocated on first use)
     uint64_t rays_traced, kernel_launches;
 };
+
+// PTB_SCATTER_AUTO: material queues pay when a warp would otherwise meet several materials' code.
+static bool use_queues(const ptb_renderer* r) {
+    if (r->params.ScatterMode == PTB_SCATTER_QUEUES) return true;
+    if (r->params.ScatterMode == PTB_SCATTER_DIRECT) return false;
+    const uint32_t f = r->scene->ds.features;
+    const uint32_t types = f & (PTB_FEAT_DIFFUSE | PTB_FEAT_METAL | PTB_FEAT_TRANSLUCENT);
+    return (types & (types - 1u)) != 0u || (f & (PTB_FEAT_TRANSLUCENT | PTB_FEAT_SCENE_SCATTER)) != 0u;
+}
+static int scatter_step(ptb_renderer* r, const RenderConsts& pc, cudaStream_t st) {
+    if (!use_queues(r)) { CU(launch_scatter(r->scene->ds, pc, r->st, r->film->accum, st)); r->kernel_launches += 1; return PTB_OK; }
+    if (!r->queue) {
+        cudaError_t e = cudaMalloc((void**)&r->queue, scatter_queue_bytes(pc.slot_count));
+        if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc(material queues)");
+    }
+    CU(launch_scatter_queues(r->scene->ds, pc, r->st, r->film->accum, r->queue, st));
+    r->kernel_launches += scatter_queue_launches(r->scene->ds);
+    return PTB_OK;
+}
 
 extern "C" {
 
@@ -308,7 +328,7 @@ int ptb_renderer_create(ptb_context* ctx, ptb_scene* scene, ptb_film* film, ptb_
     r->params.Traversal = PTB_TRAVERSAL_WIDE;
     r->params.TieMode = PTB_TIE_CANONICAL;
     r->params.TraceVariant = PTB_TRACE_VARIANT_DEFAULT;
-    r->frame_index = 0; r->rays_traced = 0; r->kernel_launches = 0;
+    r->frame_index = 0; r->rays_traced = 0; r->kernel_launches = 0; r->queue = nullptr;
     RenderConsts& pc = r->pc;
     std::memset(&pc, 0, sizeof pc);
     pc.width = film->width; pc.height = film->height;
@@ -338,11 +358,12 @@ void ptb_renderer_destroy(ptb_renderer* r) {
     cudaSetDevice(r->ctx->device);
     cudaStreamSynchronize(r->ctx->stream);
     cudaFree(r->state_block);
+    cudaFree(r->queue);
     delete r;
 }
 int ptb_renderer_set_params(ptb_renderer* r, const ptb_render_params* p) {
     if (!r || !p) return fail(PTB_E_INVALID, "ptb_renderer_set_params: NULL argument");
-    if (p->Integrator > PTB_INTEGRATOR_MEGAKERNEL || p->Traversal > PTB_TRAVERSAL_WIDE || p->TieMode > PTB_TIE_CANONICAL || p->TraceVariant > PTB_TRACE_VARIANT_MAX)
+    if (p->Integrator > PTB_INTEGRATOR_MEGAKERNEL || p->Traversal > PTB_TRAVERSAL_WIDE || p->TieMode > PTB_TIE_CANONICAL || p->TraceVariant > PTB_TRACE_VARIANT_MAX || p->ScatterMode > PTB_SCATTER_QUEUES)
         return fail(PTB_E_INVALID, "ptb_renderer_set_params: unknown enum value");
     if (p->Traversal == PTB_TRAVERSAL_WIDE && p->TieMode != PTB_TIE_CANONICAL)
         return fail(PTB_E_INVALID, "ptb_renderer_set_params: the wide traversal is order-free and needs PTB_TIE_CANONICAL");
@@ -389,10 +410,11 @@ static int run_rounds(ptb_renderer* r, uint32_t rounds, uint32_t seed_stride) {
         RenderConsts pc = r->pc;
         for (uint32_t k = 0; k < rounds; k++) {
             CU(launch_trace(ds, pc, r->st, r->params.Traversal, r->params.TieMode, r->params.TraceVariant, st));
-            CU(launch_scatter(ds, pc, r->st, r->film->accum, st));
+            r->kernel_launches += 1;
+            int rc = scatter_step(r, pc, st);
+            if (rc) return rc;
             pc.random_seed += seed_stride;
         }
-        r->kernel_launches += 2ull * rounds;
     }
     r->rays_traced += live * rounds;
     return PTB_OK;
@@ -445,7 +467,8 @@ int ptb_renderer_profile_frames(ptb_renderer* r, uint32_t frames, ptb_kernel_tim
         } else {
             CU(launch_trace(ds, pc, r->st, r->params.Traversal, r->params.TieMode, r->params.TraceVariant, st));
             CU(cudaEventRecord(e[1], st));
-            CU(launch_scatter(ds, pc, r->st, r->film->accum, st));
+            int rc2 = scatter_step(r, pc, st);
+            if (rc2) return rc2;
             CU(cudaEventRecord(e[2], st));
         }
         pc.random_seed += 1;
@@ -465,7 +488,7 @@ int ptb_renderer_profile_frames(ptb_renderer* r, uint32_t frames, ptb_kernel_tim
     for (auto& e : ev) cudaEventDestroy(e);
     r->frame_index += frames;
     r->rays_traced += (uint64_t)r->film->width * r->film->height * frames;
-    r->kernel_launches += (uint64_t)frames * (mega ? 1u : 2u);
+    r->kernel_launches += (uint64_t)frames * 1u;      // trace or megakernel; scatter_step counts its own
     return PTB_OK;
 }
 

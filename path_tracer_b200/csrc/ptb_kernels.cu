@@ -473,8 +473,26 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
 #ifndef PTB_SCATTER_MIN_BLOCKS
 #define PTB_SCATTER_MIN_BLOCKS (1024 / PTB_SCATTER_THREADS)
 #endif
-// FEATURES: compile-time scene-feature mask (PTB_FEAT_*); the launcher picks the smallest instantiation
-// that covers the scene.  The fully general kernel is ~300 KB of SASS and stalls on instruction fetch.
+// FEATURES: compile-time scene-feature mask (PTB_FEAT_*).  The fully general kernel is ~300 KB of
+// SASS; with mixed materials its divergent warps thrash the instruction cache (ncu: 45 no_instruction
+// stall cycles per issue on C3, profiles/r01_c3_scatter_generic.txt).  Two remedies, both here:
+//   * k_scatter<F>       one thread per slot in slot order; the launcher picks the smallest F covering
+//                        the scene (a diffuse-only scene runs a 5k-instruction kernel);
+//   * material queues    k_classify sorts the slots of a round into {miss, diffuse, metal, other} lists
+//                        and k_scatter_list<F> runs each list with the kernel specialised for it, so
+//                        a warp only meets one material's code (the wavefront queues of the north star).
+__device__ __forceinline__ bool scatter_slot(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st,
+                                             float4* __restrict__ accum, u32 slot, u32 x, u32 y) {
+    PathState path = load_path(st, slot);
+    Ray ray = load_ray(st, slot);
+    const PackedHit p = load_packed_hit(s, st, slot);
+    const SurfaceHit hit = unpack_hit(p, ray);
+    const bool finished = scatter_invocation(s, pc, x, y, path, ray, hit, accum);
+    store_ray(st, slot, ray);
+    store_path(st, slot, path);
+    return finished;
+}
+
 template <u32 FEATURES>
 __global__ void __launch_bounds__(PTB_SCATTER_THREADS, PTB_SCATTER_MIN_BLOCKS)
 k_scatter(const DeviceScene scene, const RenderConsts pc, const WavefrontState st, float4* __restrict__ accum) {
@@ -483,19 +501,75 @@ k_scatter(const DeviceScene scene, const RenderConsts pc, const WavefrontState s
     const u32 slot = blockIdx.x * (u32)PTB_SCATTER_THREADS + threadIdx.x;
     u32 x, y;
     bool finished = false;
-    if (slot_pixel(pc, slot, x, y)) {
-        PathState path = load_path(st, slot);
-        Ray ray = load_ray(st, slot);
-        const PackedHit p = load_packed_hit(s, st, slot);
-        const SurfaceHit hit = unpack_hit(p, ray);
-        finished = scatter_invocation(s, pc, x, y, path, ray, hit, accum);
-        store_ray(st, slot, ray);
-        store_path(st, slot, path);
-    }
+    if (slot_pixel(pc, slot, x, y)) finished = scatter_slot(s, pc, st, accum, slot, x, y);
     // finished-path counters per 256-slot tile; no block barrier, so warps retire as they finish
     const u32 c = (u32)__popc(__ballot_sync(0xFFFFFFFFu, finished));
     if ((threadIdx.x & 31u) == 0u && c != 0u) atomicAdd(&st.tile_paths[slot >> 8], c);
     if (slot == 0) *st.ray_counter = 0u;       // re-arm the dynamic ray fetch of the next trace launch
+}
+
+// ---- material queues ----
+// Class of a slot for this round: what its scatter invocation can execute.
+//   0 miss, 1 diffuse hit, 2 metal hit (all three: no enclosing medium), 3 everything else.
+#define PTB_CLASSES 4
+__global__ void __launch_bounds__(256) k_classify(const DeviceScene s, const RenderConsts pc, const WavefrontState st,
+                                                   u32* __restrict__ lists, u32* __restrict__ counts) {
+    __shared__ u32 warp_count[8][PTB_CLASSES];
+    __shared__ u32 base[PTB_CLASSES];
+    const u32 slot = blockIdx.x * 256u + threadIdx.x;
+    const u32 lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    u32 x, y, cls = PTB_CLASSES;
+    if (slot_pixel(pc, slot, x, y)) {
+        const u32 sm = st.hit0[slot].y;
+        const uint4 p0 = st.path0[slot];
+        const bool media = (p0.z & p0.w) != 0xFFFFFFFFu || (s.features & PTB_FEAT_SCENE_SCATTER) != 0u;
+        if (media) cls = 3u;
+        else if (sm == 0xFFFFFFFFu) cls = 0u;
+        else {
+            const u32 type = __ldg(&s.material_data[32u * (sm & 0xFFFFu)]);
+            cls = type == 0u ? 1u : type == 1u ? 2u : 3u;
+        }
+    }
+    u32 rank = 0;
+#pragma unroll
+    for (u32 c = 0; c < PTB_CLASSES; c++) {
+        const u32 b = __ballot_sync(0xFFFFFFFFu, cls == c);
+        if (cls == c) rank = (u32)__popc(b & ((1u << lane) - 1u));
+        if (lane == 0) warp_count[warp][c] = (u32)__popc(b);
+    }
+    __syncthreads();
+    if (threadIdx.x < PTB_CLASSES) {
+        u32 total = 0;
+        for (u32 w = 0; w < 8; w++) { const u32 n = warp_count[w][threadIdx.x]; warp_count[w][threadIdx.x] = total; total += n; }
+        base[threadIdx.x] = total ? atomicAdd(&counts[threadIdx.x], total) : 0u;
+    }
+    __syncthreads();
+    if (cls < PTB_CLASSES) lists[(size_t)cls * pc.slot_count + base[cls] + warp_count[warp][cls] + rank] = slot;
+    if (slot == 0) *st.ray_counter = 0u;       // re-arm the dynamic ray fetch of the next trace launch
+}
+
+template <u32 FEATURES>
+__global__ void __launch_bounds__(PTB_SCATTER_THREADS, PTB_SCATTER_MIN_BLOCKS)
+k_scatter_list(const DeviceScene scene, const RenderConsts pc, const WavefrontState st, float4* __restrict__ accum,
+               const u32* __restrict__ list, const u32* __restrict__ count) {
+    DeviceScene s = scene;
+    s.features = FEATURES;
+    const u32 n = *count;
+    const u32 stride = gridDim.x * (u32)PTB_SCATTER_THREADS;
+    for (u32 i = blockIdx.x * (u32)PTB_SCATTER_THREADS + threadIdx.x; (i & ~31u) < n; i += stride) {      // warp-uniform trip count
+        bool finished = false;
+        u32 slot = 0xFFFFFFFFu;
+        if (i < n) {
+            slot = list[i];
+            u32 x, y;
+            slot_pixel(pc, slot, x, y);
+            finished = scatter_slot(s, pc, st, accum, slot, x, y);
+        }
+        // finished-path counters: lanes of a warp mostly share a tile (lists keep slot order within a block)
+        const u32 tile = finished ? slot >> 8 : 0xFFFFFFFFu;
+        const u32 peers = __match_any_sync(0xFFFFFFFFu, tile);
+        if (finished && (threadIdx.x & 31u) == (u32)__ffs((int)peers) - 1u) atomicAdd(&st.tile_paths[tile], (u32)__popc(peers));
+    }
 }
 
 // ---- megakernel: rounds x {trace, scatter}, state in registers ----
@@ -647,6 +721,43 @@ cudaError_t launch_scatter(const DeviceScene& s, const RenderConsts& pc, const W
     else if ((s.features & ~opaque) == 0u) k_scatter<opaque><<<grid, PTB_SCATTER_THREADS, 0, stream>>>(s, pc, st, accum);
     else k_scatter<PTB_FEAT_ALL><<<grid, PTB_SCATTER_THREADS, 0, stream>>>(s, pc, st, accum);
     return cudaGetLastError();
+}
+
+// Material queues: classify, then one specialised kernel per class.  `queue` = PTB_CLASSES lists of slot_count
+// entries followed by PTB_CLASSES counters.
+size_t scatter_queue_bytes(unsigned slot_count) { return ((size_t)PTB_CLASSES * slot_count + PTB_CLASSES) * sizeof(u32); }
+
+template <u32 F>
+static void launch_list(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, const u32* list, const u32* count,
+                        cudaStream_t stream) {
+    static unsigned grid = 0;
+    if (!grid) {
+        int dev = 0, sms = 148, per_sm = 1;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_scatter_list<F>, PTB_SCATTER_THREADS, 0);
+        grid = (unsigned)(sms * (per_sm < 1 ? 1 : per_sm));
+    }
+    k_scatter_list<F><<<grid, PTB_SCATTER_THREADS, 0, stream>>>(s, pc, st, accum, list, count);
+}
+
+cudaError_t launch_scatter_queues(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, unsigned* queue,
+                                  cudaStream_t stream) {
+    u32* lists = queue;
+    u32* counts = queue + (size_t)PTB_CLASSES * pc.slot_count;
+    cudaError_t e = cudaMemsetAsync(counts, 0, PTB_CLASSES * sizeof(u32), stream);
+    if (e != cudaSuccess) return e;
+    k_classify<<<pc.slot_count / 256u, 256, 0, stream>>>(s, pc, st, lists, counts);
+    const size_t S = pc.slot_count;
+    launch_list<PTB_FEAT_SKY_TEXTURE>(s, pc, st, accum, lists + 0 * S, counts + 0, stream);
+    if (s.features & PTB_FEAT_DIFFUSE) launch_list<PTB_FEAT_DIFFUSE | PTB_FEAT_TEXTURES>(s, pc, st, accum, lists + 1 * S, counts + 1, stream);
+    if (s.features & PTB_FEAT_METAL) launch_list<PTB_FEAT_METAL | PTB_FEAT_TEXTURES>(s, pc, st, accum, lists + 2 * S, counts + 2, stream);
+    if (s.features & (PTB_FEAT_TRANSLUCENT | PTB_FEAT_SCENE_SCATTER)) launch_list<PTB_FEAT_ALL>(s, pc, st, accum, lists + 3 * S, counts + 3, stream);
+    return cudaGetLastError();
+}
+unsigned scatter_queue_launches(const DeviceScene& s) {
+    return 2u + ((s.features & PTB_FEAT_DIFFUSE) ? 1u : 0u) + ((s.features & PTB_FEAT_METAL) ? 1u : 0u)
+              + ((s.features & (PTB_FEAT_TRANSLUCENT | PTB_FEAT_SCENE_SCATTER)) ? 1u : 0u);
 }
 
 cudaError_t launch_megakernel(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum,

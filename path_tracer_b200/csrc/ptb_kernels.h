@@ -36,6 +36,11 @@ cudaError_t launch_trace(const DeviceScene& s, const RenderConsts& pc, const Wav
 // Debug/test: closest-hit attributes of the stored hits as {packed normal, packed tangent, u, v} per slot.
 cudaError_t launch_hit_attributes(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, uint4* out, cudaStream_t stream);
 cudaError_t launch_scatter(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, cudaStream_t stream);
+// Scatter through per-material queues (classify + one specialised kernel per class); `queue` holds scatter_queue_bytes().
+size_t scatter_queue_bytes(unsigned slot_count);
+unsigned scatter_queue_launches(const DeviceScene& s);
+cudaError_t launch_scatter_queues(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, unsigned* queue,
+                                  cudaStream_t stream);
 // `rounds` x {trace, scatter} with the path state in registers; seed = pc.random_seed + k * seed_stride for round k.
 cudaError_t launch_megakernel(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum,
                               unsigned traversal, unsigned tie, unsigned rounds, unsigned seed_stride, cudaStream_t stream);

@@ -21,7 +21,7 @@ from . import _build
 from .types import (KernelTimes, RenderParams, ResolveParams, SceneView, Stats, WideInfo, HIT_DTYPE, RAY_DTYPE,
                     RENDER_FLAG_ACCUMULATE, RENDER_FLAG_SAMPLE_JITTER, INTEGRATOR_WAVEFRONT, INTEGRATOR_MEGAKERNEL,
                     TRAVERSAL_BVH2_REFERENCE, TRAVERSAL_WIDE, TIE_FAITHFUL, TIE_CANONICAL, SCENE_DIRTY_ALL,
-                    TRACE_VARIANT_SIMPLE, TRACE_VARIANT_DEFAULT, TRACE_VARIANT_MAX,
+                    TRACE_VARIANT_SIMPLE, TRACE_VARIANT_DEFAULT, TRACE_VARIANT_MAX, SCATTER_AUTO, SCATTER_DIRECT, SCATTER_QUEUES,
                     TONE_CLAMP, TONE_REINHARD, TONE_HABLE, TONE_ACES)
 
 # every symbol include/ptb.h declares (checked by tests/test_abi.py)
@@ -233,12 +233,13 @@ class BasicRenderer:
         self.Traversal = TRAVERSAL_WIDE
         self.TieMode = TIE_CANONICAL
         self.TraceVariant = TRACE_VARIANT_DEFAULT
+        self.ScatterMode = SCATTER_AUTO
         self.h = C.c_void_p()
         _check(lib().ptb_renderer_create(ctx.h, scene.h, sample_buffer.h, C.byref(self.h)))
 
     def _push(self):
         p = RenderParams(self.CameraIndex, self.RenderFlags, self.PathLengthLimit, self.PathTerminationProbability,
-                         self.Integrator, self.Traversal, self.TieMode, self.TraceVariant)
+                         self.Integrator, self.Traversal, self.TieMode, self.TraceVariant, self.ScatterMode)
         _check(lib().ptb_renderer_set_params(self.h, C.byref(p)))
 
     def set_frame_index(self, f):

@@ -33,6 +33,7 @@ class RenderParams(C.Structure):
         ("CameraIndex", u32), ("RenderFlags", u32), ("PathLengthLimit", u32),
         ("PathTerminationProbability", C.c_float),
         ("Integrator", u32), ("Traversal", u32), ("TieMode", u32), ("TraceVariant", u32),
+        ("ScatterMode", u32), ("Reserved", u32 * 3),
     ]
 
 
@@ -83,4 +84,5 @@ INTEGRATOR_WAVEFRONT, INTEGRATOR_MEGAKERNEL = 0, 1
 TRAVERSAL_BVH2_REFERENCE, TRAVERSAL_WIDE = 0, 1
 TIE_FAITHFUL, TIE_CANONICAL = 0, 1
 TRACE_VARIANT_SIMPLE, TRACE_VARIANT_DEFAULT, TRACE_VARIANT_MAX = 0, 10, 15
+SCATTER_AUTO, SCATTER_DIRECT, SCATTER_QUEUES = 0, 1, 2
 SCENE_DIRTY_ALL = 0xFFFFFFFF

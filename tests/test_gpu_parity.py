@@ -238,6 +238,29 @@ def test_trace_kernel_variants_are_equivalent(I, gpu, dev, oracle, scenes):
         r.reset()
 
 
+def test_scatter_material_queues_equal_direct(I, gpu, dev, scenes):
+    """Scatter through per-round material queues (classify + one specialised kernel per class) against the
+    single general kernel in slot order: same per-slot arithmetic, so film, state and counters are identical."""
+    for name, params in (("cornell", ()), ("spherefield", (12, 2, 2)), ("room", (1, 512)), ("terrain", (64,))):
+        outs = []
+        for mode in (I.SCATTER_DIRECT, I.SCATTER_QUEUES, I.SCATTER_AUTO):
+            film = I.SampleBuffer(gpu, 144, 80)
+            r = I.BasicRenderer(gpu, dev(name, *params), film)
+            r.ScatterMode = mode
+            r.set_frame_index(5)
+            r.reset()
+            r.run(2)
+            r.run_frames(9)
+            outs.append((film.download(), r.state("PackedVelocity"), r.state("Throughput2"), r.state("ActiveShapeIndex01"), r.stats()))
+        for o in outs[1:]:
+            assert np.array_equal(o[0], outs[0][0]), name
+            assert np.array_equal(o[1], outs[0][1]) and np.array_equal(bits(o[2]), bits(outs[0][2])) and np.array_equal(o[3], outs[0][3])
+            assert o[4]["paths_finished"] == outs[0][4]["paths_finished"] and o[4]["rays_traced"] == outs[0][4]["rays_traced"]
+    r.ScatterMode = 7
+    with pytest.raises(I.PtbError):
+        r.reset()
+
+
 @pytest.mark.parametrize("name,params", [("cornell", ()), ("terrain", (64,))])
 def test_converged_image_within_one_percent(I, gpu, dev, oracle, scenes, name, params):
     """Wide BVH + megakernel on the GPU against the reference-order oracle at equal sample counts."""
