@@ -176,6 +176,7 @@ def main():
     ap.add_argument("--integrator", default="wavefront", choices=["wavefront", "megakernel"])
     ap.add_argument("--traversal", default="wide", choices=["wide", "bvh2"])
     ap.add_argument("--trace-variant", type=int, default=-1, help="PTB_TRACE_VARIANT_* (default: the library's)")
+    ap.add_argument("--scatter-mode", default="auto", choices=["auto", "direct", "queues"])
     ap.add_argument("--grid", type=int, default=GRID)
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS), help="BASELINE.json config (default C2, the one the metric is quoted on)")
     ap.add_argument("--ref-frames", type=int, default=8, help="frames per step of the CPU reference arm")
@@ -217,6 +218,7 @@ def main():
     r.Traversal = I.TRAVERSAL_WIDE if args.traversal == "wide" else I.TRAVERSAL_BVH2_REFERENCE
     r.TieMode = I.TIE_CANONICAL
     r.PathLengthLimit = PATH_LIMIT
+    r.ScatterMode = {"auto": I.SCATTER_AUTO, "direct": I.SCATTER_DIRECT, "queues": I.SCATTER_QUEUES}[args.scatter_mode]
     if args.trace_variant >= 0:
         r.TraceVariant = args.trace_variant
     F = args.frames
@@ -327,18 +329,31 @@ def main():
     if trace_bytes is not None:
         live = WIDTH * HEIGHT
         achieved = live * trace_bytes / (trace_ms * 1e-3) / 1e9
+        traffic, issue = None, None
+        try:        # ncu figures of the committed capture of this command (per launch of the trace kernel)
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                t = json.load(f).get(args.workload)
+            if t and args.integrator == "wavefront" and args.traversal == "wide" and args.trace_variant < 0:
+                traffic = t["dram_bytes_per_launch"]
+                issue = {"warp_instructions_per_launch": t["warp_instructions_per_launch"], "lanes_per_instruction": t["lanes_per_instruction"],
+                         "frac_of_issue_peak": t["warp_instructions_per_launch"] / (trace_ms * 1e-3 * 148 * 4 * sm_max * 1e6),
+                         "peak": "148 SMs x 4 schedulers x %.0f MHz" % sm_max, "source": t["source"]}
+        except Exception:
+            pass
         roofline = {"bound": "hbm", "kernel": "k_trace" if kt["trace_launches"] else "k_mega", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                    "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                    "frac": achieved / hbm_peak, "traffic": traffic, "sm_issue": issue, "peak_source": peak_src,
                     "algorithmic_bytes_per_ray": trace_bytes, "bytes_source": bytes_source, "rays_per_launch": live, "kernel_ms": trace_ms,
                     "segment_bytes_model": seg_bytes, "whole_segment_achieved_gbs": value * 1e6 * seg_bytes / 1e9,
                     "whole_segment_frac": value * 1e6 * seg_bytes / 1e9 / hbm_peak,
-                    "note": "geometry (~60 MB wide BVH + prims) is L2-resident: the kernel is SM-issue/latency bound, see profiles/"}
+                    "note": "achieved uses the SURVEY 8(d) per-ray bytes of the REFERENCE layout (BVH2 walk), so it can exceed the HBM peak: the BVH8 "
+                            "moves about a third of those bytes and most of them hit in L2 (traffic = ncu dram bytes per launch); "
+                            "the kernel is bound by SM issue (sm_issue), see profiles/"}
     out = {
         "metric": "Mrays/s (ray segments traced, whole job)", "value": value, "unit": "Mrays/s",
         "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_max / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "frames_per_step": F, "rays_per_step_per_gpu": WIDTH * HEIGHT * F,
-                   "integrator": args.integrator, "traversal": args.traversal, "trace_variant": r.TraceVariant, "parallelism": "sample-split x%d" % world,
+                   "integrator": args.integrator, "traversal": args.traversal, "trace_variant": r.TraceVariant, "scatter_mode": args.scatter_mode, "parallelism": "sample-split x%d" % world,
                    "l2": "per-round working set (232 MB wavefront state + ~170 MB scene) exceeds the 126 MB L2; no explicit flush",
                    "wide_bvh": {k: wide[k] for k in ("node_count", "prim_count", "depth", "build_seconds")}},
         "mpaths_per_s": paths_all / (ms_max * 1e-3) / 1e6,

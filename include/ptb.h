@@ -111,7 +111,7 @@ typedef struct { float Brightness; uint32_t ToneMappingMode; float ToneMappingWh
  * see ptb_kernels.cu).  All variants produce identical hit records. */
 #define PTB_TRACE_VARIANT_SIMPLE  0u
 #define PTB_TRACE_VARIANT_DEFAULT 10u
-#define PTB_TRACE_VARIANT_MAX     15u
+#define PTB_TRACE_VARIANT_MAX     19u
 
 /* Scatter-step structure of the wavefront integrator. */
 #define PTB_SCATTER_AUTO   0u  /* queues when the scene mixes material types or has media, else direct */

@@ -673,8 +673,9 @@ static unsigned persistent_grid(K kernel) {
 // Parking leaf work on the stack when few lanes have any (vote-driven postponing) was measured in
 // round 1 and did not pay on B200; it was removed.  Sweep: profiles/r01_v3_variant_sweep.txt.
 #define PTB_PERSISTENT_VARIANTS(X) X(1, 8) X(2, 4) X(3, 16) X(4, 32)
-#define PTB_COOP_VARIANTS(X) X(5, 8, false, 8) X(6, 8, false, 16) X(7, 8, false, 24) X(8, 8, false, 32) X(9, 8, false, 4) \
-                             X(10, 8, true, 8) X(11, 8, true, 16) X(12, 8, true, 32) X(13, 8, true, 4) X(14, 16, false, 16) X(15, 4, false, 16)
+#define PTB_COOP_VARIANTS(X) X(5, 8, false, 8) X(6, 8, false, 16) X(7, 4, true, 8) X(8, 2, true, 8) X(9, 8, false, 4) \
+                             X(10, 8, true, 8) X(11, 8, true, 16) X(12, 8, true, 32) X(13, 8, true, 4) X(14, 4, true, 16) X(15, 12, true, 8) \
+                             X(16, 16, true, 8) X(17, 6, true, 8) X(18, 6, true, 12) X(19, 1, true, 8)
 
 template <class Job>
 static cudaError_t launch_persistent(const Job& job, unsigned variant, cudaStream_t stream) {
