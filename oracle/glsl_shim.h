@@ -11,6 +11,8 @@
 //   mix(x,y,a) = x*(1-a) + y*a          fract(x) = x - floor(x)
 //   sign(x)    = 1, 0, -1               clamp(x,lo,hi) = min(max(x,lo),hi)
 //   normalize(v) = v / sqrt(dot(v,v))   (pinned; GLSL allows inversesqrt)
+//   vector / scalar = vector * (1 / scalar) with a correctly rounded reciprocal (pinned; one division instead of
+//   three or four — GLSL only asks 2.5 ULP of a division, so both readings are admissible; the CUDA kernels do the same)
 //   min/max: pinned to C fminf/fmaxf (NaN-dropping), reference quirk Q19.
 #pragma once
 #include <cmath>
@@ -51,7 +53,7 @@ inline vec3 operator*(vec3 a, vec3 b) { return {a.x * b.x, a.y * b.y, a.z * b.z}
 inline vec3 operator*(vec3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
 inline vec3 operator*(float s, vec3 a) { return {s * a.x, s * a.y, s * a.z}; }
 inline vec3 operator/(vec3 a, vec3 b) { return {a.x / b.x, a.y / b.y, a.z / b.z}; }
-inline vec3 operator/(vec3 a, float s) { return {a.x / s, a.y / s, a.z / s}; }
+inline vec3 operator/(vec3 a, float s) { float r = 1.0f / s; return {a.x * r, a.y * r, a.z * r}; }   // see header: vector / scalar
 inline vec3& operator+=(vec3& a, vec3 b) { a = a + b; return a; }
 inline float dot(vec3 a, vec3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
 // GLSL cross(): (x1*y2 - y1*x2, ...) per spec.
@@ -72,7 +74,7 @@ inline vec4 operator*(vec4 a, vec4 b) { return {a.x * b.x, a.y * b.y, a.z * b.z,
 inline vec4 operator*(vec4 a, float s) { return {a.x * s, a.y * s, a.z * s, a.w * s}; }
 inline vec4 operator*(float s, vec4 a) { return {s * a.x, s * a.y, s * a.z, s * a.w}; }
 inline vec4 operator/(vec4 a, vec4 b) { return {a.x / b.x, a.y / b.y, a.z / b.z, a.w / b.w}; }
-inline vec4 operator/(vec4 a, float s) { return {a.x / s, a.y / s, a.z / s, a.w / s}; }
+inline vec4 operator/(vec4 a, float s) { float r = 1.0f / s; return {a.x * r, a.y * r, a.z * r, a.w * r}; }
 inline vec4 operator/(float s, vec4 a) { return {s / a.x, s / a.y, s / a.z, s / a.w}; }
 inline vec4 operator+(vec4 a, float s) { return {a.x + s, a.y + s, a.z + s, a.w + s}; }
 inline vec4 operator+(float s, vec4 a) { return {s + a.x, s + a.y, s + a.z, s + a.w}; }

@@ -70,7 +70,8 @@ PTB_HD f3 operator*(f3 a, f3 b) { return mk3(a.x * b.x, a.y * b.y, a.z * b.z); }
 PTB_HD f3 operator*(f3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
 PTB_HD f3 operator*(float s, f3 a) { return mk3(s * a.x, s * a.y, s * a.z); }
 PTB_HD f3 operator/(f3 a, f3 b) { return mk3(a.x / b.x, a.y / b.y, a.z / b.z); }
-PTB_HD f3 operator/(f3 a, float s) { return mk3(a.x / s, a.y / s, a.z / s); }
+// vector / scalar = vector * (1 / scalar), correctly rounded reciprocal: the same pinned reading as oracle/glsl_shim.h
+PTB_HD f3 operator/(f3 a, float s) { const float r = 1.0f / s; return mk3(a.x * r, a.y * r, a.z * r); }
 PTB_HD float dot(f3 a, f3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
 PTB_HD f3 cross(f3 a, f3 b) { return mk3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y); }
 PTB_HD f3 normalize(f3 a) { return a / sqrtf(dot(a, a)); }
@@ -86,7 +87,7 @@ PTB_HD f4 operator*(f4 a, f4 b) { return mk4(a.x * b.x, a.y * b.y, a.z * b.z, a.
 PTB_HD f4 operator*(f4 a, float s) { return mk4(a.x * s, a.y * s, a.z * s, a.w * s); }
 PTB_HD f4 operator*(float s, f4 a) { return mk4(s * a.x, s * a.y, s * a.z, s * a.w); }
 PTB_HD f4 operator/(f4 a, f4 b) { return mk4(a.x / b.x, a.y / b.y, a.z / b.z, a.w / b.w); }
-PTB_HD f4 operator/(f4 a, float s) { return mk4(a.x / s, a.y / s, a.z / s, a.w / s); }
+PTB_HD f4 operator/(f4 a, float s) { const float r = 1.0f / s; return mk4(a.x * r, a.y * r, a.z * r, a.w * r); }
 PTB_HD f4 operator+(float s, f4 a) { return mk4(s + a.x, s + a.y, s + a.z, s + a.w); }
 PTB_HD f4 operator+(f4 a, float s) { return mk4(a.x + s, a.y + s, a.z + s, a.w + s); }
 PTB_HD f4 operator-(float s, f4 a) { return mk4(s - a.x, s - a.y, s - a.z, s - a.w); }

@@ -199,10 +199,18 @@ class SampleBuffer:
         a = np.ascontiguousarray(accum, dtype=np.float32)
         _check(lib().ptb_film_upload_accum(self.h, a.ctypes.data, a.size))
 
-    def resolve(self, Brightness=1.0, ToneMappingMode=TONE_CLAMP, ToneMappingWhiteLevel=1.0, want_linear=True, want_srgb8=True):
+    def resolve(self, Brightness=1.0, ToneMappingMode=TONE_CLAMP, ToneMappingWhiteLevel=1.0, want_linear=True, want_srgb8=True,
+                out_srgb8=None, out_linear=None):
+        """RenderSampleBuffer (integrator.cpp:110-159) into host arrays.  `out_*`: caller-owned destinations
+        (e.g. pinned memory, so the device-to-host copy is one DMA); allocated here when omitted."""
         p = ResolveParams(Brightness, ToneMappingMode, ToneMappingWhiteLevel)
-        lin = np.empty((self.Height, self.Width, 3), dtype=np.float32) if want_linear else None
-        srgb = np.empty((self.Height, self.Width, 4), dtype=np.uint8) if want_srgb8 else None
+        lin = srgb = None
+        if want_linear:
+            lin = out_linear if out_linear is not None else np.empty((self.Height, self.Width, 3), dtype=np.float32)
+            assert lin.dtype == np.float32 and lin.size == self.Height * self.Width * 3 and lin.flags["C_CONTIGUOUS"]
+        if want_srgb8:
+            srgb = out_srgb8 if out_srgb8 is not None else np.empty((self.Height, self.Width, 4), dtype=np.uint8)
+            assert srgb.dtype == np.uint8 and srgb.size == self.Height * self.Width * 4 and srgb.flags["C_CONTIGUOUS"]
         _check(lib().ptb_film_resolve(self.h, C.byref(p), srgb.ctypes.data if want_srgb8 else None, lin.ctypes.data if want_linear else None))
         return lin, srgb
 
