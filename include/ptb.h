@@ -154,6 +154,24 @@ typedef struct {
     float    bx, by, bz;
 } ptb_hit;
 
+/* Preview visualiser: the push constants of src/application/preview_render.glsl:48-60. */
+#define PTB_PREVIEW_MODE_BASE_COLOR        0u
+#define PTB_PREVIEW_MODE_BASE_COLOR_SHADED 1u
+#define PTB_PREVIEW_MODE_NORMAL            2u
+#define PTB_PREVIEW_MODE_MATERIAL_INDEX    3u
+#define PTB_PREVIEW_MODE_PRIMITIVE_INDEX   4u
+#define PTB_PREVIEW_MODE_MESH_COMPLEXITY   5u   /* BVH2 traversal: mesh-node iterations; wide: leaf primitives tested */
+#define PTB_PREVIEW_MODE_SCENE_COMPLEXITY  6u   /* BVH2 traversal: shape-node iterations; wide: BVH8 nodes visited   */
+typedef struct {
+    ptb_packed_transform CameraTransform;
+    uint32_t RenderMode;
+    float    Brightness;
+    uint32_t SelectedShapeIndex;
+    uint32_t RenderSizeX, RenderSizeY;
+    uint32_t MouseX, MouseY;
+    uint32_t Traversal;                  /* PTB_TRAVERSAL_* (ties are canonical) */
+} ptb_preview_params;
+
 typedef struct ptb_context  ptb_context;
 typedef struct ptb_scene    ptb_scene;
 typedef struct ptb_film     ptb_film;
@@ -237,6 +255,12 @@ uint32_t ptb_renderer_slot_count(ptb_renderer* r);
 int  ptb_raycast(ptb_scene* scene, const ptb_ray* host_rays, size_t n, uint32_t traversal, uint32_t tie_mode, ptb_hit* host_hits);
 /* Same with both buffers already in device memory; enqueued on the context stream, no synchronisation. */
 int  ptb_raycast_device(ptb_scene* scene, const ptb_ray* device_rays, size_t n, uint32_t traversal, uint32_t tie_mode, ptb_hit* device_hits);
+
+/* ---- preview visualiser (src/application/preview_render.glsl:96-178; application.cpp preview pass) ----
+ * One camera ray per pixel, closest hit, colour by RenderMode; no graphics API: the image is written to
+ * host_rgba (RenderSizeX*RenderSizeY*4 floats, alpha 1).  host_shapes (optional) receives Hit.ShapeIndex
+ * per pixel, *hit_shape the shape under (MouseX, MouseY) — the reference's pick query (QuerySSBO). */
+int  ptb_preview_render(ptb_scene* scene, const ptb_preview_params* params, float* host_rgba, uint32_t* host_shapes, uint32_t* hit_shape);
 
 #ifdef __cplusplus
 }

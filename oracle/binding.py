@@ -30,6 +30,13 @@ class RenderParams(C.Structure):
                 ("tile_stride", C.c_uint32)]
 
 
+class PreviewParams(C.Structure):
+    """preview_render.glsl:48-60 push constants (+ tie rule); same bytes as ptb_preview_params up to `Tie`."""
+    _fields_ = [("To", C.c_float * 16), ("From", C.c_float * 16), ("RenderMode", C.c_uint32), ("Brightness", C.c_float),
+                ("SelectedShapeIndex", C.c_uint32), ("RenderSizeX", C.c_uint32), ("RenderSizeY", C.c_uint32),
+                ("MouseX", C.c_uint32), ("MouseY", C.c_uint32), ("Tie", C.c_uint32)]
+
+
 class OStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("rays", "paths", "node_fetches", "face_tests", "shape_visits", "mesh_hits")]
 
@@ -88,6 +95,7 @@ def lib():
         L.orc_kat_camera_ray.argtypes = [vp, f32, f32, u32, vp]
         L.orc_kat_srgb8.restype = C.c_uint8
         L.orc_kat_srgb8.argtypes = [f32]
+        L.orc_preview.argtypes = [vp, C.POINTER(PreviewParams), vp, vp, vp, C.c_int]
         _lib = L
     return _lib
 
@@ -118,6 +126,20 @@ def raycast_bruteforce(view, rays, threads=0):
     out = np.zeros(len(rays), dtype=HIT_DTYPE)
     lib().orc_raycast_bruteforce(_view_ptr(view), rays.ctypes.data, len(rays), out.ctypes.data, threads or os.cpu_count())
     return out
+
+
+def preview(view, camera_to, camera_from, mode, width, height, brightness=1.0, selected=0xFFFFFFFF, mouse=(0, 0), tie=TIE_CANONICAL, threads=0):
+    """preview_render.glsl on the CPU: (H, W, 4) float image, (H, W) shape indices, shape under the mouse pixel."""
+    p = PreviewParams()
+    p.To[:] = [float(x) for x in camera_to]
+    p.From[:] = [float(x) for x in camera_from]
+    p.RenderMode, p.Brightness, p.SelectedShapeIndex = mode, brightness, selected
+    p.RenderSizeX, p.RenderSizeY, p.MouseX, p.MouseY, p.Tie = width, height, mouse[0], mouse[1], tie
+    img = np.zeros((height, width, 4), dtype=np.float32)
+    shapes = np.zeros((height, width), dtype=np.uint32)
+    pick = C.c_uint32(0xFFFFFFFF)
+    lib().orc_preview(_view_ptr(view), C.byref(p), img.ctypes.data, shapes.ctypes.data, C.addressof(pick), threads or os.cpu_count())
+    return img, shapes, pick.value
 
 
 STATE_ARRAYS = {

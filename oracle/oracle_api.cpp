@@ -10,6 +10,7 @@
 #include <vector>
 #include <algorithm>
 #include "sh_integrator.h"
+#include "sh_preview.h"
 
 using namespace orc;
 
@@ -271,5 +272,20 @@ void orc_kat_camera_ray(const packed_camera* cam, float nx, float ny, uint seed,
     out->dx = R.Velocity.x; out->dy = R.Velocity.y; out->dz = R.Velocity.z; out->duration = R.Duration;
 }
 uint8_t orc_kat_srgb8(float l) { return LinearToSRGB8(l); }
+
+// Preview visualiser (preview_render.glsl): RGBA float image (alpha 1), shape index per pixel, pick result.
+void orc_preview(const scene_view* S, const preview_params* P, float* rgba, uint* shapes, uint* hit_shape, int threads) {
+    const uint64_t n = (uint64_t)P->RenderSizeX * P->RenderSizeY;
+    parallel_for(n, 1024, threads, [&](uint64_t b, uint64_t e, int) {
+        for (uint64_t i = b; i < e; i++) {
+            const uint x = (uint)(i % P->RenderSizeX), y = (uint)(i / P->RenderSizeX);
+            uint shape;
+            vec3 c = PreviewPixel(*S, *P, x, y, &shape);
+            rgba[4 * i] = c.x; rgba[4 * i + 1] = c.y; rgba[4 * i + 2] = c.z; rgba[4 * i + 3] = 1.0f;
+            if (shapes) shapes[i] = shape;
+            if (hit_shape && x == P->MouseX && y == P->MouseY) *hit_shape = shape;
+        }
+    });
+}
 
 }  // extern "C"

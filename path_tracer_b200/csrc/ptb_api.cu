@@ -12,6 +12,7 @@
 
 #include "ptb.h"
 #include "ptb_kernels.h"
+#include "ptb_preview.cuh"
 #include "ptb_wide_build.h"
 
 using namespace ptb;
@@ -38,6 +39,12 @@ struct DevBuf {
             n = count;
         }
         if (count) return cudaMemcpyAsync(p, host, count * sizeof(T), cudaMemcpyHostToDevice, st);
+        return cudaSuccess;
+    }
+    cudaError_t alloc(size_t count) {
+        release();
+        if (count) { cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T)); if (e != cudaSuccess) return e; }
+        n = count;
         return cudaSuccess;
     }
     void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
@@ -595,6 +602,34 @@ int ptb_raycast_device(ptb_scene* s, const ptb_ray* d_rays, size_t n, uint32_t t
     if (traversal == PTB_TRAVERSAL_WIDE && s->ds.shape_count > 0 && s->wide_info.status != PTB_OK) return fail(PTB_E_UNSUPPORTED, "ptb_raycast_device: wide BVH unavailable");
     CU(cudaSetDevice(s->ctx->device));
     CU(launch_raycast(s->ds, d_rays, n, traversal, tie, s->raycast_variant, s->ctx->counter, d_hits, s->ctx->stream));
+    return PTB_OK;
+}
+
+int ptb_preview_render(ptb_scene* s, const ptb_preview_params* p, float* host_rgba, uint32_t* host_shapes, uint32_t* hit_shape) {
+    if (!s || !p || !host_rgba) return fail(PTB_E_INVALID, "ptb_preview_render: NULL argument");
+    if (p->RenderMode > PTB_PREVIEW_MODE_SCENE_COMPLEXITY || p->Traversal > PTB_TRAVERSAL_WIDE) return fail(PTB_E_INVALID, "ptb_preview_render: unknown mode");
+    if (p->Traversal == PTB_TRAVERSAL_WIDE && s->wide_info.status != PTB_OK) return fail(PTB_E_UNSUPPORTED, "ptb_preview_render: wide BVH unavailable");
+    const size_t n = (size_t)p->RenderSizeX * p->RenderSizeY;
+    if (n == 0 || n > 0x7FFFFFFFull) return fail(PTB_E_INVALID, "ptb_preview_render: bad render size");
+    CU(cudaSetDevice(s->ctx->device));
+    cudaStream_t st = s->ctx->stream;
+    PreviewConsts c;
+    std::memcpy(c.to, p->CameraTransform.To, sizeof c.to);
+    c.mode = p->RenderMode; c.brightness = p->Brightness; c.selected_shape = p->SelectedShapeIndex;
+    c.width = p->RenderSizeX; c.height = p->RenderSizeY; c.mouse_x = p->MouseX; c.mouse_y = p->MouseY;
+    DevBuf<float4> rgba;
+    DevBuf<uint32_t> shapes, pick;
+    CU(rgba.alloc(n));
+    CU(shapes.alloc(n));
+    const uint32_t none = 0xFFFFFFFFu;
+    CU(pick.upload(&none, 1, st));
+    cudaError_t e = launch_preview(s->ds, c, p->Traversal, PTB_TIE_CANONICAL, rgba.p, shapes.p, pick.p, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(host_rgba, rgba.p, n * sizeof(float4), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess && host_shapes) e = cudaMemcpyAsync(host_shapes, shapes.p, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess && hit_shape) e = cudaMemcpyAsync(hit_shape, pick.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    rgba.release(); shapes.release(); pick.release();
+    if (e != cudaSuccess) return cuda_fail(e, "ptb_preview_render");
     return PTB_OK;
 }
 

@@ -11,6 +11,7 @@
 #include "ptb_kernels.h"
 #include "ptb_resolve.cuh"
 #include "ptb_wide.cuh"
+#include "ptb_preview.cuh"
 
 namespace ptb {
 
@@ -261,6 +262,8 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_TRACE_MIN_BLOCKS) k_
 //   SPEC    a lane keeps traversing while its primitives wait in the queue (its reach is stale until
 //           the flush: more node steps, full lanes) or stalls until they have been tested;
 //   WAIT_T  a partial flush happens when this many lanes cannot go on without one.
+// Measured and rejected (profiles/r01_v3_ab_builds.txt): prefetch.global.L1 of the next node and of the queued
+// primitives right after a node step (+13 % time: extra address arithmetic, L1 churn); 64 registers / 8 blocks per SM.
 // Rays are fetched from the global counter in chunks of PTB_COOP_CHUNK consecutive slots per warp
 // (32: measured best on B200; 128 costs 8 % to tail imbalance, profiles/r01_v3_ab_builds.txt).
 #define PTB_COOP_QUEUE 64           // groups; >= 31 (left by a flush) + 32 (one per lane and round), power of two
@@ -650,6 +653,20 @@ __global__ void __launch_bounds__(256) k_hit_attributes(const DeviceScene s, con
     out[slot] = make_uint4(p.normal, p.tangent, __float_as_uint(p.u), __float_as_uint(p.v));
 }
 
+// ---- preview visualiser (preview_render.glsl): one thread per pixel, image + shape ids to device buffers ----
+template <int MODE>
+__global__ void __launch_bounds__(128) k_preview(const DeviceScene s, const PreviewConsts p, float4* __restrict__ rgba, u32* __restrict__ shapes,
+                                                  u32* __restrict__ hit_shape) {
+    const u32 i = blockIdx.x * 128u + threadIdx.x;
+    if (i >= p.width * p.height) return;
+    const u32 px = i % p.width, py = i / p.width;
+    u32 shape;
+    const f3 c = preview_pixel<MODE>(s, p, px, py, &shape);
+    rgba[i] = make_float4(c.x, c.y, c.z, 1.0f);
+    if (shapes) shapes[i] = shape;
+    if (px == p.mouse_x && py == p.mouse_y) *hit_shape = shape;      // the pick query (preview_render.glsl:172-173)
+}
+
 // ---- launchers ----
 cudaError_t launch_restart(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, cudaStream_t stream) {
     k_restart<<<pc.slot_count / 256u, 256, 0, stream>>>(s, pc, st, accum);
@@ -768,6 +785,19 @@ cudaError_t launch_megakernel(const DeviceScene& s, const RenderConsts& pc, cons
         case MODE_BVH2_FAITHFUL: k_mega<MODE_BVH2_FAITHFUL><<<grid, 128, 0, stream>>>(s, pc, st, accum, rounds, seed_stride); break;
         case MODE_BVH2_CANONICAL: k_mega<MODE_BVH2_CANONICAL><<<grid, 128, 0, stream>>>(s, pc, st, accum, rounds, seed_stride); break;
         default: k_mega<MODE_WIDE><<<grid, 128, 0, stream>>>(s, pc, st, accum, rounds, seed_stride); break;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_preview(const DeviceScene& s, const PreviewConsts& p, unsigned traversal, unsigned tie, float4* rgba, unsigned* shapes,
+                           unsigned* hit_shape, cudaStream_t stream) {
+    const unsigned n = p.width * p.height;
+    if (n == 0) return cudaSuccess;
+    const unsigned grid = (n + 127u) / 128u;
+    switch (mode_of(traversal, tie)) {
+        case MODE_BVH2_FAITHFUL: k_preview<MODE_BVH2_FAITHFUL><<<grid, 128, 0, stream>>>(s, p, rgba, shapes, hit_shape); break;
+        case MODE_BVH2_CANONICAL: k_preview<MODE_BVH2_CANONICAL><<<grid, 128, 0, stream>>>(s, p, rgba, shapes, hit_shape); break;
+        default: k_preview<MODE_WIDE><<<grid, 128, 0, stream>>>(s, p, rgba, shapes, hit_shape); break;
     }
     return cudaGetLastError();
 }

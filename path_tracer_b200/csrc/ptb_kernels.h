@@ -44,6 +44,10 @@ cudaError_t launch_scatter_queues(const DeviceScene& s, const RenderConsts& pc, 
 // `rounds` x {trace, scatter} with the path state in registers; seed = pc.random_seed + k * seed_stride for round k.
 cudaError_t launch_megakernel(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum,
                               unsigned traversal, unsigned tie, unsigned rounds, unsigned seed_stride, cudaStream_t stream);
+struct PreviewConsts;
+// Preview visualiser: RGBA32F image, optional shape index per pixel, shape under the mouse pixel.
+cudaError_t launch_preview(const DeviceScene& s, const PreviewConsts& p, unsigned traversal, unsigned tie, float4* rgba, unsigned* shapes,
+                           unsigned* hit_shape, cudaStream_t stream);
 cudaError_t launch_resolve(const float4* accum, unsigned width, unsigned height, ptb_resolve_params params,
                            uchar4* out_srgb8, float* out_linear_rgb, cudaStream_t stream);
 // counter: device u32 (zeroed by the launcher) for the persistent variant; may be null for variant 0.

@@ -36,6 +36,10 @@ struct Surface {
     u32 material;
 };
 
+// Traversal counters of the preview visualiser (scene.glsl.inc:117-118): loop iterations over shape
+// nodes / mesh nodes in the reference's BVH2; node steps / primitive tests in the wide BVH.
+struct Complexity { u32 scene, mesh; };
+
 PTB_HD bool lower_id(u32 shape, u32 prim, const HitId& h) { return shape < h.shape || (shape == h.shape && prim < h.prim); }
 
 // common.glsl.inc:153-185.  `canonical` visits boxes whose entry time equals the
@@ -155,11 +159,12 @@ PTB_HD Node2 load_node2(const void* base, u32 index) {
 
 // scene.glsl.inc:336-399 — near child first, far child pushed; mesh children are adjacent.
 template <bool CANONICAL>
-PTB_HD void traverse_mesh_bvh2(const DeviceScene& s, const Ray& r, u32 root, u32 shape, HitId& h) {
+PTB_HD void traverse_mesh_bvh2(const DeviceScene& s, const Ray& r, u32 root, u32 shape, HitId& h, Complexity* cx = nullptr) {
     u32 stack[PTB_BVH2_STACK];
     u32 depth = 0;
     Node2 node = load_node2(s.mesh_nodes, root);
     while (true) {
+        if (cx) cx->mesh++;                                  // scene.glsl.inc:345
         if (node.w1 > 0) {
             for (u32 f = node.w0; f < node.w1; f++) test_face<CANONICAL>(s, r, f, shape, h);
         } else {
@@ -185,16 +190,16 @@ PTB_HD void traverse_mesh_bvh2(const DeviceScene& s, const Ray& r, u32 root, u32
 }
 
 template <bool CANONICAL>
-PTB_HD void intersect_shape_bvh2(const DeviceScene& s, const Ray& world, u32 shape, HitId& h) {
+PTB_HD void intersect_shape_bvh2(const DeviceScene& s, const Ray& world, u32 shape, HitId& h, Complexity* cx = nullptr) {
     const uint4 head = PTB_LDG((const uint4*)&s.shapes[shape]);   // type, material, mesh root, pad
     Ray r = object_ray(s, world, shape);
-    if (head.x == PTB_SHAPE_MESH) traverse_mesh_bvh2<CANONICAL>(s, r, head.z, shape, h);
+    if (head.x == PTB_SHAPE_MESH) traverse_mesh_bvh2<CANONICAL>(s, r, head.z, shape, h, cx);
     else test_analytic<CANONICAL>(r, head.x, shape, h);
 }
 
 // scene.glsl.inc:468-520 — top level over shapes; 16-bit child indices, leaf when 0.
 template <bool CANONICAL>
-PTB_HD HitId closest_hit_bvh2(const DeviceScene& s, const Ray& r) {
+PTB_HD HitId closest_hit_bvh2(const DeviceScene& s, const Ray& r, Complexity* cx = nullptr) {
     HitId h;
     h.t = r.duration; h.shape = PTB_SHAPE_NONE; h.prim = 0xFFFFFFFFu; h.shape_type = 0; h.coords = mk3(0, 0, 0);
     if (s.globals.ShapeCount == 0) return h;
@@ -202,8 +207,9 @@ PTB_HD HitId closest_hit_bvh2(const DeviceScene& s, const Ray& r) {
     u32 depth = 0;
     Node2 na = load_node2(s.shape_nodes, 0);
     while (true) {
+        if (cx) cx->scene++;                                 // scene.glsl.inc:480
         if (na.w0 == 0) {
-            intersect_shape_bvh2<CANONICAL>(s, r, na.w1, h);
+            intersect_shape_bvh2<CANONICAL>(s, r, na.w1, h, cx);
         } else {
             u32 ia = na.w0 & 0xFFFFu, ib = na.w0 >> 16;
             na = load_node2(s.shape_nodes, ia);

@@ -237,7 +237,7 @@ struct LocalStack {
 
 // Canonical closest hit: lexicographically lowest (t, shape, face) among all
 // primitives the reference tests would accept with t <= ray.duration.
-PTB_HD HitId closest_hit_wide(const DeviceScene& s, const Ray& r) {
+PTB_HD HitId closest_hit_wide(const DeviceScene& s, const Ray& r, Complexity* cx = nullptr) {
     HitId h = wide_begin(s, r);
     if (s.wide_tlas_root == 0xFFFFFFFFu) return h;
     const WideCtx c = wide_ctx(r);
@@ -249,6 +249,7 @@ PTB_HD HitId closest_hit_wide(const DeviceScene& s, const Ray& r) {
     while (true) {
         PrimGroup pg;
         wide_node_step(s, c, h.t, ng, pg, stack);
+        if (cx) { cx->scene++; cx->mesh += popcount(pg.bits); }
         while (pg.bits) wide_prim_step(s, r, pg, cur_shape, obj, h);
         if (ng.y <= 0x00FFFFFFu) {
             if (stack.empty()) break;

@@ -18,7 +18,7 @@ import os
 import numpy as np
 
 from . import _build
-from .types import (KernelTimes, RenderParams, ResolveParams, SceneView, Stats, WideInfo, HIT_DTYPE, RAY_DTYPE,
+from .types import (KernelTimes, PreviewParams, PREVIEW_MODES, RenderParams, ResolveParams, SceneView, Stats, WideInfo, HIT_DTYPE, RAY_DTYPE,
                     RENDER_FLAG_ACCUMULATE, RENDER_FLAG_SAMPLE_JITTER, INTEGRATOR_WAVEFRONT, INTEGRATOR_MEGAKERNEL,
                     TRAVERSAL_BVH2_REFERENCE, TRAVERSAL_WIDE, TIE_FAITHFUL, TIE_CANONICAL, SCENE_DIRTY_ALL,
                     TRACE_VARIANT_SIMPLE, TRACE_VARIANT_DEFAULT, TRACE_VARIANT_MAX, SCATTER_AUTO, SCATTER_DIRECT, SCATTER_QUEUES,
@@ -33,7 +33,7 @@ ABI_SYMBOLS = [
     "ptb_film_resolve", "ptb_film_resolve_device",
     "ptb_renderer_create", "ptb_renderer_destroy", "ptb_renderer_set_params", "ptb_renderer_set_frame_index",
     "ptb_renderer_reset", "ptb_renderer_run", "ptb_renderer_run_frames", "ptb_renderer_profile_frames", "ptb_renderer_sync", "ptb_renderer_stats",
-    "ptb_renderer_download_state", "ptb_renderer_slot_count", "ptb_raycast", "ptb_raycast_device",
+    "ptb_renderer_download_state", "ptb_renderer_slot_count", "ptb_raycast", "ptb_raycast_device", "ptb_preview_render",
 ]
 
 STATE_ARRAYS = {
@@ -99,6 +99,7 @@ def lib():
         L.ptb_renderer_slot_count.restype = u32
         L.ptb_raycast.argtypes = [vp, vp, sz, u32, u32, vp]
         L.ptb_raycast_device.argtypes = [vp, vp, sz, u32, u32, vp]
+        L.ptb_preview_render.argtypes = [vp, C.POINTER(PreviewParams), vp, vp, vp]
         _lib = L
     return _lib
 
@@ -161,6 +162,21 @@ class DeviceScene:
         out = np.zeros(len(rays), dtype=HIT_DTYPE)
         _check(lib().ptb_raycast(self.h, rays.ctypes.data, len(rays), traversal, tie, out.ctypes.data))
         return out
+
+    def preview(self, camera_to, camera_from, mode, width, height, brightness=1.0, selected=0xFFFFFFFF, mouse=(0, 0),
+                traversal=TRAVERSAL_WIDE):
+        """The reference's preview visualiser (preview_render.glsl:96-178) as a CUDA kernel: returns the (H, W, 4)
+        float image, the (H, W) shape indices and the shape under the mouse pixel (the pick query)."""
+        p = PreviewParams()
+        p.To[:] = [float(x) for x in camera_to]
+        p.From[:] = [float(x) for x in camera_from]
+        p.RenderMode, p.Brightness, p.SelectedShapeIndex = mode, brightness, selected
+        p.RenderSizeX, p.RenderSizeY, p.MouseX, p.MouseY, p.Traversal = width, height, mouse[0], mouse[1], traversal
+        img = np.empty((height, width, 4), dtype=np.float32)
+        shapes = np.empty((height, width), dtype=np.uint32)
+        pick = C.c_uint32(0xFFFFFFFF)
+        _check(lib().ptb_preview_render(self.h, C.byref(p), img.ctypes.data, shapes.ctypes.data, C.addressof(pick)))
+        return img, shapes, pick.value
 
     def raycast_device(self, d_rays, n, d_hits, traversal=TRAVERSAL_WIDE, tie=TIE_CANONICAL):
         """Same on device-resident buffers (raw pointers); asynchronous on the context stream."""

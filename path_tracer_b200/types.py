@@ -28,6 +28,16 @@ class ResolveParams(C.Structure):
     _fields_ = [("Brightness", C.c_float), ("ToneMappingMode", u32), ("ToneMappingWhiteLevel", C.c_float)]
 
 
+class PreviewParams(C.Structure):
+    """ptb_preview_params = the push constants of preview_render.glsl:48-60 (+ traversal)."""
+    _fields_ = [("To", C.c_float * 16), ("From", C.c_float * 16), ("RenderMode", u32), ("Brightness", C.c_float),
+                ("SelectedShapeIndex", u32), ("RenderSizeX", u32), ("RenderSizeY", u32), ("MouseX", u32), ("MouseY", u32),
+                ("Traversal", u32)]
+
+
+PREVIEW_MODES = ("BASE_COLOR", "BASE_COLOR_SHADED", "NORMAL", "MATERIAL_INDEX", "PRIMITIVE_INDEX", "MESH_COMPLEXITY", "SCENE_COMPLEXITY")
+
+
 class RenderParams(C.Structure):
     _fields_ = [
         ("CameraIndex", u32), ("RenderFlags", u32), ("PathLengthLimit", u32),

@@ -238,6 +238,33 @@ def test_trace_kernel_variants_are_equivalent(I, gpu, dev, oracle, scenes):
         r.reset()
 
 
+def test_preview_visualiser_matches_oracle(I, gpu, dev, oracle, scenes):
+    """preview_render.glsl as a CUDA kernel: all seven render modes and the pick query against the CPU restatement.
+    Colours agree to 2e-5 (expf in the observer); shape ids and the complexity counters of the reference BVH2 are exact."""
+    for name, params, w, h in (("cornell", (), 96, 64), ("room", (1, 512), 80, 48), ("spherefield", (12, 2, 0), 64, 48)):
+        sc = scenes(name, *params)
+        cam = sc.cameras[0]
+        to, fr = cam["To"].ravel(), cam["From"].ravel()
+        d = dev(name, *params)
+        mouse = (w // 2, h // 2 + 3)
+        for mode in range(7):
+            for trav in (I.TRAVERSAL_BVH2_REFERENCE, I.TRAVERSAL_WIDE):
+                if mode >= 5 and trav == I.TRAVERSAL_WIDE:
+                    continue                  # counts nodes of the wide BVH: no reference counterpart (checked below)
+                ref, rshape, rpick = oracle.preview(sc.view, to, fr, mode, w, h, brightness=1.25, selected=2, mouse=mouse, tie=oracle.TIE_CANONICAL)
+                img, shape, pick = d.preview(to, fr, mode, w, h, brightness=1.25, selected=2, mouse=mouse, traversal=trav)
+                same = shape == rshape
+                assert same.mean() > 0.999, (name, mode, trav)           # silhouette pixels may fall either way of an edge tie
+                assert pick == shape[mouse[1], mouse[0]]
+                assert np.abs(img - ref)[same].max() <= 2e-5, (name, mode, trav, float(np.abs(img - ref)[same].max()))
+                assert (img[..., 3] == 1.0).all()
+        img5, _, _ = d.preview(to, fr, 5, w, h, selected=0xFFFFFFFE)
+        img6, _, _ = d.preview(to, fr, 6, w, h, selected=0xFFFFFFFE)
+        assert img6[..., 1].min() >= 1.0 / 256.0 and (img5[..., 0] == 0).all() and np.isfinite(img5).all()      # every ray visits the root
+    with pytest.raises(I.PtbError):
+        d.preview(to, fr, 9, w, h)
+
+
 def test_scatter_material_queues_equal_direct(I, gpu, dev, scenes):
     """Scatter through per-round material queues (classify + one specialised kernel per class) against the
     single general kernel in slot order: same per-slot arithmetic, so film, state and counters are identical."""
