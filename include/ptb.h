@@ -110,7 +110,7 @@ typedef struct { float Brightness; uint32_t ToneMappingMode; float ToneMappingWh
  * with dynamic ray fetch; 5..MAX = the same with cooperative leaf tests (numbered tuning points,
  * see ptb_kernels.cu).  All variants produce identical hit records. */
 #define PTB_TRACE_VARIANT_SIMPLE  0u
-#define PTB_TRACE_VARIANT_DEFAULT 10u
+#define PTB_TRACE_VARIANT_DEFAULT 14u
 #define PTB_TRACE_VARIANT_MAX     19u
 
 /* Scatter-step structure of the wavefront integrator. */

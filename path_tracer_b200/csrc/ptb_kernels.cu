@@ -266,6 +266,9 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_TRACE_MIN_BLOCKS) k_
 // primitives right after a node step (+13 % time: extra address arithmetic, L1 churn); 64 registers / 8 blocks per SM.
 // Rays are fetched from the global counter in chunks of PTB_COOP_CHUNK consecutive slots per warp
 // (32: measured best on B200; 128 costs 8 % to tail imbalance, profiles/r01_v3_ab_builds.txt).
+#ifndef PTB_COOP_POOL
+#define PTB_COOP_POOL 1
+#endif
 #define PTB_COOP_QUEUE 64           // groups; >= 31 (left by a flush) + 32 (one per lane and round), power of two
 #ifndef PTB_COOP_CHUNK
 #define PTB_COOP_CHUNK 32
@@ -280,6 +283,9 @@ struct CoopWarp {
     float ray[6][32];                 // world-space origin, velocity of each lane's ray
     u32 detail[7][32];                // t, shape, face, shape type, coords of the hit `key` names
     uint4 group[PTB_COOP_QUEUE];      // {owner lane << 27 | primitive base, pending bits, valid bits, -}
+#if PTB_COOP_POOL
+    u32 pool[15][32];                 // the next rays, prepared by the whole warp: origin, velocity, key, slot, plane hit
+#endif
     u32 starts[32];                   // flush scratch: queue position (relative to the head) of the group starting at primitive i
 };
 
@@ -375,6 +381,78 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
     { Ray z; z.origin = z.velocity = mk3(0, 0, 0); z.duration = 0; c = wide_ctx(z); }
 
     for (;;) {
+#if PTB_COOP_POOL
+        // ---- refill: whole-warp preparation of the next 32 rays into a shared-memory pool, cheap pick-up by idle lanes ----
+        const u32 idle = __ballot_sync(0xFFFFFFFFu, !active);
+        if (__popc(idle) >= REFILL || idle == 0xFFFFFFFFu) {
+            if (pool_next == pool_end && !drained) {
+                u32 base = 0;
+                if (lane == 0) base = atomicAdd(job.counter(), 32u);
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                if (base + 32u >= total) drained = true;
+                // every lane loads one ray, tests the unbounded shapes (planes) and publishes the prepared record
+                const u32 my = base + lane;
+                Ray ray;
+                ray.origin = ray.velocity = mk3(0, 0, 0); ray.duration = 0;
+                bool valid = my < total && job.load(my, ray);
+                HitId h;
+                h.t = ray.duration; h.shape = PTB_SHAPE_NONE; h.prim = 0xFFFFFFFFu; h.shape_type = 0; h.coords = mk3(0, 0, 0);
+                u32 tag = 0xFFFFFFFFu;
+                if (valid) {
+                    for (u32 i = 0; i < s.wide_plane_count; i++) {
+                        const uint2 pl = PTB_LDG((const uint2*)s.wide_planes + i);
+                        const u32 before = h.shape;
+                        test_analytic<true>(object_ray(s, ray, pl.x), PTB_SHAPE_PLANE, pl.x, h);
+                        if (h.shape != before) tag = pl.y;
+                    }
+                    if (s.wide_tlas_root == 0xFFFFFFFFu) { job.store(my, h); valid = false; }
+                }
+                const u32 vmask = __ballot_sync(0xFFFFFFFFu, valid);
+                __syncwarp();                                   // the previous pool has been consumed by all lanes
+                if (valid) {
+                    const u32 e = (u32)__popc(vmask & lt_mask);
+                    u32 tb = f2u(h.t);
+                    if (tb == 0x80000000u) tb = 0u;
+                    W.pool[0][e] = f2u(ray.origin.x); W.pool[1][e] = f2u(ray.origin.y); W.pool[2][e] = f2u(ray.origin.z);
+                    W.pool[3][e] = f2u(ray.velocity.x); W.pool[4][e] = f2u(ray.velocity.y); W.pool[5][e] = f2u(ray.velocity.z);
+                    W.pool[6][e] = tag; W.pool[7][e] = tb; W.pool[8][e] = my;
+                    W.pool[9][e] = f2u(h.t); W.pool[10][e] = h.shape; W.pool[11][e] = h.shape_type;
+                    W.pool[12][e] = f2u(h.coords.x); W.pool[13][e] = f2u(h.coords.y); W.pool[14][e] = f2u(h.coords.z);
+                }
+                pool_next = 0; pool_end = (u32)__popc(vmask);
+                __syncwarp();
+            }
+            const u32 avail = pool_end - pool_next;
+            const u32 rank = (u32)__popc(idle & lt_mask);
+            if (!active && rank < avail) {
+                const u32 e = pool_next + rank;
+                Ray ray;
+                ray.origin = mk3(u2f(W.pool[0][e]), u2f(W.pool[1][e]), u2f(W.pool[2][e]));
+                ray.velocity = mk3(u2f(W.pool[3][e]), u2f(W.pool[4][e]), u2f(W.pool[5][e]));
+                ray.duration = 0;
+                index = W.pool[8][e];
+                c = wide_ctx(ray);
+                ng = make_uint2(0u, 0x80000000u);
+                stack.sp = 0;
+                last_seq = ghead;
+                active = true;
+                W.ray[0][lane] = ray.origin.x; W.ray[1][lane] = ray.origin.y; W.ray[2][lane] = ray.origin.z;
+                W.ray[3][lane] = ray.velocity.x; W.ray[4][lane] = ray.velocity.y; W.ray[5][lane] = ray.velocity.z;
+                W.key[lane] = ((unsigned long long)W.pool[7][e] << 32) | W.pool[6][e];
+                const u32 hs = W.pool[10][e];
+                W.detail[0][lane] = W.pool[9][e]; W.detail[1][lane] = hs; W.detail[2][lane] = hs == PTB_SHAPE_NONE ? 0xFFFFFFFFu : 0u;
+                W.detail[3][lane] = W.pool[11][e];
+                W.detail[4][lane] = W.pool[12][e]; W.detail[5][lane] = W.pool[13][e]; W.detail[6][lane] = W.pool[14][e];
+            }
+            pool_next += min((u32)__popc(idle), avail);
+            __syncwarp();
+        }
+        if (!__any_sync(0xFFFFFFFFu, active)) {
+            if (drained && pool_next == pool_end) break;
+            continue;
+        }
+
+#else
         // ---- refill ----
         const u32 idle = __ballot_sync(0xFFFFFFFFu, !active);
         if (__popc(idle) >= REFILL || idle == 0xFFFFFFFFu) {
@@ -428,6 +506,7 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
             continue;
         }
 
+#endif
         // ---- node ----
         PrimGroup pg;
         pg.base = pg.bits = pg.valid = 0u;
