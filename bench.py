@@ -177,6 +177,7 @@ def main():
     ap.add_argument("--traversal", default="wide", choices=["wide", "bvh2"])
     ap.add_argument("--trace-variant", type=int, default=-1, help="PTB_TRACE_VARIANT_* (default: the library's)")
     ap.add_argument("--scatter-mode", default="auto", choices=["auto", "direct", "queues"])
+    ap.add_argument("--pipelines", type=int, default=0, choices=[0, 1, 2], help="0 = the library's choice")
     ap.add_argument("--grid", type=int, default=GRID)
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS), help="BASELINE.json config (default C2, the one the metric is quoted on)")
     ap.add_argument("--ref-frames", type=int, default=8, help="frames per step of the CPU reference arm")
@@ -218,6 +219,7 @@ def main():
     r.Traversal = I.TRAVERSAL_WIDE if args.traversal == "wide" else I.TRAVERSAL_BVH2_REFERENCE
     r.TieMode = I.TIE_CANONICAL
     r.PathLengthLimit = PATH_LIMIT
+    r.Pipelines = args.pipelines
     r.ScatterMode = {"auto": I.SCATTER_AUTO, "direct": I.SCATTER_DIRECT, "queues": I.SCATTER_QUEUES}[args.scatter_mode]
     if args.trace_variant >= 0:
         r.TraceVariant = args.trace_variant
@@ -354,7 +356,7 @@ def main():
         "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_max / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "frames_per_step": F, "rays_per_step_per_gpu": WIDTH * HEIGHT * F,
-                   "integrator": args.integrator, "traversal": args.traversal, "trace_variant": r.TraceVariant, "scatter_mode": args.scatter_mode, "parallelism": "sample-split x%d" % world,
+                   "integrator": args.integrator, "traversal": args.traversal, "trace_variant": r.TraceVariant, "scatter_mode": args.scatter_mode, "pipelines": args.pipelines, "parallelism": "sample-split x%d" % world,
                    "l2": "per-round working set (232 MB wavefront state + ~170 MB scene) exceeds the 126 MB L2; no explicit flush",
                    "wide_bvh": {k: wide[k] for k in ("node_count", "prim_count", "depth", "build_seconds")}},
         "mpaths_per_s": paths_all / (ms_max * 1e-3) / 1e6,

@@ -135,7 +135,9 @@ typedef struct {
     uint32_t TieMode;                    /* PTB_TIE_*        */
     uint32_t TraceVariant;               /* PTB_TRACE_VARIANT_*: kernel shape of the wide-BVH trace step */
     uint32_t ScatterMode;                /* PTB_SCATTER_* */
-    uint32_t Reserved[3];                /* must be 0 */
+    uint32_t Pipelines;                  /* 0 = automatic (one), 1 = one stream, 2 = the film's slots as two halves on two
+                                            streams (kernel tails overlap the other half's next kernel; same results) */
+    uint32_t Reserved[2];                /* must be 0 */
 } ptb_render_params;
 
 typedef struct {

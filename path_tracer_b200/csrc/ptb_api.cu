@@ -89,7 +89,9 @@ struct ptb_renderer {
     RenderConsts pc;
     WavefrontState st;
     void* state_block;
-    unsigned* queue;              // material queues of the scatter step (allocated on first use)
+    unsigned* queue[2];           // material queues of the scatter step, one per pipeline (allocated on first use)
+    cudaStream_t aux;             // second pipeline
+    cudaEvent_t ev_fork, ev_join;
     uint64_t rays_traced, kernel_launches;
 };
 
@@ -101,15 +103,23 @@ static bool use_queues(const ptb_renderer* r) {
     const uint32_t types = f & (PTB_FEAT_DIFFUSE | PTB_FEAT_METAL | PTB_FEAT_TRANSLUCENT);
     return (types & (types - 1u)) != 0u || (f & (PTB_FEAT_TRANSLUCENT | PTB_FEAT_SCENE_SCATTER)) != 0u;
 }
-static int scatter_step(ptb_renderer* r, const RenderConsts& pc, cudaStream_t st) {
-    if (!use_queues(r)) { CU(launch_scatter(r->scene->ds, pc, r->st, r->film->accum, st)); r->kernel_launches += 1; return PTB_OK; }
-    if (!r->queue) {
-        cudaError_t e = cudaMalloc((void**)&r->queue, scatter_queue_bytes(pc.slot_count));
+static int scatter_step(ptb_renderer* r, const RenderConsts& pc, const WavefrontState& wst, unsigned pipe, cudaStream_t st) {
+    if (!use_queues(r)) { CU(launch_scatter(r->scene->ds, pc, wst, r->film->accum, st)); r->kernel_launches += 1; return PTB_OK; }
+    if (!r->queue[pipe]) {
+        cudaError_t e = cudaMalloc((void**)&r->queue[pipe], scatter_queue_bytes(r->pc.slot_count));
         if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc(material queues)");
     }
-    CU(launch_scatter_queues(r->scene->ds, pc, r->st, r->film->accum, r->queue, st));
+    CU(launch_scatter_queues(r->scene->ds, pc, wst, r->film->accum, r->queue[pipe], st));
     r->kernel_launches += scatter_queue_launches(r->scene->ds);
     return PTB_OK;
+}
+// Pipelines: the slot range of the film split at a tile boundary; each half has its own ray counter.
+static unsigned pipeline_count(const ptb_renderer* r) {
+    if (r->params.Pipelines == 1u || r->pc.slot_count < 512u) return 1u;
+    // automatic = one: on B200 the two-stream split measured 3.5 % slower on C2/C3 and neutral on C4
+    // (profiles/r01_v6_pipelines.txt): the persistent trace kernel of the other half takes the SMs, so only the
+    // kernel tails overlap, and that does not pay for two half-sized launches per kernel.
+    return r->params.Pipelines == 2u ? 2u : 1u;
 }
 
 extern "C" {
@@ -335,7 +345,8 @@ int ptb_renderer_create(ptb_context* ctx, ptb_scene* scene, ptb_film* film, ptb_
     r->params.Traversal = PTB_TRAVERSAL_WIDE;
     r->params.TieMode = PTB_TIE_CANONICAL;
     r->params.TraceVariant = PTB_TRACE_VARIANT_DEFAULT;
-    r->frame_index = 0; r->rays_traced = 0; r->kernel_launches = 0; r->queue = nullptr;
+    r->frame_index = 0; r->rays_traced = 0; r->kernel_launches = 0; r->queue[0] = r->queue[1] = nullptr;
+    r->aux = nullptr; r->ev_fork = r->ev_join = nullptr;
     RenderConsts& pc = r->pc;
     std::memset(&pc, 0, sizeof pc);
     pc.width = film->width; pc.height = film->height;
@@ -365,12 +376,15 @@ void ptb_renderer_destroy(ptb_renderer* r) {
     cudaSetDevice(r->ctx->device);
     cudaStreamSynchronize(r->ctx->stream);
     cudaFree(r->state_block);
-    cudaFree(r->queue);
+    cudaFree(r->queue[0]); cudaFree(r->queue[1]);
+    if (r->aux) cudaStreamDestroy(r->aux);
+    if (r->ev_fork) cudaEventDestroy(r->ev_fork);
+    if (r->ev_join) cudaEventDestroy(r->ev_join);
     delete r;
 }
 int ptb_renderer_set_params(ptb_renderer* r, const ptb_render_params* p) {
     if (!r || !p) return fail(PTB_E_INVALID, "ptb_renderer_set_params: NULL argument");
-    if (p->Integrator > PTB_INTEGRATOR_MEGAKERNEL || p->Traversal > PTB_TRAVERSAL_WIDE || p->TieMode > PTB_TIE_CANONICAL || p->TraceVariant > PTB_TRACE_VARIANT_MAX || p->ScatterMode > PTB_SCATTER_QUEUES)
+    if (p->Integrator > PTB_INTEGRATOR_MEGAKERNEL || p->Traversal > PTB_TRAVERSAL_WIDE || p->TieMode > PTB_TIE_CANONICAL || p->TraceVariant > PTB_TRACE_VARIANT_MAX || p->ScatterMode > PTB_SCATTER_QUEUES || p->Pipelines > 2u)
         return fail(PTB_E_INVALID, "ptb_renderer_set_params: unknown enum value");
     if (p->Traversal == PTB_TRAVERSAL_WIDE && p->TieMode != PTB_TIE_CANONICAL)
         return fail(PTB_E_INVALID, "ptb_renderer_set_params: the wide traversal is order-free and needs PTB_TIE_CANONICAL");
@@ -414,13 +428,36 @@ static int run_rounds(ptb_renderer* r, uint32_t rounds, uint32_t seed_stride) {
         CU(launch_megakernel(ds, r->pc, r->st, r->film->accum, r->params.Traversal, r->params.TieMode, rounds, seed_stride, st));
         r->kernel_launches += 1;
     } else {
-        RenderConsts pc = r->pc;
+        const unsigned pipes = pipeline_count(r);
+        RenderConsts pc[2] = {r->pc, r->pc};
+        WavefrontState wst[2] = {r->st, r->st};
+        cudaStream_t str[2] = {st, st};
+        if (pipes == 2u) {
+            if (!r->aux) {
+                CU(cudaStreamCreateWithFlags(&r->aux, cudaStreamNonBlocking));
+                CU(cudaEventCreateWithFlags(&r->ev_fork, cudaEventDisableTiming));
+                CU(cudaEventCreateWithFlags(&r->ev_join, cudaEventDisableTiming));
+            }
+            const uint32_t half = (r->pc.slot_count / 512u) * 256u;
+            pc[0].slot_count = half;
+            pc[1].slot_base = half; pc[1].slot_count = r->pc.slot_count - half;
+            wst[1].ray_counter = r->st.ray_counter + 1;
+            str[1] = r->aux;
+            CU(cudaEventRecord(r->ev_fork, st));
+            CU(cudaStreamWaitEvent(r->aux, r->ev_fork, 0));
+        }
         for (uint32_t k = 0; k < rounds; k++) {
-            CU(launch_trace(ds, pc, r->st, r->params.Traversal, r->params.TieMode, r->params.TraceVariant, st));
-            r->kernel_launches += 1;
-            int rc = scatter_step(r, pc, st);
-            if (rc) return rc;
-            pc.random_seed += seed_stride;
+            for (unsigned p = 0; p < pipes; p++) CU(launch_trace(ds, pc[p], wst[p], r->params.Traversal, r->params.TieMode, r->params.TraceVariant, str[p]));
+            r->kernel_launches += pipes;
+            for (unsigned p = 0; p < pipes; p++) {
+                int rc = scatter_step(r, pc[p], wst[p], p, str[p]);
+                if (rc) return rc;
+                pc[p].random_seed += seed_stride;
+            }
+        }
+        if (pipes == 2u) {
+            CU(cudaEventRecord(r->ev_join, r->aux));
+            CU(cudaStreamWaitEvent(st, r->ev_join, 0));
         }
     }
     r->rays_traced += live * rounds;
@@ -474,7 +511,7 @@ int ptb_renderer_profile_frames(ptb_renderer* r, uint32_t frames, ptb_kernel_tim
         } else {
             CU(launch_trace(ds, pc, r->st, r->params.Traversal, r->params.TieMode, r->params.TraceVariant, st));
             CU(cudaEventRecord(e[1], st));
-            int rc2 = scatter_step(r, pc, st);
+            int rc2 = scatter_step(r, pc, r->st, 0u, st);
             if (rc2) return rc2;
             CU(cudaEventRecord(e[2], st));
         }

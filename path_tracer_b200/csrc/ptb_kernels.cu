@@ -35,7 +35,7 @@ __device__ __forceinline__ bool slot_pixel(const RenderConsts& pc, u32 slot, u32
     const u32 tx = tile % pc.tiles_x, ty = tile / pc.tiles_x;
     x = tx * 16u + (l & 15u);
     y = ty * 16u + (l >> 4);
-    return slot < pc.slot_count && x < pc.width && y < pc.height;
+    return x < pc.width && y < pc.height;        // slots beyond the last tile row have y >= height
 }
 
 // ---- state records <-> register structs ----
@@ -107,13 +107,13 @@ __global__ void __launch_bounds__(256) k_restart(const DeviceScene s, const Rend
     store_path(st, slot, path);
     accum[y * pc.width + x] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (threadIdx.x == 0) st.tile_paths[blockIdx.x] = 0u;
-    if (slot == 0) *st.ray_counter = 0u;
+    if (slot < 2) st.ray_counter[slot] = 0u;        // one counter per pipeline
 }
 
 // ---- K1: trace ----
 template <int MODE>
 __global__ void __launch_bounds__(128) k_trace(const DeviceScene s, const RenderConsts pc, const WavefrontState st) {
-    const u32 slot = blockIdx.x * 128u + threadIdx.x;
+    const u32 slot = pc.slot_base + blockIdx.x * 128u + threadIdx.x;
     u32 x, y;
     if (!slot_pixel(pc, slot, x, y)) return;
     const Ray ray = load_ray(st, slot);
@@ -163,8 +163,8 @@ struct WavefrontJob {
     DeviceScene s; RenderConsts pc; WavefrontState st;
     __device__ __forceinline__ u32 total() const { return pc.slot_count; }
     __device__ __forceinline__ unsigned* counter() const { return st.ray_counter; }
-    __device__ __forceinline__ bool load(u32 i, Ray& r) const { u32 x, y; if (!slot_pixel(pc, i, x, y)) return false; r = load_ray(st, i); return true; }
-    __device__ __forceinline__ void store(u32 i, const HitId& h) const { store_hit(s, st, i, h); }
+    __device__ __forceinline__ bool load(u32 i, Ray& r) const { u32 x, y; if (!slot_pixel(pc, pc.slot_base + i, x, y)) return false; r = load_ray(st, pc.slot_base + i); return true; }
+    __device__ __forceinline__ void store(u32 i, const HitId& h) const { store_hit(s, st, pc.slot_base + i, h); }
 };
 // Caller rays (parity harness).
 struct RaycastJob {
@@ -580,14 +580,14 @@ __global__ void __launch_bounds__(PTB_SCATTER_THREADS, PTB_SCATTER_MIN_BLOCKS)
 k_scatter(const DeviceScene scene, const RenderConsts pc, const WavefrontState st, float4* __restrict__ accum) {
     DeviceScene s = scene;
     s.features = FEATURES;               // a constant from here on: absent features fold away
-    const u32 slot = blockIdx.x * (u32)PTB_SCATTER_THREADS + threadIdx.x;
+    const u32 slot = pc.slot_base + blockIdx.x * (u32)PTB_SCATTER_THREADS + threadIdx.x;
     u32 x, y;
     bool finished = false;
     if (slot_pixel(pc, slot, x, y)) finished = scatter_slot(s, pc, st, accum, slot, x, y);
     // finished-path counters per 256-slot tile; no block barrier, so warps retire as they finish
     const u32 c = (u32)__popc(__ballot_sync(0xFFFFFFFFu, finished));
     if ((threadIdx.x & 31u) == 0u && c != 0u) atomicAdd(&st.tile_paths[slot >> 8], c);
-    if (slot == 0) *st.ray_counter = 0u;       // re-arm the dynamic ray fetch of the next trace launch
+    if (slot == pc.slot_base) *st.ray_counter = 0u;       // re-arm the dynamic ray fetch of the next trace launch
 }
 
 // ---- material queues ----
@@ -598,7 +598,7 @@ __global__ void __launch_bounds__(256) k_classify(const DeviceScene s, const Ren
                                                    u32* __restrict__ lists, u32* __restrict__ counts) {
     __shared__ u32 warp_count[8][PTB_CLASSES];
     __shared__ u32 base[PTB_CLASSES];
-    const u32 slot = blockIdx.x * 256u + threadIdx.x;
+    const u32 slot = pc.slot_base + blockIdx.x * 256u + threadIdx.x;
     const u32 lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     u32 x, y, cls = PTB_CLASSES;
     if (slot_pixel(pc, slot, x, y)) {
@@ -627,7 +627,7 @@ __global__ void __launch_bounds__(256) k_classify(const DeviceScene s, const Ren
     }
     __syncthreads();
     if (cls < PTB_CLASSES) lists[(size_t)cls * pc.slot_count + base[cls] + warp_count[warp][cls] + rank] = slot;
-    if (slot == 0) *st.ray_counter = 0u;       // re-arm the dynamic ray fetch of the next trace launch
+    if (slot == pc.slot_base) *st.ray_counter = 0u;       // re-arm the dynamic ray fetch of the next trace launch
 }
 
 template <u32 FEATURES>

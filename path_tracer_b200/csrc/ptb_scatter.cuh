@@ -22,7 +22,9 @@ struct RenderConsts {
     u32 camera_index, render_flags, path_length_limit;
     float termination_probability;
     u32 random_seed;
-    u32 width, height, tiles_x, slot_count;
+    u32 width, height, tiles_x;
+    u32 slot_count;         // slots covered by this launch (multiple of 256)
+    u32 slot_base;          // first slot of this launch: a film may be rendered as several slot ranges (pipelines)
 };
 
 struct PathState {

@@ -258,12 +258,13 @@ class BasicRenderer:
         self.TieMode = TIE_CANONICAL
         self.TraceVariant = TRACE_VARIANT_DEFAULT
         self.ScatterMode = SCATTER_AUTO
+        self.Pipelines = 0
         self.h = C.c_void_p()
         _check(lib().ptb_renderer_create(ctx.h, scene.h, sample_buffer.h, C.byref(self.h)))
 
     def _push(self):
         p = RenderParams(self.CameraIndex, self.RenderFlags, self.PathLengthLimit, self.PathTerminationProbability,
-                         self.Integrator, self.Traversal, self.TieMode, self.TraceVariant, self.ScatterMode)
+                         self.Integrator, self.Traversal, self.TieMode, self.TraceVariant, self.ScatterMode, self.Pipelines)
         _check(lib().ptb_renderer_set_params(self.h, C.byref(p)))
 
     def set_frame_index(self, f):

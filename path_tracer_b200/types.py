@@ -43,7 +43,7 @@ class RenderParams(C.Structure):
         ("CameraIndex", u32), ("RenderFlags", u32), ("PathLengthLimit", u32),
         ("PathTerminationProbability", C.c_float),
         ("Integrator", u32), ("Traversal", u32), ("TieMode", u32), ("TraceVariant", u32),
-        ("ScatterMode", u32), ("Reserved", u32 * 3),
+        ("ScatterMode", u32), ("Pipelines", u32), ("Reserved", u32 * 2),
     ]
 
 

@@ -267,13 +267,15 @@ def test_preview_visualiser_matches_oracle(I, gpu, dev, oracle, scenes):
 
 def test_scatter_material_queues_equal_direct(I, gpu, dev, scenes):
     """Scatter through per-round material queues (classify + one specialised kernel per class) against the
-    single general kernel in slot order: same per-slot arithmetic, so film, state and counters are identical."""
+    single general kernel in slot order, and one stream against two half-film pipelines: same per-slot
+    arithmetic, so film, state and counters are identical."""
     for name, params in (("cornell", ()), ("spherefield", (12, 2, 2)), ("room", (1, 512)), ("terrain", (64,))):
         outs = []
-        for mode in (I.SCATTER_DIRECT, I.SCATTER_QUEUES, I.SCATTER_AUTO):
+        for mode, pipes in ((I.SCATTER_DIRECT, 1), (I.SCATTER_QUEUES, 1), (I.SCATTER_AUTO, 0), (I.SCATTER_DIRECT, 2), (I.SCATTER_QUEUES, 2)):
             film = I.SampleBuffer(gpu, 144, 80)
             r = I.BasicRenderer(gpu, dev(name, *params), film)
             r.ScatterMode = mode
+            r.Pipelines = pipes              # 2: the film's slots as two halves on two streams
             r.set_frame_index(5)
             r.reset()
             r.run(2)
