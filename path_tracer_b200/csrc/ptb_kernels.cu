@@ -269,6 +269,12 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_TRACE_MIN_BLOCKS) k_
 #ifndef PTB_COOP_POOL
 #define PTB_COOP_POOL 1
 #endif
+#ifndef PTB_COOP_FLUSH_GROUPS
+#define PTB_COOP_FLUSH_GROUPS 0        // > 0: flush on a group count instead of the exact primitive count
+#endif
+#ifndef PTB_COOP_FLUSH_PRIMS
+#define PTB_COOP_FLUSH_PRIMS 24         // 24: measured best (16..32 within 2 %, profiles/r01_v3_ab_builds.txt)
+#endif
 #define PTB_COOP_QUEUE 64           // groups; >= 31 (left by a flush) + 32 (one per lane and round), power of two
 #ifndef PTB_COOP_CHUNK
 #define PTB_COOP_CHUNK 32
@@ -289,7 +295,7 @@ struct CoopWarp {
     u32 starts[32];                   // flush scratch: queue position (relative to the head) of the group starting at primitive i
 };
 
-// Tests the first min(32, queued) primitives of the group queue, one per lane.  ghead / qprims are updated.
+// Tests the first min(32, queued) primitives of the group queue, one per lane.  ghead is updated.
 __device__ __forceinline__ void coop_flush(const DeviceScene& s, CoopWarp& W, u32 lane, u32& ghead, u32 gtail, u32& qprims) {
     __syncwarp();
     const u32 groups = min(gtail - ghead, 32u);
@@ -303,7 +309,7 @@ __device__ __forceinline__ void coop_flush(const DeviceScene& s, CoopWarp& W, u3
     const bool starts_here = n != 0u && excl < 32u;
     const u32 start_mask = __reduce_or_sync(0xFFFFFFFFu, starts_here ? 1u << excl : 0u);
     if (starts_here) W.starts[excl] = lane;
-    const u32 take = min(qprims, 32u);
+    const u32 take = min(__shfl_sync(0xFFFFFFFFu, incl, 31), 32u);      // primitives held by the first 32 groups
     __syncwarp();
 
     bool won = false;
@@ -355,7 +361,7 @@ __device__ __forceinline__ void coop_flush(const DeviceScene& s, CoopWarp& W, u3
         W.group[(ghead + lane) & (PTB_COOP_QUEUE - 1)].y = bits;
     }
     ghead += (u32)__popc(__ballot_sync(0xFFFFFFFFu, n != 0u && used == n));
-    qprims -= take;
+    qprims -= min(qprims, take);
     __syncwarp();
 }
 
@@ -446,10 +452,10 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
             }
             pool_next += min((u32)__popc(idle), avail);
             __syncwarp();
-        }
-        if (!__any_sync(0xFFFFFFFFu, active)) {
-            if (drained && pool_next == pool_end) break;
-            continue;
+            if (!__any_sync(0xFFFFFFFFu, active)) {          // only possible right after a refill attempt
+                if (drained && pool_next == pool_end) break;
+                continue;
+            }
         }
 
 #else
@@ -525,16 +531,22 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
                 last_seq = q + 1u;
             }
             gtail += (u32)__popc(has);
+#if PTB_COOP_FLUSH_GROUPS
+            // a flush is due when enough groups wait (a group holds 1..24 primitives); counting groups saves a warp reduction
+            while (gtail - ghead >= (u32)PTB_COOP_FLUSH_GROUPS) coop_flush(s, W, lane, ghead, gtail, qprims);
+#else
             qprims += __reduce_add_sync(0xFFFFFFFFu, (u32)__popc(pg.bits));
-            while (qprims >= 32u) coop_flush(s, W, lane, ghead, gtail, qprims);
+            while (qprims >= (u32)PTB_COOP_FLUSH_PRIMS) coop_flush(s, W, lane, ghead, gtail, qprims);
+#endif
         }
 
         // ---- partial flush when too many lanes wait for their tests ----
-        if (qprims != 0u) {
+        if (gtail != ghead) {
             const bool pending = (int)(last_seq - ghead) > 0;
             const bool stepper = active && ng.y > 0x00FFFFFFu && (SPEC || !pending);
-            const u32 waiting = __ballot_sync(0xFFFFFFFFu, active && pending && !stepper);
-            if (__popc(waiting) >= WAIT_T || !__any_sync(0xFFFFFFFFu, stepper)) coop_flush(s, W, lane, ghead, gtail, qprims);
+            const bool waiting = active && pending && !stepper;
+            const u32 votes = __reduce_add_sync(0xFFFFFFFFu, (stepper ? 1u : 0u) | (waiting ? 0x100u : 0u));      // both counts, one reduction
+            if ((votes >> 8) >= (u32)WAIT_T || (votes & 0xFFu) == 0u) coop_flush(s, W, lane, ghead, gtail, qprims);
         }
 
         // ---- retire ----

@@ -33,7 +33,7 @@ struct Prim { uint32_t shape, face, kind, tag; };   // kind: 0 triangle, 2 spher
 struct B2 { Box b; uint32_t left, right, first, count; };   // leaf when count > 0
 
 constexpr int BINS = 16;
-static uint32_t MAX_LEAF = 3;           // a wide-node child slot holds 1..3 primitives
+static uint32_t MAX_LEAF = 2;           // a wide-node child slot holds 1..3 primitives; 2 measured best (profiles/r01_v6_build_sweep.txt)
 
 inline void xform_point(const float* m, const float* p, double* out) {   // column-major To * (p,1), in double
     for (int r = 0; r < 3; r++) out[r] = (double)m[r] * p[0] + (double)m[4 + r] * p[1] + (double)m[8 + r] * p[2] + (double)m[12 + r];
