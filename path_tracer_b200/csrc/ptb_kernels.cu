@@ -262,23 +262,17 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_TRACE_MIN_BLOCKS) k_
 //   SPEC    a lane keeps traversing while its primitives wait in the queue (its reach is stale until
 //           the flush: more node steps, full lanes) or stalls until they have been tested;
 //   WAIT_T  a partial flush happens when this many lanes cannot go on without one.
+// Refill: when REFILL lanes are idle and the warp's pool is empty, the whole warp fetches 32 consecutive rays from
+// the global counter, decodes them, tests the unbounded shapes and parks the prepared records in shared memory;
+// idle lanes then pick their next ray up with a few shared-memory loads (refill work at 32 lanes instead of ~10).
 // Measured and rejected (profiles/r01_v3_ab_builds.txt): prefetch.global.L1 of the next node and of the queued
-// primitives right after a node step (+13 % time: extra address arithmetic, L1 churn); 64 registers / 8 blocks per SM.
-// Rays are fetched from the global counter in chunks of PTB_COOP_CHUNK consecutive slots per warp
-// (32: measured best on B200; 128 costs 8 % to tail imbalance, profiles/r01_v3_ab_builds.txt).
-#ifndef PTB_COOP_POOL
-#define PTB_COOP_POOL 1
-#endif
-#ifndef PTB_COOP_FLUSH_GROUPS
-#define PTB_COOP_FLUSH_GROUPS 0        // > 0: flush on a group count instead of the exact primitive count
-#endif
+// primitives right after a node step (+13 % time: extra address arithmetic, L1 churn); 64 registers / 8 blocks per
+// SM; fetch chunks of 64 / 128 rays (tail imbalance, +8 % at 128); flushing on a group count instead of the exact
+// primitive count; __fns for the k-th pending bit.
 #ifndef PTB_COOP_FLUSH_PRIMS
 #define PTB_COOP_FLUSH_PRIMS 24         // 24: measured best (16..32 within 2 %, profiles/r01_v3_ab_builds.txt)
 #endif
 #define PTB_COOP_QUEUE 64           // groups; >= 31 (left by a flush) + 32 (one per lane and round), power of two
-#ifndef PTB_COOP_CHUNK
-#define PTB_COOP_CHUNK 32
-#endif
 #ifndef PTB_COOP_MIN_BLOCKS
 #define PTB_COOP_MIN_BLOCKS 6
 #endif
@@ -289,9 +283,7 @@ struct CoopWarp {
     float ray[6][32];                 // world-space origin, velocity of each lane's ray
     u32 detail[7][32];                // t, shape, face, shape type, coords of the hit `key` names
     uint4 group[PTB_COOP_QUEUE];      // {owner lane << 27 | primitive base, pending bits, valid bits, -}
-#if PTB_COOP_POOL
     u32 pool[15][32];                 // the next rays, prepared by the whole warp: origin, velocity, key, slot, plane hit
-#endif
     u32 starts[32];                   // flush scratch: queue position (relative to the head) of the group starting at primitive i
 };
 
@@ -387,7 +379,6 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
     { Ray z; z.origin = z.velocity = mk3(0, 0, 0); z.duration = 0; c = wide_ctx(z); }
 
     for (;;) {
-#if PTB_COOP_POOL
         // ---- refill: whole-warp preparation of the next 32 rays into a shared-memory pool, cheap pick-up by idle lanes ----
         const u32 idle = __ballot_sync(0xFFFFFFFFu, !active);
         if (__popc(idle) >= REFILL || idle == 0xFFFFFFFFu) {
@@ -458,61 +449,6 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
             }
         }
 
-#else
-        // ---- refill ----
-        const u32 idle = __ballot_sync(0xFFFFFFFFu, !active);
-        if (__popc(idle) >= REFILL || idle == 0xFFFFFFFFu) {
-            if (pool_next == pool_end && !drained) {
-                u32 base = 0;
-                if (lane == 0) base = atomicAdd(job.counter(), (unsigned)PTB_COOP_CHUNK);
-                base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                pool_next = min(base, total);
-                pool_end = min(base + PTB_COOP_CHUNK, total);
-                if (base + PTB_COOP_CHUNK >= total) drained = true;
-            }
-            const u32 avail = pool_end - pool_next;
-            const u32 rank = (u32)__popc(idle & lt_mask);
-            if (!active && rank < avail) {
-                index = pool_next + rank;
-                Ray ray;
-                if (job.load(index, ray)) {
-                    // unbounded shapes (planes) are tested by the owner, up front
-                    HitId h;
-                    h.t = ray.duration; h.shape = PTB_SHAPE_NONE; h.prim = 0xFFFFFFFFu; h.shape_type = 0; h.coords = mk3(0, 0, 0);
-                    u32 tag = 0xFFFFFFFFu;
-                    for (u32 i = 0; i < s.wide_plane_count; i++) {
-                        const uint2 pl = PTB_LDG((const uint2*)s.wide_planes + i);
-                        const u32 before = h.shape;
-                        test_analytic<true>(object_ray(s, ray, pl.x), PTB_SHAPE_PLANE, pl.x, h);
-                        if (h.shape != before) tag = pl.y;
-                    }
-                    if (s.wide_tlas_root == 0xFFFFFFFFu) {
-                        job.store(index, h);
-                    } else {
-                        c = wide_ctx(ray);
-                        ng = make_uint2(0u, 0x80000000u);
-                        stack.sp = 0;
-                        last_seq = ghead;
-                        active = true;
-                        W.ray[0][lane] = ray.origin.x; W.ray[1][lane] = ray.origin.y; W.ray[2][lane] = ray.origin.z;
-                        W.ray[3][lane] = ray.velocity.x; W.ray[4][lane] = ray.velocity.y; W.ray[5][lane] = ray.velocity.z;
-                        u32 tb = f2u(h.t);
-                        if (tb == 0x80000000u) tb = 0u;
-                        W.key[lane] = ((unsigned long long)tb << 32) | tag;
-                        W.detail[0][lane] = f2u(h.t); W.detail[1][lane] = h.shape; W.detail[2][lane] = h.prim; W.detail[3][lane] = h.shape_type;
-                        W.detail[4][lane] = f2u(h.coords.x); W.detail[5][lane] = f2u(h.coords.y); W.detail[6][lane] = f2u(h.coords.z);
-                    }
-                }
-            }
-            pool_next += min((u32)__popc(idle), avail);
-            __syncwarp();
-        }
-        if (!__any_sync(0xFFFFFFFFu, active)) {
-            if (drained && pool_next == pool_end) break;
-            continue;
-        }
-
-#endif
         // ---- node ----
         PrimGroup pg;
         pg.base = pg.bits = pg.valid = 0u;
@@ -531,13 +467,8 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
                 last_seq = q + 1u;
             }
             gtail += (u32)__popc(has);
-#if PTB_COOP_FLUSH_GROUPS
-            // a flush is due when enough groups wait (a group holds 1..24 primitives); counting groups saves a warp reduction
-            while (gtail - ghead >= (u32)PTB_COOP_FLUSH_GROUPS) coop_flush(s, W, lane, ghead, gtail, qprims);
-#else
             qprims += __reduce_add_sync(0xFFFFFFFFu, (u32)__popc(pg.bits));
             while (qprims >= (u32)PTB_COOP_FLUSH_PRIMS) coop_flush(s, W, lane, ghead, gtail, qprims);
-#endif
         }
 
         // ---- partial flush when too many lanes wait for their tests ----
