@@ -1,7 +1,9 @@
 // Procedural scene generators (see procedural.hpp).  All randomness comes from
 // SplitMix64 with the seeds named in SURVEY.md §8(d).
 #include "procedural.hpp"
+#include <atomic>
 #include <map>
+#include <thread>
 
 namespace ptb { namespace host {
 
@@ -96,7 +98,7 @@ void icosphere(uint32_t level, std::vector<vec3>& P, std::vector<mesh_face>& F) 
 }
 
 // Displaced icosphere mesh with area-weighted smooth normals and spherical UVs.
-mesh* displaced_sphere_mesh(scene* S, const char* name, uint32_t level, uint64_t seed, float amplitude) {
+mesh* displaced_sphere_mesh(scene* S, const char* name, uint32_t level, uint64_t seed, float amplitude) {      // S == nullptr: build only
     std::vector<vec3> P; std::vector<mesh_face> F;
     icosphere(level, P, F);
     for (auto& p : P) { float d = 1.0f + amplitude * (fbm3(seed, p * 2.5f + vec3{7.1f, 3.3f, 5.7f}, 4) - 0.5f); p = p * d; }
@@ -112,7 +114,7 @@ mesh* displaced_sphere_mesh(scene* S, const char* name, uint32_t level, uint64_t
         V[i].Normal = normalize3(N[i]);
         V[i].UV = {0.5f + std::atan2(d.y, d.x) / 6.2831853f, 0.5f + std::asin(std::max(-1.0f, std::min(1.0f, d.z))) / 3.14159265f};
     }
-    return CreateMesh(S, name, std::move(V), std::move(F));
+    return S ? CreateMesh(S, name, std::move(V), std::move(F)) : BuildMesh(name, std::move(V), std::move(F));
 }
 
 // Regular grid patch in the local xy plane, displaced along +z by h(u,v); normals by central differences.
@@ -299,20 +301,44 @@ scene* MakeSphereFieldScene(uint32_t Copies, uint32_t Level, int CameraModel) {
     // Jittered grid around the origin; the cell at the centre is left empty for the 360 camera.
     uint32_t side = (uint32_t)std::ceil(std::sqrt((double)Copies + 1));
     splitmix R{Seed};
-    uint32_t made = 0;
-    for (uint32_t j = 0; j < side && made < Copies; j++) for (uint32_t i = 0; i < side && made < Copies; i++) {
+    // Placement first (one RNG stream, consumed in the order of the sequential recipe), then the meshes — copied, not
+    // instanced: every blob is its own mesh with its own BVH — on all host threads, then attached
+    // in order: the packed arrays are identical to a sequential build.
+    struct blob { vec3 Position, Scale, Rotation; };
+    std::vector<blob> Blobs;
+    for (uint32_t j = 0; j < side && Blobs.size() < Copies; j++) for (uint32_t i = 0; i < side && Blobs.size() < Copies; i++) {
         float cx = ((float)i - 0.5f * (side - 1)) * 2.6f, cy = ((float)j - 0.5f * (side - 1)) * 2.6f;
         float jx = (R.unit() - 0.5f) * 0.8f, jy = (R.unit() - 0.5f) * 0.8f, jz = (R.unit() - 0.5f) * 1.0f, rs = 0.8f + 0.4f * R.unit();
         if (std::fabs(cx) < 1.4f && std::fabs(cy) < 1.4f) continue;
-        char nm[32]; std::snprintf(nm, sizeof nm, "Blob %u", made);
-        // Copied (not instanced) geometry: every blob is its own mesh with its own BVH.
-        mesh* M = displaced_sphere_mesh(S, nm, Level, Seed + 1000 + made, 0.4f);
+        blob B;
+        B.Position = {cx + jx, cy + jy, jz};
+        B.Scale = {rs, rs, rs};
+        float rx = R.unit() * 6.28f, ry = R.unit() * 6.28f, rz = R.unit() * 6.28f;
+        B.Rotation = {rx, ry, rz};
+        Blobs.push_back(B);
+    }
+    std::vector<mesh*> Built(Blobs.size(), nullptr);
+    {
+        std::atomic<size_t> Next(0);
+        auto work = [&]() {
+            for (size_t k = Next.fetch_add(1); k < Blobs.size(); k = Next.fetch_add(1)) {
+                char nm[32]; std::snprintf(nm, sizeof nm, "Blob %u", (unsigned)k);
+                Built[k] = displaced_sphere_mesh(nullptr, nm, Level, Seed + 1000 + k, 0.4f);
+            }
+        };
+        unsigned T = std::max(1u, std::min<unsigned>(std::thread::hardware_concurrency(), (unsigned)Blobs.size()));
+        std::vector<std::thread> Pool;
+        for (unsigned t = 1; t < T; t++) Pool.emplace_back(work);
+        work();
+        for (auto& th : Pool) th.join();
+    }
+    for (size_t k = 0; k < Blobs.size(); k++) {
+        mesh* M = AttachMesh(S, Built[k]);
         entity* E = CreateEntity(S, ENTITY_TYPE_MESH_INSTANCE);
-        E->Mesh = M; E->Material = Mats[made % 6];
-        E->Transform.Position = {cx + jx, cy + jy, jz};
-        E->Transform.Scale = {rs, rs, rs};
-        E->Transform.Rotation = {R.unit() * 6.28f, R.unit() * 6.28f, R.unit() * 6.28f};
-        made++;
+        E->Mesh = M; E->Material = Mats[k % 6];
+        E->Transform.Position = Blobs[k].Position;
+        E->Transform.Scale = Blobs[k].Scale;
+        E->Transform.Rotation = Blobs[k].Rotation;
     }
     entity* Cam;
     if (CameraModel == CAMERA_MODEL_360) {

@@ -196,7 +196,9 @@ struct builder {
 
 }  // namespace
 
-mesh* CreateMesh(scene* Scene, char const* Name, std::vector<mesh_vertex>&& Vertices, std::vector<mesh_face>&& Faces) {
+// The mesh and its BVH without touching any scene: safe to run for several meshes at once (each build is the
+// reference's sequential algorithm, so node and face order per mesh are unchanged).
+mesh* BuildMesh(char const* Name, std::vector<mesh_vertex>&& Vertices, std::vector<mesh_face>&& Faces) {
     mesh* M = new mesh;
     M->Name = Name ? Name : "Mesh";
     M->Vertices = std::move(Vertices);
@@ -206,9 +208,15 @@ mesh* CreateMesh(scene* Scene, char const* Name, std::vector<mesh_vertex>&& Vert
     M->Nodes.push_back(Root);
     builder B(M);
     B.build(0, 0);
+    return M;
+}
+mesh* AttachMesh(scene* Scene, mesh* M) {
     Scene->Meshes.push_back(M);
     Scene->DirtyFlags |= SCENE_DIRTY_MATERIALS | SCENE_DIRTY_MESHES;   // scene.cpp:868-869
     return M;
+}
+mesh* CreateMesh(scene* Scene, char const* Name, std::vector<mesh_vertex>&& Vertices, std::vector<mesh_face>&& Faces) {
+    return AttachMesh(Scene, BuildMesh(Name, std::move(Vertices), std::move(Faces)));
 }
 
 // scene.cpp:912-943

@@ -155,6 +155,9 @@ texture* CreateTexture(scene* Scene, char const* Name, texture_type Type, uint32
 // Programmatic twin of the tail of LoadModelAsPrefab (scene.cpp:851-866): takes
 // ownership of the vertex/face lists, builds the mesh BVH2 (BuildMeshNode).
 mesh* CreateMesh(scene* Scene, char const* Name, std::vector<mesh_vertex>&& Vertices, std::vector<mesh_face>&& Faces);
+// CreateMesh in two steps, so that independent meshes can be built on several threads and attached in order.
+mesh* BuildMesh(char const* Name, std::vector<mesh_vertex>&& Vertices, std::vector<mesh_face>&& Faces);
+mesh* AttachMesh(scene* Scene, mesh* M);
 // CreateScene (scene.cpp:912-943).  WithDefaults adds the reference's default
 // checker plane + camera.  The RGB->spectrum table is process-wide (see below).
 scene* CreateScene(bool WithDefaults = true);
