@@ -493,7 +493,10 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
 
 // ---- K2: scatter ----
 #ifndef PTB_SCATTER_THREADS
-#define PTB_SCATTER_THREADS 128
+#define PTB_SCATTER_THREADS 256
+#endif
+#ifndef PTB_SCATTER_SORT
+#define PTB_SCATTER_SORT 1
 #endif
 #ifndef PTB_SCATTER_MIN_BLOCKS
 #define PTB_SCATTER_MIN_BLOCKS (1024 / PTB_SCATTER_THREADS)
@@ -523,14 +526,42 @@ __global__ void __launch_bounds__(PTB_SCATTER_THREADS, PTB_SCATTER_MIN_BLOCKS)
 k_scatter(const DeviceScene scene, const RenderConsts pc, const WavefrontState st, float4* __restrict__ accum) {
     DeviceScene s = scene;
     s.features = FEATURES;               // a constant from here on: absent features fold away
-    const u32 slot = pc.slot_base + blockIdx.x * (u32)PTB_SCATTER_THREADS + threadIdx.x;
+    const u32 first = pc.slot_base + blockIdx.x * (u32)PTB_SCATTER_THREADS;
+    u32 slot = first + threadIdx.x;
     u32 x, y;
+    bool valid = slot_pixel(pc, slot, x, y);
+#if PTB_SCATTER_SORT
+    // Hits and misses run different code (BSDF sampling vs sky + new camera path): the block's slots are dealt to
+    // its threads hits first, so that all but one warp of a block are uniform.  The block still covers the same
+    // PTB_SCATTER_THREADS consecutive slots, so its state traffic touches the same cache lines.
+    __shared__ u32 order[PTB_SCATTER_THREADS];
+    __shared__ u32 warp_hits[PTB_SCATTER_THREADS / 32], warp_rest[PTB_SCATTER_THREADS / 32];
+    {
+        const u32 lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+        const bool hit = valid && st.hit0[slot].y != 0xFFFFFFFFu;
+        const u32 hb = __ballot_sync(0xFFFFFFFFu, hit);
+        if (lane == 0) { warp_hits[warp] = (u32)__popc(hb); warp_rest[warp] = 32u - (u32)__popc(hb); }
+        __syncthreads();
+        u32 hits_before = 0, rest_before = 0, hits_total = 0;
+#pragma unroll
+        for (u32 w = 0; w < PTB_SCATTER_THREADS / 32; w++) {
+            if (w < warp) { hits_before += warp_hits[w]; rest_before += warp_rest[w]; }
+            hits_total += warp_hits[w];
+        }
+        const u32 below = (1u << lane) - 1u;
+        const u32 pos = hit ? hits_before + (u32)__popc(hb & below) : hits_total + rest_before + (u32)__popc(~hb & below);
+        order[pos] = threadIdx.x;
+        __syncthreads();
+        slot = first + order[threadIdx.x];
+        valid = slot_pixel(pc, slot, x, y);
+    }
+#endif
     bool finished = false;
-    if (slot_pixel(pc, slot, x, y)) finished = scatter_slot(s, pc, st, accum, slot, x, y);
-    // finished-path counters per 256-slot tile; no block barrier, so warps retire as they finish
+    if (valid) finished = scatter_slot(s, pc, st, accum, slot, x, y);
+    // finished-path counters per 256-slot tile; no block barrier here, so warps retire as they finish
     const u32 c = (u32)__popc(__ballot_sync(0xFFFFFFFFu, finished));
-    if ((threadIdx.x & 31u) == 0u && c != 0u) atomicAdd(&st.tile_paths[slot >> 8], c);
-    if (slot == pc.slot_base) *st.ray_counter = 0u;       // re-arm the dynamic ray fetch of the next trace launch
+    if ((threadIdx.x & 31u) == 0u && c != 0u) atomicAdd(&st.tile_paths[first >> 8], c);
+    if (first + threadIdx.x == pc.slot_base) *st.ray_counter = 0u;       // re-arm the dynamic ray fetch of the next trace launch
 }
 
 // ---- material queues ----
