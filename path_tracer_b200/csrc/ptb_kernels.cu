@@ -324,9 +324,12 @@ __device__ __forceinline__ void coop_flush(const DeviceScene& s, CoopWarp& W, u3
         w.velocity = mk3(W.ray[3][owner], W.ray[4][owner], W.ray[5][owner]);
         h.t = w.duration = u2f((u32)(W.key[owner] >> 32));
         Ray o;
-        if (tag & 4u) {        // identity transform: the same arithmetic on constants, no matrix fetch
-            const float I[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
-            o.origin = mat_mul_point(I, w.origin); o.velocity = mat_mul_vector(I, w.velocity); o.duration = w.duration;
+        if (tag & 4u) {
+            // identity transform: ((1*x + 0*y) + 0*z) + 0 of mat_mul_point / mat_mul_vector is x + 0.0f for every
+            // finite ray (the zero products only matter for x = -0, which ends as +0 either way): no matrix fetch
+            o.origin = mk3(w.origin.x + 0.0f, w.origin.y + 0.0f, w.origin.z + 0.0f);
+            o.velocity = mk3(w.velocity.x + 0.0f, w.velocity.y + 0.0f, w.velocity.z + 0.0f);
+            o.duration = w.duration;
         } else {
             o = object_ray(s, w, shape);
         }
