@@ -178,6 +178,7 @@ def main():
     ap.add_argument("--trace-variant", type=int, default=-1, help="PTB_TRACE_VARIANT_* (default: the library's)")
     ap.add_argument("--scatter-mode", default="auto", choices=["auto", "direct", "queues"])
     ap.add_argument("--pipelines", type=int, default=0, choices=[0, 1, 2], help="0 = the library's choice")
+    ap.add_argument("--builder", default="sah-host", choices=["sah-host", "lbvh-gpu"], help="who flattens the scene into the BVH8 (ptb_scene_set_builder)")
     ap.add_argument("--grid", type=int, default=GRID)
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS), help="BASELINE.json config (default C2, the one the metric is quoted on)")
     ap.add_argument("--ref-frames", type=int, default=8, help="frames per step of the CPU reference arm")
@@ -209,7 +210,7 @@ def main():
     S.ensure_spectrum_table()
     scene = S.Scene.make(SCENE_NAME, *SCENE_PARAMS)
     ctx = I.Context(local_rank)
-    dscene = I.DeviceScene(ctx, scene)
+    dscene = I.DeviceScene(ctx, scene, builder=I.BUILDER_LBVH_GPU if args.builder == "lbvh-gpu" else I.BUILDER_SAH_HOST)
     wide = dscene.wide_info()
     film_t = torch.zeros((HEIGHT, WIDTH, 4), dtype=torch.float32, device=device)       # torch owns the film so NCCL can reduce it
     torch.cuda.synchronize()
@@ -358,7 +359,7 @@ def main():
         "config": {"workload": WORKLOAD, "frames_per_step": F, "rays_per_step_per_gpu": WIDTH * HEIGHT * F,
                    "integrator": args.integrator, "traversal": args.traversal, "trace_variant": r.TraceVariant, "scatter_mode": args.scatter_mode, "pipelines": args.pipelines, "parallelism": "sample-split x%d" % world,
                    "l2": "per-round working set (232 MB wavefront state + ~170 MB scene) exceeds the 126 MB L2; no explicit flush",
-                   "wide_bvh": {k: wide[k] for k in ("node_count", "prim_count", "depth", "build_seconds")}},
+                   "wide_bvh": dict({k: wide[k] for k in ("node_count", "prim_count", "depth", "build_seconds", "sah_cost", "device_build_ms")}, builder=args.builder)},
         "mpaths_per_s": paths_all / (ms_max * 1e-3) / 1e6,
         "grays_per_s_per_gpu": value / world / 1e3,
         "seconds_to_1024_paths_per_pixel_1080p": 1024.0 * WIDTH * HEIGHT / (paths_all / world / (ms_max * 1e-3)) if paths_all else None,

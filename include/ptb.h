@@ -205,8 +205,21 @@ typedef struct {
     int32_t  status;
     uint32_t node_count, prim_count, plane_count, depth, bvh2_depth;
     double   sah_cost, build_seconds;
+    uint32_t builder;                    /* PTB_BUILDER_* that produced the tree */
+    float    device_build_ms;            /* GPU builder: CUDA-event time of its kernels; 0 for the host builder */
 } ptb_wide_info;
 int  ptb_scene_wide_info(ptb_scene* scene, ptb_wide_info* out);
+/* Which builder flattens the scene at the next ptb_scene_update that touches shapes or meshes.
+ * The reference has one builder, the single-threaded binned-SAH recursion BuildMeshNode
+ * (src/scene/scene.cpp:435-599), run at import time; here the traversal tree is rebuilt from the
+ * packed arrays, so the choice is a property of the device scene:
+ *   SAH_HOST  threaded binned SAH + SAH-optimal 8-wide collapse on the host (best traversal speed; default)
+ *   LBVH_GPU  Morton-order radix tree + greedy collapse as CUDA kernels (milliseconds per 10 M triangles;
+ *             slower to traverse).  Hits are bit-identical either way: the tree only culls.
+ * If the GPU builder cannot represent a scene (tree deeper than the traversal stack) the host builder runs. */
+#define PTB_BUILDER_SAH_HOST 0u
+#define PTB_BUILDER_LBVH_GPU 1u
+int  ptb_scene_set_builder(ptb_scene* scene, uint32_t builder);
 
 /* CreateSampleBuffer / DestroySampleBuffer (src/integrator/integrator.hpp:51-53):
  * the RGBA32F accumulator (rgb = sum of CIE XYZ, a = sample count).

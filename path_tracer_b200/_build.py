@@ -14,7 +14,7 @@ REPO = os.path.dirname(ROOT)
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
 HOST_SOURCES = ["scene.cpp", "pack.cpp", "spectrum.cpp", "procedural.cpp", "capi.cpp"]
-CUDA_SOURCES = ["ptb_api.cu", "ptb_kernels.cu", "ptb_wide_build.cpp"]
+CUDA_SOURCES = ["ptb_api.cu", "ptb_kernels.cu", "ptb_gpu_build.cu", "ptb_wide_build.cpp"]
 
 SPECTRUM_TABLE = os.path.join(ROOT, "data", "sRGBSpectrumTable.dat")
 
@@ -46,18 +46,46 @@ def build_scene(force=False):
 def cuda_flags():
     return ["-std=c++17", "-O3", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a",
             "--fmad=false",            # numerical contract with the oracle: no implicit contraction
-            "-Xcompiler", "-fPIC", "-shared", "-cudart", "static"]
+            "-Xcompiler", "-fPIC"]
+
+
+def _includes(path, seen):
+    """Transitive closure of the quoted #includes of one source (for per-object rebuilds)."""
+    if path in seen or not os.path.exists(path):
+        return
+    seen.add(path)
+    with open(path, errors="replace") as f:
+        for line in f:
+            if line.startswith("#include \""):
+                name = line.split('"')[1]
+                for base in (os.path.dirname(path), os.path.join(REPO, "include")):
+                    _includes(os.path.normpath(os.path.join(base, name)), seen)
 
 
 def build_cuda(force=False, verbose=False):
+    """One object per source (rebuilt only when it or a header it includes changed), then one link."""
     d = os.path.join(ROOT, "csrc")
     out = os.path.join(ROOT, "libptb.so")
-    deps = [os.path.join(d, f) for f in os.listdir(d)] + [os.path.join(REPO, "include", "ptb.h")]
-    if force or _newer(out, deps):
-        cmd = [NVCC] + cuda_flags() + (["-Xptxas", "-v"] if verbose else []) + ["-I", os.path.join(REPO, "include"), "-I", d, "-o", out] + CUDA_SOURCES
-        log = _run(cmd, d)
+    objdir = os.path.join(ROOT, "build")
+    os.makedirs(objdir, exist_ok=True)
+    objs, procs = [], []
+    for src in CUDA_SOURCES:
+        obj = os.path.join(objdir, src + ".o")
+        objs.append(obj)
+        deps = set()
+        _includes(os.path.join(d, src), deps)
+        if force or _newer(obj, sorted(deps) + [os.path.abspath(__file__)]):
+            cmd = [NVCC] + cuda_flags() + (["-Xptxas", "-v"] if verbose else []) + ["-I", os.path.join(REPO, "include"), "-I", d, "-c", "-o", obj, src]
+            procs.append((cmd, subprocess.Popen(cmd, cwd=d, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    for cmd, p in procs:
+        log = p.communicate()[0]
+        if p.returncode != 0:
+            sys.stderr.write(log)
+            raise RuntimeError("build failed: " + " ".join(cmd))
         if verbose:
             print(log)
+    if procs or force or _newer(out, objs):
+        _run([NVCC, "-shared", "-cudart", "static", "-gencode", "arch=compute_100a,code=sm_100a", "-o", out] + objs, d)
     return out
 
 

@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -14,6 +15,7 @@
 #include "ptb_kernels.h"
 #include "ptb_preview.cuh"
 #include "ptb_wide_build.h"
+#include "ptb_gpu_build.h"
 
 using namespace ptb;
 
@@ -72,6 +74,7 @@ struct ptb_scene {
     DeviceScene ds;
     ptb_wide_info wide_info;
     unsigned raycast_variant;
+    uint32_t builder;                // PTB_BUILDER_*
     uint32_t material_features;      // PTB_FEAT_DIFFUSE/METAL/TRANSLUCENT bits of the uploaded material slots
 };
 
@@ -172,6 +175,8 @@ int ptb_scene_create(ptb_context* ctx, ptb_scene** out) {
     s->ds.wide_tlas_root = 0xFFFFFFFFu;
     s->ds.globals.SkyboxTextureIndex = 0xFFFFFFFFu;
     s->raycast_variant = PTB_TRACE_VARIANT_DEFAULT;
+    s->builder = PTB_BUILDER_SAH_HOST;
+    if (const char* e = std::getenv("PTB_BUILDER")) s->builder = std::atoi(e) == 1 ? PTB_BUILDER_LBVH_GPU : PTB_BUILDER_SAH_HOST;
     s->material_features = 0;
     *out = s;
     return PTB_OK;
@@ -231,24 +236,53 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
                    | (s->ds.globals.SceneScatterRate > 0.0f ? PTB_FEAT_SCENE_SCATTER : 0u);
     if (dirty & (PTB_SCENE_DIRTY_SHAPES | PTB_SCENE_DIRTY_MESHES)) {
         // scene flattening: packed two-level BVH2 scene -> one compressed BVH8
-        WideBuild wb;
         std::string err;
-        int rc = build_wide_bvh(v, &wb, &err);
+        int rc = PTB_E_UNSUPPORTED;
+        bool built = false;
+        if (s->builder == PTB_BUILDER_LBVH_GPU) {
+            // needs the device copies of the shapes and faces this very update may not have refreshed
+            if (!(dirty & PTB_SCENE_DIRTY_SHAPES)) CU(s->shapes.upload(v->Shapes, v->ShapeCount, st));
+            if (!(dirty & PTB_SCENE_DIRTY_MESHES)) CU(s->faces.upload(v->MeshFaces, v->MeshFaceCount, st));
+            GpuWideBuild gb;
+            rc = build_wide_bvh_gpu(v, s->shapes.p, s->faces.p, st, &gb, &err);
+            if (rc == PTB_OK) {
+                s->wide_nodes.release(); s->wide_prims.release();
+                s->wide_nodes.p = gb.nodes; s->wide_nodes.n = (size_t)gb.node_count * 20;
+                s->wide_prims.p = gb.prims; s->wide_prims.n = (size_t)gb.prim_count * 12;
+                CU(s->wide_planes.upload(gb.planes.data(), gb.planes.size(), st));
+                CU(cudaStreamSynchronize(st));
+                s->ds.wide_plane_count = (uint32_t)(gb.planes.size() / 2);
+                s->ds.wide_tlas_root = gb.node_count ? 0u : 0xFFFFFFFFu;
+                s->wide_info.node_count = gb.node_count; s->wide_info.prim_count = gb.prim_count;
+                s->wide_info.plane_count = s->ds.wide_plane_count;
+                s->wide_info.depth = gb.depth; s->wide_info.bvh2_depth = gb.bvh2_depth;
+                s->wide_info.sah_cost = gb.sah_cost; s->wide_info.build_seconds = gb.build_seconds;
+                s->wide_info.builder = PTB_BUILDER_LBVH_GPU; s->wide_info.device_build_ms = gb.device_ms;
+                built = true;
+            }
+        }
+        if (!built) {
+            WideBuild wb;
+            rc = build_wide_bvh(v, &wb, &err);
+            if (rc == PTB_OK) {
+                CU(s->wide_nodes.upload(wb.nodes.data(), wb.nodes.size(), st));
+                CU(s->wide_prims.upload(wb.prims.data(), wb.prims.size(), st));
+                CU(s->wide_planes.upload(wb.planes.data(), wb.planes.size(), st));
+                CU(cudaStreamSynchronize(st));
+                s->ds.wide_plane_count = (uint32_t)(wb.planes.size() / 2);
+                s->ds.wide_tlas_root = wb.node_count ? 0u : 0xFFFFFFFFu;
+                s->wide_info.node_count = wb.node_count; s->wide_info.prim_count = wb.prim_count;
+                s->wide_info.plane_count = (uint32_t)(wb.planes.size() / 2);
+                s->wide_info.depth = wb.depth; s->wide_info.bvh2_depth = wb.bvh2_depth;
+                s->wide_info.sah_cost = wb.sah_cost; s->wide_info.build_seconds = wb.build_seconds;
+                s->wide_info.builder = PTB_BUILDER_SAH_HOST; s->wide_info.device_build_ms = 0.0f;
+            }
+        }
         s->wide_info.status = rc;
         if (rc == PTB_OK) {
-            CU(s->wide_nodes.upload(wb.nodes.data(), wb.nodes.size(), st));
-            CU(s->wide_prims.upload(wb.prims.data(), wb.prims.size(), st));
-            CU(s->wide_planes.upload(wb.planes.data(), wb.planes.size(), st));
-            CU(cudaStreamSynchronize(st));
             s->ds.wide_nodes = (const uint4*)s->wide_nodes.p;
             s->ds.wide_tris = (const float4*)s->wide_prims.p;
             s->ds.wide_planes = s->wide_planes.p;
-            s->ds.wide_plane_count = (uint32_t)(wb.planes.size() / 2);
-            s->ds.wide_tlas_root = wb.node_count ? 0u : 0xFFFFFFFFu;
-            s->wide_info.node_count = wb.node_count; s->wide_info.prim_count = wb.prim_count;
-            s->wide_info.plane_count = (uint32_t)(wb.planes.size() / 2);
-            s->wide_info.depth = wb.depth; s->wide_info.bvh2_depth = wb.bvh2_depth;
-            s->wide_info.sah_cost = wb.sah_cost; s->wide_info.build_seconds = wb.build_seconds;
         } else {
             // The reference-layout traversal stays usable; the wide backend reports the reason.
             s->ds.wide_nodes = nullptr; s->ds.wide_tlas_root = 0xFFFFFFFFu; s->ds.wide_plane_count = 0;
@@ -270,6 +304,12 @@ void ptb_scene_destroy(ptb_scene* s) {
     delete s;
 }
 
+int ptb_scene_set_builder(ptb_scene* s, uint32_t builder) {
+    if (!s) return fail(PTB_E_INVALID, "ptb_scene_set_builder: NULL scene");
+    if (builder != PTB_BUILDER_SAH_HOST && builder != PTB_BUILDER_LBVH_GPU) return fail(PTB_E_INVALID, "ptb_scene_set_builder: unknown builder");
+    s->builder = builder;
+    return PTB_OK;
+}
 int ptb_scene_wide_info(ptb_scene* s, ptb_wide_info* out) {
     if (!s || !out) return fail(PTB_E_INVALID, "ptb_scene_wide_info: NULL argument");
     *out = s->wide_info;

@@ -1,0 +1,515 @@
+// See ptb_gpu_build.h.  CUDA kernels for sm_100a; the only library call is cub's radix sort.
+#include "ptb_gpu_build.h"
+
+#include <cub/device/device_radix_sort.cuh>
+
+#include <chrono>
+#include <cmath>
+#include <cstring>
+
+namespace ptb {
+namespace {
+
+constexpr uint32_t LEAF = 0x80000000u;      // node id flag: index into the sorted primitive order instead of the internal nodes
+constexpr uint32_t NONE = 0xFFFFFFFFu;
+constexpr uint32_t MAX_LEAF = 2;            // primitives per child slot, as in ptb_wide_build.cpp
+
+struct ShapeTable {                          // one entry per shape, built on the host (tiny)
+    const uint32_t* prim_base;               // [S+1] prefix sum of bounded primitives
+    const uint32_t* face_begin;              // [S]   first global face of a mesh shape
+    const uint32_t* rank_base;               // [S]   canonical rank of the shape's first primitive
+    const uint32_t* flags;                   // [S]   type | identity << 8
+    uint32_t shape_count;
+};
+
+struct Tree {
+    // primitives (unsorted order)
+    float4* box_lo;        // xyz = padded world lower corner, w = shape index bits
+    float4* box_hi;        // xyz = upper corner,               w = face index bits
+    uint32_t* tag;
+    // sorted order
+    const uint32_t* sorted;          // position -> primitive
+    const unsigned long long* keys;  // position -> Morton key
+    // internal nodes [0, n-1)
+    uint32_t* left; uint32_t* right; uint32_t* first; uint32_t* last;
+    uint32_t* parent;                // [n-1] internal, then [n] leaves
+    float4* ibox_lo; float4* ibox_hi;
+    uint32_t* visits;
+    uint32_t n;
+};
+
+__device__ __forceinline__ void atomic_min_float(float* a, float v) {
+    if (v >= 0.0f) atomicMin((int*)a, __float_as_int(v)); else atomicMax((unsigned*)a, __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_max_float(float* a, float v) {
+    if (v >= 0.0f) atomicMax((int*)a, __float_as_int(v)); else atomicMin((unsigned*)a, __float_as_uint(v));
+}
+
+// World-space bounds of every bounded primitive, in the arithmetic of the host builder
+// (transform in double, outward padding that covers the rounding of the object-space test).
+// bounds6 = centroid bounds {lo xyz, hi xyz}; *invalid counts primitives with non-finite bounds.
+__global__ void k_prim_bounds(ShapeTable T, const ptb_packed_shape* __restrict__ shapes, const ptb_packed_mesh_face* __restrict__ faces,
+                              Tree t, float* bounds6, uint32_t* invalid) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    float c[3] = {0, 0, 0};
+    bool ok = false;
+    if (i < t.n) {
+        uint32_t lo = 0, hi = T.shape_count;               // last shape with prim_base <= i
+        while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (T.prim_base[mid] <= i) lo = mid; else hi = mid; }
+        const uint32_t s = lo, fl = T.flags[s], type = fl & 0xFFu, k = i - T.prim_base[s];
+        const float* to = shapes[s].Transform.To;
+        double m[12];
+#pragma unroll
+        for (int r = 0; r < 3; r++) { m[r] = to[r]; m[3 + r] = to[4 + r]; m[6 + r] = to[8 + r]; m[9 + r] = to[12 + r]; }
+        float blo[3] = {INFINITY, INFINITY, INFINITY}, bhi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        uint32_t face = 0;
+        bool nan = false;                                    // fminf/fmaxf drop a NaN operand
+        auto grow = [&](float px, float py, float pz) {
+#pragma unroll
+            for (int r = 0; r < 3; r++) {
+                const float w = (float)(m[r] * px + m[3 + r] * py + m[6 + r] * pz + m[9 + r]);
+                blo[r] = fminf(blo[r], w); bhi[r] = fmaxf(bhi[r], w);
+                nan = nan || !(w == w);
+            }
+        };
+        if (type == 0u) {
+            face = T.face_begin[s] + k;
+            const float4* f = (const float4*)(faces + face);
+            const float4 a = f[0], b = f[1], d = f[2];
+            grow(a.x, a.y, a.z); grow(b.x, b.y, b.z); grow(d.x, d.y, d.z);
+        } else {
+            for (int q = 0; q < 8; q++) grow((q & 1) ? 1.f : -1.f, (q & 2) ? 1.f : -1.f, (q & 4) ? 1.f : -1.f);
+        }
+        ok = !nan;
+#pragma unroll
+        for (int r = 0; r < 3; r++) ok = ok && isfinite(blo[r]) && isfinite(bhi[r]);
+        if (ok) {
+#pragma unroll
+            for (int r = 0; r < 3; r++) {
+                const float mx = fmaxf(fabsf(blo[r]), fabsf(bhi[r]));
+                const float e = 4e-6f * (mx + (bhi[r] - blo[r])) + 1e-30f;
+                blo[r] -= e; bhi[r] += e;
+                c[r] = 0.5f * blo[r] + 0.5f * bhi[r];
+            }
+        } else {
+            blo[0] = blo[1] = blo[2] = bhi[0] = bhi[1] = bhi[2] = __int_as_float(0x7FC00000);
+        }
+        t.box_lo[i] = make_float4(blo[0], blo[1], blo[2], __uint_as_float(s));
+        t.box_hi[i] = make_float4(bhi[0], bhi[1], bhi[2], __uint_as_float(face));
+        t.tag[i] = ((T.rank_base[s] + k) << 3) | ((fl >> 8) & 1u) << 2 | (type & 3u);
+    }
+    // block reduction of the centroid bounds, then six atomics per block
+    __shared__ float s_lo[3][8], s_hi[3][8];
+    __shared__ uint32_t s_bad[8];
+    float lo3[3], hi3[3];
+#pragma unroll
+    for (int r = 0; r < 3; r++) { lo3[r] = ok ? c[r] : INFINITY; hi3[r] = ok ? c[r] : -INFINITY; }
+    uint32_t bad = (i < t.n && !ok) ? 1u : 0u;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+            lo3[r] = fminf(lo3[r], __shfl_xor_sync(0xFFFFFFFFu, lo3[r], o));
+            hi3[r] = fmaxf(hi3[r], __shfl_xor_sync(0xFFFFFFFFu, hi3[r], o));
+        }
+        bad += __shfl_xor_sync(0xFFFFFFFFu, bad, o);
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { for (int r = 0; r < 3; r++) { s_lo[r][warp] = lo3[r]; s_hi[r][warp] = hi3[r]; } s_bad[warp] = bad; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        const int r = threadIdx.x;
+        float a = INFINITY, b = -INFINITY;
+        for (int w = 0; w < (int)(blockDim.x >> 5); w++) { a = fminf(a, s_lo[r][w]); b = fmaxf(b, s_hi[r][w]); }
+        if (a <= b) { atomic_min_float(&bounds6[r], a); atomic_max_float(&bounds6[3 + r], b); }
+    }
+    if (threadIdx.x == 32) {
+        uint32_t sum = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); w++) sum += s_bad[w];
+        if (sum) atomicAdd(invalid, sum);
+    }
+}
+
+__device__ __forceinline__ unsigned long long spread21(unsigned long long x) {
+    x &= 0x1FFFFFull;
+    x = (x | x << 32) & 0x001F00000000FFFFull;
+    x = (x | x << 16) & 0x001F0000FF0000FFull;
+    x = (x | x << 8) & 0x100F00F00F00F00Full;
+    x = (x | x << 4) & 0x10C30C30C30C30C3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+// 63-bit Morton key of the box centre inside the centroid bounds; non-finite primitives sort last.
+__global__ void k_morton(Tree t, const float* __restrict__ bounds6, unsigned long long* keys, uint32_t* vals) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= t.n) return;
+    const float4 lo = t.box_lo[i], hi = t.box_hi[i];
+    unsigned long long key = ~0ull;
+    if (lo.x == lo.x) {
+        const float c[3] = {0.5f * lo.x + 0.5f * hi.x, 0.5f * lo.y + 0.5f * hi.y, 0.5f * lo.z + 0.5f * hi.z};
+        unsigned long long q[3];
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+            const float e = bounds6[3 + r] - bounds6[r];
+            float u = e > 0.0f ? (c[r] - bounds6[r]) / e : 0.0f;
+            u = fminf(fmaxf(u, 0.0f), 1.0f);
+            q[r] = (unsigned long long)fminf(u * 2097152.0f, 2097151.0f);
+        }
+        key = spread21(q[0]) | (spread21(q[1]) << 1) | (spread21(q[2]) << 2);
+    }
+    keys[i] = key;
+    vals[i] = i;
+}
+
+// Length of the common prefix of the keys at sorted positions i and j; equal keys are told apart by position.
+__device__ __forceinline__ int delta(const unsigned long long* __restrict__ keys, uint32_t n, int i, int j) {
+    if (j < 0 || j >= (int)n) return -1;
+    const unsigned long long a = keys[i], b = keys[j];
+    if (a == b) return 64 + __clz(i ^ j);
+    return __clzll((long long)(a ^ b));
+}
+
+// Binary radix tree over the sorted keys (Karras, "Maximizing Parallelism in the Construction of BVHs,
+// Octrees, and k-d Trees", HPG 2012): internal node i covers [first, last] and splits after gamma.
+__global__ void k_radix_tree(Tree t) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t n = t.n;
+    if (i >= (int)n - 1) return;
+    const unsigned long long* keys = t.keys;
+    const int d = delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1) >= 0 ? 1 : -1;
+    const int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int s = lmax >> 1; s >= 1; s >>= 1) if (delta(keys, n, i, i + (l + s) * d) > dmin) l += s;
+    const int j = i + l * d;
+    const int dnode = delta(keys, n, i, j);
+    int s = 0, step = l;
+    do {
+        step = (step + 1) >> 1;
+        if (delta(keys, n, i, i + (s + step) * d) > dnode) s += step;
+    } while (step > 1);
+    const int gamma = i + s * d + min(d, 0);
+    const int lo = min(i, j), hi = max(i, j);
+    const uint32_t L = lo == gamma ? ((uint32_t)gamma | LEAF) : (uint32_t)gamma;
+    const uint32_t R = hi == gamma + 1 ? ((uint32_t)(gamma + 1) | LEAF) : (uint32_t)(gamma + 1);
+    t.left[i] = L; t.right[i] = R; t.first[i] = (uint32_t)lo; t.last[i] = (uint32_t)hi;
+    t.parent[(L & LEAF) ? (n - 1) + (L & ~LEAF) : L] = (uint32_t)i;
+    t.parent[(R & LEAF) ? (n - 1) + (R & ~LEAF) : R] = (uint32_t)i;
+    if (i == 0) t.parent[0] = NONE;
+}
+
+__device__ __forceinline__ void node_box(const Tree& t, uint32_t id, float4& lo, float4& hi) {
+    if (id & LEAF) { const uint32_t p = t.sorted[id & ~LEAF]; lo = t.box_lo[p]; hi = t.box_hi[p]; }
+    else { lo = __ldcg(&t.ibox_lo[id]); hi = __ldcg(&t.ibox_hi[id]); }
+}
+__device__ __forceinline__ uint32_t node_count(const Tree& t, uint32_t id) { return (id & LEAF) ? 1u : t.last[id] - t.first[id] + 1u; }
+__device__ __forceinline__ uint32_t node_first(const Tree& t, uint32_t id) { return (id & LEAF) ? (id & ~LEAF) : t.first[id]; }
+
+// Bottom-up bounds: one thread per leaf climbs; the second thread to arrive at a node computes it.
+// ibox_lo.w carries the height of the subtree (levels, a leaf counts 1) for the depth diagnostic.
+__global__ void k_fit_bounds(Tree t, uint32_t* max_depth) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= t.n) return;
+    uint32_t node = t.parent[(t.n - 1) + i];
+    uint32_t height = 1;
+    while (node != NONE) {
+        __threadfence();
+        if (atomicAdd(&t.visits[node], 1u) == 0u) return;
+        const uint32_t L = t.left[node], R = t.right[node];
+        float4 al, ah, bl, bh;
+        node_box(t, L, al, ah);
+        node_box(t, R, bl, bh);
+        const uint32_t hl = (L & LEAF) ? 1u : __float_as_uint(al.w), hr = (R & LEAF) ? 1u : __float_as_uint(bl.w);
+        height = 1u + max(hl, hr);
+        __stcg(&t.ibox_lo[node], make_float4(fminf(al.x, bl.x), fminf(al.y, bl.y), fminf(al.z, bl.z), __uint_as_float(height)));
+        __stcg(&t.ibox_hi[node], make_float4(fmaxf(ah.x, bh.x), fmaxf(ah.y, bh.y), fmaxf(ah.z, bh.z), 0.0f));
+        node = t.parent[node];
+    }
+    *max_depth = height;                // only the thread that completes the root gets here
+}
+
+__device__ __forceinline__ double box_area(const float4& lo, const float4& hi) {
+    const double x = (double)hi.x - lo.x, y = (double)hi.y - lo.y, z = (double)hi.z - lo.z;
+    if (x < 0 || y < 0 || z < 0) return 0.0;
+    return 2.0 * (x * y + y * z + z * x);
+}
+
+__device__ __forceinline__ uint32_t exponent_byte(double extent) {     // smallest e with 255 * 2^e >= extent, biased
+    if (!(extent > 0.0)) return 1u;
+    int e;
+    const double m = frexp(extent / 255.0, &e);
+    if (m == 0.5) e -= 1;
+    int biased = e + 127;
+    biased = biased < 1 ? 1 : (biased > 254 ? 254 : biased);
+    return (uint32_t)biased;
+}
+
+struct Collapse {
+    uint32_t* wide_src;          // wide node index -> radix-tree node it was made from
+    uint32_t* nodes;             // 20 words per wide node
+    float4*   prims;             // 3 x float4 per leaf primitive
+    uint32_t* counters;          // [0] wide nodes allocated, [1] primitives emitted, [2] overflow flag
+    double*   sah;               // [0] accumulated SAH cost (relative to the root area)
+    uint32_t  node_capacity;
+};
+
+// One thread per wide node of the current level: open the largest-area child until 8 slots are
+// used (a subtree of <= MAX_LEAF primitives is one leaf slot), place children in octant order,
+// quantise, allocate the next level's nodes and this node's primitive records.
+__global__ void k_collapse_level(Tree t, Collapse c, const ptb_packed_mesh_face* __restrict__ faces, uint32_t level_begin, uint32_t level_end) {
+    const uint32_t w = level_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= level_end) return;
+    const uint32_t src = c.wide_src[w];
+    uint32_t item[8]; float4 ilo[8], ihi[8]; double area[8]; uint32_t cnt[8];
+    int m = 0;
+    float4 slo, shi;
+    node_box(t, src, slo, shi);
+    auto put = [&](int k, uint32_t id) { item[k] = id; node_box(t, id, ilo[k], ihi[k]); area[k] = box_area(ilo[k], ihi[k]); cnt[k] = node_count(t, id); };
+    if (node_count(t, src) <= MAX_LEAF) { put(0, src); m = 1; }
+    else { put(0, t.left[src]); put(1, t.right[src]); m = 2; }
+    while (m < 8) {
+        int best = -1; double ba = -1.0;
+        for (int k = 0; k < m; k++) if (cnt[k] > MAX_LEAF && area[k] > ba) { ba = area[k]; best = k; }
+        if (best < 0) break;
+        const uint32_t id = item[best];
+        put(best, t.left[id]); put(m, t.right[id]); m++;
+    }
+    // octant slot assignment: greedy on (child centre - node centre) . octant sign
+    float dx[8], dy[8], dz[8];
+    const float ncx = 0.5f * slo.x + 0.5f * shi.x, ncy = 0.5f * slo.y + 0.5f * shi.y, ncz = 0.5f * slo.z + 0.5f * shi.z;
+    for (int k = 0; k < m; k++) {
+        dx[k] = (0.5f * ilo[k].x + 0.5f * ihi[k].x) - ncx; dy[k] = (0.5f * ilo[k].y + 0.5f * ihi[k].y) - ncy; dz[k] = (0.5f * ilo[k].z + 0.5f * ihi[k].z) - ncz;
+    }
+    int child_in_slot[8];
+    for (int s = 0; s < 8; s++) child_in_slot[s] = -1;
+    uint32_t done = 0, used = 0;
+    for (int it = 0; it < m; it++) {
+        int bc = -1, bs = -1; float bv = -INFINITY;
+        for (int k = 0; k < m; k++) {
+            if (done >> k & 1u) continue;
+            for (int s = 0; s < 8; s++) {
+                if (used >> s & 1u) continue;
+                const float v = ((s & 1) ? dx[k] : -dx[k]) + ((s & 2) ? dy[k] : -dy[k]) + ((s & 4) ? dz[k] : -dz[k]);
+                if (v > bv || bc < 0) { bv = v; bc = k; bs = s; }
+            }
+        }
+        done |= 1u << bc; used |= 1u << bs; child_in_slot[bs] = bc;
+    }
+    uint32_t inner = 0, leaf_prims = 0;
+    for (int s = 0; s < 8; s++) { const int k = child_in_slot[s]; if (k < 0) continue; if (cnt[k] > MAX_LEAF) inner++; else leaf_prims += cnt[k]; }
+    const uint32_t child_base = inner ? atomicAdd(&c.counters[0], inner) : 0u;
+    const uint32_t prim_base = leaf_prims ? atomicAdd(&c.counters[1], leaf_prims) : 0u;
+    if (inner && child_base + inner > c.node_capacity) { atomicExch(&c.counters[2], 1u); return; }
+
+    uint32_t word[20];
+    for (int k = 0; k < 20; k++) word[k] = 0;
+    const float plo[3] = {slo.x, slo.y, slo.z}, phi[3] = {shi.x, shi.y, shi.z};
+    uint32_t ebyte[3]; double escale[3];
+    for (int a = 0; a < 3; a++) {
+        ebyte[a] = exponent_byte((double)phi[a] - (double)plo[a]);
+        escale[a] = ldexp(1.0, (int)ebyte[a] - 127);
+        word[a] = __float_as_uint(plo[a]);
+    }
+    uint32_t imask = 0, valid24 = 0, next_child = child_base, next_prim = prim_base;
+    double sah = box_area(slo, shi);
+    for (int s = 0; s < 8; s++) {
+        const int k = child_in_slot[s];
+        if (k < 0) continue;
+        const float clo[3] = {ilo[k].x, ilo[k].y, ilo[k].z}, chi[3] = {ihi[k].x, ihi[k].y, ihi[k].z};
+        for (int a = 0; a < 3; a++) {
+            double lo = floor(((double)clo[a] - (double)plo[a]) / escale[a]);
+            double hi = ceil(((double)chi[a] - (double)plo[a]) / escale[a]);
+            lo = fmin(255.0, fmax(0.0, lo)); hi = fmin(255.0, fmax(0.0, hi));
+            word[8 + 2 * a + (s >> 2)] |= (uint32_t)lo << (8 * (s & 3));
+            word[14 + 2 * a + (s >> 2)] |= (uint32_t)hi << (8 * (s & 3));
+        }
+        if (cnt[k] > MAX_LEAF) {
+            imask |= 1u << s;
+            c.wide_src[next_child++] = item[k];
+        } else {
+            valid24 |= ((1u << cnt[k]) - 1u) << (3 * s);
+            const uint32_t first = node_first(t, item[k]);
+            for (uint32_t q = 0; q < cnt[k]; q++) {
+                const uint32_t p = t.sorted[first + q];
+                const uint32_t shape = __float_as_uint(t.box_lo[p].w), face = __float_as_uint(t.box_hi[p].w), tag = t.tag[p];
+                float4 r0 = make_float4(0, 0, 0, 0), r1 = r0, r2 = r0;
+                if ((tag & 3u) == 0u) { const float4* f = (const float4*)(faces + face); r0 = f[0]; r1 = f[1]; r2 = f[2]; }
+                r0.w = __uint_as_float(face); r1.w = __uint_as_float(shape); r2.w = __uint_as_float(tag);
+                float4* out = c.prims + 3 * (size_t)next_prim++;
+                out[0] = r0; out[1] = r1; out[2] = r2;
+            }
+            sah += area[k] * cnt[k];
+        }
+    }
+    word[3] = ebyte[0] | (ebyte[1] << 8) | (ebyte[2] << 16) | (imask << 24);
+    word[4] = child_base; word[5] = prim_base; word[6] = valid24;
+    uint4* out = (uint4*)(c.nodes + 20 * (size_t)w);
+#pragma unroll
+    for (int k = 0; k < 5; k++) out[k] = make_uint4(word[4 * k], word[4 * k + 1], word[4 * k + 2], word[4 * k + 3]);
+    atomicAdd(c.sah, sah);
+}
+
+struct Scratch {                  // frees everything it handed out
+    std::vector<void*> ptrs;
+    template <class T> cudaError_t get(T** p, size_t count) {
+        *p = nullptr;
+        cudaError_t e = cudaMalloc((void**)p, (count ? count : 1) * sizeof(T));
+        if (e == cudaSuccess) ptrs.push_back(*p);
+        return e;
+    }
+    ~Scratch() { for (void* p : ptrs) cudaFree(p); }
+};
+
+}  // namespace
+
+#define GB(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { *err = std::string(#x) + ": " + cudaGetErrorString(e_); if (out->nodes) cudaFree(out->nodes); if (out->prims) cudaFree(out->prims); out->nodes = nullptr; out->prims = nullptr; return PTB_E_CUDA; } } while (0)
+
+int build_wide_bvh_gpu(const ptb_scene_view* v, const ptb_packed_shape* d_shapes, const ptb_packed_mesh_face* d_faces,
+                       cudaStream_t st, GpuWideBuild* out, std::string* err) {
+    const auto t0 = std::chrono::steady_clock::now();
+    *out = GpuWideBuild();
+
+    // ---- per-shape table (host, O(shapes x mesh depth)) ----
+    const uint32_t S = v->ShapeCount;
+    std::vector<uint32_t> prim_base(S + 1, 0), face_begin(S, 0), rank_base(S, 0), flags(S, 0), plane_list;
+    static const float I16[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+    uint64_t prims = 0, rank = 0;
+    for (uint32_t s = 0; s < S; s++) {
+        const ptb_packed_shape& sh = v->Shapes[s];
+        const bool identity = !std::memcmp(sh.Transform.From, I16, 64) && !std::memcmp(sh.Transform.To, I16, 64);
+        flags[s] = ((uint32_t)sh.Type & 0xFFu) | (identity ? 0x100u : 0u);
+        prim_base[s] = (uint32_t)prims; rank_base[s] = (uint32_t)rank;
+        uint32_t count = 0;
+        if (sh.Type == 1) { plane_list.push_back(s); plane_list.push_back(((uint32_t)rank << 3) | 1u); rank += 1; }
+        else if (sh.Type == 2 || sh.Type == 3) count = 1;
+        else if (sh.Type == 0) {
+            // the faces of a mesh are one contiguous range: first face of the leftmost leaf .. end of the rightmost
+            // (the packer appends each mesh's faces in node order, src/scene/scene.cpp:1265-1330)
+            if (sh.MeshRootNodeIndex >= v->MeshNodeCount) { *err = "shape mesh root out of range"; return PTB_E_INVALID; }
+            uint32_t a = sh.MeshRootNodeIndex, b = sh.MeshRootNodeIndex;
+            for (int guard = 0; v->MeshNodes[a].FaceEndIndex == 0; guard++) {
+                a = v->MeshNodes[a].FaceBeginOrNodeIndex;
+                if (a >= v->MeshNodeCount || guard > 256) { *err = "mesh node chain out of range"; return PTB_E_INVALID; }
+            }
+            for (int guard = 0; v->MeshNodes[b].FaceEndIndex == 0; guard++) {
+                b = v->MeshNodes[b].FaceBeginOrNodeIndex + 1;
+                if (b >= v->MeshNodeCount || guard > 256) { *err = "mesh node chain out of range"; return PTB_E_INVALID; }
+            }
+            const uint32_t fb = v->MeshNodes[a].FaceBeginOrNodeIndex, fe = v->MeshNodes[b].FaceEndIndex;
+            if (fe > v->MeshFaceCount || fb > fe) { *err = "mesh face range out of range"; return PTB_E_INVALID; }
+            face_begin[s] = fb; count = fe - fb;
+        }
+        prims += count; rank += count;
+        if (prims + plane_list.size() / 2 >= (1ull << 27)) { *err = "more than 2^27 primitives"; return PTB_E_UNSUPPORTED; }
+    }
+    prim_base[S] = (uint32_t)prims;
+    out->planes = plane_list;
+    const uint32_t N = (uint32_t)prims;
+    if (N == 0) { out->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); return PTB_OK; }
+
+    Scratch mem;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    GB(cudaEventCreate(&ev0)); GB(cudaEventCreate(&ev1));
+    struct EvGuard { cudaEvent_t a, b; ~EvGuard() { cudaEventDestroy(a); cudaEventDestroy(b); } } evg{ev0, ev1};
+    GB(cudaEventRecord(ev0, st));
+
+    uint32_t *d_prim_base, *d_face_begin, *d_rank_base, *d_flags;
+    GB(mem.get(&d_prim_base, S + 1)); GB(mem.get(&d_face_begin, S)); GB(mem.get(&d_rank_base, S)); GB(mem.get(&d_flags, S));
+    GB(cudaMemcpyAsync(d_prim_base, prim_base.data(), (S + 1) * 4, cudaMemcpyHostToDevice, st));
+    GB(cudaMemcpyAsync(d_face_begin, face_begin.data(), S * 4, cudaMemcpyHostToDevice, st));
+    GB(cudaMemcpyAsync(d_rank_base, rank_base.data(), S * 4, cudaMemcpyHostToDevice, st));
+    GB(cudaMemcpyAsync(d_flags, flags.data(), S * 4, cudaMemcpyHostToDevice, st));
+    ShapeTable T{d_prim_base, d_face_begin, d_rank_base, d_flags, S};
+
+    Tree t;
+    std::memset(&t, 0, sizeof t);
+    t.n = N;
+    unsigned long long *keys_a, *keys_b;
+    uint32_t *vals_a, *vals_b, *d_small;
+    float* d_bounds;
+    GB(mem.get(&t.box_lo, N)); GB(mem.get(&t.box_hi, N)); GB(mem.get(&t.tag, N));
+    GB(mem.get(&keys_a, N)); GB(mem.get(&keys_b, N)); GB(mem.get(&vals_a, N)); GB(mem.get(&vals_b, N));
+    GB(mem.get(&d_bounds, 8)); GB(mem.get(&d_small, 8));
+    const float binit[6] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
+    GB(cudaMemcpyAsync(d_bounds, binit, sizeof binit, cudaMemcpyHostToDevice, st));
+    GB(cudaMemsetAsync(d_small, 0, 8 * 4, st));           // [0] invalid primitives, [1] radix-tree height
+
+    const uint32_t B = 256, G = (N + B - 1) / B;
+    k_prim_bounds<<<G, B, 0, st>>>(T, d_shapes, d_faces, t, d_bounds, d_small);
+    k_morton<<<G, B, 0, st>>>(t, d_bounds, keys_a, vals_a);
+    size_t temp_bytes = 0;
+    cub::DoubleBuffer<unsigned long long> dk(keys_a, keys_b);
+    cub::DoubleBuffer<uint32_t> dv(vals_a, vals_b);
+    GB(cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, dk, dv, (int)N, 0, 64, st));
+    char* d_temp;
+    GB(mem.get(&d_temp, temp_bytes));
+    GB(cub::DeviceRadixSort::SortPairs(d_temp, temp_bytes, dk, dv, (int)N, 0, 64, st));
+    uint32_t invalid = 0;
+    GB(cudaMemcpyAsync(&invalid, d_small, 4, cudaMemcpyDeviceToHost, st));
+    GB(cudaStreamSynchronize(st));
+    const uint32_t n = N - invalid;                        // non-finite primitives sorted to the end are left out
+    out->prim_count = n;
+    if (n == 0) { out->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); return PTB_OK; }
+    t.n = n; t.keys = dk.Current(); t.sorted = dv.Current();
+
+    const uint32_t ni = n > 1 ? n - 1 : 1;
+    GB(mem.get(&t.left, ni)); GB(mem.get(&t.right, ni)); GB(mem.get(&t.first, ni)); GB(mem.get(&t.last, ni));
+    GB(mem.get(&t.parent, (size_t)ni + n)); GB(mem.get(&t.ibox_lo, ni)); GB(mem.get(&t.ibox_hi, ni)); GB(mem.get(&t.visits, ni));
+    GB(cudaMemsetAsync(t.visits, 0, (size_t)ni * 4, st));
+    if (n > 1) {
+        k_radix_tree<<<(n - 1 + B - 1) / B, B, 0, st>>>(t);
+        k_fit_bounds<<<(n + B - 1) / B, B, 0, st>>>(t, d_small + 1);
+    }
+
+    Collapse c;
+    c.node_capacity = n / 2 + 16;
+    uint32_t* big_nodes;
+    double* d_sah;
+    GB(mem.get(&c.wide_src, c.node_capacity)); GB(mem.get(&big_nodes, (size_t)c.node_capacity * 20)); GB(mem.get(&c.counters, 4)); GB(mem.get(&d_sah, 1));
+    c.nodes = big_nodes; c.sah = d_sah;
+    GB(cudaMalloc((void**)&out->prims, (size_t)n * 48));
+    c.prims = (float4*)out->prims;
+    const uint32_t root = n > 1 ? 0u : LEAF;
+    const uint32_t cinit[4] = {1u, 0u, 0u, 0u};
+    GB(cudaMemcpyAsync(c.wide_src, &root, 4, cudaMemcpyHostToDevice, st));
+    GB(cudaMemcpyAsync(c.counters, cinit, sizeof cinit, cudaMemcpyHostToDevice, st));
+    GB(cudaMemsetAsync(d_sah, 0, 8, st));
+    uint32_t level_begin = 0, level_end = 1, depth = 0, host_counters[4] = {1, 0, 0, 0};
+    while (level_begin < level_end) {
+        depth++;
+        const uint32_t count = level_end - level_begin;
+        k_collapse_level<<<(count + 127) / 128, 128, 0, st>>>(t, c, d_faces, level_begin, level_end);
+        GB(cudaMemcpyAsync(host_counters, c.counters, sizeof host_counters, cudaMemcpyDeviceToHost, st));
+        GB(cudaStreamSynchronize(st));
+        if (host_counters[2]) { *err = "wide node buffer overflow"; cudaFree(out->prims); out->prims = nullptr; return PTB_E_UNSUPPORTED; }
+        level_begin = level_end; level_end = host_counters[0];
+        if (depth > 64) break;
+    }
+    if (depth > 30) { *err = "wide BVH deeper than the traversal stack"; cudaFree(out->prims); out->prims = nullptr; return PTB_E_UNSUPPORTED; }
+    if (host_counters[1] != n) { *err = "collapse emitted a different number of primitives than it was given"; cudaFree(out->prims); out->prims = nullptr; return PTB_E_UNSUPPORTED; }
+    out->node_count = host_counters[0];
+    out->depth = depth;
+    GB(cudaMalloc((void**)&out->nodes, (size_t)out->node_count * 80));
+    GB(cudaMemcpyAsync(out->nodes, big_nodes, (size_t)out->node_count * 80, cudaMemcpyDeviceToDevice, st));
+    double sah = 0.0, root_area = 1.0;
+    float4 rl, rh;
+    uint32_t height = 1;
+    GB(cudaMemcpyAsync(&sah, d_sah, 8, cudaMemcpyDeviceToHost, st));
+    GB(cudaMemcpyAsync(&height, d_small + 1, 4, cudaMemcpyDeviceToHost, st));
+    if (n > 1) { GB(cudaMemcpyAsync(&rl, t.ibox_lo, 16, cudaMemcpyDeviceToHost, st)); GB(cudaMemcpyAsync(&rh, t.ibox_hi, 16, cudaMemcpyDeviceToHost, st)); }
+    GB(cudaEventRecord(ev1, st));
+    GB(cudaStreamSynchronize(st));
+    if (n > 1) {
+        const double x = (double)rh.x - rl.x, y = (double)rh.y - rl.y, z = (double)rh.z - rl.z;
+        root_area = std::max(2.0 * (x * y + y * z + z * x), 1e-300);
+        out->sah_cost = sah / root_area;
+    }
+    out->bvh2_depth = height;
+    cudaEventElapsedTime(&out->device_ms, ev0, ev1);
+    out->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return PTB_OK;
+}
+
+}  // namespace ptb

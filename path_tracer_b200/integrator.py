@@ -20,7 +20,7 @@ import numpy as np
 from . import _build
 from .types import (KernelTimes, PreviewParams, PREVIEW_MODES, RenderParams, ResolveParams, SceneView, Stats, WideInfo, HIT_DTYPE, RAY_DTYPE,
                     RENDER_FLAG_ACCUMULATE, RENDER_FLAG_SAMPLE_JITTER, INTEGRATOR_WAVEFRONT, INTEGRATOR_MEGAKERNEL,
-                    TRAVERSAL_BVH2_REFERENCE, TRAVERSAL_WIDE, TIE_FAITHFUL, TIE_CANONICAL, SCENE_DIRTY_ALL,
+                    TRAVERSAL_BVH2_REFERENCE, TRAVERSAL_WIDE, TIE_FAITHFUL, TIE_CANONICAL, SCENE_DIRTY_ALL, BUILDER_SAH_HOST, BUILDER_LBVH_GPU,
                     TRACE_VARIANT_SIMPLE, TRACE_VARIANT_DEFAULT, TRACE_VARIANT_MAX, SCATTER_AUTO, SCATTER_DIRECT, SCATTER_QUEUES,
                     TONE_CLAMP, TONE_REINHARD, TONE_HABLE, TONE_ACES)
 
@@ -28,7 +28,7 @@ from .types import (KernelTimes, PreviewParams, PREVIEW_MODES, RenderParams, Res
 ABI_SYMBOLS = [
     "ptb_last_error", "ptb_version",
     "ptb_context_create", "ptb_context_destroy", "ptb_context_sync", "ptb_context_stream",
-    "ptb_scene_create", "ptb_scene_update", "ptb_scene_destroy", "ptb_scene_wide_info",
+    "ptb_scene_create", "ptb_scene_update", "ptb_scene_destroy", "ptb_scene_wide_info", "ptb_scene_set_builder",
     "ptb_film_create", "ptb_film_destroy", "ptb_film_device_accum", "ptb_film_download_accum", "ptb_film_upload_accum",
     "ptb_film_resolve", "ptb_film_resolve_device",
     "ptb_renderer_create", "ptb_renderer_destroy", "ptb_renderer_set_params", "ptb_renderer_set_frame_index",
@@ -74,6 +74,7 @@ def lib():
         L.ptb_scene_destroy.argtypes = [vp]
         L.ptb_scene_destroy.restype = None
         L.ptb_scene_wide_info.argtypes = [vp, C.POINTER(WideInfo)]
+        L.ptb_scene_set_builder.argtypes = [vp, u32]
         L.ptb_film_create.argtypes = [vp, u32, u32, vp, C.POINTER(vp)]
         L.ptb_film_destroy.argtypes = [vp]
         L.ptb_film_destroy.restype = None
@@ -139,10 +140,12 @@ class Context:
 class DeviceScene:
     """CreateVulkanScene / UpdateVulkanScene / DestroyVulkanScene (scene.hpp:440-442)."""
 
-    def __init__(self, ctx, host_scene=None):
+    def __init__(self, ctx, host_scene=None, builder=None):
         self.ctx = ctx
         self.h = C.c_void_p()
         _check(lib().ptb_scene_create(ctx.h, C.byref(self.h)))
+        if builder is not None:
+            self.set_builder(builder)
         if host_scene is not None:
             self.update(host_scene, SCENE_DIRTY_ALL)
 
@@ -150,6 +153,10 @@ class DeviceScene:
         """host_scene: path_tracer_b200.scene.Scene (packed) or a raw SceneView."""
         view = host_scene if isinstance(host_scene, SceneView) else host_scene.view
         _check(lib().ptb_scene_update(self.h, C.byref(view), dirty_flags))
+
+    def set_builder(self, builder):
+        """BUILDER_SAH_HOST (default) or BUILDER_LBVH_GPU: who flattens the scene at the next update."""
+        _check(lib().ptb_scene_set_builder(self.h, builder))
 
     def wide_info(self):
         w = WideInfo()

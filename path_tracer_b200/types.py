@@ -59,7 +59,10 @@ class KernelTimes(C.Structure):
 
 class WideInfo(C.Structure):
     _fields_ = [("status", C.c_int32), ("node_count", u32), ("prim_count", u32), ("plane_count", u32), ("depth", u32),
-                ("bvh2_depth", u32), ("sah_cost", C.c_double), ("build_seconds", C.c_double)]
+                ("bvh2_depth", u32), ("sah_cost", C.c_double), ("build_seconds", C.c_double), ("builder", u32), ("device_build_ms", C.c_float)]
+
+
+BUILDER_SAH_HOST, BUILDER_LBVH_GPU = 0, 1
 
 
 # numpy record layouts of the packed arrays (src/scene/scene.hpp:82-173)

@@ -29,7 +29,7 @@ def test_header_symbols_are_exported():
 def test_pod_sizes_match_header():
     from path_tracer_b200 import types as T
     assert C.sizeof(T.RenderParams) == 48 and C.sizeof(T.ResolveParams) == 12 and C.sizeof(T.Stats) == 32
-    assert C.sizeof(T.WideInfo) == 40
+    assert C.sizeof(T.WideInfo) == 48
     assert T.RAY_DTYPE.itemsize == 28 and T.HIT_DTYPE.itemsize == 64
     assert C.sizeof(T.SceneView) == 8 * 16 + 8 + 4 + 4 + 4 + 4 + 8
 

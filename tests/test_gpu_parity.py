@@ -126,6 +126,61 @@ def test_raycast_axis_parallel_and_empty(I, gpu, dev, oracle, scenes):
     assert one["shape"][0] == oracle.raycast(sc.view, rays[:1])["shape"][0]
 
 
+# ---------------------------------------------------------------- GPU builder
+@pytest.mark.parametrize("name,params", SCENES + [("terrain", (300,)), ("spherefield", (40, 3, 2))])
+def test_gpu_builder_tree_gives_identical_hits(I, gpu, dev, oracle, scenes, name, params):
+    """The Morton-order tree built by CUDA kernels culls differently from the host SAH tree, but leaf
+    primitives and the canonical rank are the same, so every hit record must be bit-identical —
+    and identical to the oracle's brute-force closest hit."""
+    sc = scenes(name, *params)
+    g = I.DeviceScene(gpu, sc, builder=I.BUILDER_LBVH_GPU)
+    gi, hi = g.wide_info(), dev(name, *params).wide_info()
+    assert gi["status"] == 0 and gi["builder"] == I.BUILDER_LBVH_GPU and hi["builder"] == I.BUILDER_SAH_HOST
+    assert gi["prim_count"] == hi["prim_count"] and gi["plane_count"] == hi["plane_count"]
+    assert 0 < gi["depth"] <= 30 and gi["node_count"] >= 1
+    n = 200000
+    rays = random_rays(sc, n, 11, oracle)
+    a = g.raycast(rays, I.TRAVERSAL_WIDE, I.TIE_CANONICAL)
+    b = dev(name, *params).raycast(rays, I.TRAVERSAL_WIDE, I.TIE_CANONICAL)
+    assert a.tobytes() == b.tobytes()
+    sample = np.arange(0, n, 53)
+    bf = oracle.raycast_bruteforce(sc.view, rays[sample])
+    assert ids_equal(a[sample], bf).all() and (bits(a["t"][sample]) == bits(bf["t"])).all()
+    # the whole integrator on top of it: film and wavefront state bit-identical to the host-built tree
+    outs = []
+    for d in (g, dev(name, *params)):
+        film = I.SampleBuffer(gpu, 96, 64)
+        r = I.BasicRenderer(gpu, d, film)
+        r.set_frame_index(2)
+        r.reset()
+        r.run(2)
+        r.run_frames(5)
+        outs.append((film.download(), r.state("PrimitiveIndex"), r.state("Time")))
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+    assert np.array_equal(bits(outs[0][2]), bits(outs[1][2]))
+
+
+def test_gpu_builder_edge_cases(I, gpu, oracle, scenes):
+    """No bounded primitive, one primitive, two primitives, and a rebuild after switching builders."""
+    from path_tracer_b200 import scene as S
+    for n_spheres in (0, 1, 2, 3):
+        sc = S.Scene(with_defaults=True)             # checker plane + camera
+        for k in range(n_spheres):
+            sc.create_entity(S.ENTITY_SPHERE if k != 1 else S.ENTITY_CUBE, position=(2.5 * k - 2.0, 0.3 * k, 1.0), scale=(1.0, 0.7, 1.2))
+        sc.pack()
+        g = I.DeviceScene(gpu, sc, builder=I.BUILDER_LBVH_GPU)
+        info = g.wide_info()
+        assert info["status"] == 0 and info["prim_count"] == n_spheres and info["plane_count"] == 1
+        rays = random_rays(sc, 20000, 3, oracle)
+        out = g.raycast(rays, I.TRAVERSAL_WIDE, I.TIE_CANONICAL)
+        bf = oracle.raycast_bruteforce(sc.view, rays)
+        assert ids_equal(out, bf).all() and (bits(out["t"]) == bits(bf["t"])).all()
+        g.set_builder(I.BUILDER_SAH_HOST)
+        g.update(sc, I.SCENE_DIRTY_ALL)
+        assert g.wide_info()["builder"] == I.BUILDER_SAH_HOST
+        assert g.raycast(rays, I.TRAVERSAL_WIDE, I.TIE_CANONICAL).tobytes() == out.tobytes()
+
+
 # ---------------------------------------------------------------- radiance
 def assert_radiance_close(a, b, tol=1e-4, max_outlier_fraction=2e-3):
     """|a-b| <= tol * max(|b|, 1) per channel; a path whose random branch flips on an ulp
