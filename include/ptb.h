@@ -214,11 +214,15 @@ int  ptb_scene_wide_info(ptb_scene* scene, ptb_wide_info* out);
  * (src/scene/scene.cpp:435-599), run at import time; here the traversal tree is rebuilt from the
  * packed arrays, so the choice is a property of the device scene:
  *   SAH_HOST  threaded binned SAH + SAH-optimal 8-wide collapse on the host (best traversal speed; default)
- *   LBVH_GPU  Morton-order radix tree + greedy collapse as CUDA kernels (milliseconds per 10 M triangles;
- *             slower to traverse).  Hits are bit-identical either way: the tree only culls.
+ *   LBVH_GPU  Morton-order radix tree + SAH-optimal collapse as CUDA kernels (milliseconds per 10 M triangles;
+ *             slowest to traverse).
+ *   PLOC_GPU  locally-ordered agglomerative clustering on the Morton order as CUDA kernels (tens of
+ *             milliseconds per 10 M triangles; between the two in traversal speed).
+ * Hits are bit-identical whichever builder ran: the tree only culls.
  * If the GPU builder cannot represent a scene (tree deeper than the traversal stack) the host builder runs. */
 #define PTB_BUILDER_SAH_HOST 0u
 #define PTB_BUILDER_LBVH_GPU 1u
+#define PTB_BUILDER_PLOC_GPU 2u
 int  ptb_scene_set_builder(ptb_scene* scene, uint32_t builder);
 
 /* CreateSampleBuffer / DestroySampleBuffer (src/integrator/integrator.hpp:51-53):

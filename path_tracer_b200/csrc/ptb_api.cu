@@ -176,7 +176,7 @@ int ptb_scene_create(ptb_context* ctx, ptb_scene** out) {
     s->ds.globals.SkyboxTextureIndex = 0xFFFFFFFFu;
     s->raycast_variant = PTB_TRACE_VARIANT_DEFAULT;
     s->builder = PTB_BUILDER_SAH_HOST;
-    if (const char* e = std::getenv("PTB_BUILDER")) s->builder = std::atoi(e) == 1 ? PTB_BUILDER_LBVH_GPU : PTB_BUILDER_SAH_HOST;
+    if (const char* e = std::getenv("PTB_BUILDER")) s->builder = std::atoi(e) == 1 ? PTB_BUILDER_LBVH_GPU : std::atoi(e) == 2 ? PTB_BUILDER_PLOC_GPU : PTB_BUILDER_SAH_HOST;
     s->material_features = 0;
     *out = s;
     return PTB_OK;
@@ -239,12 +239,12 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
         std::string err;
         int rc = PTB_E_UNSUPPORTED;
         bool built = false;
-        if (s->builder == PTB_BUILDER_LBVH_GPU) {
+        if (s->builder == PTB_BUILDER_LBVH_GPU || s->builder == PTB_BUILDER_PLOC_GPU) {
             // needs the device copies of the shapes and faces this very update may not have refreshed
             if (!(dirty & PTB_SCENE_DIRTY_SHAPES)) CU(s->shapes.upload(v->Shapes, v->ShapeCount, st));
             if (!(dirty & PTB_SCENE_DIRTY_MESHES)) CU(s->faces.upload(v->MeshFaces, v->MeshFaceCount, st));
             GpuWideBuild gb;
-            rc = build_wide_bvh_gpu(v, s->shapes.p, s->faces.p, st, &gb, &err);
+            rc = build_wide_bvh_gpu(v, s->shapes.p, s->faces.p, st, s->builder == PTB_BUILDER_PLOC_GPU ? 1 : 0, &gb, &err);
             if (rc == PTB_OK) {
                 s->wide_nodes.release(); s->wide_prims.release();
                 s->wide_nodes.p = gb.nodes; s->wide_nodes.n = (size_t)gb.node_count * 20;
@@ -257,7 +257,7 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
                 s->wide_info.plane_count = s->ds.wide_plane_count;
                 s->wide_info.depth = gb.depth; s->wide_info.bvh2_depth = gb.bvh2_depth;
                 s->wide_info.sah_cost = gb.sah_cost; s->wide_info.build_seconds = gb.build_seconds;
-                s->wide_info.builder = PTB_BUILDER_LBVH_GPU; s->wide_info.device_build_ms = gb.device_ms;
+                s->wide_info.builder = s->builder; s->wide_info.device_build_ms = gb.device_ms;
                 built = true;
             }
         }
@@ -306,7 +306,7 @@ void ptb_scene_destroy(ptb_scene* s) {
 
 int ptb_scene_set_builder(ptb_scene* s, uint32_t builder) {
     if (!s) return fail(PTB_E_INVALID, "ptb_scene_set_builder: NULL scene");
-    if (builder != PTB_BUILDER_SAH_HOST && builder != PTB_BUILDER_LBVH_GPU) return fail(PTB_E_INVALID, "ptb_scene_set_builder: unknown builder");
+    if (builder != PTB_BUILDER_SAH_HOST && builder != PTB_BUILDER_LBVH_GPU && builder != PTB_BUILDER_PLOC_GPU) return fail(PTB_E_INVALID, "ptb_scene_set_builder: unknown builder");
     s->builder = builder;
     return PTB_OK;
 }

@@ -2,9 +2,12 @@
 #include "ptb_gpu_build.h"
 
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 
 #include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 namespace ptb {
@@ -31,11 +34,16 @@ struct Tree {
     const uint32_t* sorted;          // position -> primitive
     const unsigned long long* keys;  // position -> Morton key
     // internal nodes [0, n-1)
-    uint32_t* left; uint32_t* right; uint32_t* first; uint32_t* last;
+    uint32_t* left; uint32_t* right; uint32_t* cnt;     // cnt = primitives below the node
     uint32_t* parent;                // [n-1] internal, then [n] leaves
     float4* ibox_lo; float4* ibox_hi;
     uint32_t* visits;
+    // SAH-optimal collapse (the forest-cost recurrence of Ylitie et al. 2017, as in ptb_wide_build.cpp):
+    // dp_cost[7 n + i - 1] = C(n, i), cheapest way to put the subtree of n into at most i child slots;
+    // dp_split[8 n + j - 1] = slots given to the left child in D(n, j) (0: C(n, j) inherited from C(n, j - 1)).
+    float* dp_cost; uint8_t* dp_split;
     uint32_t n;
+    uint32_t greedy;                 // 1: open the largest-area child instead (kept for comparison)
 };
 
 __device__ __forceinline__ void atomic_min_float(float* a, float v) {
@@ -194,7 +202,7 @@ __global__ void k_radix_tree(Tree t) {
     const int lo = min(i, j), hi = max(i, j);
     const uint32_t L = lo == gamma ? ((uint32_t)gamma | LEAF) : (uint32_t)gamma;
     const uint32_t R = hi == gamma + 1 ? ((uint32_t)(gamma + 1) | LEAF) : (uint32_t)(gamma + 1);
-    t.left[i] = L; t.right[i] = R; t.first[i] = (uint32_t)lo; t.last[i] = (uint32_t)hi;
+    t.left[i] = L; t.right[i] = R; t.cnt[i] = (uint32_t)(hi - lo + 1);
     t.parent[(L & LEAF) ? (n - 1) + (L & ~LEAF) : L] = (uint32_t)i;
     t.parent[(R & LEAF) ? (n - 1) + (R & ~LEAF) : R] = (uint32_t)i;
     if (i == 0) t.parent[0] = NONE;
@@ -204,10 +212,46 @@ __device__ __forceinline__ void node_box(const Tree& t, uint32_t id, float4& lo,
     if (id & LEAF) { const uint32_t p = t.sorted[id & ~LEAF]; lo = t.box_lo[p]; hi = t.box_hi[p]; }
     else { lo = __ldcg(&t.ibox_lo[id]); hi = __ldcg(&t.ibox_hi[id]); }
 }
-__device__ __forceinline__ uint32_t node_count(const Tree& t, uint32_t id) { return (id & LEAF) ? 1u : t.last[id] - t.first[id] + 1u; }
-__device__ __forceinline__ uint32_t node_first(const Tree& t, uint32_t id) { return (id & LEAF) ? (id & ~LEAF) : t.first[id]; }
+__device__ __forceinline__ uint32_t node_count(const Tree& t, uint32_t id) { return (id & LEAF) ? 1u : t.cnt[id]; }
 
-// Bottom-up bounds: one thread per leaf climbs; the second thread to arrive at a node computes it.
+__device__ __forceinline__ double box_area(const float4& lo, const float4& hi) {
+    const double x = (double)hi.x - lo.x, y = (double)hi.y - lo.y, z = (double)hi.z - lo.z;
+    if (x < 0 || y < 0 || z < 0) return 0.0;
+    return 2.0 * (x * y + y * z + z * x);
+}
+constexpr double C_NODE = 1.0, C_PRIM = 0.4;      // the host builder's cost model
+
+__device__ __forceinline__ void load_dp(const Tree& t, uint32_t id, const float4& lo, const float4& hi, float* c) {
+    if (id & LEAF) { const float v = (float)(box_area(lo, hi) * C_PRIM); for (int i = 0; i < 7; i++) c[i] = v; }
+    else for (int i = 0; i < 7; i++) c[i] = __ldcg(&t.dp_cost[7 * (size_t)id + i]);
+}
+
+// Collapse costs of an internal node from those of its (finished) children.
+__device__ __forceinline__ void node_costs(const Tree& t, uint32_t node, uint32_t L, uint32_t R, const float4& al, const float4& ah,
+                                           const float4& bl, const float4& bh, double area, uint32_t count) {
+    float cl[7], cr[7], cn[7];
+    load_dp(t, L, al, ah, cl);
+    load_dp(t, R, bl, bh, cr);
+    double D[9]; int K[9];
+    for (int j = 2; j <= 8; j++) {
+        D[j] = INFINITY; K[j] = 1;
+        for (int k = 1; k < j; k++) {
+            if (k > 7 || j - k > 7) continue;
+            const double v = (double)cl[k - 1] + (double)cr[j - k - 1];
+            if (v < D[j]) { D[j] = v; K[j] = k; }
+        }
+    }
+    uint8_t* sp = t.dp_split + 8 * (size_t)node;
+    cn[0] = (float)(count <= MAX_LEAF ? area * count * C_PRIM : area * C_NODE + D[8]);
+    sp[0] = 0; sp[7] = (uint8_t)K[8];
+    for (int i = 2; i <= 7; i++) {
+        if (D[i] < cn[i - 2]) { cn[i - 1] = (float)D[i]; sp[i - 1] = (uint8_t)K[i]; }
+        else { cn[i - 1] = cn[i - 2]; sp[i - 1] = 0; }
+    }
+    for (int i = 0; i < 7; i++) __stcg(&t.dp_cost[7 * (size_t)node + i], cn[i]);
+}
+
+// Bottom-up bounds and collapse costs: one thread per leaf climbs; the second thread to arrive at a node computes it.
 // ibox_lo.w carries the height of the subtree (levels, a leaf counts 1) for the depth diagnostic.
 __global__ void k_fit_bounds(Tree t, uint32_t* max_depth) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -223,17 +267,14 @@ __global__ void k_fit_bounds(Tree t, uint32_t* max_depth) {
         node_box(t, R, bl, bh);
         const uint32_t hl = (L & LEAF) ? 1u : __float_as_uint(al.w), hr = (R & LEAF) ? 1u : __float_as_uint(bl.w);
         height = 1u + max(hl, hr);
-        __stcg(&t.ibox_lo[node], make_float4(fminf(al.x, bl.x), fminf(al.y, bl.y), fminf(al.z, bl.z), __uint_as_float(height)));
-        __stcg(&t.ibox_hi[node], make_float4(fmaxf(ah.x, bh.x), fmaxf(ah.y, bh.y), fmaxf(ah.z, bh.z), 0.0f));
+        const float4 nl = make_float4(fminf(al.x, bl.x), fminf(al.y, bl.y), fminf(al.z, bl.z), __uint_as_float(height));
+        const float4 nh = make_float4(fmaxf(ah.x, bh.x), fmaxf(ah.y, bh.y), fmaxf(ah.z, bh.z), 0.0f);
+        __stcg(&t.ibox_lo[node], nl);
+        __stcg(&t.ibox_hi[node], nh);
+        node_costs(t, node, L, R, al, ah, bl, bh, box_area(nl, nh), t.cnt[node]);
         node = t.parent[node];
     }
     *max_depth = height;                // only the thread that completes the root gets here
-}
-
-__device__ __forceinline__ double box_area(const float4& lo, const float4& hi) {
-    const double x = (double)hi.x - lo.x, y = (double)hi.y - lo.y, z = (double)hi.z - lo.z;
-    if (x < 0 || y < 0 || z < 0) return 0.0;
-    return 2.0 * (x * y + y * z + z * x);
 }
 
 __device__ __forceinline__ uint32_t exponent_byte(double extent) {     // smallest e with 255 * 2^e >= extent, biased
@@ -244,6 +285,92 @@ __device__ __forceinline__ uint32_t exponent_byte(double extent) {     // smalle
     int biased = e + 127;
     biased = biased < 1 ? 1 : (biased > 254 ? 254 : biased);
     return (uint32_t)biased;
+}
+
+// ---- PLOC: parallel locally-ordered clustering (Meister & Bittner, "Parallel Locally-Ordered Clustering for
+// Bounding Volume Hierarchy Construction", TVCG 2018).  The clusters start as the primitives in Morton order; per
+// round every cluster looks PLOC_RADIUS positions left and right for the neighbour with which it makes the smallest
+// box, mutual choices merge into a new node, and the survivors are compacted in order.  Same node arrays as the
+// radix tree (children are created before parents, so collapse costs are computed at merge time).
+constexpr int PLOC_RADIUS = 16;
+constexpr int PLOC_BLOCK = 256;
+
+struct Ploc {
+    uint32_t* id; float4* lo; float4* hi;              // current clusters (compacted)
+    uint32_t* id2; float4* lo2; float4* hi2;           // next round
+    uint32_t* nn; uint32_t* keep; uint32_t* offset;    // nearest neighbour, survivor flag, exclusive scan of the flags
+    uint32_t* node_counter; uint32_t* m_out;
+};
+
+__global__ void k_ploc_init(Tree t, Ploc p) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= t.n) return;
+    const uint32_t prim = t.sorted[i];
+    p.id[i] = i | LEAF; p.lo[i] = t.box_lo[prim]; p.hi[i] = t.box_hi[prim];
+}
+
+__global__ void __launch_bounds__(PLOC_BLOCK) k_ploc_nearest(Ploc p, uint32_t m) {
+    __shared__ float4 s_lo[PLOC_BLOCK + 2 * PLOC_RADIUS], s_hi[PLOC_BLOCK + 2 * PLOC_RADIUS];
+    const int base = (int)(blockIdx.x * PLOC_BLOCK) - PLOC_RADIUS;
+    for (int k = threadIdx.x; k < PLOC_BLOCK + 2 * PLOC_RADIUS; k += PLOC_BLOCK) {
+        const int g = base + k;
+        if (g >= 0 && g < (int)m) { s_lo[k] = p.lo[g]; s_hi[k] = p.hi[g]; }
+    }
+    __syncthreads();
+    const int i = (int)(blockIdx.x * PLOC_BLOCK + threadIdx.x);
+    if (i >= (int)m) return;
+    const float4 a = s_lo[threadIdx.x + PLOC_RADIUS], b = s_hi[threadIdx.x + PLOC_RADIUS];
+    // total order on unordered pairs {i, j}: merged area, then "j is i's pair partner (i ^ 1)", then (min, max):
+    // the smallest pair overall is a mutual choice, so every round merges, and equal boxes pair up at once
+    float best = INFINITY; int bj = -1; bool bpartner = false;
+    const int j0 = max(i - PLOC_RADIUS, 0), j1 = min(i + PLOC_RADIUS, (int)m - 1);
+    for (int j = j0; j <= j1; j++) {
+        if (j == i) continue;
+        const float4 c = s_lo[j - base], d = s_hi[j - base];
+        const float x = fmaxf(b.x, d.x) - fminf(a.x, c.x), y = fmaxf(b.y, d.y) - fminf(a.y, c.y), z = fmaxf(b.z, d.z) - fminf(a.z, c.z);
+        const float area = x * y + y * z + z * x;
+        const bool partner = j == (i ^ 1);
+        bool better = area < best || bj < 0;
+        if (!better && area == best) {
+            if (partner != bpartner) better = partner;
+            else {
+                const int n0 = min(i, j), n1 = max(i, j), o0 = min(i, bj), o1 = max(i, bj);
+                better = n0 < o0 || (n0 == o0 && n1 < o1);
+            }
+        }
+        if (better) { best = area; bj = j; bpartner = partner; }
+    }
+    p.nn[i] = (uint32_t)bj;
+}
+
+__global__ void k_ploc_merge(Tree t, Ploc p, uint32_t m) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const uint32_t j = p.nn[i];
+    const bool mutual = p.nn[j] == i;
+    if (mutual && i > j) { p.keep[i] = 0u; return; }
+    p.keep[i] = 1u;
+    if (!mutual) return;
+    const uint32_t node = atomicAdd(p.node_counter, 1u);
+    const uint32_t L = p.id[i], R = p.id[j];
+    const float4 al = p.lo[i], ah = p.hi[i], bl = p.lo[j], bh = p.hi[j];
+    const uint32_t hl = (L & LEAF) ? 1u : __float_as_uint(t.ibox_lo[L].w), hr = (R & LEAF) ? 1u : __float_as_uint(t.ibox_lo[R].w);
+    const uint32_t count = node_count(t, L) + node_count(t, R);
+    const float4 nl = make_float4(fminf(al.x, bl.x), fminf(al.y, bl.y), fminf(al.z, bl.z), __uint_as_float(1u + max(hl, hr)));
+    const float4 nh = make_float4(fmaxf(ah.x, bh.x), fmaxf(ah.y, bh.y), fmaxf(ah.z, bh.z), 0.0f);
+    t.left[node] = L; t.right[node] = R; t.cnt[node] = count;
+    t.ibox_lo[node] = nl; t.ibox_hi[node] = nh;
+    node_costs(t, node, L, R, al, ah, bl, bh, box_area(nl, nh), count);
+    p.id[i] = node; p.lo[i] = nl; p.hi[i] = nh;      // only this thread reads slot i's box in this kernel
+}
+
+__global__ void k_ploc_compact(Ploc p, uint32_t m) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    if (i == m - 1) *p.m_out = p.offset[i] + p.keep[i];
+    if (!p.keep[i]) return;
+    const uint32_t d = p.offset[i];
+    p.id2[d] = p.id[i]; p.lo2[d] = p.lo[i]; p.hi2[d] = p.hi[i];
 }
 
 struct Collapse {
@@ -268,13 +395,31 @@ __global__ void k_collapse_level(Tree t, Collapse c, const ptb_packed_mesh_face*
     node_box(t, src, slo, shi);
     auto put = [&](int k, uint32_t id) { item[k] = id; node_box(t, id, ilo[k], ihi[k]); area[k] = box_area(ilo[k], ihi[k]); cnt[k] = node_count(t, id); };
     if (node_count(t, src) <= MAX_LEAF) { put(0, src); m = 1; }
-    else { put(0, t.left[src]); put(1, t.right[src]); m = 2; }
-    while (m < 8) {
-        int best = -1; double ba = -1.0;
-        for (int k = 0; k < m; k++) if (cnt[k] > MAX_LEAF && area[k] > ba) { ba = area[k]; best = k; }
-        if (best < 0) break;
-        const uint32_t id = item[best];
-        put(best, t.left[id]); put(m, t.right[id]); m++;
+    else if (t.greedy) {
+        put(0, t.left[src]); put(1, t.right[src]); m = 2;
+        while (m < 8) {
+            int best = -1; double ba = -1.0;
+            for (int k = 0; k < m; k++) if (cnt[k] > MAX_LEAF && area[k] > ba) { ba = area[k]; best = k; }
+            if (best < 0) break;
+            const uint32_t id = item[best];
+            put(best, t.left[id]); put(m, t.right[id]); m++;
+        }
+    } else {
+        // the optimal 8-slot forest below src
+        uint32_t wn[16]; int ws[16]; int nw = 0;
+        const int k8 = t.dp_split[8 * (size_t)src + 7];
+        wn[nw] = t.right[src]; ws[nw++] = 8 - k8;
+        wn[nw] = t.left[src]; ws[nw++] = k8;
+        while (nw > 0) {
+            const uint32_t id = wn[--nw]; int i = ws[nw];
+            if ((id & LEAF) || i == 1) { put(m++, id); continue; }
+            const uint8_t* sp = t.dp_split + 8 * (size_t)id;
+            while (i > 1 && sp[i - 1] == 0) i--;
+            if (i == 1) { put(m++, id); continue; }
+            const int k = sp[i - 1];
+            wn[nw] = t.right[id]; ws[nw++] = i - k;
+            wn[nw] = t.left[id]; ws[nw++] = k;
+        }
     }
     // octant slot assignment: greedy on (child centre - node centre) . octant sign
     float dx[8], dy[8], dz[8];
@@ -330,9 +475,10 @@ __global__ void k_collapse_level(Tree t, Collapse c, const ptb_packed_mesh_face*
             c.wide_src[next_child++] = item[k];
         } else {
             valid24 |= ((1u << cnt[k]) - 1u) << (3 * s);
-            const uint32_t first = node_first(t, item[k]);
+            static_assert(MAX_LEAF == 2, "a leaf slot is one leaf or a node with two leaf children");
+            const uint32_t pos[2] = {((item[k] & LEAF) ? item[k] : t.left[item[k]]) & ~LEAF, ((item[k] & LEAF) ? 0u : t.right[item[k]]) & ~LEAF};
             for (uint32_t q = 0; q < cnt[k]; q++) {
-                const uint32_t p = t.sorted[first + q];
+                const uint32_t p = t.sorted[pos[q]];
                 const uint32_t shape = __float_as_uint(t.box_lo[p].w), face = __float_as_uint(t.box_hi[p].w), tag = t.tag[p];
                 float4 r0 = make_float4(0, 0, 0, 0), r1 = r0, r2 = r0;
                 if ((tag & 3u) == 0u) { const float4* f = (const float4*)(faces + face); r0 = f[0]; r1 = f[1]; r2 = f[2]; }
@@ -367,7 +513,7 @@ struct Scratch {                  // frees everything it handed out
 #define GB(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { *err = std::string(#x) + ": " + cudaGetErrorString(e_); if (out->nodes) cudaFree(out->nodes); if (out->prims) cudaFree(out->prims); out->nodes = nullptr; out->prims = nullptr; return PTB_E_CUDA; } } while (0)
 
 int build_wide_bvh_gpu(const ptb_scene_view* v, const ptb_packed_shape* d_shapes, const ptb_packed_mesh_face* d_faces,
-                       cudaStream_t st, GpuWideBuild* out, std::string* err) {
+                       cudaStream_t st, int algorithm, GpuWideBuild* out, std::string* err) {
     const auto t0 = std::chrono::steady_clock::now();
     *out = GpuWideBuild();
 
@@ -455,23 +601,53 @@ int build_wide_bvh_gpu(const ptb_scene_view* v, const ptb_packed_shape* d_shapes
     t.n = n; t.keys = dk.Current(); t.sorted = dv.Current();
 
     const uint32_t ni = n > 1 ? n - 1 : 1;
-    GB(mem.get(&t.left, ni)); GB(mem.get(&t.right, ni)); GB(mem.get(&t.first, ni)); GB(mem.get(&t.last, ni));
+    GB(mem.get(&t.left, ni)); GB(mem.get(&t.right, ni)); GB(mem.get(&t.cnt, ni));
     GB(mem.get(&t.parent, (size_t)ni + n)); GB(mem.get(&t.ibox_lo, ni)); GB(mem.get(&t.ibox_hi, ni)); GB(mem.get(&t.visits, ni));
+    GB(mem.get(&t.dp_cost, (size_t)ni * 7)); GB(mem.get(&t.dp_split, (size_t)ni * 8));
+    t.greedy = std::getenv("PTB_LBVH_GREEDY") ? 1u : 0u;
     GB(cudaMemsetAsync(t.visits, 0, (size_t)ni * 4, st));
-    if (n > 1) {
+    uint32_t root = n > 1 ? 0u : LEAF;
+    if (n > 1 && algorithm == 0) {
         k_radix_tree<<<(n - 1 + B - 1) / B, B, 0, st>>>(t);
         k_fit_bounds<<<(n + B - 1) / B, B, 0, st>>>(t, d_small + 1);
+    } else if (n > 1) {
+        Ploc p;
+        GB(mem.get(&p.id, n)); GB(mem.get(&p.lo, n)); GB(mem.get(&p.hi, n));
+        GB(mem.get(&p.id2, n)); GB(mem.get(&p.lo2, n)); GB(mem.get(&p.hi2, n));
+        GB(mem.get(&p.nn, n)); GB(mem.get(&p.keep, n)); GB(mem.get(&p.offset, n));
+        p.node_counter = d_small + 2; p.m_out = d_small + 3;
+        size_t scan_bytes = 0;
+        GB(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, p.keep, p.offset, (int)n, st));
+        char* d_scan;
+        GB(mem.get(&d_scan, scan_bytes));
+        k_ploc_init<<<(n + B - 1) / B, B, 0, st>>>(t, p);
+        uint32_t m = n, rounds = 0;
+        while (m > 1) {
+            const uint32_t g = (m + PLOC_BLOCK - 1) / PLOC_BLOCK;
+            k_ploc_nearest<<<g, PLOC_BLOCK, 0, st>>>(p, m);
+            k_ploc_merge<<<g, PLOC_BLOCK, 0, st>>>(t, p, m);
+            GB(cub::DeviceScan::ExclusiveSum(d_scan, scan_bytes, p.keep, p.offset, (int)m, st));
+            k_ploc_compact<<<g, PLOC_BLOCK, 0, st>>>(p, m);
+            uint32_t next = 0;
+            GB(cudaMemcpyAsync(&next, p.m_out, 4, cudaMemcpyDeviceToHost, st));
+            GB(cudaStreamSynchronize(st));
+            if (next == 0 || next >= m || ++rounds > 4096) { *err = "PLOC made no progress"; return PTB_E_UNSUPPORTED; }
+            if (std::getenv("PTB_BUILD_VERBOSE")) fprintf(stderr, "ploc round %u: %u -> %u\n", rounds, m, next);
+            m = next;
+            std::swap(p.id, p.id2); std::swap(p.lo, p.lo2); std::swap(p.hi, p.hi2);
+        }
+        root = n - 2;                       // the last node created
+        out->rounds = rounds;
     }
 
     Collapse c;
-    c.node_capacity = n / 2 + 16;
+    c.node_capacity = n + 16;           // every wide node stands for a distinct radix-tree node
     uint32_t* big_nodes;
     double* d_sah;
     GB(mem.get(&c.wide_src, c.node_capacity)); GB(mem.get(&big_nodes, (size_t)c.node_capacity * 20)); GB(mem.get(&c.counters, 4)); GB(mem.get(&d_sah, 1));
     c.nodes = big_nodes; c.sah = d_sah;
     GB(cudaMalloc((void**)&out->prims, (size_t)n * 48));
     c.prims = (float4*)out->prims;
-    const uint32_t root = n > 1 ? 0u : LEAF;
     const uint32_t cinit[4] = {1u, 0u, 0u, 0u};
     GB(cudaMemcpyAsync(c.wide_src, &root, 4, cudaMemcpyHostToDevice, st));
     GB(cudaMemcpyAsync(c.counters, cinit, sizeof cinit, cudaMemcpyHostToDevice, st));
@@ -497,14 +673,14 @@ int build_wide_bvh_gpu(const ptb_scene_view* v, const ptb_packed_shape* d_shapes
     float4 rl, rh;
     uint32_t height = 1;
     GB(cudaMemcpyAsync(&sah, d_sah, 8, cudaMemcpyDeviceToHost, st));
-    GB(cudaMemcpyAsync(&height, d_small + 1, 4, cudaMemcpyDeviceToHost, st));
-    if (n > 1) { GB(cudaMemcpyAsync(&rl, t.ibox_lo, 16, cudaMemcpyDeviceToHost, st)); GB(cudaMemcpyAsync(&rh, t.ibox_hi, 16, cudaMemcpyDeviceToHost, st)); }
+    if (n > 1) { GB(cudaMemcpyAsync(&rl, t.ibox_lo + root, 16, cudaMemcpyDeviceToHost, st)); GB(cudaMemcpyAsync(&rh, t.ibox_hi + root, 16, cudaMemcpyDeviceToHost, st)); }
     GB(cudaEventRecord(ev1, st));
     GB(cudaStreamSynchronize(st));
     if (n > 1) {
         const double x = (double)rh.x - rl.x, y = (double)rh.y - rl.y, z = (double)rh.z - rl.z;
         root_area = std::max(2.0 * (x * y + y * z + z * x), 1e-300);
         out->sah_cost = sah / root_area;
+        std::memcpy(&height, &rl.w, 4);
     }
     out->bvh2_depth = height;
     cudaEventElapsedTime(&out->device_ms, ev0, ev1);

@@ -127,15 +127,17 @@ def test_raycast_axis_parallel_and_empty(I, gpu, dev, oracle, scenes):
 
 
 # ---------------------------------------------------------------- GPU builder
+@pytest.mark.parametrize("builder", ["lbvh", "ploc"])
 @pytest.mark.parametrize("name,params", SCENES + [("terrain", (300,)), ("spherefield", (40, 3, 2))])
-def test_gpu_builder_tree_gives_identical_hits(I, gpu, dev, oracle, scenes, name, params):
+def test_gpu_builder_tree_gives_identical_hits(I, gpu, dev, oracle, scenes, name, params, builder):
     """The Morton-order tree built by CUDA kernels culls differently from the host SAH tree, but leaf
     primitives and the canonical rank are the same, so every hit record must be bit-identical —
     and identical to the oracle's brute-force closest hit."""
     sc = scenes(name, *params)
-    g = I.DeviceScene(gpu, sc, builder=I.BUILDER_LBVH_GPU)
+    which = I.BUILDER_LBVH_GPU if builder == "lbvh" else I.BUILDER_PLOC_GPU
+    g = I.DeviceScene(gpu, sc, builder=which)
     gi, hi = g.wide_info(), dev(name, *params).wide_info()
-    assert gi["status"] == 0 and gi["builder"] == I.BUILDER_LBVH_GPU and hi["builder"] == I.BUILDER_SAH_HOST
+    assert gi["status"] == 0 and gi["builder"] == which and hi["builder"] == I.BUILDER_SAH_HOST
     assert gi["prim_count"] == hi["prim_count"] and gi["plane_count"] == hi["plane_count"]
     assert 0 < gi["depth"] <= 30 and gi["node_count"] >= 1
     n = 200000
@@ -160,15 +162,16 @@ def test_gpu_builder_tree_gives_identical_hits(I, gpu, dev, oracle, scenes, name
     assert np.array_equal(bits(outs[0][2]), bits(outs[1][2]))
 
 
-def test_gpu_builder_edge_cases(I, gpu, oracle, scenes):
+@pytest.mark.parametrize("builder", ["lbvh", "ploc"])
+def test_gpu_builder_edge_cases(I, gpu, oracle, scenes, builder):
     """No bounded primitive, one primitive, two primitives, and a rebuild after switching builders."""
     from path_tracer_b200 import scene as S
-    for n_spheres in (0, 1, 2, 3):
+    for n_spheres in (0, 1, 2, 3, 7):
         sc = S.Scene(with_defaults=True)             # checker plane + camera
         for k in range(n_spheres):
             sc.create_entity(S.ENTITY_SPHERE if k != 1 else S.ENTITY_CUBE, position=(2.5 * k - 2.0, 0.3 * k, 1.0), scale=(1.0, 0.7, 1.2))
         sc.pack()
-        g = I.DeviceScene(gpu, sc, builder=I.BUILDER_LBVH_GPU)
+        g = I.DeviceScene(gpu, sc, builder=I.BUILDER_LBVH_GPU if builder == "lbvh" else I.BUILDER_PLOC_GPU)
         info = g.wide_info()
         assert info["status"] == 0 and info["prim_count"] == n_spheres and info["plane_count"] == 1
         rays = random_rays(sc, 20000, 3, oracle)
