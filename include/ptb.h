@@ -225,6 +225,17 @@ int  ptb_scene_wide_info(ptb_scene* scene, ptb_wide_info* out);
 #define PTB_BUILDER_PLOC_GPU 2u
 int  ptb_scene_set_builder(ptb_scene* scene, uint32_t builder);
 
+/* Spectral upsampling (src/core/spectrum.hpp:13-21).
+ * ptb_spectrum_table_build replaces BuildParametricSpectrumTableForSRGB (src/core/spectrum.cpp:365-411,
+ * called from CreateScene when sRGBSpectrumTable.dat is missing, src/scene/scene.cpp:918-927): it fits the
+ * float[3][64][64][64][3] table on the GPU (one warp per column) and writes it to host memory in the layout
+ * SaveParametricSpectrumTable dumps (spectrum.cpp:413-424), so the file stays interchangeable.
+ * ptb_spectrum_upsample is the texel conversion of the atlas packer (src/scene/scene.cpp:1187-1212) over
+ * `texels` RGBA32F values: texture_type 0 raw, 1 reflectance with alpha, 2 radiance. */
+int  ptb_spectrum_table_build(ptb_context* ctx, float* host_table, size_t count_floats, float* device_ms);
+int  ptb_spectrum_upsample(ptb_context* ctx, const float* host_table, size_t count_floats, const float* host_rgba_in,
+                           float* host_rgba_out, size_t texels, uint32_t texture_type);
+
 /* CreateSampleBuffer / DestroySampleBuffer (src/integrator/integrator.hpp:51-53):
  * the RGBA32F accumulator (rgb = sum of CIE XYZ, a = sample count).
  * `external_device_rgba` (may be NULL) lets the caller own the device buffer,

@@ -56,6 +56,12 @@ struct DevBuf {
 
 struct ptb_context { int device; cudaStream_t stream; unsigned* counter; };
 
+namespace ptb {     // for the other translation units of the library (ptb_spectrum.cu)
+int api_fail(int code, const std::string& msg) { return fail(code, msg); }
+cudaStream_t api_stream(ptb_context* ctx) { return ctx->stream; }
+int api_device(ptb_context* ctx) { return ctx->device; }
+}
+
 struct ptb_scene {
     ptb_context* ctx;
     DevBuf<ptb_packed_texture> textures;

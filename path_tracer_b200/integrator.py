@@ -34,6 +34,7 @@ ABI_SYMBOLS = [
     "ptb_renderer_create", "ptb_renderer_destroy", "ptb_renderer_set_params", "ptb_renderer_set_frame_index",
     "ptb_renderer_reset", "ptb_renderer_run", "ptb_renderer_run_frames", "ptb_renderer_profile_frames", "ptb_renderer_sync", "ptb_renderer_stats",
     "ptb_renderer_download_state", "ptb_renderer_slot_count", "ptb_raycast", "ptb_raycast_device", "ptb_preview_render",
+    "ptb_spectrum_table_build", "ptb_spectrum_upsample",
 ]
 
 STATE_ARRAYS = {
@@ -75,6 +76,8 @@ def lib():
         L.ptb_scene_destroy.restype = None
         L.ptb_scene_wide_info.argtypes = [vp, C.POINTER(WideInfo)]
         L.ptb_scene_set_builder.argtypes = [vp, u32]
+        L.ptb_spectrum_table_build.argtypes = [vp, vp, sz, C.POINTER(C.c_float)]
+        L.ptb_spectrum_upsample.argtypes = [vp, vp, sz, vp, vp, sz, u32]
         L.ptb_film_create.argtypes = [vp, u32, u32, vp, C.POINTER(vp)]
         L.ptb_film_destroy.argtypes = [vp]
         L.ptb_film_destroy.restype = None
@@ -135,6 +138,29 @@ class Context:
             self.close()
         except Exception:
             pass
+
+
+SPECTRUM_TABLE_SHAPE = (3, 64, 64, 64, 3)      # float[3][SCALE][COLOR][COLOR][3], spectrum.cpp:413-437
+
+
+def build_spectrum_table(ctx, save_path=None):
+    """BuildParametricSpectrumTableForSRGB on the GPU (spectrum.cpp:365-411).  Returns (table, device_ms);
+    with save_path the table is written in the reference's raw file format."""
+    table = np.zeros(SPECTRUM_TABLE_SHAPE, dtype=np.float32)
+    ms = C.c_float(0.0)
+    _check(lib().ptb_spectrum_table_build(ctx.h, table.ctypes.data, table.size, C.byref(ms)))
+    if save_path:
+        table.tofile(save_path)
+    return table, float(ms.value)
+
+
+def upsample_texels(ctx, table, rgba, texture_type):
+    """The atlas packer's texel conversion (scene.cpp:1187-1212) on the GPU; rgba is (..., 4) float32."""
+    table = np.ascontiguousarray(table, dtype=np.float32)
+    src = np.ascontiguousarray(rgba, dtype=np.float32)
+    out = np.empty_like(src)
+    _check(lib().ptb_spectrum_upsample(ctx.h, table.ctypes.data, table.size, src.ctypes.data, out.ctypes.data, src.size // 4, texture_type))
+    return out
 
 
 class DeviceScene:

@@ -92,9 +92,14 @@ def _f3(v):
     return (C.c_float * len(v))(*[float(x) for x in v])
 
 
-def ensure_spectrum_table():
-    """Loads the sRGB->spectrum table, building it (all host threads) on first use."""
-    return lib().ptbh_ensure_spectrum_table()
+def ensure_spectrum_table(ctx=None):
+    """Loads the sRGB->spectrum table.  When the file is missing it is fitted first: on the GPU through
+    ptb_spectrum_table_build when a Context is given (about 55 ms on a B200), else on all host threads (seconds)."""
+    L = lib()
+    if ctx is not None and not os.path.exists(_build.SPECTRUM_TABLE):
+        from . import integrator
+        integrator.build_spectrum_table(ctx, _build.SPECTRUM_TABLE)
+    return L.ptbh_ensure_spectrum_table()
 
 
 def rgb_to_spectrum(rgb):

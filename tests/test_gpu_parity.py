@@ -184,6 +184,77 @@ def test_gpu_builder_edge_cases(I, gpu, oracle, scenes, builder):
         assert g.raycast(rays, I.TRAVERSAL_WIDE, I.TIE_CANONICAL).tobytes() == out.tobytes()
 
 
+# ---------------------------------------------------------------- spectral upsampling
+def test_spectrum_table_built_on_gpu_matches_host(I, gpu, scenes):
+    """Same Gauss-Newton fits (spectrum.cpp:240-304).  The GPU sums the 471-sample integrals in another order and
+    its pow differs in the last bits, so coefficients are not bit-equal.  Where the fit is well conditioned
+    (scale bins >= 8) the fitted SPECTRA must agree; for the near-black bins below (max component < 0.004, where
+    any spectrum that is ~0 over the visible range fits and the iteration is chaotic) the check is the fit's own
+    criterion: the CIELAB distance to the target colour, which must be as small as the host's."""
+    from path_tracer_b200 import _build
+    from util import d65_observation_weights, xyz_to_lab
+    scenes("cornell")                                   # makes sure the host table exists
+    host = np.fromfile(_build.SPECTRUM_TABLE, dtype=np.float32).reshape(I.SPECTRUM_TABLE_SHAPE)
+    dev_table, ms = I.build_spectrum_table(gpu)
+    assert dev_table.shape == host.shape and np.isfinite(dev_table).all() and ms > 0.0
+    lam, w = d65_observation_weights()
+
+    def spectra(t, l):
+        b = t.reshape(-1, 3).astype(np.float64)
+        x = (b[:, 0:1] * l + b[:, 1:2]) * l + b[:, 2:3]
+        return 0.5 + x / (2.0 * np.sqrt(1.0 + x * x))
+    coarse = np.linspace(360.0, 830.0, 48)
+    diff = np.abs(spectra(dev_table[:, 8:], coarse) - spectra(host[:, 8:], coarse))
+    assert diff.max() <= 2e-3, diff.max()
+    assert diff.mean() <= 1e-5
+
+    # colour-space check on a subsample of every bin, all of the dark bins included
+    def lab_error(t, l, k, j, i):
+        s = k / 63.0
+        s = s * s * (3 - 2 * s)
+        s = s * s * (3 - 2 * s)
+        c = np.zeros(k.shape + (3,))
+        np.put_along_axis(c, l[..., None], 1.0, axis=-1)
+        np.put_along_axis(c, ((l + 1) % 3)[..., None], (i / 63.0)[..., None], axis=-1)
+        np.put_along_axis(c, ((l + 2) % 3)[..., None], (j / 63.0)[..., None], axis=-1)
+        c *= s[..., None]
+        m = np.array([[0.4124, 0.3576, 0.1805], [0.2126, 0.7152, 0.0722], [0.0193, 0.1192, 0.9505]])
+        target = xyz_to_lab(c @ m.T)
+        got = xyz_to_lab(spectra(t[l, k, j, i], lam) @ w)
+        return np.linalg.norm(got - target, axis=-1)
+    l, k, j, i = np.meshgrid(np.arange(3), np.arange(64), np.arange(0, 64, 3), np.arange(0, 64, 3), indexing="ij")
+    l, k, j, i = (a.ravel() for a in (l, k, j, i))
+    eg, eh = lab_error(dev_table, l, k, j, i), lab_error(host, l, k, j, i)
+    assert np.percentile(eg, 99) <= max(np.percentile(eh, 99) * 1.5, 2e-3)
+    assert (eg > np.maximum(2.0 * eh, 5e-3)).mean() <= 2e-3          # no worse than the host's fits, entry by entry
+
+
+def test_texel_upsampling_is_bit_exact_with_the_host_packer(I, gpu, scenes):
+    from path_tracer_b200 import _build, scene as S
+    scenes("cornell")
+    table = np.fromfile(_build.SPECTRUM_TABLE, dtype=np.float32).reshape(I.SPECTRUM_TABLE_SHAPE)
+    rng = np.random.default_rng(5)
+    rgba = rng.uniform(0.0, 1.0, size=(4000, 4)).astype(np.float32)
+    rgba[:50, :3] = 0.0                                 # black (radiance: intensity below threshold)
+    rgba[50:100, :3] = rng.uniform(0.0, 8.0, size=(50, 3)).astype(np.float32)     # HDR / out of gamut: clamped
+    rgba[100:150, 0] = rgba[100:150, 1]                 # ties in the max-component choice
+    rgba[150:160, :3] = 1.0
+    refl = I.upsample_texels(gpu, table, rgba, 1)
+    rad = I.upsample_texels(gpu, table, rgba, 2)
+    raw = I.upsample_texels(gpu, table, rgba, 0)
+    assert raw.tobytes() == rgba.tobytes()
+    for n in range(len(rgba)):
+        want = S.rgb_to_spectrum(rgba[n, :3])
+        assert refl[n, :3].tobytes() == want.tobytes() and refl[n, 3] == rgba[n, 3], n
+        inten = np.float32(2.0) * rgba[n, :3].max()
+        if inten > np.float32(1e-6):
+            want = S.rgb_to_spectrum(rgba[n, :3] / inten)
+            assert rad[n, :3].tobytes() == want.tobytes() and rad[n, 3] == inten, n
+        else:
+            assert not rad[n].any()
+    assert I.upsample_texels(gpu, table, rgba[:0], 1).shape == (0, 4)
+
+
 # ---------------------------------------------------------------- radiance
 def assert_radiance_close(a, b, tol=1e-4, max_outlier_fraction=2e-3):
     """|a-b| <= tol * max(|b|, 1) per channel; a path whose random branch flips on an ulp

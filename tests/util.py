@@ -44,3 +44,33 @@ def unpack_unit_vectors(oracle, packed):
         L.orc_kat_unpack_unit_vector(int(p), tmp)
         out[i] = tmp[:]
     return out
+
+
+def d65_observation_weights():
+    """observer(lambda) * D65(lambda) / 10566.864005 at the 471 integer wavelengths 360..830 nm
+    (spectrum.cpp:137-143,151-176,190-208), float64, for checking fitted spectra in colour space."""
+    import os
+    import re
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "path_tracer_b200", "host", "d65_table.inc")
+    txt = "".join(l for l in open(path) if not l.lstrip().startswith("//"))
+    d65 = np.array([float(x) for x in re.findall(r"([0-9.]+)f", txt)])
+    assert len(d65) == 471
+    lam = np.arange(360.0, 831.0)
+
+    def g(mu, s1, s2):
+        t = (lam - mu) * np.where(lam < mu, s1, s2)
+        return np.exp(-0.5 * t * t)
+    x = 0.362 * g(442.0, 0.0624, 0.0374) + 1.056 * g(599.8, 0.0264, 0.0323) - 0.065 * g(501.1, 0.0490, 0.0382)
+    y = 0.821 * g(568.8, 0.0213, 0.0247) + 0.286 * g(530.9, 0.0613, 0.0322)
+    z = 1.217 * g(437.0, 0.0845, 0.0278) + 0.681 * g(459.0, 0.0385, 0.0725)
+    return lam, np.stack([x, y, z], axis=1) * (d65 / 10566.864005)[:, None]
+
+
+def xyz_to_lab(c):
+    """spectrum.cpp:213-233 (L driven by f(X), as the reference has it)."""
+    d = 6 / 29.0
+
+    def f(t):
+        return np.where(t > d ** 3, np.cbrt(np.maximum(t, 0.0)), t / (3 * d * d) + 4 / 29.0)
+    fx, fy, fz = f(c[..., 0] / 0.950489), f(c[..., 1]), f(c[..., 2] / 1.088840)
+    return np.stack([116.0 * fx - 16.0, 500.0 * (fx - fy), 200.0 * (fy - fz)], axis=-1)
