@@ -135,6 +135,40 @@ void* ptbh_scene_mesh(void* s, uint32_t i) { return ((scene*)s)->Meshes[i]; }
 // Face vertex indices after the builder reordered them (nf x 3).
 void ptbh_mesh_faces(void* m, uint32_t* out) { mesh* M = (mesh*)m; std::memcpy(out, M->Faces.data(), M->Faces.size() * sizeof(mesh_face)); }
 
+// ---- model import, prefabs, image files (model.cpp) ----
+// vertex_transform: 16 floats column-major or NULL (identity; also used for normals with w = 0).
+void* ptbh_load_model(void* s, const char* path, const char* name, void* default_material, const float* vertex_transform) {
+    load_model_options O;
+    O.Name = name && name[0] ? name : nullptr;
+    O.DefaultMaterial = (material*)default_material;
+    if (vertex_transform) {
+        std::memcpy((void*)&O.VertexTransform, vertex_transform, 64);
+        mat4 N = O.VertexTransform;                       // rotation/scale part for directions
+        N.c[3] = {0, 0, 0, 1};
+        O.NormalTransform = N;
+    }
+    return LoadModelAsPrefab((scene*)s, path, &O);
+}
+void* ptbh_create_prefab_instance(void* s, void* prefab_, void* parent) { return CreateEntity((scene*)s, (prefab*)prefab_, (entity*)parent); }
+void ptbh_destroy_prefab(void* s, void* prefab_) { DestroyPrefab((scene*)s, (prefab*)prefab_); }
+uint32_t ptbh_prefab_mesh_count(void* prefab_) {
+    entity* E = ((prefab*)prefab_)->Entity;
+    return E->Type == ENTITY_TYPE_MESH_INSTANCE ? 1u : (uint32_t)E->Children.size();
+}
+void* ptbh_load_texture(void* s, const char* path, int type, const char* name) { return LoadTexture((scene*)s, path, (texture_type)type, name && name[0] ? name : nullptr); }
+int ptbh_write_png(const char* path, uint32_t w, uint32_t h, const uint8_t* rgba) { return WriteImagePNG(path, w, h, rgba) ? 0 : -1; }
+int ptbh_write_pfm(const char* path, uint32_t w, uint32_t h, const float* rgb) { return WriteImagePFM(path, w, h, rgb) ? 0 : -1; }
+uint32_t ptbh_mesh_vertex_count(void* m) { return (uint32_t)((mesh*)m)->Vertices.size(); }
+// nv x 8 floats (px,py,pz, nx,ny,nz, u,v)
+void ptbh_mesh_vertices(void* m, float* out) {
+    mesh* M = (mesh*)m;
+    for (size_t i = 0; i < M->Vertices.size(); i++) {
+        const mesh_vertex& V = M->Vertices[i];
+        float* o = out + 8 * i;
+        o[0] = V.Position.x; o[1] = V.Position.y; o[2] = V.Position.z; o[3] = V.Normal.x; o[4] = V.Normal.y; o[5] = V.Normal.z; o[6] = V.UV.x; o[7] = V.UV.y;
+    }
+}
+
 // 4x4 helpers exposed for unit tests of the matrix kit.
 void ptbh_make_transform(const float* pos, const float* rot, const float* scale, float* out16) {
     mat4 m = make_transform({pos[0], pos[1], pos[2]}, {rot[0], rot[1], rot[2]}, {scale[0], scale[1], scale[2]});

@@ -247,6 +247,7 @@ scene* CreateScene(bool WithDefaults) {
 // scene.cpp:945-959
 void DestroyScene(scene* Scene) {
     while (!Scene->Root.Children.empty()) DestroyEntity(Scene, Scene->Root.Children[0]);
+    while (!Scene->Prefabs.empty()) DestroyPrefab(Scene, Scene->Prefabs.back());
     for (mesh* M : Scene->Meshes) delete M;
     for (material* M : Scene->Materials) delete M;
     for (texture* T : Scene->Textures) delete T;

@@ -119,8 +119,20 @@ struct entity {
     mesh* Mesh = nullptr;
 };
 
+struct prefab { entity* Entity = nullptr; };            // scene.hpp:318-321
+
+struct load_model_options {        // scene.hpp:381-389
+    char const* Name = nullptr;
+    material*   DefaultMaterial = nullptr;
+    std::string DirectoryPath;                          // empty: the directory of the model file
+    mat4        VertexTransform = mat4::identity();
+    mat4        NormalTransform = mat4::identity();
+    float       TextureCoordinateTransform[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};   // column-major mat3
+};
+
 struct scene {                     // scene.hpp:335-362
     entity Root;
+    std::vector<prefab*> Prefabs;
     std::vector<mesh*> Meshes;
     std::vector<material*> Materials;
     std::vector<texture*> Textures;
@@ -158,6 +170,14 @@ mesh* CreateMesh(scene* Scene, char const* Name, std::vector<mesh_vertex>&& Vert
 // CreateMesh in two steps, so that independent meshes can be built on several threads and attached in order.
 mesh* BuildMesh(char const* Name, std::vector<mesh_vertex>&& Vertices, std::vector<mesh_face>&& Faces);
 mesh* AttachMesh(scene* Scene, mesh* M);
+// Model import and prefabs (scene.hpp:415,428-429; model.cpp).  Wavefront OBJ + MTL; textures from PPM/PFM files.
+texture* LoadTexture(scene* Scene, char const* Path, texture_type Type, char const* Name = nullptr);
+prefab* LoadModelAsPrefab(scene* Scene, char const* Path, load_model_options* Options = nullptr);
+entity* CreateEntity(scene* Scene, prefab* Prefab, entity* Parent = nullptr);
+void DestroyPrefab(scene* Scene, prefab* Prefab);
+// Image files for the resolved film (the reference presents to a swapchain and has no writer).
+bool WriteImagePNG(char const* Path, uint32_t Width, uint32_t Height, uint8_t const* RGBA);
+bool WriteImagePFM(char const* Path, uint32_t Width, uint32_t Height, float const* RGB);
 // CreateScene (scene.cpp:912-943).  WithDefaults adds the reference's default
 // checker plane + camera.  The RGB->spectrum table is process-wide (see below).
 scene* CreateScene(bool WithDefaults = true);

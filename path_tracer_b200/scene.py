@@ -71,6 +71,20 @@ def lib():
         L.ptbh_scene_mesh.restype = vp
         L.ptbh_scene_mesh.argtypes = [vp, u32]
         L.ptbh_mesh_faces.argtypes = [vp, C.POINTER(u32)]
+        L.ptbh_load_model.restype = vp
+        L.ptbh_load_model.argtypes = [vp, C.c_char_p, C.c_char_p, vp, f32p]
+        L.ptbh_create_prefab_instance.restype = vp
+        L.ptbh_create_prefab_instance.argtypes = [vp, vp, vp]
+        L.ptbh_destroy_prefab.argtypes = [vp, vp]
+        L.ptbh_prefab_mesh_count.restype = u32
+        L.ptbh_prefab_mesh_count.argtypes = [vp]
+        L.ptbh_load_texture.restype = vp
+        L.ptbh_load_texture.argtypes = [vp, C.c_char_p, C.c_int, C.c_char_p]
+        L.ptbh_write_png.argtypes = [C.c_char_p, u32, u32, vp]
+        L.ptbh_write_pfm.argtypes = [C.c_char_p, u32, u32, vp]
+        L.ptbh_mesh_vertex_count.restype = u32
+        L.ptbh_mesh_vertex_count.argtypes = [vp]
+        L.ptbh_mesh_vertices.argtypes = [vp, f32p]
         L.ptbh_set_spectrum_table_path.argtypes = [C.c_char_p]
         L.ptbh_rgb_to_spectrum.argtypes = [f32p, f32p]
         L.ptbh_fit_spectrum.argtypes = [f32p, f32p]
@@ -112,6 +126,20 @@ def fit_spectrum(rgb):
     out = (C.c_float * 3)()
     lib().ptbh_fit_spectrum(_f3(rgb), out)
     return np.array(out[:], dtype=np.float32)
+
+
+def write_png(path, srgb8):
+    """The resolved 8-bit frame (H, W, 4) as a PNG file (the reference presents to a swapchain instead)."""
+    a = np.ascontiguousarray(srgb8, dtype=np.uint8)
+    if lib().ptbh_write_png(os.fsencode(path), a.shape[1], a.shape[0], a.ctypes.data) != 0:
+        raise OSError("cannot write " + str(path))
+
+
+def write_pfm(path, linear_rgb):
+    """Linear float RGB (H, W, 3) as a PFM file."""
+    a = np.ascontiguousarray(linear_rgb, dtype=np.float32)
+    if lib().ptbh_write_pfm(os.fsencode(path), a.shape[1], a.shape[0], a.ctypes.data) != 0:
+        raise OSError("cannot write " + str(path))
 
 
 def _view_array(ptr, count, dtype):
@@ -212,6 +240,53 @@ class Scene:
         f = np.ascontiguousarray(faces, dtype=np.uint32)
         return self._L.ptbh_create_mesh(self.h, name.encode(), v.ctypes.data_as(C.POINTER(C.c_float)), n,
                                         f.ctypes.data_as(C.POINTER(C.c_uint32)), len(f))
+
+    # -- model import and prefabs (scene.hpp:415,428-429) --
+    def load_model(self, path, name=None, default_material=None, vertex_transform=None):
+        """LoadModelAsPrefab: Wavefront OBJ (+ MTL) -> prefab handle.  vertex_transform: 4x4 column-major or None."""
+        vt = None
+        if vertex_transform is not None:
+            vt = np.ascontiguousarray(vertex_transform, dtype=np.float32).reshape(16).ctypes.data_as(C.POINTER(C.c_float))
+        p = self._L.ptbh_load_model(self.h, os.fsencode(path), (name or "").encode(), default_material, vt)
+        if not p:
+            raise OSError("cannot load model " + str(path))
+        return p
+
+    def create_prefab_instance(self, prefab, parent=None, position=None, rotation=(0, 0, 0), scale=(1, 1, 1)):
+        e = self._L.ptbh_create_prefab_instance(self.h, prefab, parent)
+        if position is not None:
+            self._L.ptbh_entity_set_transform(self.h, e, _f3(position), _f3(rotation), _f3(scale))
+        return e
+
+    def destroy_prefab(self, prefab):
+        self._L.ptbh_destroy_prefab(self.h, prefab)
+
+    def prefab_mesh_count(self, prefab):
+        return self._L.ptbh_prefab_mesh_count(prefab)
+
+    def load_texture(self, path, ttype, name=None):
+        """LoadTexture for PPM (P6, sRGB-encoded) and PFM (linear float) files."""
+        t = self._L.ptbh_load_texture(self.h, os.fsencode(path), ttype, (name or "").encode())
+        if not t:
+            raise OSError("cannot load texture " + str(path))
+        return t
+
+    def source_mesh_vertices(self, i=0):
+        m = self._L.ptbh_scene_mesh(self.h, i)
+        out = np.zeros((self._L.ptbh_mesh_vertex_count(m), 8), dtype=np.float32)
+        if len(out):
+            self._L.ptbh_mesh_vertices(m, out.ctypes.data_as(C.POINTER(C.c_float)))
+        return out
+
+    def mesh_count(self):
+        return self._L.ptbh_scene_mesh_count(self.h)
+
+    def atlas_layer(self, i=0):
+        v = self.view
+        n = v.AtlasWidth * v.AtlasHeight * 4
+        ptrs = (C.c_void_p * v.AtlasLayerCount).from_address(v.AtlasLayers)
+        buf = (C.c_float * n).from_address(ptrs[i])
+        return np.frombuffer(buf, dtype=np.float32).reshape(v.AtlasHeight, v.AtlasWidth, 4)
 
     def shape_index(self, e):
         return self._L.ptbh_entity_shape_index(e)
