@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(ROOT)
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
-HOST_SOURCES = ["scene.cpp", "pack.cpp", "spectrum.cpp", "procedural.cpp", "model.cpp", "capi.cpp"]
+HOST_SOURCES = ["scene.cpp", "pack.cpp", "spectrum.cpp", "procedural.cpp", "model.cpp", "serializer.cpp", "capi.cpp"]
 CUDA_SOURCES = ["ptb_api.cu", "ptb_kernels.cu", "ptb_gpu_build.cu", "ptb_spectrum.cu", "ptb_wide_build.cpp"]
 
 SPECTRUM_TABLE = os.path.join(ROOT, "data", "sRGBSpectrumTable.dat")
@@ -39,7 +39,7 @@ def build_scene(force=False):
     out = os.path.join(ROOT, "libptb_scene.so")
     deps = [os.path.join(d, f) for f in os.listdir(d)] + [os.path.join(REPO, "include", "ptb.h")]
     if force or _newer(out, deps):
-        _run(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-pthread", "-shared", "-o", out] + HOST_SOURCES, d)
+        _run(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-pthread", "-shared", "-o", out] + HOST_SOURCES + ["-lz"], d)
     return out
 
 

@@ -169,6 +169,12 @@ void ptbh_mesh_vertices(void* m, float* out) {
     }
 }
 
+// ---- scene files (serializer.cpp) ----
+static thread_local std::string g_io_error;
+const char* ptbh_last_error() { return g_io_error.c_str(); }
+int ptbh_save_scene(void* s, const char* path) { return SaveScene(path, (scene*)s, &g_io_error) ? 0 : -1; }
+void* ptbh_load_scene(const char* path) { return LoadScene(path, &g_io_error); }
+
 // 4x4 helpers exposed for unit tests of the matrix kit.
 void ptbh_make_transform(const float* pos, const float* rot, const float* scale, float* out16) {
     mat4 m = make_transform({pos[0], pos[1], pos[2]}, {rot[0], rot[1], rot[2]}, {scale[0], scale[1], scale[2]});

@@ -178,6 +178,9 @@ void DestroyPrefab(scene* Scene, prefab* Prefab);
 // Image files for the resolved film (the reference presents to a swapchain and has no writer).
 bool WriteImagePNG(char const* Path, uint32_t Width, uint32_t Height, uint8_t const* RGBA);
 bool WriteImagePFM(char const* Path, uint32_t Width, uint32_t Height, float const* RGB);
+// Scene files (scene.hpp:432-433; serializer.cpp): the reference's JSON + zlib side-file format.
+scene* LoadScene(char const* Path, std::string* Error = nullptr);
+bool SaveScene(char const* Path, scene* Scene, std::string* Error = nullptr);
 // CreateScene (scene.cpp:912-943).  WithDefaults adds the reference's default
 // checker plane + camera.  The RGB->spectrum table is process-wide (see below).
 scene* CreateScene(bool WithDefaults = true);

@@ -85,6 +85,10 @@ def lib():
         L.ptbh_mesh_vertex_count.restype = u32
         L.ptbh_mesh_vertex_count.argtypes = [vp]
         L.ptbh_mesh_vertices.argtypes = [vp, f32p]
+        L.ptbh_last_error.restype = C.c_char_p
+        L.ptbh_save_scene.argtypes = [vp, C.c_char_p]
+        L.ptbh_load_scene.restype = vp
+        L.ptbh_load_scene.argtypes = [C.c_char_p]
         L.ptbh_set_spectrum_table_path.argtypes = [C.c_char_p]
         L.ptbh_rgb_to_spectrum.argtypes = [f32p, f32p]
         L.ptbh_fit_spectrum.argtypes = [f32p, f32p]
@@ -168,6 +172,19 @@ class Scene:
         if not h:
             raise ValueError("unknown scene " + name)
         return cls(handle=h)
+
+    # -- LoadScene / SaveScene (scene.hpp:432-433): the reference's JSON + side-file format --
+    @classmethod
+    def load(cls, path):
+        h = lib().ptbh_load_scene(os.fsencode(path))
+        if not h:
+            raise OSError(lib().ptbh_last_error().decode(errors="replace"))
+        return cls(handle=h)
+
+    def save(self, path):
+        os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+        if self._L.ptbh_save_scene(self.h, os.fsencode(path)) != 0:
+            raise OSError(self._L.ptbh_last_error().decode(errors="replace"))
 
     def close(self):
         if self.h:
