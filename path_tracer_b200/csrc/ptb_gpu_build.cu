@@ -497,15 +497,27 @@ __global__ void k_collapse_level(Tree t, Collapse c, const ptb_packed_mesh_face*
     atomicAdd(c.sah, sah);
 }
 
-struct Scratch {                  // frees everything it handed out
+// Scratch memory of one build: one cudaMalloc sized from the primitive count, handed out by bumping a pointer
+// (a build makes ~35 arrays; that many cudaMalloc/cudaFree pairs cost more than the kernels at 1 M triangles).
+// Requests that do not fit fall back to their own allocation.  Frees everything it handed out.
+struct Scratch {
+    char* pool = nullptr; size_t pool_bytes = 0, used = 0;
     std::vector<void*> ptrs;
+    cudaError_t reserve(size_t bytes) {
+        cudaError_t e = cudaMalloc((void**)&pool, bytes);
+        if (e != cudaSuccess) { pool = nullptr; cudaGetLastError(); return cudaSuccess; }     // no pool: individual allocations
+        pool_bytes = bytes;
+        return cudaSuccess;
+    }
     template <class T> cudaError_t get(T** p, size_t count) {
+        const size_t bytes = ((count ? count : 1) * sizeof(T) + 255) & ~(size_t)255;
+        if (pool && used + bytes <= pool_bytes) { *p = (T*)(pool + used); used += bytes; return cudaSuccess; }
         *p = nullptr;
-        cudaError_t e = cudaMalloc((void**)p, (count ? count : 1) * sizeof(T));
+        cudaError_t e = cudaMalloc((void**)p, bytes);
         if (e == cudaSuccess) ptrs.push_back(*p);
         return e;
     }
-    ~Scratch() { for (void* p : ptrs) cudaFree(p); }
+    ~Scratch() { for (void* p : ptrs) cudaFree(p); if (pool) cudaFree(pool); }
 };
 
 }  // namespace
@@ -556,6 +568,8 @@ int build_wide_bvh_gpu(const ptb_scene_view* v, const ptb_packed_shape* d_shapes
     if (N == 0) { out->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); return PTB_OK; }
 
     Scratch mem;
+    // per primitive: boxes 32 + tag 4 + keys 16 + values 8 + tree 92 + collapse 84 (+ PLOC clusters 84) bytes, plus sort/scan scratch
+    mem.reserve((size_t)N * (algorithm == 0 ? 240 : 324) + ((size_t)S * 20) + (32u << 20));
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     GB(cudaEventCreate(&ev0)); GB(cudaEventCreate(&ev1));
     struct EvGuard { cudaEvent_t a, b; ~EvGuard() { cudaEventDestroy(a); cudaEventDestroy(b); } } evg{ev0, ev1};
