@@ -292,7 +292,7 @@ __device__ __forceinline__ uint32_t exponent_byte(double extent) {     // smalle
 // round every cluster looks PLOC_RADIUS positions left and right for the neighbour with which it makes the smallest
 // box, mutual choices merge into a new node, and the survivors are compacted in order.  Same node arrays as the
 // radix tree (children are created before parents, so collapse costs are computed at merge time).
-constexpr int PLOC_RADIUS = 16;
+constexpr int PLOC_RADIUS_MAX = 128;
 constexpr int PLOC_BLOCK = 256;
 
 struct Ploc {
@@ -309,8 +309,8 @@ __global__ void k_ploc_init(Tree t, Ploc p) {
     p.id[i] = i | LEAF; p.lo[i] = t.box_lo[prim]; p.hi[i] = t.box_hi[prim];
 }
 
-__global__ void __launch_bounds__(PLOC_BLOCK) k_ploc_nearest(Ploc p, uint32_t m) {
-    __shared__ float4 s_lo[PLOC_BLOCK + 2 * PLOC_RADIUS], s_hi[PLOC_BLOCK + 2 * PLOC_RADIUS];
+__global__ void __launch_bounds__(PLOC_BLOCK) k_ploc_nearest(Ploc p, uint32_t m, int PLOC_RADIUS) {
+    __shared__ float4 s_lo[PLOC_BLOCK + 2 * PLOC_RADIUS_MAX], s_hi[PLOC_BLOCK + 2 * PLOC_RADIUS_MAX];
     const int base = (int)(blockIdx.x * PLOC_BLOCK) - PLOC_RADIUS;
     for (int k = threadIdx.x; k < PLOC_BLOCK + 2 * PLOC_RADIUS; k += PLOC_BLOCK) {
         const int g = base + k;
@@ -634,11 +634,13 @@ int build_wide_bvh_gpu(const ptb_scene_view* v, const ptb_packed_shape* d_shapes
         GB(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, p.keep, p.offset, (int)n, st));
         char* d_scan;
         GB(mem.get(&d_scan, scan_bytes));
+        int radius = 64;           // profiles/r01_v9_ploc_radius_sweep.txt: C4 trace 2.59 ms at 16, 2.45 at 64, 2.47 at 128; C2 indifferent
+        if (const char* e = std::getenv("PTB_PLOC_RADIUS")) radius = std::max(1, std::min(PLOC_RADIUS_MAX, std::atoi(e)));
         k_ploc_init<<<(n + B - 1) / B, B, 0, st>>>(t, p);
         uint32_t m = n, rounds = 0;
         while (m > 1) {
             const uint32_t g = (m + PLOC_BLOCK - 1) / PLOC_BLOCK;
-            k_ploc_nearest<<<g, PLOC_BLOCK, 0, st>>>(p, m);
+            k_ploc_nearest<<<g, PLOC_BLOCK, 0, st>>>(p, m, radius);
             k_ploc_merge<<<g, PLOC_BLOCK, 0, st>>>(t, p, m);
             GB(cub::DeviceScan::ExclusiveSum(d_scan, scan_bytes, p.keep, p.offset, (int)m, st));
             k_ploc_compact<<<g, PLOC_BLOCK, 0, st>>>(p, m);
