@@ -224,6 +224,9 @@ int  ptb_scene_wide_info(ptb_scene* scene, ptb_wide_info* out);
 #define PTB_BUILDER_LBVH_GPU 1u
 #define PTB_BUILDER_PLOC_GPU 2u
 int  ptb_scene_set_builder(ptb_scene* scene, uint32_t builder);
+/* Debug/test: copies the flattened tree to the host (20 words per node, 12 floats per leaf primitive; layout in
+ * csrc/ptb_wide.cuh) so that a checker can verify it structurally.  Counts come from ptb_scene_wide_info. */
+int  ptb_scene_wide_download(ptb_scene* scene, uint32_t* host_nodes, size_t node_words, float* host_prims, size_t prim_floats);
 
 /* Spectral upsampling (src/core/spectrum.hpp:13-21).
  * ptb_spectrum_table_build replaces BuildParametricSpectrumTableForSRGB (src/core/spectrum.cpp:365-411,

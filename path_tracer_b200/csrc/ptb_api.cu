@@ -316,6 +316,17 @@ int ptb_scene_set_builder(ptb_scene* s, uint32_t builder) {
     s->builder = builder;
     return PTB_OK;
 }
+int ptb_scene_wide_download(ptb_scene* s, uint32_t* host_nodes, size_t node_words, float* host_prims, size_t prim_floats) {
+    if (!s) return fail(PTB_E_INVALID, "ptb_scene_wide_download: NULL scene");
+    if (s->wide_info.status != PTB_OK) return fail(PTB_E_UNSUPPORTED, "ptb_scene_wide_download: no wide BVH");
+    if (node_words != (size_t)s->wide_info.node_count * 20 || prim_floats != (size_t)s->wide_info.prim_count * 12)
+        return fail(PTB_E_INVALID, "ptb_scene_wide_download: sizes do not match ptb_scene_wide_info");
+    CU(cudaSetDevice(s->ctx->device));
+    CU(cudaStreamSynchronize(s->ctx->stream));
+    if (node_words) CU(cudaMemcpy(host_nodes, s->wide_nodes.p, node_words * 4, cudaMemcpyDeviceToHost));
+    if (prim_floats) CU(cudaMemcpy(host_prims, s->wide_prims.p, prim_floats * 4, cudaMemcpyDeviceToHost));
+    return PTB_OK;
+}
 int ptb_scene_wide_info(ptb_scene* s, ptb_wide_info* out) {
     if (!s || !out) return fail(PTB_E_INVALID, "ptb_scene_wide_info: NULL argument");
     *out = s->wide_info;

@@ -28,7 +28,7 @@ from .types import (KernelTimes, PreviewParams, PREVIEW_MODES, RenderParams, Res
 ABI_SYMBOLS = [
     "ptb_last_error", "ptb_version",
     "ptb_context_create", "ptb_context_destroy", "ptb_context_sync", "ptb_context_stream",
-    "ptb_scene_create", "ptb_scene_update", "ptb_scene_destroy", "ptb_scene_wide_info", "ptb_scene_set_builder",
+    "ptb_scene_create", "ptb_scene_update", "ptb_scene_destroy", "ptb_scene_wide_info", "ptb_scene_set_builder", "ptb_scene_wide_download",
     "ptb_film_create", "ptb_film_destroy", "ptb_film_device_accum", "ptb_film_download_accum", "ptb_film_upload_accum",
     "ptb_film_resolve", "ptb_film_resolve_device",
     "ptb_renderer_create", "ptb_renderer_destroy", "ptb_renderer_set_params", "ptb_renderer_set_frame_index",
@@ -76,6 +76,7 @@ def lib():
         L.ptb_scene_destroy.restype = None
         L.ptb_scene_wide_info.argtypes = [vp, C.POINTER(WideInfo)]
         L.ptb_scene_set_builder.argtypes = [vp, u32]
+        L.ptb_scene_wide_download.argtypes = [vp, vp, sz, vp, sz]
         L.ptb_spectrum_table_build.argtypes = [vp, vp, sz, C.POINTER(C.c_float)]
         L.ptb_spectrum_upsample.argtypes = [vp, vp, sz, vp, vp, sz, u32]
         L.ptb_film_create.argtypes = [vp, u32, u32, vp, C.POINTER(vp)]
@@ -183,6 +184,14 @@ class DeviceScene:
     def set_builder(self, builder):
         """BUILDER_SAH_HOST (default), BUILDER_LBVH_GPU or BUILDER_PLOC_GPU: who flattens the scene at the next update."""
         _check(lib().ptb_scene_set_builder(self.h, builder))
+
+    def wide_download(self):
+        """(nodes[N, 20] uint32, prims[P, 12] float32) of the flattened tree, for structural checks."""
+        info = self.wide_info()
+        nodes = np.zeros((info["node_count"], 20), dtype=np.uint32)
+        prims = np.zeros((info["prim_count"], 12), dtype=np.float32)
+        _check(lib().ptb_scene_wide_download(self.h, nodes.ctypes.data, nodes.size, prims.ctypes.data, prims.size))
+        return nodes, prims
 
     def wide_info(self):
         w = WideInfo()

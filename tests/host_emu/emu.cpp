@@ -71,6 +71,12 @@ void* emu_create(const ptb_scene_view* v, u32 w, u32 h) {
 void emu_destroy(void* p) { delete (Emu*)p; }
 void emu_wide_info(void* p, u32* out) { Emu* e = (Emu*)p; out[0] = e->wb.node_count; out[1] = e->wb.prim_count; out[2] = e->wb.depth; out[3] = e->wb.bvh2_depth; out[4] = (u32)(e->wb.build_seconds * 1000); }
 
+void emu_wide_download(void* p, u32* nodes, float* prims) {
+    Emu* e = (Emu*)p;
+    memcpy(nodes, e->wb.nodes.data(), (size_t)e->wb.node_count * 80);
+    memcpy(prims, e->wb.prims.data(), (size_t)e->wb.prim_count * 48);
+}
+
 void emu_raycast(void* p, const ptb_ray* rays, uint64_t n, int mode, ptb_hit* out) {
     Emu* e = (Emu*)p;
     parallel_for(n, 1024, [&](uint64_t b, uint64_t en) {

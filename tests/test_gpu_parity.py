@@ -140,6 +140,11 @@ def test_gpu_builder_tree_gives_identical_hits(I, gpu, dev, oracle, scenes, name
     assert gi["status"] == 0 and gi["builder"] == which and hi["builder"] == I.BUILDER_SAH_HOST
     assert gi["prim_count"] == hi["prim_count"] and gi["plane_count"] == hi["plane_count"]
     assert 0 < gi["depth"] <= 30 and gi["node_count"] >= 1
+    # structure: every primitive once, every slot box contains everything below it (all three builders)
+    from util import check_wide_tree
+    for d in (g, dev(name, *params)):
+        nodes, prims = d.wide_download()
+        assert check_wide_tree(nodes, prims, sc.shapes) == d.wide_info()["depth"]
     n = 200000
     rays = random_rays(sc, n, 11, oracle)
     a = g.raycast(rays, I.TRAVERSAL_WIDE, I.TIE_CANONICAL)

@@ -30,6 +30,7 @@ def emu():
     L.emu_destroy.argtypes = [C.c_void_p]
     L.emu_raycast.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
     L.emu_wide_info.argtypes = [C.c_void_p, C.c_void_p]
+    L.emu_wide_download.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.emu_set.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float, C.c_uint32]
     L.emu_reset.argtypes = [C.c_void_p]
     L.emu_run.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_int]
@@ -81,6 +82,11 @@ def test_wide_flattening_equals_brute_force(emu, oracle, scenes, name, params):
     info = (C.c_uint32 * 5)()
     emu.emu_wide_info(e, info)
     assert info[2] <= 30                                    # depth fits the traversal stack
+    # structure: every primitive once, every child slot box contains the world bounds of everything below it
+    from util import check_wide_tree
+    nodes, prims = np.zeros((info[0], 20), np.uint32), np.zeros((info[1], 12), np.float32)
+    emu.emu_wide_download(e, nodes.ctypes.data, prims.ctypes.data)
+    assert check_wide_tree(nodes, prims, sc.shapes) == info[2]
     n = 6000
     rays = random_rays(sc, n, 21, oracle)
     # axis-parallel and signed-zero directions are the classic slab-test traps

@@ -74,3 +74,90 @@ def xyz_to_lab(c):
         return np.where(t > d ** 3, np.cbrt(np.maximum(t, 0.0)), t / (3 * d * d) + 4 / 29.0)
     fx, fy, fz = f(c[..., 0] / 0.950489), f(c[..., 1]), f(c[..., 2] / 1.088840)
     return np.stack([116.0 * fx - 16.0, 500.0 * (fx - fy), 200.0 * (fy - fz)], axis=-1)
+
+
+def check_wide_tree(nodes, prims, shapes):
+    """Structural check of a flattened BVH8 (layout: csrc/ptb_wide.cuh): every node reachable once, every leaf
+    primitive referenced once, and every child slot's dequantised box CONTAINS the world-space bounds of
+    everything below it (so culling can never lose a hit).  Returns the depth.  numpy, level by level."""
+    n_nodes, n_prims = len(nodes), len(prims)
+    if n_nodes == 0:
+        assert n_prims == 0
+        return 0
+    # world bounds of the leaf primitives (float64, exact transform of float32 inputs)
+    tag = prims[:, 11].view(np.uint32)
+    shape = prims[:, 7].view(np.uint32)
+    kind = tag & 3
+    to = shapes["To"].reshape(-1, 4, 4).astype(np.float64)            # column-major: to[s, col, row]
+    corners = np.array([[(c & 1) * 2 - 1, ((c >> 1) & 1) * 2 - 1, ((c >> 2) & 1) * 2 - 1] for c in range(8)], np.float64)
+    plo = np.full((n_prims, 3), np.inf)
+    phi = np.full((n_prims, 3), -np.inf)
+    m = to[shape]
+    for pts in ([prims[:, 0:3], prims[:, 4:7], prims[:, 8:11]], [np.broadcast_to(c, (n_prims, 3)) for c in corners]):
+        tri = pts is not None and len(pts) == 3
+        sel = (kind == 0) if tri else (kind != 0)
+        for p in pts:
+            w = np.einsum("nk,nkr->nr", np.asarray(p, np.float64), m[:, :3, :3]) + m[:, 3, :3]
+            plo[sel] = np.minimum(plo[sel], w[sel])
+            phi[sel] = np.maximum(phi[sel], w[sel])
+    w3 = nodes[:, 3]
+    scale = np.stack([np.ldexp(1.0, ((w3 >> (8 * a)) & 0xFF).astype(np.int64) - 127) for a in range(3)], axis=1)
+    origin = nodes[:, 0:3].view(np.float32).astype(np.float64)
+    imask = (w3 >> 24) & 0xFF
+    q = nodes[:, 8:20].copy().view(np.uint8).reshape(n_nodes, 6, 8).astype(np.float64)   # [node, qlo xyz | qhi xyz, slot]
+    slot_lo = origin[:, :, None] + q[:, 0:3, :] * scale[:, :, None]
+    slot_hi = origin[:, :, None] + q[:, 3:6, :] * scale[:, :, None]
+    valid24 = nodes[:, 6]
+    # top-down: levels and parent slots; bottom-up: true bounds
+    level = [np.array([0])]
+    seen_nodes = np.zeros(n_nodes, bool)
+    seen_nodes[0] = True
+    seen_prims = np.zeros(n_prims, np.int64)
+    child_of = {}
+    while True:
+        cur = level[-1]
+        nxt = []
+        for s in range(8):
+            inner = cur[(imask[cur] >> s) & 1 == 1]
+            if len(inner):
+                rel = np.array([bin(int(x) & ((1 << s) - 1)).count("1") for x in imask[inner]])
+                ch = nodes[inner, 4] + rel
+                assert ch.max() < n_nodes and not seen_nodes[ch].any() and len(np.unique(ch)) == len(ch)
+                seen_nodes[ch] = True
+                child_of[s] = child_of.get(s, []) + [(inner, ch)]
+                nxt.append(ch)
+        if not nxt:
+            break
+        level.append(np.concatenate(nxt))
+        assert len(level) <= 64
+    assert seen_nodes.all()
+    blo = np.full((n_nodes, 3), np.inf)
+    bhi = np.full((n_nodes, 3), -np.inf)
+    for cur in reversed(level):
+        for s in range(8):
+            bits = (valid24[cur] >> (3 * s)) & 7
+            leaf = cur[bits != 0]
+            if len(leaf):
+                assert ((imask[leaf] >> s) & 1 == 0).all()
+                below = np.array([bin(int(v) & ((1 << (3 * s)) - 1)).count("1") for v in valid24[leaf]])
+                for k in range(3):
+                    has = leaf[((valid24[leaf] >> (3 * s + k)) & 1) == 1]
+                    if not len(has):
+                        continue
+                    off = below[((valid24[leaf] >> (3 * s + k)) & 1) == 1] + np.array(
+                        [bin(int(v >> (3 * s)) & ((1 << k) - 1)).count("1") for v in valid24[has]])
+                    pi = nodes[has, 5] + off
+                    assert pi.max() < n_prims
+                    np.add.at(seen_prims, pi, 1)
+                    assert (slot_lo[has, :, s] <= plo[pi]).all() and (slot_hi[has, :, s] >= phi[pi]).all(), "leaf slot box misses its primitive"
+                    np.minimum.at(blo, has, plo[pi])
+                    np.maximum.at(bhi, has, phi[pi])
+            inner = cur[(imask[cur] >> s) & 1 == 1]
+            if len(inner):
+                rel = np.array([bin(int(x) & ((1 << s) - 1)).count("1") for x in imask[inner]])
+                ch = nodes[inner, 4] + rel
+                assert (slot_lo[inner, :, s] <= blo[ch]).all() and (slot_hi[inner, :, s] >= bhi[ch]).all(), "inner slot box misses its subtree"
+                np.minimum.at(blo, inner, blo[ch])
+                np.maximum.at(bhi, inner, bhi[ch])
+    assert (seen_prims == 1).all()
+    return len(level)
