@@ -154,7 +154,7 @@ def run_reference(args, rank, world):
     rays, paths = s1["rays"] - s0["rays"], s1["paths"] - s0["paths"]
     mrays = rays / dt / 1e6
     sample = "every %d-th 16x16 tile of the %dx%d film (%d rays/frame), %d frames/step" % (stride, WIDTH, HEIGHT, rays // max(1, args.steps * args.ref_frames), args.ref_frames)
-    print(json.dumps({
+    _emit(({
         "impl": "reference", "metric": "Mrays/s (ray segments traced, whole job)", "value": mrays, "unit": "Mrays/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -166,7 +166,31 @@ def run_reference(args, rank, world):
     }))
 
 
+_RESULT_FD = None
+
+
+def _claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version line on the first
+    communicator), so everything else is sent to stderr and the result line goes to the original descriptor."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def _emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_RESULT_FD, line)
+
+
 def main():
+    _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=40)
@@ -373,7 +397,7 @@ def main():
         "roofline": roofline,
         "cpu_baseline": cpu,
     }
-    print(json.dumps(out))
+    _emit(out)
 
 
 if __name__ == "__main__":
