@@ -89,5 +89,26 @@ def build_cuda(force=False, verbose=False):
     return out
 
 
+def build_experiment(tag, defines):
+    """A/B builds: build_exp/libptb_<tag>.so from the same sources with extra -D macros (loaded through PTB_LIB)."""
+    d = os.path.join(ROOT, "csrc")
+    objdir = os.path.join(REPO, "build_exp", tag)
+    os.makedirs(objdir, exist_ok=True)
+    out = os.path.join(REPO, "build_exp", "libptb_%s.so" % tag)
+    objs, procs = [], []
+    for src in CUDA_SOURCES:
+        obj = os.path.join(objdir, src + ".o")
+        objs.append(obj)
+        cmd = [NVCC] + cuda_flags() + ["-D" + x for x in defines] + ["-I", os.path.join(REPO, "include"), "-I", d, "-c", "-o", obj, src]
+        procs.append((cmd, subprocess.Popen(cmd, cwd=d, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    for cmd, p in procs:
+        log = p.communicate()[0]
+        if p.returncode != 0:
+            sys.stderr.write(log)
+            raise RuntimeError("build failed: " + " ".join(cmd))
+    _run([NVCC, "-shared", "-cudart", "static", "-gencode", "arch=compute_100a,code=sm_100a", "-o", out] + objs, d)
+    return out
+
+
 def build_all(force=False):
     return build_scene(force), build_cuda(force)

@@ -504,6 +504,16 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
 #ifndef PTB_SCATTER_MIN_BLOCKS
 #define PTB_SCATTER_MIN_BLOCKS (1024 / PTB_SCATTER_THREADS)
 #endif
+// L2 prefetch distance of the direct scatter kernel, in blocks (0 = off).  A block's seven state records are seven
+// contiguous 4 KB runs; one thread asks the L2 for the runs of the block that will start about half a wave of
+// resident blocks later (148 SMs x 4 blocks / 2), with one bulk-prefetch instruction per run (TMA unit, no registers,
+// no shared memory).  The kernel's loads then find their lines in L2 instead of waiting on HBM.
+#ifndef PTB_SCATTER_PREFETCH_BLOCKS
+#define PTB_SCATTER_PREFETCH_BLOCKS 296
+#endif
+__device__ __forceinline__ void prefetch_l2_bulk(const void* p, u32 bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p), "r"(bytes) : "memory");
+}
 // FEATURES: compile-time scene-feature mask (PTB_FEAT_*).  The fully general kernel is ~300 KB of
 // SASS; with mixed materials its divergent warps thrash the instruction cache (ncu: 45 no_instruction
 // stall cycles per issue on C3, profiles/r01_c3_scatter_generic.txt).  Two remedies, both here:
@@ -533,6 +543,17 @@ k_scatter(const DeviceScene scene, const RenderConsts pc, const WavefrontState s
     u32 slot = first + threadIdx.x;
     u32 x, y;
     bool valid = slot_pixel(pc, slot, x, y);
+#if PTB_SCATTER_PREFETCH_BLOCKS > 0
+    if (threadIdx.x == 0) {
+        const u32 ahead = first + (u32)PTB_SCATTER_PREFETCH_BLOCKS * (u32)PTB_SCATTER_THREADS;
+        if (ahead + (u32)PTB_SCATTER_THREADS <= pc.slot_base + pc.slot_count) {
+            const u32 bytes = (u32)PTB_SCATTER_THREADS * 16u;
+            prefetch_l2_bulk(st.hit0 + ahead, bytes); prefetch_l2_bulk(st.hit1 + ahead, bytes); prefetch_l2_bulk(st.ray + ahead, bytes);
+            prefetch_l2_bulk(st.path0 + ahead, bytes); prefetch_l2_bulk(st.path1 + ahead, bytes);
+            prefetch_l2_bulk(st.path2 + ahead, bytes); prefetch_l2_bulk(st.path3 + ahead, bytes);
+        }
+    }
+#endif
 #if PTB_SCATTER_SORT
     // Hits and misses run different code (BSDF sampling vs sky + new camera path): the block's slots are dealt to
     // its threads hits first, so that all but one warp of a block are uniform.  The block still covers the same
