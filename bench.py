@@ -202,7 +202,7 @@ def main():
     ap.add_argument("--trace-variant", type=int, default=-1, help="PTB_TRACE_VARIANT_* (default: the library's)")
     ap.add_argument("--scatter-mode", default="auto", choices=["auto", "direct", "queues"])
     ap.add_argument("--pipelines", type=int, default=0, choices=[0, 1, 2], help="0 = the library's choice")
-    ap.add_argument("--builder", default="sah-host", choices=["sah-host", "lbvh-gpu", "ploc-gpu"], help="who flattens the scene into the BVH8 (ptb_scene_set_builder)")
+    ap.add_argument("--builder", default="sah-host", choices=["sah-host", "lbvh-gpu", "ploc-gpu", "auto"], help="who flattens the scene into the BVH8 (ptb_scene_set_builder)")
     ap.add_argument("--grid", type=int, default=GRID)
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS), help="BASELINE.json config (default C2, the one the metric is quoted on)")
     ap.add_argument("--ref-frames", type=int, default=8, help="frames per step of the CPU reference arm")
@@ -234,7 +234,7 @@ def main():
     S.ensure_spectrum_table()
     scene = S.Scene.make(SCENE_NAME, *SCENE_PARAMS)
     ctx = I.Context(local_rank)
-    dscene = I.DeviceScene(ctx, scene, builder={"sah-host": I.BUILDER_SAH_HOST, "lbvh-gpu": I.BUILDER_LBVH_GPU, "ploc-gpu": I.BUILDER_PLOC_GPU}[args.builder])
+    dscene = I.DeviceScene(ctx, scene, builder={"sah-host": I.BUILDER_SAH_HOST, "lbvh-gpu": I.BUILDER_LBVH_GPU, "ploc-gpu": I.BUILDER_PLOC_GPU, "auto": I.BUILDER_AUTO}[args.builder])
     wide = dscene.wide_info()
     film_t = torch.zeros((HEIGHT, WIDTH, 4), dtype=torch.float32, device=device)       # torch owns the film so NCCL can reduce it
     torch.cuda.synchronize()

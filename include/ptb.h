@@ -218,11 +218,16 @@ int  ptb_scene_wide_info(ptb_scene* scene, ptb_wide_info* out);
  *             slowest to traverse).
  *   PLOC_GPU  locally-ordered agglomerative clustering on the Morton order as CUDA kernels (tens of
  *             milliseconds per 10 M triangles; between the two in traversal speed).
+ *   AUTO      both: first image after milliseconds, full traversal speed once the host build is done.
  * Hits are bit-identical whichever builder ran: the tree only culls.
  * If the GPU builder cannot represent a scene (tree deeper than the traversal stack) the host builder runs. */
 #define PTB_BUILDER_SAH_HOST 0u
 #define PTB_BUILDER_LBVH_GPU 1u
 #define PTB_BUILDER_PLOC_GPU 2u
+#define PTB_BUILDER_AUTO     3u   /* PLOC_GPU at once; a host thread then builds the SAH_HOST tree from the device copies of
+                                   * the packed arrays and the next call that traverses the scene swaps it in (one stream
+                                   * synchronise).  Results do not change at the swap.  ptb_scene_wide_info reports the
+                                   * builder of the tree in use. */
 int  ptb_scene_set_builder(ptb_scene* scene, uint32_t builder);
 /* Debug/test: copies the flattened tree to the host (20 words per node, 12 floats per leaf primitive; layout in
  * csrc/ptb_wide.cuh) so that a checker can verify it structurally.  Counts come from ptb_scene_wide_info. */

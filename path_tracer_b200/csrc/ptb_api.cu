@@ -7,8 +7,11 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <atomic>
 #include <cstring>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "ptb.h"
@@ -62,8 +65,24 @@ cudaStream_t api_stream(ptb_context* ctx) { return ctx->stream; }
 int api_device(ptb_context* ctx) { return ctx->device; }
 }
 
+// PTB_BUILDER_AUTO: the tree built on the GPU is in use at once; a host thread builds the SAH tree from the device
+// copies of the packed arrays and parks it here until the next call that uses the scene swaps it in.  Any tree gives
+// bit-identical hits (leaf primitives and the canonical rank are the same), so the swap is invisible in the results.
+struct TreeUpgrade {
+    std::thread th;
+    std::mutex mu;                       // device copies of shapes / faces / mesh nodes vs. re-upload; the hand-over below
+    bool running = false;                // under mu
+    uint64_t wanted = 0;                 // under mu: generation of the scene geometry
+    std::atomic<int> ready{0};           // 1: nodes/prims below hold the tree of generation `wanted`
+    std::atomic<bool> quit{false};
+    uint32_t* nodes = nullptr; float* prims = nullptr;
+    uint32_t node_count = 0, prim_count = 0, depth = 0, bvh2_depth = 0;
+    double sah_cost = 0.0, build_seconds = 0.0;
+};
+
 struct ptb_scene {
     ptb_context* ctx;
+    TreeUpgrade* upgrade;
     DevBuf<ptb_packed_texture> textures;
     DevBuf<uint32_t> materials;
     DevBuf<ptb_packed_shape> shapes;
@@ -103,6 +122,104 @@ struct ptb_renderer {
     cudaEvent_t ev_fork, ev_join;
     uint64_t rays_traced, kernel_launches;
 };
+
+static void upgrade_thread(ptb_scene* s) {
+    TreeUpgrade* u = s->upgrade;
+    cudaSetDevice(s->ctx->device);
+    for (;;) {
+        uint64_t gen;
+        std::vector<ptb_packed_shape> shapes;
+        std::vector<ptb_packed_mesh_face> faces;
+        std::vector<ptb_packed_mesh_node> nodes;
+        bool ok = true;
+        {
+            std::lock_guard<std::mutex> l(u->mu);
+            gen = u->wanted;
+            shapes.resize(s->shapes.n); faces.resize(s->faces.n); nodes.resize(s->mesh_nodes.n);
+            ok = ok && (shapes.empty() || cudaMemcpy(shapes.data(), s->shapes.p, shapes.size() * sizeof shapes[0], cudaMemcpyDeviceToHost) == cudaSuccess);
+            ok = ok && (faces.empty() || cudaMemcpy(faces.data(), s->faces.p, faces.size() * sizeof faces[0], cudaMemcpyDeviceToHost) == cudaSuccess);
+            ok = ok && (nodes.empty() || cudaMemcpy(nodes.data(), s->mesh_nodes.p, nodes.size() * sizeof nodes[0], cudaMemcpyDeviceToHost) == cudaSuccess);
+        }
+        WideBuild wb;
+        std::string err;
+        if (ok) {
+            ptb_scene_view v;
+            std::memset(&v, 0, sizeof v);
+            v.Shapes = shapes.data(); v.ShapeCount = (uint32_t)shapes.size();
+            v.MeshFaces = faces.data(); v.MeshFaceCount = (uint32_t)faces.size();
+            v.MeshNodes = nodes.data(); v.MeshNodeCount = (uint32_t)nodes.size();
+            ok = build_wide_bvh(&v, &wb, &err) == PTB_OK;
+        }
+        uint32_t* d_nodes = nullptr; float* d_prims = nullptr;
+        if (ok && !u->quit.load() && wb.node_count) {
+            ok = cudaMalloc((void**)&d_nodes, wb.nodes.size() * 4) == cudaSuccess && cudaMalloc((void**)&d_prims, wb.prims.size() * 4) == cudaSuccess
+              && cudaMemcpy(d_nodes, wb.nodes.data(), wb.nodes.size() * 4, cudaMemcpyHostToDevice) == cudaSuccess
+              && cudaMemcpy(d_prims, wb.prims.data(), wb.prims.size() * 4, cudaMemcpyHostToDevice) == cudaSuccess;
+        }
+        std::lock_guard<std::mutex> l(u->mu);
+        if (ok && !u->quit.load() && u->wanted == gen && wb.node_count) {
+            u->nodes = d_nodes; u->prims = d_prims;
+            u->node_count = wb.node_count; u->prim_count = wb.prim_count; u->depth = wb.depth; u->bvh2_depth = wb.bvh2_depth;
+            u->sah_cost = wb.sah_cost; u->build_seconds = wb.build_seconds;
+            u->ready.store(1);
+            u->running = false;
+            return;
+        }
+        if (d_nodes) cudaFree(d_nodes);
+        if (d_prims) cudaFree(d_prims);
+        if (u->quit.load() || !ok || u->wanted == gen) { u->running = false; return; }      // failed or nothing to build: the GPU tree stays
+        // the geometry changed while this tree was being built: build the new one
+    }
+}
+
+// Called (host thread of the API) after a GPU build has been installed for new geometry.
+static void upgrade_request(ptb_scene* s) {
+    if (!s->upgrade) s->upgrade = new TreeUpgrade();
+    TreeUpgrade* u = s->upgrade;
+    bool start = false;
+    {
+        std::lock_guard<std::mutex> l(u->mu);
+        u->wanted++;
+        if (u->ready.exchange(0)) { cudaFree(u->nodes); cudaFree(u->prims); u->nodes = nullptr; u->prims = nullptr; }   // a tree of the old geometry
+        if (!u->running) { u->running = true; start = true; }
+    }
+    if (start) {
+        if (u->th.joinable()) u->th.join();
+        u->th = std::thread(upgrade_thread, s);
+    }
+}
+
+// Swaps a finished host-built tree in.  Called at the top of every entry point that traverses the scene.
+static int upgrade_poll(ptb_scene* s) {
+    TreeUpgrade* u = s->upgrade;
+    if (!u || !u->ready.load()) return PTB_OK;
+    CU(cudaSetDevice(s->ctx->device));
+    CU(cudaStreamSynchronize(s->ctx->stream));          // no kernel may still be walking the old tree
+    std::lock_guard<std::mutex> l(u->mu);
+    if (!u->ready.exchange(0)) return PTB_OK;
+    s->wide_nodes.release(); s->wide_prims.release();
+    s->wide_nodes.p = u->nodes; s->wide_nodes.n = (size_t)u->node_count * 20;
+    s->wide_prims.p = u->prims; s->wide_prims.n = (size_t)u->prim_count * 12;
+    u->nodes = nullptr; u->prims = nullptr;
+    s->ds.wide_nodes = (const uint4*)s->wide_nodes.p;
+    s->ds.wide_tris = (const float4*)s->wide_prims.p;
+    s->wide_info.node_count = u->node_count; s->wide_info.prim_count = u->prim_count;
+    s->wide_info.depth = u->depth; s->wide_info.bvh2_depth = u->bvh2_depth;
+    s->wide_info.sah_cost = u->sah_cost; s->wide_info.build_seconds = u->build_seconds;
+    s->wide_info.builder = PTB_BUILDER_SAH_HOST; s->wide_info.device_build_ms = 0.0f;
+    return PTB_OK;
+}
+
+static void upgrade_shutdown(ptb_scene* s) {
+    TreeUpgrade* u = s->upgrade;
+    if (!u) return;
+    u->quit.store(true);
+    if (u->th.joinable()) u->th.join();
+    if (u->nodes) cudaFree(u->nodes);
+    if (u->prims) cudaFree(u->prims);
+    delete u;
+    s->upgrade = nullptr;
+}
 
 // PTB_SCATTER_AUTO: material queues pay when a warp would otherwise meet several materials' code.
 static bool use_queues(const ptb_renderer* r) {
@@ -176,13 +293,14 @@ int ptb_scene_create(ptb_context* ctx, ptb_scene** out) {
     if (!ctx || !out) return fail(PTB_E_INVALID, "ptb_scene_create: NULL argument");
     ptb_scene* s = new ptb_scene();
     s->ctx = ctx;
+    s->upgrade = nullptr;
     std::memset(&s->ds, 0, sizeof s->ds);
     std::memset(&s->wide_info, 0, sizeof s->wide_info);
     s->ds.wide_tlas_root = 0xFFFFFFFFu;
     s->ds.globals.SkyboxTextureIndex = 0xFFFFFFFFu;
     s->raycast_variant = PTB_TRACE_VARIANT_DEFAULT;
     s->builder = PTB_BUILDER_SAH_HOST;
-    if (const char* e = std::getenv("PTB_BUILDER")) s->builder = std::atoi(e) == 1 ? PTB_BUILDER_LBVH_GPU : std::atoi(e) == 2 ? PTB_BUILDER_PLOC_GPU : PTB_BUILDER_SAH_HOST;
+    if (const char* e = std::getenv("PTB_BUILDER")) s->builder = std::atoi(e) == 1 ? PTB_BUILDER_LBVH_GPU : std::atoi(e) == 2 ? PTB_BUILDER_PLOC_GPU : std::atoi(e) == 3 ? PTB_BUILDER_AUTO : PTB_BUILDER_SAH_HOST;
     s->material_features = 0;
     *out = s;
     return PTB_OK;
@@ -217,6 +335,9 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
             s->material_features |= type == 0u ? PTB_FEAT_DIFFUSE : type == 1u ? PTB_FEAT_METAL : type == 2u ? PTB_FEAT_TRANSLUCENT : 0u;
         }
     }
+    // a background tree build reads the device copies of shapes / faces / mesh nodes
+    std::unique_lock<std::mutex> geometry_lock;
+    if (s->upgrade && (dirty & (PTB_SCENE_DIRTY_SHAPES | PTB_SCENE_DIRTY_MESHES))) geometry_lock = std::unique_lock<std::mutex>(s->upgrade->mu);
     if (dirty & PTB_SCENE_DIRTY_SHAPES) {
         CU(s->shapes.upload(v->Shapes, v->ShapeCount, st));
         CU(s->shape_nodes.upload(v->ShapeNodes, v->ShapeNodeCount, st));
@@ -231,6 +352,7 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
         s->ds.mesh_vertices = s->vertices.p;
         s->ds.mesh_nodes = s->mesh_nodes.p; s->ds.mesh_node_count = v->MeshNodeCount;
     }
+    if (geometry_lock.owns_lock()) { CU(cudaStreamSynchronize(st)); geometry_lock.unlock(); }
     if (dirty & PTB_SCENE_DIRTY_CAMERAS) {
         CU(s->cameras.upload(v->Cameras, v->CameraCount, st));
         s->ds.cameras = s->cameras.p; s->ds.camera_count = v->CameraCount;
@@ -245,12 +367,17 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
         std::string err;
         int rc = PTB_E_UNSUPPORTED;
         bool built = false;
-        if (s->builder == PTB_BUILDER_LBVH_GPU || s->builder == PTB_BUILDER_PLOC_GPU) {
+        const bool gpu_builder = s->builder == PTB_BUILDER_LBVH_GPU || s->builder == PTB_BUILDER_PLOC_GPU || s->builder == PTB_BUILDER_AUTO;
+        if (s->upgrade && s->upgrade->ready.load()) {        // a host-built tree of the previous geometry was never used
+            std::lock_guard<std::mutex> l(s->upgrade->mu);
+            if (s->upgrade->ready.exchange(0)) { cudaFree(s->upgrade->nodes); cudaFree(s->upgrade->prims); s->upgrade->nodes = nullptr; s->upgrade->prims = nullptr; }
+        }
+        if (gpu_builder) {
             // needs the device copies of the shapes and faces this very update may not have refreshed
             if (!(dirty & PTB_SCENE_DIRTY_SHAPES)) CU(s->shapes.upload(v->Shapes, v->ShapeCount, st));
             if (!(dirty & PTB_SCENE_DIRTY_MESHES)) CU(s->faces.upload(v->MeshFaces, v->MeshFaceCount, st));
             GpuWideBuild gb;
-            rc = build_wide_bvh_gpu(v, s->shapes.p, s->faces.p, st, s->builder == PTB_BUILDER_PLOC_GPU ? 1 : 0, &gb, &err);
+            rc = build_wide_bvh_gpu(v, s->shapes.p, s->faces.p, st, s->builder == PTB_BUILDER_LBVH_GPU ? 0 : 1, &gb, &err);
             if (rc == PTB_OK) {
                 s->wide_nodes.release(); s->wide_prims.release();
                 s->wide_nodes.p = gb.nodes; s->wide_nodes.n = (size_t)gb.node_count * 20;
@@ -263,8 +390,14 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
                 s->wide_info.plane_count = s->ds.wide_plane_count;
                 s->wide_info.depth = gb.depth; s->wide_info.bvh2_depth = gb.bvh2_depth;
                 s->wide_info.sah_cost = gb.sah_cost; s->wide_info.build_seconds = gb.build_seconds;
-                s->wide_info.builder = s->builder; s->wide_info.device_build_ms = gb.device_ms;
+                s->wide_info.builder = s->builder == PTB_BUILDER_LBVH_GPU ? PTB_BUILDER_LBVH_GPU : PTB_BUILDER_PLOC_GPU;
+                s->wide_info.device_build_ms = gb.device_ms;
                 built = true;
+                if (s->builder == PTB_BUILDER_AUTO && gb.node_count) {
+                    if (!(dirty & PTB_SCENE_DIRTY_MESHES)) CU(s->mesh_nodes.upload(v->MeshNodes, v->MeshNodeCount, st));
+                    CU(cudaStreamSynchronize(st));
+                    upgrade_request(s);
+                }
             }
         }
         if (!built) {
@@ -303,6 +436,7 @@ void ptb_scene_destroy(ptb_scene* s) {
     if (!s) return;
     cudaSetDevice(s->ctx->device);
     cudaStreamSynchronize(s->ctx->stream);
+    upgrade_shutdown(s);
     s->textures.release(); s->materials.release(); s->shapes.release(); s->shape_nodes.release();
     s->faces.release(); s->vertices.release(); s->mesh_nodes.release(); s->cameras.release();
     for (auto& l : s->layers) l.release();
@@ -312,12 +446,13 @@ void ptb_scene_destroy(ptb_scene* s) {
 
 int ptb_scene_set_builder(ptb_scene* s, uint32_t builder) {
     if (!s) return fail(PTB_E_INVALID, "ptb_scene_set_builder: NULL scene");
-    if (builder != PTB_BUILDER_SAH_HOST && builder != PTB_BUILDER_LBVH_GPU && builder != PTB_BUILDER_PLOC_GPU) return fail(PTB_E_INVALID, "ptb_scene_set_builder: unknown builder");
+    if (builder > PTB_BUILDER_AUTO) return fail(PTB_E_INVALID, "ptb_scene_set_builder: unknown builder");
     s->builder = builder;
     return PTB_OK;
 }
 int ptb_scene_wide_download(ptb_scene* s, uint32_t* host_nodes, size_t node_words, float* host_prims, size_t prim_floats) {
     if (!s) return fail(PTB_E_INVALID, "ptb_scene_wide_download: NULL scene");
+    { int rc = upgrade_poll(s); if (rc) return rc; }
     if (s->wide_info.status != PTB_OK) return fail(PTB_E_UNSUPPORTED, "ptb_scene_wide_download: no wide BVH");
     if (node_words != (size_t)s->wide_info.node_count * 20 || prim_floats != (size_t)s->wide_info.prim_count * 12)
         return fail(PTB_E_INVALID, "ptb_scene_wide_download: sizes do not match ptb_scene_wide_info");
@@ -329,6 +464,7 @@ int ptb_scene_wide_download(ptb_scene* s, uint32_t* host_nodes, size_t node_word
 }
 int ptb_scene_wide_info(ptb_scene* s, ptb_wide_info* out) {
     if (!s || !out) return fail(PTB_E_INVALID, "ptb_scene_wide_info: NULL argument");
+    { int rc = upgrade_poll(s); if (rc) return rc; }
     *out = s->wide_info;
     return PTB_OK;
 }
@@ -455,6 +591,7 @@ int ptb_renderer_set_frame_index(ptb_renderer* r, uint32_t f) {
 }
 
 static int prepare(ptb_renderer* r) {
+    { int rc = upgrade_poll(r->scene); if (rc) return rc; }
     const DeviceScene& ds = r->scene->ds;
     if (r->params.CameraIndex >= ds.camera_count) return fail(PTB_E_INVALID, "renderer: CameraIndex out of range");
     if (r->params.Traversal == PTB_TRAVERSAL_WIDE && ds.shape_count > 0 && r->scene->wide_info.status != PTB_OK)
@@ -670,6 +807,7 @@ int ptb_renderer_download_state(ptb_renderer* r, const char* name, void* host, s
 // ---- ray cast harness ----
 int ptb_raycast(ptb_scene* s, const ptb_ray* host_rays, size_t n, uint32_t traversal, uint32_t tie, ptb_hit* host_hits) {
     if (!s || (n && (!host_rays || !host_hits))) return fail(PTB_E_INVALID, "ptb_raycast: NULL argument");
+    { int rc = upgrade_poll(s); if (rc) return rc; }
     if (traversal > PTB_TRAVERSAL_WIDE || tie > PTB_TIE_CANONICAL) return fail(PTB_E_INVALID, "ptb_raycast: unknown enum value");
     if (traversal == PTB_TRAVERSAL_WIDE && tie != PTB_TIE_CANONICAL) return fail(PTB_E_INVALID, "ptb_raycast: the wide traversal needs PTB_TIE_CANONICAL");
     if (traversal == PTB_TRAVERSAL_WIDE && s->ds.shape_count > 0 && s->wide_info.status != PTB_OK) return fail(PTB_E_UNSUPPORTED, "ptb_raycast: wide BVH unavailable");
@@ -691,6 +829,7 @@ int ptb_raycast(ptb_scene* s, const ptb_ray* host_rays, size_t n, uint32_t trave
 
 int ptb_raycast_device(ptb_scene* s, const ptb_ray* d_rays, size_t n, uint32_t traversal, uint32_t tie, ptb_hit* d_hits) {
     if (!s || (n && (!d_rays || !d_hits))) return fail(PTB_E_INVALID, "ptb_raycast_device: NULL argument");
+    { int rc = upgrade_poll(s); if (rc) return rc; }
     if (traversal > PTB_TRAVERSAL_WIDE || tie > PTB_TIE_CANONICAL) return fail(PTB_E_INVALID, "ptb_raycast_device: unknown enum value");
     if (traversal == PTB_TRAVERSAL_WIDE && tie != PTB_TIE_CANONICAL) return fail(PTB_E_INVALID, "ptb_raycast_device: the wide traversal needs PTB_TIE_CANONICAL");
     if (traversal == PTB_TRAVERSAL_WIDE && s->ds.shape_count > 0 && s->wide_info.status != PTB_OK) return fail(PTB_E_UNSUPPORTED, "ptb_raycast_device: wide BVH unavailable");
@@ -701,6 +840,7 @@ int ptb_raycast_device(ptb_scene* s, const ptb_ray* d_rays, size_t n, uint32_t t
 
 int ptb_preview_render(ptb_scene* s, const ptb_preview_params* p, float* host_rgba, uint32_t* host_shapes, uint32_t* hit_shape) {
     if (!s || !p || !host_rgba) return fail(PTB_E_INVALID, "ptb_preview_render: NULL argument");
+    { int rc = upgrade_poll(s); if (rc) return rc; }
     if (p->RenderMode > PTB_PREVIEW_MODE_SCENE_COMPLEXITY || p->Traversal > PTB_TRAVERSAL_WIDE) return fail(PTB_E_INVALID, "ptb_preview_render: unknown mode");
     if (p->Traversal == PTB_TRAVERSAL_WIDE && s->wide_info.status != PTB_OK) return fail(PTB_E_UNSUPPORTED, "ptb_preview_render: wide BVH unavailable");
     const size_t n = (size_t)p->RenderSizeX * p->RenderSizeY;

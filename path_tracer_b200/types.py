@@ -62,7 +62,7 @@ class WideInfo(C.Structure):
                 ("bvh2_depth", u32), ("sah_cost", C.c_double), ("build_seconds", C.c_double), ("builder", u32), ("device_build_ms", C.c_float)]
 
 
-BUILDER_SAH_HOST, BUILDER_LBVH_GPU, BUILDER_PLOC_GPU = 0, 1, 2
+BUILDER_SAH_HOST, BUILDER_LBVH_GPU, BUILDER_PLOC_GPU, BUILDER_AUTO = 0, 1, 2, 3
 
 
 # numpy record layouts of the packed arrays (src/scene/scene.hpp:82-173)

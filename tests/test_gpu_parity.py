@@ -189,6 +189,53 @@ def test_gpu_builder_edge_cases(I, gpu, oracle, scenes, builder):
         assert g.raycast(rays, I.TRAVERSAL_WIDE, I.TIE_CANONICAL).tobytes() == out.tobytes()
 
 
+def test_auto_builder_swaps_the_host_tree_in_without_changing_results(I, gpu, dev, oracle, scenes):
+    """BUILDER_AUTO: the GPU tree is usable at once, the host SAH tree arrives later from a background thread and is
+    swapped in between calls.  The film of a render that straddles the swap is bit-identical to a render on either tree."""
+    import time
+    name, params = "terrain", (300,)
+    sc = scenes(name, *params)
+    d = I.DeviceScene(gpu, sc, builder=I.BUILDER_AUTO)
+    first = d.wide_info()
+    assert first["status"] == 0
+    film = I.SampleBuffer(gpu, 128, 64)
+    r = I.BasicRenderer(gpu, d, film)
+    r.set_frame_index(4)
+    r.reset()
+    r.run(2)
+    r.run_frames(3)                                         # most likely still on the GPU-built tree
+    seen = {first["builder"]}
+    t0 = time.time()
+    while d.wide_info()["builder"] != I.BUILDER_SAH_HOST and time.time() - t0 < 60.0:
+        time.sleep(0.02)
+    seen.add(d.wide_info()["builder"])
+    assert I.BUILDER_SAH_HOST in seen                       # the upgrade arrived
+    r.run_frames(3)
+    r.sync()
+    ref_film = I.SampleBuffer(gpu, 128, 64)
+    rr = I.BasicRenderer(gpu, dev(name, *params), ref_film)
+    rr.set_frame_index(4)
+    rr.reset()
+    rr.run(2)
+    rr.run_frames(6)
+    assert np.array_equal(film.download(), ref_film.download())
+    hi = dev(name, *params).wide_info()
+    now = d.wide_info()
+    assert now["node_count"] == hi["node_count"] and now["prim_count"] == hi["prim_count"]
+    # edits while a build is in flight: the stale tree is dropped, the newest geometry wins
+    other = scenes("terrain", 64)
+    d.update(sc)
+    d.update(other)
+    rays = random_rays(other, 50000, 2, oracle)
+    a = d.raycast(rays)
+    t0 = time.time()
+    while d.wide_info()["builder"] != I.BUILDER_SAH_HOST and time.time() - t0 < 60.0:
+        time.sleep(0.02)
+    assert d.wide_info()["builder"] == I.BUILDER_SAH_HOST and d.wide_info()["prim_count"] == 2 * 64 * 64
+    assert d.raycast(rays).tobytes() == a.tobytes() == dev("terrain", 64).raycast(rays).tobytes()
+    d.close() if hasattr(d, "close") else None
+
+
 # ---------------------------------------------------------------- spectral upsampling (SURVEY 8(f) N2)
 def test_spectrum_table_built_on_gpu_matches_host(I, gpu, scenes):
     """Same Gauss-Newton fits (spectrum.cpp:240-304).  The GPU sums the 471-sample integrals in another order and

@@ -25,7 +25,7 @@ def main():
     ap.add_argument("--camera", type=int, default=0)
     ap.add_argument("--tone", default="aces", choices=["clamp", "reinhard", "hable", "aces"])
     ap.add_argument("--brightness", type=float, default=1.0)
-    ap.add_argument("--builder", default="sah-host", choices=["sah-host", "lbvh-gpu", "ploc-gpu"])
+    ap.add_argument("--builder", default="sah-host", choices=["sah-host", "lbvh-gpu", "ploc-gpu", "auto"])
     ap.add_argument("--out", default="render.png")
     ap.add_argument("--pfm", default=None)
     args = ap.parse_args()
@@ -47,7 +47,7 @@ def main():
         args.camera = sc.camera_index(cam)
     else:
         sc = S.Scene.make(args.scene, *args.scene_params)
-    builder = {"sah-host": I.BUILDER_SAH_HOST, "lbvh-gpu": I.BUILDER_LBVH_GPU, "ploc-gpu": I.BUILDER_PLOC_GPU}[args.builder]
+    builder = {"sah-host": I.BUILDER_SAH_HOST, "lbvh-gpu": I.BUILDER_LBVH_GPU, "ploc-gpu": I.BUILDER_PLOC_GPU, "auto": I.BUILDER_AUTO}[args.builder]
     t0 = time.time()
     dev = I.DeviceScene(ctx, sc, builder=builder)
     info = dev.wide_info()
