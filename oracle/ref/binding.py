@@ -1,0 +1,141 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY.
+
+oracle/_ref/libref.so: the reference's own trace / scatter shader sources compiled as C++ (see ref_api.cpp,
+transpile.py, ref_glsl.h).  It can only be BUILT where /root/reference exists (this container); the built library
+travels to the GPU box with gpurun like the other .so files, and the golden vectors generated from it
+(tests/golden/ref_*.npz, tests/golden/make_ref_golden.py) are committed.  Same call shapes as oracle/binding.py.
+"""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+OUT = os.path.join(os.path.dirname(HERE), "_ref")
+LIB = os.path.join(OUT, "libref.so")
+REFERENCE_SRC = "/root/reference/src"
+
+RAY_DTYPE = np.dtype([("o", "<f4", 3), ("d", "<f4", 3), ("duration", "<f4")])
+HIT_DTYPE = np.dtype([("t", "<f4"), ("shape", "<u4"), ("prim", "<u4"), ("material", "<u4"), ("shape_type", "<u4"),
+                      ("n", "<f4", 3), ("tan", "<f4", 3), ("uv", "<f4", 2), ("bary", "<f4", 3),
+                      ("scene_complexity", "<u4"), ("mesh_complexity", "<u4")])
+STATE_ARRAYS = {
+    "OriginX": "f4", "OriginY": "f4", "OriginZ": "f4", "Duration": "f4", "PackedVelocity": "u4",
+    "Time": "f4", "TextureU": "f4", "TextureV": "f4", "ShapeAndMaterialIndex": "u4", "PackedNormal": "u4", "PackedTangentX": "u4",
+    "ImagePosition": "i4", "NormalizedLambda0": "f4", "Throughput0": "f4", "Throughput1": "f4", "Throughput2": "f4", "Throughput3": "f4",
+    "Probability0": "f4", "Probability1": "f4", "Probability2": "f4", "Probability3": "f4", "SampleR": "f4", "SampleG": "f4", "SampleB": "f4",
+    "ActiveShapeIndex01": "u4", "ActiveShapeIndex23": "u4",
+}
+
+
+class Params(C.Structure):
+    _fields_ = [("CameraIndex", C.c_uint32), ("RenderFlags", C.c_uint32), ("PathLengthLimit", C.c_uint32),
+                ("PathTerminationProbability", C.c_float)]
+
+
+def available():
+    """True when the library exists or can be built (the reference sources are present)."""
+    return os.path.exists(LIB) or os.path.isdir(REFERENCE_SRC)
+
+
+def build(force=False):
+    """transpile.py + g++ on the reference's shader sources where they lie; outputs only under oracle/_ref/."""
+    if not os.path.isdir(REFERENCE_SRC):
+        if os.path.exists(LIB):
+            return LIB
+        raise RuntimeError("oracle/_ref: %s is not here and no prebuilt libref.so travelled with the repository" % REFERENCE_SRC)
+    deps = [os.path.join(HERE, f) for f in ("ref_api.cpp", "ref_glsl.h", "transpile.py")]
+    if force or not os.path.exists(LIB) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in deps):
+        os.makedirs(OUT, exist_ok=True)
+        gen = os.path.join(OUT, "gen")
+        subprocess.check_call([sys.executable, os.path.join(HERE, "transpile.py"), REFERENCE_SRC, gen], stdout=subprocess.DEVNULL)
+        cmd = ["g++", "-std=c++20", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared", "-w",
+               "-I", gen, "-I", HERE, "-I", os.path.join(ROOT, "include"), "-o", LIB, os.path.join(HERE, "ref_api.cpp")]
+        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("oracle/_ref build failed:\n" + r.stdout)
+    return LIB
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = C.CDLL(build())
+        vp, u32, u64, f32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_float
+        L.ref_bind_scene.argtypes = [vp]
+        L.ref_raycast.argtypes = [vp, u64, vp]
+        L.ref_bind_film.argtypes = [vp, u32, u32]
+        L.ref_reset.argtypes = [C.POINTER(Params), u32]
+        L.ref_run.argtypes = [C.POINTER(Params), u32, u32]
+        L.ref_state_array.restype = vp
+        L.ref_state_array.argtypes = [C.c_char_p]
+        L.ref_pack_unit_vector.restype = u32
+        L.ref_pack_unit_vector.argtypes = [f32, f32, f32]
+        L.ref_unpack_unit_vector.argtypes = [u32, vp]
+        L.ref_observer.argtypes = [f32, vp]
+        L.ref_rng.argtypes = [u32, u32, vp]
+        _lib = L
+    return _lib
+
+
+def raycast(view, rays):
+    """Trace() of the reference's scene.glsl.inc on caller rays (visiting order and tie rules are the reference's)."""
+    L = lib()
+    L.ref_bind_scene(C.addressof(view))
+    rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+    out = np.zeros(len(rays), dtype=HIT_DTYPE)
+    L.ref_raycast(rays.ctypes.data, len(rays), out.ctypes.data)
+    return out
+
+
+class Renderer:
+    """ResetBasicRenderer / RunBasicRenderer (basic.cpp:285-332) over the reference's shaders.  One at a time: the
+    shaders' buffers are globals of the library."""
+
+    def __init__(self, view, width, height, camera_index=0, render_flags=3, path_length_limit=0, path_termination_probability=0.0):
+        assert width % 16 == 0 and height % 16 == 0, "the reference's slot index formula assumes whole 16x16 tiles"
+        self.L = lib()
+        self.view = view
+        self.w, self.h = width, height
+        self.film = np.zeros((height, width, 4), dtype=np.float32)
+        self.p = Params(camera_index, render_flags, path_length_limit, path_termination_probability)
+        self.frame_index = 0
+
+    def _bind(self):
+        self.L.ref_bind_scene(C.addressof(self.view))
+        self.L.ref_bind_film(self.film.ctypes.data, self.w, self.h)
+
+    def set_frame_index(self, f):
+        self.frame_index = f
+
+    def reset(self):
+        self._bind()
+        self.L.ref_reset(C.byref(self.p), self.frame_index)
+
+    def run(self, rounds=1):
+        self._bind()
+        self.frame_index += 1                       # basic.cpp:315
+        self.L.ref_run(C.byref(self.p), self.frame_index, rounds)
+
+    def run_frames(self, frames):
+        for _ in range(frames):
+            self.run(1)
+
+    @property
+    def slot_count(self):
+        return (self.w // 16) * (self.h // 16) * 256
+
+    def accum(self):
+        return self.film.copy()
+
+    def state(self, name):
+        ptr = self.L.ref_state_array(name.encode())
+        n = self.slot_count
+        buf = (C.c_char * (n * 4)).from_address(ptr)
+        return np.frombuffer(buf, dtype=np.dtype("<" + STATE_ARRAYS[name]), count=n).copy()

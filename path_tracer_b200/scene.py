@@ -17,6 +17,7 @@ ENTITY_ROOT, ENTITY_CONTAINER, ENTITY_CAMERA, ENTITY_MESH_INSTANCE, ENTITY_PLANE
 MATERIAL_BASIC_DIFFUSE, MATERIAL_BASIC_METAL, MATERIAL_BASIC_TRANSLUCENT, MATERIAL_OPENPBR = range(4)
 TEXTURE_RAW, TEXTURE_REFLECTANCE_WITH_ALPHA, TEXTURE_RADIANCE = range(3)
 CAMERA_PINHOLE, CAMERA_THIN_LENS, CAMERA_360 = range(3)
+TEXTURE_TYPE_RAW, TEXTURE_TYPE_REFLECTANCE_WITH_ALPHA, TEXTURE_TYPE_RADIANCE = range(3)     # scene.hpp:10-16
 
 _lib = None
 

@@ -1,9 +1,10 @@
 """Generates the golden fixtures under tests/golden/ from the oracle.
 
-The reference has no test vectors of its own and cannot be run here (Vulkan/GLSL
-only), so these files pin the ORACLE's behaviour at the time of
-writing: tests/test_oracle_kats.py checks the oracle still reproduces them, and
-the -m gpu tests check the CUDA path against the same numbers.
+These files pin the ORACLE's behaviour at the time of writing (canonical tie mode and
+brute force included, which the reference does not have): tests/test_oracle_kats.py
+checks the oracle still reproduces them, and the -m gpu tests check the CUDA path
+against the same numbers.  Vectors written by the reference's own shader sources are
+make_ref_golden.py's ref_*.npz.
 
     python tests/golden/make_golden.py
 """

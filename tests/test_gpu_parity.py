@@ -9,7 +9,7 @@ import os
 import numpy as np
 import pytest
 
-from util import bits, ids_equal, random_rays
+from util import REF_CASES, bits, ids_equal, make_test_scene, random_rays
 
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
@@ -401,6 +401,51 @@ def test_first_bounce_golden(I, gpu, dev, scenes):
     a = film.download()
     assert np.array_equal(a[..., 3], g["accum"][..., 3])
     assert_radiance_close(a[..., :3], g["accum"][..., :3])
+
+
+# ---------------------------------------------------------------- vectors written by the reference's own shader sources
+@pytest.mark.parametrize("tag", sorted(REF_CASES))
+def test_reference_shader_vectors(I, gpu, scenes, tag):
+    """tests/golden/ref_*.npz come from oracle/_ref (basic_trace.glsl / basic_scatter.glsl compiled as C++ from
+    /root/reference; tests/golden/make_ref_golden.py), not from the oracle restatement.  Reference-layout traversal
+    with the reference's tie rules: hit records bit-exact; first-bounce film within 1e-4; the film after further
+    frames likewise, except for the bounded fraction of paths an ulp of libdevice-vs-glibc sends another way."""
+    from path_tracer_b200 import scene as S
+    from path_tracer_b200.types import RAY_DTYPE
+    name, params, camera, flags, term = REF_CASES[tag]
+    g = np.load(os.path.join(GOLD, "ref_" + tag + ".npz"))
+    scenes("cornell")                                            # spectrum table
+    sc = make_test_scene(S, name, params)
+    d = I.DeviceScene(gpu, sc)
+    rays = np.ascontiguousarray(g["rays"]).view(RAY_DTYPE).reshape(-1)
+    out = d.raycast(rays, I.TRAVERSAL_BVH2_REFERENCE, I.TIE_FAITHFUL)
+    assert np.array_equal(out["shape"], g["hit_shape"]) and np.array_equal(bits(out["t"]), bits(g["hit_t"]))
+    hit = out["shape"] != MISS
+    for f in ("prim", "material", "shape_type", "n", "tan", "uv", "bary"):
+        assert np.array_equal(bits(out[f][hit]), bits(g["hit_" + f][hit])), f
+    wide = d.raycast(rays, I.TRAVERSAL_WIDE, I.TIE_CANONICAL)    # the product path: same hits up to exact-tie order
+    same = ids_equal(wide, out)
+    assert same.mean() > 0.999 and np.array_equal(bits(wide["t"][same]), bits(out["t"][same]))
+    w, h = int(g["size"][0]), int(g["size"][1])
+    film = I.SampleBuffer(gpu, w, h)
+    r = I.BasicRenderer(gpu, d, film)
+    r.CameraIndex, r.RenderFlags, r.PathLengthLimit, r.PathTerminationProbability = camera, flags, 0, term
+    r.Traversal, r.TieMode = I.TRAVERSAL_BVH2_REFERENCE, I.TIE_FAITHFUL
+    r.set_frame_index(0)
+    r.reset()
+    r.run(2)
+    a = film.download()
+    outliers = 5e-3 if term > 0.0 else 2e-3
+    assert np.mean(a[..., 3] != g["accum_first"][..., 3]) <= outliers
+    assert_radiance_close(a[..., :3], g["accum_first"][..., :3], max_outlier_fraction=outliers)
+    live = r.state("ImagePosition") == g["state_ImagePosition"]
+    assert live.mean() > 0.99
+    for arr in ("NormalizedLambda0", "OriginX", "OriginY", "OriginZ", "PackedVelocity", "ShapeAndMaterialIndex"):
+        assert (bits(r.state(arr))[live] == bits(g["state_" + arr])[live]).mean() > 0.99, arr
+    r.run_frames(int(g["frames"][0]))
+    b = film.download()
+    assert abs(b[..., 3].sum() - g["accum_frames"][..., 3].sum()) <= 0.01 * g["accum_frames"][..., 3].sum()
+    assert_radiance_close(b[..., :3], g["accum_frames"][..., :3], max_outlier_fraction=2e-2)
 
 
 @pytest.mark.parametrize("w,h", [(50, 30), (17, 33), (16, 16)])

@@ -161,3 +161,55 @@ def check_wide_tree(nodes, prims, shapes):
                 np.maximum.at(bhi, inner, bhi[ch])
     assert (seen_prims == 1).all()
     return len(level)
+
+
+def mixed_material_scene(S, fog=0.0):
+    """One small scene through every branch the basic integrator's scatter pass has: the three basic materials
+    (textured base colour, textured + anisotropic roughness, dispersive glass with an interior scattering medium),
+    an importance-sampled sky texture, a thin-lens camera and a 360 camera; fog > 0 fills the root with a scattering
+    medium (no path then reaches the sky: paths end by Russian roulette only, radiance stays 0)."""
+    sc = S.Scene()
+    rng = np.random.default_rng(5)
+    sky = np.zeros((16, 32, 4), np.float32)
+    sky[..., :3] = rng.uniform(0.1, 0.6, size=(16, 32, 3))
+    sky[3:6, 8:12, :3] = 20.0                                     # a bright patch for the von Mises-Fisher lobe
+    sky[..., 3] = 1.0
+    sky_t = sc.create_texture("sky", S.TEXTURE_TYPE_RADIANCE, sky)
+    sc.set_root(scatter_rate=fog, sky_brightness=1.5, sky_sampling_probability=0.5, sky_texture=sky_t)
+    check = sc.create_checker_texture("check", S.TEXTURE_TYPE_REFLECTANCE_WITH_ALPHA, (0.8, 0.8, 0.8, 1.0), (0.2, 0.3, 0.7, 1.0), nearest=True)
+    rough = np.zeros((8, 8, 4), np.float32)
+    rough[..., 0] = rng.uniform(0.05, 0.6, size=(8, 8))
+    rough[..., 3] = 1.0
+    rough_t = sc.create_texture("rough", S.TEXTURE_TYPE_RAW, rough)
+    floor = sc.create_material(S.MATERIAL_BASIC_DIFFUSE, "floor", textures={"BaseTexture": check}, BaseColor=(0.9, 0.9, 0.9))
+    metal = sc.create_material(S.MATERIAL_BASIC_METAL, "metal", textures={"RoughnessTexture": rough_t}, BaseColor=(0.9, 0.6, 0.3),
+                               SpecularColor=(1.0, 0.9, 0.8), Roughness=0.4, RoughnessAnisotropy=0.6)
+    glass = sc.create_material(S.MATERIAL_BASIC_TRANSLUCENT, "glass", IOR=1.5, AbbeNumber=30.0, Roughness=0.1, TransmissionColor=(0.8, 0.9, 1.0),
+                               TransmissionDepth=0.7, ScatteringColor=(0.9, 0.5, 0.4), ScatteringAnisotropy=0.3)
+    mirror = sc.create_material(S.MATERIAL_BASIC_METAL, "mirror", BaseColor=(0.95, 0.95, 0.95), Roughness=0.0)
+    sc.create_entity(S.ENTITY_PLANE, position=(0, 0, 0), scale=(6, 6, 1), material=floor)
+    sc.create_entity(S.ENTITY_SPHERE, position=(-1.2, 0.3, 1.0), material=glass)
+    sc.create_entity(S.ENTITY_CUBE, position=(1.3, 0.0, 0.8), rotation=(0.0, 0.0, 0.5), scale=(0.8, 0.8, 0.8), material=metal)
+    sc.create_entity(S.ENTITY_SPHERE, position=(0.2, 2.0, 0.7), scale=(0.7, 0.7, 0.7), material=mirror)
+    sc.create_entity(S.ENTITY_SPHERE, position=(0.0, -0.8, 0.4), scale=(0.4, 0.4, 0.4), material=glass)
+    sc.create_camera((0.0, -5.0, 2.0), (0.0, 0.0, 0.8), model=S.CAMERA_THIN_LENS, params=(36.0, 24.0, 35.0, 8.0, 5.2))
+    sc.create_camera((0.0, -1.5, 1.5), (0.0, 0.0, 0.8), model=S.CAMERA_360)
+    sc.pack()
+    return sc
+
+
+# Cases of tests/golden/make_ref_golden.py: tag -> (scene, params, camera, render flags, termination probability).
+# PathLengthLimit stays 0: the reference's scatter shader never reads it (DESIGN.md D5).
+REF_CASES = {
+    "cornell": ("cornell", (), 0, 3, 0.0),
+    "terrain32": ("terrain", (32,), 0, 3, 0.0),
+    "room": ("room", (1, 256), 0, 3, 0.0),
+    "spherefield": ("spherefield", (6, 1, 2), 0, 3, 0.0),
+    "mixed_lens": ("mixed", (0.0,), 0, 3, 0.25),
+    "mixed_360": ("mixed", (0.0,), 1, 1, 0.0),
+    "mixed_fog": ("mixed", (0.3,), 0, 3, 0.25),
+}
+
+
+def make_test_scene(S, name, params):
+    return mixed_material_scene(S, *params) if name == "mixed" else S.Scene.make(name, *params)
