@@ -4,9 +4,9 @@
 // __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
 // Nothing under path_tracer_b200/ links or loads this library.
 //
-// Parity: trace + scatter are pinned bit for bit against the reference's own GLSL sources compiled
-// as C++ (oracle/ref -> oracle/_ref/libref.so, tests/test_reference_shaders.py, tests/golden/ref_*.npz);
-// resolve and the preview visualiser by known-answer tests only.
+// Parity: trace, scatter, resolve and the preview visualiser are pinned bit for bit against the
+// reference's own GLSL sources compiled as C++ (oracle/ref -> oracle/_ref/libref.so,
+// tests/test_reference_shaders.py, tests/golden/ref_*.npz).
 //
 // Build: see oracle/Makefile  (g++ -O2 -ffp-contract=off, no -ffast-math).
 #include <atomic>

@@ -36,6 +36,12 @@ class Params(C.Structure):
                 ("PathTerminationProbability", C.c_float)]
 
 
+class PreviewParams(C.Structure):
+    _fields_ = [("To", C.c_float * 16), ("From", C.c_float * 16), ("RenderMode", C.c_uint32), ("Brightness", C.c_float),
+                ("SelectedShapeIndex", C.c_uint32), ("RenderSizeX", C.c_uint32), ("RenderSizeY", C.c_uint32),
+                ("MouseX", C.c_uint32), ("MouseY", C.c_uint32)]
+
+
 def available():
     """True when the library exists or can be built (the reference sources are present)."""
     return os.path.exists(LIB) or os.path.isdir(REFERENCE_SRC)
@@ -47,13 +53,13 @@ def build(force=False):
         if os.path.exists(LIB):
             return LIB
         raise RuntimeError("oracle/_ref: %s is not here and no prebuilt libref.so travelled with the repository" % REFERENCE_SRC)
-    deps = [os.path.join(HERE, f) for f in ("ref_api.cpp", "ref_glsl.h", "transpile.py")]
+    deps = [os.path.join(HERE, f) for f in ("ref_api.cpp", "ref_frag.cpp", "ref_bind_scene.inc", "ref_glsl.h", "transpile.py")]
     if force or not os.path.exists(LIB) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in deps):
         os.makedirs(OUT, exist_ok=True)
         gen = os.path.join(OUT, "gen")
         subprocess.check_call([sys.executable, os.path.join(HERE, "transpile.py"), REFERENCE_SRC, gen], stdout=subprocess.DEVNULL)
         cmd = ["g++", "-std=c++20", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared", "-w",
-               "-I", gen, "-I", HERE, "-I", os.path.join(ROOT, "include"), "-o", LIB, os.path.join(HERE, "ref_api.cpp")]
+               "-I", gen, "-I", HERE, "-I", os.path.join(ROOT, "include"), "-o", LIB, os.path.join(HERE, "ref_api.cpp"), os.path.join(HERE, "ref_frag.cpp")]
         r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         if r.returncode != 0:
             raise RuntimeError("oracle/_ref build failed:\n" + r.stdout)
@@ -80,6 +86,8 @@ def lib():
         L.ref_unpack_unit_vector.argtypes = [u32, vp]
         L.ref_observer.argtypes = [f32, vp]
         L.ref_rng.argtypes = [u32, u32, vp]
+        L.ref_resolve.argtypes = [vp, u32, u32, f32, u32, f32, vp]
+        L.ref_preview.argtypes = [vp, C.POINTER(PreviewParams), vp, vp]
         _lib = L
     return _lib
 
@@ -92,6 +100,28 @@ def raycast(view, rays):
     out = np.zeros(len(rays), dtype=HIT_DTYPE)
     L.ref_raycast(rays.ctypes.data, len(rays), out.ctypes.data)
     return out
+
+
+def resolve(accum, brightness=1.0, mode=0, white=1.0):
+    """resolve.glsl's fragment stage over a film: (H, W, 3) linear RGB after tone mapping."""
+    a = np.ascontiguousarray(accum, dtype=np.float32)
+    h, w = a.shape[0], a.shape[1]
+    lin = np.zeros((h, w, 3), dtype=np.float32)
+    lib().ref_resolve(a.ctypes.data, w, h, brightness, mode, white, lin.ctypes.data)
+    return lin
+
+
+def preview(view, camera_to, camera_from, mode, width, height, brightness=1.0, selected=0xFFFFFFFF, mouse=(0, 0)):
+    """preview_render.glsl's fragment stage: (H, W, 4) float image and the shape under the mouse pixel."""
+    p = PreviewParams()
+    p.To[:] = [float(x) for x in camera_to]
+    p.From[:] = [float(x) for x in camera_from]
+    p.RenderMode, p.Brightness, p.SelectedShapeIndex = mode, brightness, selected
+    p.RenderSizeX, p.RenderSizeY, p.MouseX, p.MouseY = width, height, mouse[0], mouse[1]
+    img = np.zeros((height, width, 4), dtype=np.float32)
+    pick = C.c_uint32(0xFFFFFFFF)
+    lib().ref_preview(C.addressof(view), C.byref(p), img.ctypes.data, C.addressof(pick))
+    return img, pick.value
 
 
 class Renderer:

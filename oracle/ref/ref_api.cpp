@@ -39,27 +39,7 @@ struct ref_params { uint32_t CameraIndex, RenderFlags, PathLengthLimit; float Pa
 
 // UpdateVulkanScene (scene.cpp:1698-1960): binds the packed arrays to the shaders' interface blocks.
 void ref_bind_scene(const ptb_scene_view* v) {
-    const ptb_packed_scene_globals* g = v->Globals;
-    Scene.SkyboxMeanDirection = vec3(g->SkyboxMeanDirection[0], g->SkyboxMeanDirection[1], g->SkyboxMeanDirection[2]);
-    Scene.SkyboxConcentration = g->SkyboxConcentration;
-    Scene.SkyboxSamplingProbability = g->SkyboxSamplingProbability;
-    Scene.SkyboxBrightness = g->SkyboxBrightness;
-    Scene.SkyboxTextureIndex = g->SkyboxTextureIndex;
-    Scene.ShapeCount = g->ShapeCount;
-    Scene.SceneScatterRate = g->SceneScatterRate;
-    Textures = (packed_texture*)v->Textures;
-    MaterialData = (uint*)v->MaterialData;
-    Shapes = (packed_shape*)v->Shapes;
-    ShapeNodes = (packed_shape_node*)v->ShapeNodes;
-    MeshFaces = (packed_mesh_face*)v->MeshFaces;
-    MeshVertices = (packed_mesh_vertex*)v->MeshVertices;
-    MeshNodes = (packed_mesh_node*)v->MeshNodes;
-    Cameras = (packed_camera*)v->Cameras;
-    for (sampler2DArray* s : {&TextureArrayNearest, &TextureArrayLinear}) {
-        s->layers = v->AtlasLayers; s->width = (int)v->AtlasWidth; s->height = (int)v->AtlasHeight;
-    }
-    TextureArrayNearest.nearest = true;
-    TextureArrayLinear.nearest = false;
+#include "ref_bind_scene.inc"
 }
 
 // Trace() (scene.glsl.inc:522-611) on caller rays.

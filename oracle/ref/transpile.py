@@ -13,6 +13,7 @@ are nearly C++ already; what is rewritten, mechanically and line by line:
   * floating literals get the `f` suffix (GLSL literals are single precision);
   * a vector constructor with more than one Random*() call among its arguments is written with braces: GLSL
     evaluates arguments left to right, C++ only does so inside a braced initialiser list;
+  * array constructors `T[n](a, b, ..)` become braced initialisers; stage inputs / outputs (`in vec2 X;`) globals;
   * `void main()` is renamed after the file (basic_trace.glsl -> basic_trace_main).
 
 oracle/ref/ref_glsl.h supplies the GLSL types and built-ins; oracle/ref/ref_api.cpp includes the generated files
@@ -25,7 +26,8 @@ import sys
 FILES = [
     "core/common.glsl.inc", "core/spectrum.glsl.inc", "scene/scene.glsl.inc", "scene/basic_diffuse.glsl.inc",
     "scene/basic_metal.glsl.inc", "scene/basic_translucent.glsl.inc", "integrator/basic.glsl.inc",
-    "integrator/basic_trace.glsl", "integrator/basic_scatter.glsl",
+    "integrator/basic_trace.glsl", "integrator/basic_scatter.glsl", "integrator/resolve.glsl",
+    "application/preview_render.glsl",
 ]
 
 FLOAT_LITERAL = re.compile(r"(?<![\w.])((?:\d+\.\d*|\.\d+)(?:[eE][-+]?\d+)?|\d+[eE][-+]?\d+)(?![\w.])")
@@ -65,7 +67,25 @@ def rewrite_code(code):
     return code
 
 
+ARRAY_CONSTRUCTOR = re.compile(r"=\s*\w+\s*\[\s*\d*\s*\]\s*\(")
+
+
+def brace_array_constructors(text):
+    """`= vec3[20]( ... )` -> `= { ... }` (may span lines)."""
+    while True:
+        m = ARRAY_CONSTRUCTOR.search(text)
+        if not m:
+            return text
+        depth, j = 0, m.end() - 1
+        for j in range(m.end() - 1, len(text)):
+            depth += (text[j] == "(") - (text[j] == ")")
+            if depth == 0:
+                break
+        text = text[:m.start()] + "= {" + text[m.end():j] + "}" + text[j + 1:]
+
+
 def transpile(text, stem):
+    text = brace_array_constructors(text)
     out = []
     lines = text.split("\n")
     i = 0
@@ -116,7 +136,7 @@ def transpile(text, stem):
                     mm = re.match(r"^(\w+)\s+(\w+)\s*\[\s*\]\s*;$", member)
                     out.append("%s* %s;" % (mm.group(1), mm.group(2)) if mm else rewrite_code(member))
                 continue
-            m = re.match(r"^uniform\s+(\w+)\s+(\w+)\s*;$", rest)
+            m = re.match(r"^(?:uniform|in|out)\s+(\w+)\s+(\w+)\s*;$", rest)
             if m:
                 out.append("%s %s;" % (m.group(1), m.group(2)))
                 continue

@@ -606,6 +606,37 @@ def test_resolve_tone_mapping(I, gpu, oracle, mode):
     assert (srgb[..., 3] == 255).all()
 
 
+def test_reference_fragment_shader_vectors(I, gpu, scenes):
+    """tests/golden/ref_resolve.npz / ref_preview.npz: outputs of the reference's resolve.glsl and preview_render.glsl
+    fragment stages (compiled as C++ by oracle/ref, make_ref_golden.py) against k_resolve and the preview kernel."""
+    from path_tracer_b200 import scene as S
+    g = np.load(os.path.join(GOLD, "ref_resolve.npz"))
+    accum = g["film"]
+    film = I.SampleBuffer(gpu, accum.shape[1], accum.shape[0])
+    film.upload(accum)
+    for k, (brightness, mode, white) in enumerate(g["settings"]):
+        lin, _ = film.resolve(float(brightness), int(mode), float(white))
+        want = g["linear_%d" % k]
+        ok = np.isfinite(want)
+        assert (np.isfinite(lin) == ok).all(), k
+        assert np.allclose(lin[ok], want[ok], rtol=1e-5, atol=1e-6), k
+    g = np.load(os.path.join(GOLD, "ref_preview.npz"))
+    w, h = int(g["size"][0]), int(g["size"][1])
+    scenes("cornell")
+    for tag in ("cornell", "room", "mixed_lens"):
+        name, params, *_ = REF_CASES[tag]
+        sc = make_test_scene(S, name, params)
+        d = I.DeviceScene(gpu, sc)
+        cam = sc.cameras[0]
+        for mode in range(7):
+            img, shape, pick = d.preview(cam["To"].ravel(), cam["From"].ravel(), mode, w, h, brightness=1.25, selected=2, mouse=(20, 17),
+                                         traversal=I.TRAVERSAL_BVH2_REFERENCE)
+            want = g["%s_mode%d" % (tag, mode)]
+            close = np.abs(img - want).max(axis=-1) <= 2e-5
+            assert close.mean() > 0.998, (tag, mode, float(close.mean()))     # a silhouette pixel may fall either way of an exact tie
+            assert pick == int(g[tag + "_pick"][0]), (tag, mode)
+
+
 # ---------------------------------------------------------------- API behaviour
 def test_error_behaviour(I, gpu, dev):
     film = I.SampleBuffer(gpu, 32, 32)

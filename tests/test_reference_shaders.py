@@ -144,3 +144,45 @@ def test_oracle_reproduces_reference_golden_vectors(oracle, case_scene, tag):
     same = bits(b) == bits(g["accum_frames"])
     assert same.mean() > 0.99                                                # bit-exact on this box; an ulp of libm can fork a path elsewhere
     assert abs(b[..., 3].sum() - g["accum_frames"][..., 3].sum()) <= 0.01 * g["accum_frames"][..., 3].sum()
+
+
+# ---------------------------------------------------------------- the two fragment shaders: resolve.glsl, preview_render.glsl
+def nan_or_bit_equal(a, b):
+    return ((bits(a) == bits(b)) | (np.isnan(a) & np.isnan(b))).all()
+
+
+def test_oracle_resolve_is_bit_identical_to_the_reference_shader(ref, oracle):
+    from golden.make_ref_golden import resolve_film
+    film = resolve_film()
+    for mode in range(4):
+        for brightness, white in ((1.0, 1.0), (2.5, 4.0), (0.1, 0.5)):
+            assert nan_or_bit_equal(ref.resolve(film, brightness, mode, white), oracle.resolve(film, brightness, mode, white)[0]), (mode, brightness)
+
+
+@pytest.mark.parametrize("tag", ["cornell", "room", "mixed_lens", "spherefield", "terrain32"])
+def test_oracle_preview_is_bit_identical_to_the_reference_shader(ref, oracle, case_scene, tag):
+    name, params, *_ = REF_CASES[tag]
+    sc = case_scene(name, params)
+    cam = sc.cameras[0]
+    to, fr = cam["To"].ravel(), cam["From"].ravel()
+    for mode in range(7):
+        a, pick_a = ref.preview(sc.view, to, fr, mode, 48, 32, brightness=1.25, selected=2, mouse=(20, 17))
+        b, _, pick_b = oracle.preview(sc.view, to, fr, mode, 48, 32, brightness=1.25, selected=2, mouse=(20, 17), tie=oracle.TIE_FAITHFUL)
+        assert np.array_equal(bits(a), bits(b)) and pick_a == pick_b, mode
+
+
+def test_oracle_reproduces_reference_resolve_and_preview_vectors(oracle, case_scene):
+    g = np.load(os.path.join(GOLD, "ref_resolve.npz"))
+    for k, (brightness, mode, white) in enumerate(g["settings"]):
+        lin, _ = oracle.resolve(g["film"], float(brightness), int(mode), float(white))
+        assert np.allclose(lin, g["linear_%d" % k], rtol=1e-6, atol=1e-7, equal_nan=True)
+    g = np.load(os.path.join(GOLD, "ref_preview.npz"))
+    w, h = int(g["size"][0]), int(g["size"][1])
+    for tag in ("cornell", "room", "mixed_lens"):
+        name, params, *_ = REF_CASES[tag]
+        sc = case_scene(name, params)
+        cam = sc.cameras[0]
+        for mode in range(7):
+            img, _, pick = oracle.preview(sc.view, cam["To"].ravel(), cam["From"].ravel(), mode, w, h, brightness=1.25, selected=2, mouse=(20, 17),
+                                          tie=oracle.TIE_FAITHFUL)
+            assert np.allclose(img, g["%s_mode%d" % (tag, mode)], rtol=1e-6, atol=1e-7) and pick == int(g[tag + "_pick"][0]), (tag, mode)
