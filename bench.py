@@ -12,9 +12,11 @@ frame, src/application/application.cpp:114).
 Prints ONE JSON line (contract in the task statement): `value` = whole-job Mrays/s
 with everything resident in HBM; `e2e` = the same metric through the public API with
 host-side inputs/outputs inside the timed region; `roofline` for the dominant kernel
-(the trace kernel); `cpu_baseline` = the oracle (CPU restatement of the reference
-shaders) on a bounded sample of the same workload.  `--impl reference` times that CPU
-restatement alone (the reference's own Vulkan path is unavailable on this box).
+(the trace kernel); `cpu_baseline` = oracle/_ref (the reference's own trace / scatter
+GLSL compiled as C++, one forked process per host core; kind "reference") on a bounded
+sample of the same workload, or the oracle port where that library is unavailable.
+`--impl reference` times that CPU code alone (the reference's own Vulkan path is
+unavailable on this box).
 """
 import argparse
 import ctypes as C
@@ -122,6 +124,56 @@ def oracle_sample(scene, frames, tile_stride, threads):
     return d
 
 
+def _ref_worker(view_addr, p, procs, stride, warm_frames, frames, barrier, out):
+    """One host core's share of the reference-shader run: its own copy of libref.so's globals (fork), every
+    (stride * procs)-th 16x16 work group starting at p * stride."""
+    import ctypes as C
+    from oracle.ref import binding as R
+    from path_tracer_b200.types import SceneView
+    view = SceneView.from_address(view_addr)
+    r = R.Renderer(view, WIDTH, HEIGHT, path_length_limit=PATH_LIMIT)
+    r.set_groups(stride * procs, p * stride)
+    r.set_frame_index(0)
+    r.reset()
+    r.run(2)
+    r.run_frames(warm_frames)
+    rays0, paths0 = r.rays_traced(), float(r.film[..., 3].sum(dtype=np.float64))
+    barrier.wait()
+    t0 = time.perf_counter()
+    r.run_frames(frames)
+    t1 = time.perf_counter()
+    out.put((p, r.rays_traced() - rays0, float(r.film[..., 3].sum(dtype=np.float64)) - paths0, t0, t1))
+
+
+def reference_shader_sample(scene, stride, warm_frames, frames, procs):
+    """oracle/_ref (the reference's own trace / scatter GLSL compiled as C++) on every `stride`-th 16x16 tile of the
+    full-size film, the tiles dealt round-robin to `procs` forked processes (the library is single-threaded: the
+    shaders' interface blocks are globals).  Returns None when the library is unavailable, the film needs more path
+    slots than the reference's TRACE_COUNT (2 Mi), or the workload sets a path length limit."""
+    import ctypes as C
+    import multiprocessing as mp
+    from oracle.ref import binding as R
+    if not R.available():
+        return None
+    try:
+        L = R.lib()
+    except Exception:
+        return None
+    if R.Renderer.slots_needed(WIDTH, HEIGHT) > L.ref_slot_capacity() or WIDTH % 16 or PATH_LIMIT:
+        return None                              # (the shader never reads PathLengthLimit: a limited workload needs the port)
+    ctx = mp.get_context("fork")
+    barrier, out = ctx.Barrier(procs), ctx.Queue()
+    addr = C.addressof(scene.view)
+    ws = [ctx.Process(target=_ref_worker, args=(addr, p, procs, stride, warm_frames, frames, barrier, out)) for p in range(procs)]
+    for w in ws:
+        w.start()
+    res = [out.get() for _ in ws]
+    for w in ws:
+        w.join()
+    dt = max(r[4] for r in res) - min(r[3] for r in res)
+    return {"rays": sum(r[1] for r in res), "paths": sum(r[2] for r in res), "seconds": dt, "procs": procs}
+
+
 def bytes_per_segment(counts):
     """32*N_node + 48*N_face + 144*N_shape + 24*[mesh hit] + 256 per ray segment,
     counts taken from the oracle's traversal of the reference BVH2 for the same workload."""
@@ -136,32 +188,39 @@ def run_reference(args, rank, world):
     from path_tracer_b200 import scene as S
     S.ensure_spectrum_table()
     sc = S.Scene.make(SCENE_NAME, *SCENE_PARAMS)
-    from oracle import binding as O
     threads = os.cpu_count() or 1
     stride = args.ref_tile_stride
-    r = O.Renderer(sc.view, WIDTH, HEIGHT, tie=O.TIE_FAITHFUL, threads=threads, tile_stride=stride, path_length_limit=PATH_LIMIT)
-    r.set_frame_index(0)
-    r.reset()
-    r.run(2)
-    for _ in range(args.warmup):
-        r.run_frames(args.ref_frames)
-    s0 = r.stats()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        r.run_frames(args.ref_frames)
-    dt = time.perf_counter() - t0
-    s1 = r.stats()
-    rays, paths = s1["rays"] - s0["rays"], s1["paths"] - s0["paths"]
+    kind, note = "reference", ("the reference's own basic_trace.glsl / basic_scatter.glsl compiled as C++ from its sources (oracle/_ref), "
+                                "one process per host core; its Vulkan path is unavailable on this box")
+    c = None if args.ref_port else reference_shader_sample(sc, stride, args.warmup * args.ref_frames, args.steps * args.ref_frames, threads)
+    if c is not None:
+        rays, paths, dt = c["rays"], c["paths"], c["seconds"]
+    else:
+        kind, note = "port", ("CPU restatement of the reference's trace/scatter shaders (oracle port: " + ("selected with --ref-port" if args.ref_port else
+                              "oracle/_ref is not available for this workload") + "); the reference's own Vulkan/GLSL path is unavailable on this box")
+        from oracle import binding as O
+        r = O.Renderer(sc.view, WIDTH, HEIGHT, tie=O.TIE_FAITHFUL, threads=threads, tile_stride=stride, path_length_limit=PATH_LIMIT)
+        r.set_frame_index(0)
+        r.reset()
+        r.run(2)
+        for _ in range(args.warmup):
+            r.run_frames(args.ref_frames)
+        s0 = r.stats()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            r.run_frames(args.ref_frames)
+        dt = time.perf_counter() - t0
+        s1 = r.stats()
+        rays, paths = s1["rays"] - s0["rays"], s1["paths"] - s0["paths"]
     mrays = rays / dt / 1e6
     sample = "every %d-th 16x16 tile of the %dx%d film (%d rays/frame), %d frames/step" % (stride, WIDTH, HEIGHT, rays // max(1, args.steps * args.ref_frames), args.ref_frames)
     _emit(({
         "impl": "reference", "metric": "Mrays/s (ray segments traced, whole job)", "value": mrays, "unit": "Mrays/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "note": "CPU restatement of the reference's trace/scatter shaders (oracle port); "
-                   "the reference's own Vulkan/GLSL path is unavailable on this box"},
+        "config": {"workload": WORKLOAD, "note": note},
         "mpaths_per_s": paths / dt / 1e6,
-        "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -209,6 +268,7 @@ def main():
     ap.add_argument("--ref-tile-stride", type=int, default=0, help="CPU arms process every n-th 16x16 tile (bounded sample)")
     ap.add_argument("--cpu-frames", type=int, default=96, help="frames of the cpu_baseline sample (about 10-30 s of CPU work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-port", action="store_true", help="time the oracle port instead of oracle/_ref (the reference's shaders compiled as C++)")
     ap.add_argument("--spp-target", type=int, default=0, help="also measure the seconds from reset until every pixel holds this many samples")
     args = ap.parse_args()
     select_workload(args)
@@ -346,12 +406,17 @@ def main():
     seg_bytes, trace_bytes = None, None
     if not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1
-        c = oracle_sample(scene, args.cpu_frames, args.ref_tile_stride, threads)
+        # the reference's own shader code (oracle/_ref) gives the timed baseline; the oracle port, which counts what
+        # the traversal touches, gives the algorithmic byte model (and the baseline where _ref is unavailable)
+        shader = None if args.ref_port else reference_shader_sample(scene, args.ref_tile_stride, 2, args.cpu_frames, threads)
+        c = oracle_sample(scene, args.cpu_frames if shader is None else max(8, args.cpu_frames // 4), args.ref_tile_stride, threads)
         seg_bytes, trace_bytes = bytes_per_segment(c)
-        cpu = {"value": c["rays"] / c["seconds"] / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
-               "sample": "every %d-th 16x16 tile of the same 1920x1080 film, %d frames, %d rays in %.1f s"
-                         .replace("1920x1080", "%dx%d" % (WIDTH, HEIGHT)) % (args.ref_tile_stride, args.cpu_frames, c["rays"], c["seconds"]),
-               "mpaths_per_s": c["paths"] / c["seconds"] / 1e6,
+        t = shader if shader is not None else c
+        cpu = {"value": t["rays"] / t["seconds"] / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "reference" if shader is not None else "port",
+               "sample": "every %d-th 16x16 tile of the same %dx%d film, %d frames, %d rays in %.1f s"
+                         % (args.ref_tile_stride, WIDTH, HEIGHT, args.cpu_frames, t["rays"], t["seconds"]),
+               "mpaths_per_s": t["paths"] / t["seconds"] / 1e6,
+               "port_value": c["rays"] / c["seconds"] / 1e6,
                "per_ray": {"node_fetches": c["node_fetches"] / c["rays"], "face_tests": c["face_tests"] / c["rays"],
                            "shape_visits": c["shape_visits"] / c["rays"], "mesh_hit_fraction": c["mesh_hits"] / c["rays"]}}
     bytes_source = "oracle traversal counters of this run's CPU sample"

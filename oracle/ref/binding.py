@@ -86,6 +86,9 @@ def lib():
         L.ref_unpack_unit_vector.argtypes = [u32, vp]
         L.ref_observer.argtypes = [f32, vp]
         L.ref_rng.argtypes = [u32, u32, vp]
+        L.ref_set_groups.argtypes = [u32, u32]
+        L.ref_rays_traced.restype = u64
+        L.ref_slot_capacity.restype = C.c_int
         L.ref_resolve.argtypes = [vp, u32, u32, f32, u32, f32, vp]
         L.ref_preview.argtypes = [vp, C.POINTER(PreviewParams), vp, vp]
         _lib = L
@@ -129,8 +132,9 @@ class Renderer:
     shaders' buffers are globals of the library."""
 
     def __init__(self, view, width, height, camera_index=0, render_flags=3, path_length_limit=0, path_termination_probability=0.0):
-        assert width % 16 == 0 and height % 16 == 0, "the reference's slot index formula assumes whole 16x16 tiles"
+        assert width % 16 == 0, "the reference's slot index formula (ImageSize.x / 16) assumes whole tiles per row"
         self.L = lib()
+        assert self.slots_needed(width, height) <= self.L.ref_slot_capacity(), "more path slots than the reference's TRACE_COUNT"
         self.view = view
         self.w, self.h = width, height
         self.film = np.zeros((height, width, 4), dtype=np.float32)
@@ -157,9 +161,20 @@ class Renderer:
         for _ in range(frames):
             self.run(1)
 
+    @staticmethod
+    def slots_needed(width, height):
+        return (width // 16) * ((height + 15) // 16) * 256
+
     @property
     def slot_count(self):
-        return (self.w // 16) * (self.h // 16) * 256
+        return self.slots_needed(self.w, self.h)
+
+    def set_groups(self, modulus, residue):
+        """Only 16x16 work groups with index % modulus == residue are dispatched (a bounded / sharded sample)."""
+        self.L.ref_set_groups(modulus, residue)
+
+    def rays_traced(self):
+        return int(self.L.ref_rays_traced())
 
     def accum(self):
         return self.film.copy()

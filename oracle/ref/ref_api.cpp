@@ -76,24 +76,41 @@ static void push(const ref_params* p, uint32_t seed, uint32_t restart) {
     CameraIndex = p->CameraIndex; RenderFlags = p->RenderFlags; PathLengthLimit = p->PathLengthLimit;
     PathTerminationProbability = p->PathTerminationProbability; RandomSeed = seed; Restart = restart;
 }
+// A bounded, shardable sample of the dispatch (bench.py's reference arm: one process per host core, each with its
+// own copy of this library's globals): only work groups whose linear index g has g % modulus == residue run.
+static uint32_t g_modulus = 1, g_residue = 0;
+static uint64_t g_rays = 0;
+void ref_set_groups(uint32_t modulus, uint32_t residue) { g_modulus = modulus ? modulus : 1; g_residue = residue; }
+uint64_t ref_rays_traced() { return g_rays; }
+int ref_slot_capacity() { return TRACE_COUNT; }
+
 // vkCmdDispatch of basic_scatter.glsl over 16x16 work groups (basic.cpp:101-118).
 static void dispatch_scatter() {
     const uint gx = ((uint)SampleAccumulatorImage.width + 15u) / 16u, gy = ((uint)SampleAccumulatorImage.height + 15u) / 16u;
-    for (uint wy = 0; wy < gy; wy++) for (uint wx = 0; wx < gx; wx++)
+    for (uint wy = 0; wy < gy; wy++) for (uint wx = 0; wx < gx; wx++) {
+        if ((wy * gx + wx) % g_modulus != g_residue) continue;
         for (uint ly = 0; ly < 16; ly++) for (uint lx = 0; lx < 16; lx++) {
             gl_WorkGroupID = uvec3(wx, wy, 0); gl_LocalInvocationID = uvec3(lx, ly, 0);
             gl_GlobalInvocationID = uvec3(wx * 16 + lx, wy * 16 + ly, 0);
             basic_scatter_main();
         }
+    }
 }
-// basic_trace.glsl over the slots the film uses (the reference dispatches all TRACE_COUNT slots, basic.cpp:32-60;
-// slots beyond the film hold no path and their results are never read).
+// basic_trace.glsl over the slots that hold a path (the reference dispatches all TRACE_COUNT slots, basic.cpp:32-60;
+// slots outside the film hold no path and their results are never read).
 static void dispatch_trace() {
-    const uint gx = ((uint)SampleAccumulatorImage.width + 15u) / 16u, gy = ((uint)SampleAccumulatorImage.height + 15u) / 16u;
-    const uint slots = gx * gy * 256u;
-    for (uint i = 0; i < slots && i < (uint)TRACE_COUNT; i++) {
-        gl_GlobalInvocationID = uvec3(i, 0, 0); gl_WorkGroupID = uvec3(i / 256u, 0, 0); gl_LocalInvocationID = uvec3(i % 256u, 0, 0);
-        basic_trace_main();
+    const uint W = (uint)SampleAccumulatorImage.width, H = (uint)SampleAccumulatorImage.height;
+    const uint gx = W / 16u, gy = (H + 15u) / 16u;                     // the slot formula of basic_scatter.glsl:325-329
+    for (uint g = 0; g < gx * gy; g++) {
+        if (g % g_modulus != g_residue) continue;
+        const uint wy = g / gx;
+        for (uint l = 0; l < 256u; l++) {
+            const uint i = g * 256u + l;
+            if (i >= (uint)TRACE_COUNT || wy * 16u + l / 16u >= H) continue;
+            gl_GlobalInvocationID = uvec3(i, 0, 0); gl_WorkGroupID = uvec3(i / 256u, 0, 0); gl_LocalInvocationID = uvec3(i % 256u, 0, 0);
+            basic_trace_main();
+            g_rays++;
+        }
     }
 }
 // ResetBasicRenderer / RunBasicRenderer (basic.cpp:285-332); the caller keeps FrameIndex like basic_renderer does.
