@@ -110,5 +110,21 @@ def build_experiment(tag, defines):
     return out
 
 
+def build_headless(force=False):
+    """bin/ptb_headless: the reference application's frame loop without a window, in C++ over host/integrator.hpp
+    (the reference's integrator interface on top of the C ABI).  Links libptb.so and libptb_scene.so next to it."""
+    build_scene(force)
+    build_cuda(force)
+    out = os.path.join(ROOT, "bin", "ptb_headless")
+    srcs = [os.path.join(ROOT, "app", "headless.cpp"), os.path.join(ROOT, "host", "integrator.cpp")]
+    deps = srcs + [os.path.join(ROOT, "host", f) for f in ("integrator.hpp", "scene.hpp", "procedural.hpp")] + \
+        [os.path.join(REPO, "include", "ptb.h"), os.path.join(ROOT, "libptb.so"), os.path.join(ROOT, "libptb_scene.so")]
+    if force or _newer(out, deps):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        _run(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-pthread", "-I", os.path.join(REPO, "include"), "-o", out] + srcs +
+             ["-L", ROOT, "-lptb", "-lptb_scene", "-Wl,-rpath,$ORIGIN/.."], ROOT)
+    return out
+
+
 def build_all(force=False):
-    return build_scene(force), build_cuda(force)
+    return build_scene(force), build_cuda(force), build_headless(force)
