@@ -4,7 +4,7 @@
 // RenderSampleBuffer would present is written as a PNG, the film optionally as raw RGBA32F.
 //
 //   ptb_headless --scene cornell|terrain[:grid]|room[:detail[:atlas]]|spherefield[:copies[:level[:camera]]]|FILE.json
-//                [--size WxH] [--spp N] [--camera I] [--tone clamp|reinhard|hable|aces] [--brightness B] [--white W]
+//                [--size WxH] [--spp N] [--max-frames F] [--camera I] [--tone clamp|reinhard|hable|aces] [--brightness B] [--white W]
 //                [--device D] [--builder sah-host|lbvh-gpu|ploc-gpu|auto] [--out frame.png] [--film film.rgba32f] [--table PATH]
 #include <chrono>
 #include <cstdio>
@@ -69,7 +69,7 @@ static scene* OpenScene(std::string const& Spec, std::string* Error) {
 
 int main(int argc, char** argv) {
     std::string SceneSpec = "cornell", Out, FilmOut, Tone = "aces", Builder, Table;
-    uint Width = 640, Height = 480, Spp = 64, Camera = 0;
+    uint Width = 640, Height = 480, Spp = 64, Camera = 0, MaxFrames = 1u << 20;
     int CudaDevice = 0;
     float Brightness = 1.0f, White = 1.0f;
     for (int I = 1; I < argc; I++) {
@@ -78,6 +78,7 @@ int main(int argc, char** argv) {
         if (A == "--scene") SceneSpec = Next();
         else if (A == "--size") { if (std::sscanf(Next(), "%ux%u", &Width, &Height) != 2) { std::fprintf(stderr, "ptb_headless: --size WxH\n"); return 2; } }
         else if (A == "--spp") Spp = (uint)std::atoi(Next());
+        else if (A == "--max-frames") MaxFrames = (uint)std::atoi(Next());
         else if (A == "--camera") Camera = (uint)std::atoi(Next());
         else if (A == "--tone") Tone = Next();
         else if (A == "--brightness") Brightness = (float)std::atof(Next());
@@ -88,7 +89,7 @@ int main(int argc, char** argv) {
         else if (A == "--film") FilmOut = Next();
         else if (A == "--table") Table = Next();
         else if (A == "--help" || A == "-h") {
-            std::printf("usage: ptb_headless --scene NAME[:params]|FILE.json [--size WxH] [--spp N] [--camera I] [--tone clamp|reinhard|hable|aces]\n"
+            std::printf("usage: ptb_headless --scene NAME[:params]|FILE.json [--size WxH] [--spp N] [--max-frames F] [--camera I] [--tone clamp|reinhard|hable|aces]\n"
                         "                    [--brightness B] [--white W] [--device D] [--builder sah-host|lbvh-gpu|ploc-gpu|auto]\n"
                         "                    [--out frame.png] [--film film.rgba32f] [--table spectrum_table.dat]\n");
             return 0;
@@ -131,7 +132,8 @@ int main(int argc, char** argv) {
     App.SampleBuffer = CreateSampleBuffer(App.Device, Width, Height);
     if (!App.DeviceScene || !App.SampleBuffer) return 1;
     if (!Builder.empty() && ptb_scene_set_builder(App.DeviceScene->Handle, BuilderId) != PTB_OK) { std::fprintf(stderr, "ptb_headless: %s\n", ptb_last_error()); return 1; }
-    UpdateDeviceScene(App.Device, App.DeviceScene, App.Scene, PackSceneData(App.Scene));     // everything is dirty in a new scene
+    PackSceneData(App.Scene);                     // (the Make*Scene helpers and LoadScene may have packed already: nothing is dirty then)
+    UpdateDeviceScene(App.Device, App.DeviceScene, App.Scene, SCENE_DIRTY_ALL);     // a new device scene needs every array
     App.BasicRenderer = CreateBasicRenderer(App.Device, App.DeviceScene, App.SampleBuffer);
     if (!App.BasicRenderer) return 1;
     App.CameraIndex = Camera;
@@ -146,8 +148,14 @@ int main(int argc, char** argv) {
     uint Frames = 0;
     double const Target = (double)Spp * Width * Height;
     for (;;) {
-        ptb_renderer_stats(App.BasicRenderer->Handle, &Stats);
+        uint64_t const Before = Stats.rays_traced;
+        if (ptb_renderer_stats(App.BasicRenderer->Handle, &Stats) != PTB_OK) { std::fprintf(stderr, "ptb_headless: %s\n", ptb_last_error()); return 1; }
         if ((double)Stats.paths_finished >= Target) break;
+        if (Stats.rays_traced == Before || Frames >= MaxFrames) {      // a failed Run* has already said why on stderr
+            std::fprintf(stderr, "ptb_headless: giving up after %u frames (%llu of %.0f paths finished)\n", Frames + 1,
+                         (unsigned long long)Stats.paths_finished, Target);
+            return 1;
+        }
         uint Batch = Frames < 64 ? 8 : 64;
         for (uint K = 0; K < Batch; K++) Update(&App, false);
         Frames += Batch;

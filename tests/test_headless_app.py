@@ -33,10 +33,13 @@ def test_headless_renders_what_the_python_binding_renders(exe, gpu, scenes, tmp_
     sc = scenes(name, *params)                                   # also makes sure the spectrum table file exists
     w, h, spp = 96, 64, 6
     film_path, png_path = str(tmp_path / "film.bin"), str(tmp_path / "frame.png")
-    out = subprocess.run([exe, "--scene", spec, "--size", "%dx%d" % (w, h), "--spp", str(spp), "--tone", "hable", "--brightness", "1.5",
-                          "--table", _build.SPECTRUM_TABLE, "--film", film_path, "--out", png_path],
-                         stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
-    assert out.returncode == 0, out.stderr
+    log_path = str(tmp_path / "stderr.txt")
+    with open(log_path, "wb") as log:                            # (a file, not a pipe: a misbehaving child must not fill this process)
+        out = subprocess.run([exe, "--scene", spec, "--size", "%dx%d" % (w, h), "--spp", str(spp), "--max-frames", "2000", "--tone", "hable",
+                              "--brightness", "1.5", "--table", _build.SPECTRUM_TABLE, "--film", film_path, "--out", png_path],
+                             stdout=subprocess.PIPE, stderr=log, text=True, timeout=120)
+    with open(log_path, "rb") as log:
+        assert out.returncode == 0, log.read(4000).decode(errors="replace")
     info = json.loads(out.stdout.strip().splitlines()[-1])
     assert info["paths_finished"] >= spp * w * h and info["rays_traced"] == (info["frames"] + 1) * w * h
     a = np.fromfile(film_path, dtype=np.float32).reshape(h, w, 4)
