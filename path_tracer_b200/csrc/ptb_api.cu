@@ -542,8 +542,7 @@ int ptb_renderer_create(ptb_context* ctx, ptb_scene* scene, ptb_film* film, ptb_
     r->aux = nullptr; r->ev_fork = r->ev_join = nullptr;
     RenderConsts& pc = r->pc;
     std::memset(&pc, 0, sizeof pc);
-    pc.width = film->width; pc.height = film->height;
-    pc.tiles_x = (film->width + 15) / 16;
+    set_film_geometry(pc, film->width, film->height);
     const uint32_t tiles = pc.tiles_x * ((film->height + 15) / 16);
     pc.slot_count = tiles * 256u;
     const size_t S = pc.slot_count;

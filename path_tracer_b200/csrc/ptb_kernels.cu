@@ -32,7 +32,8 @@ static int mode_of(unsigned traversal, unsigned tie) {
 // slot -> pixel (tile-major 16x16, basic_scatter.glsl:324-328)
 __device__ __forceinline__ bool slot_pixel(const RenderConsts& pc, u32 slot, u32& x, u32& y) {
     const u32 tile = slot >> 8, l = slot & 255u;
-    const u32 tx = tile % pc.tiles_x, ty = tile / pc.tiles_x;
+    u32 tx, ty;
+    udivmod(tile, pc.tiles_x, pc.tiles_x_magic, ty, tx);
     x = tx * 16u + (l & 15u);
     y = ty * 16u + (l >> 4);
     return x < pc.width && y < pc.height;        // slots beyond the last tile row have y >= height

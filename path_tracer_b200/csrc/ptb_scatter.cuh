@@ -25,7 +25,27 @@ struct RenderConsts {
     u32 width, height, tiles_x;
     u32 slot_count;         // slots covered by this launch (multiple of 256)
     u32 slot_base;          // first slot of this launch: a film may be rendered as several slot ranges (pipelines)
+    u32 width_magic, tiles_x_magic;   // floor(2^32 / width), floor(2^32 / tiles_x): see udivmod (set_film_geometry fills them)
 };
+
+// n / d and n % d for a launch-uniform divisor with m = floor(2^32 / d) (0xFFFFFFFF for d = 1): the high half of
+// n * m is the quotient or one less, for every 32-bit n, so one correction step makes it exact - a multiply-high and a
+// few ALU operations instead of the ~20-instruction general unsigned division.
+PTB_HD void udivmod(u32 n, u32 d, u32 m, u32& q, u32& r) {
+#ifdef __CUDA_ARCH__
+    q = __umulhi(n, m);
+#else
+    q = (u32)(((unsigned long long)n * m) >> 32);
+#endif
+    r = n - q * d;
+    if (r >= d) { q += 1u; r -= d; }
+}
+inline void set_film_geometry(RenderConsts& pc, u32 width, u32 height) {
+    pc.width = width; pc.height = height;
+    pc.tiles_x = (width + 15u) / 16u;
+    pc.width_magic = width > 1u ? (u32)(0x100000000ull / width) : 0xFFFFFFFFu;
+    pc.tiles_x_magic = pc.tiles_x > 1u ? (u32)(0x100000000ull / pc.tiles_x) : 0xFFFFFFFFu;
+}
 
 struct PathState {
     u32 pixel;              // y * width + x
@@ -261,7 +281,8 @@ PTB_HD bool scatter_invocation(const DeviceScene& s, const RenderConsts& pc, u32
         v.x += old.x; v.y += old.y; v.z += old.z; v.w += old.w;
     }
     *px = v;
-    const u32 px_x = path.pixel % pc.width, px_y = path.pixel / pc.width;
+    u32 px_x, px_y;
+    udivmod(path.pixel, pc.width, pc.width_magic, px_y, px_x);
     generate_new_path(s, pc, g, px_x, px_y, path, ray);
     return true;
 }

@@ -146,10 +146,18 @@ PTB_HD u32 pack_snorm2x16(f2 v) {
     int y = (int)roundf(gclamp(v.y, -1.0f, 1.0f) * 32767.0f);
     return ((u32)x & 0xFFFFu) | (((u32)y & 0xFFFFu) << 16);
 }
+// x / 32767.0f, correctly rounded, for x the value of an int16: q = RN(x * RN(1/32767)) and one correction step with
+// the exact residual (two fused multiply-adds) instead of the general IEEE division sequence.  Equal to the division
+// for all 65536 inputs (tests/test_host_layer.py checks every one through the host build of this header).
+PTB_HD float snorm16_to_float(float x) {
+    const float r = 0x1.0002p-15f;
+    const float q = x * r;
+    return fmaf(fmaf(-q, 32767.0f, x), r, q);
+}
 PTB_HD f2 unpack_snorm2x16(u32 p) {
     float x = (float)(int16_t)(p & 0xFFFFu);
     float y = (float)(int16_t)(p >> 16);
-    return mk2(gclamp(x / 32767.0f, -1.0f, 1.0f), gclamp(y / 32767.0f, -1.0f, 1.0f));
+    return mk2(gclamp(snorm16_to_float(x), -1.0f, 1.0f), gclamp(snorm16_to_float(y), -1.0f, 1.0f));
 }
 
 // binary16 -> binary32, exact (unpackHalf2x16).

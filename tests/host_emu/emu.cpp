@@ -62,13 +62,15 @@ void* emu_create(const ptb_scene_view* v, u32 w, u32 h) {
     e->ds.wide_tlas_root = e->wb.node_count ? 0u : 0xFFFFFFFFu;
     e->ds.features = PTB_FEAT_ALL;
     memset(&e->pc, 0, sizeof e->pc);
-    e->pc.width = w; e->pc.height = h; e->pc.tiles_x = (w + 15) / 16; e->pc.slot_count = w * h;
+    set_film_geometry(e->pc, w, h); e->pc.slot_count = w * h;
     e->pc.render_flags = 3;
     size_t n = (size_t)w * h;
     e->path.resize(n); e->ray.resize(n); e->hit.resize(n); e->prim.assign(n, 0xFFFFFFFFu); e->accum.assign(n, make_float4(0, 0, 0, 0));
     return e;
 }
 void emu_destroy(void* p) { delete (Emu*)p; }
+void emu_udivmod(u32 n, u32 d, u32* out2) { RenderConsts pc{}; set_film_geometry(pc, d, 16); udivmod(n, d, pc.width_magic, out2[0], out2[1]); }
+void emu_unpack_snorm2x16(u32 p, float* out2) { f2 v = unpack_snorm2x16(p); out2[0] = v.x; out2[1] = v.y; }
 void emu_wide_info(void* p, u32* out) { Emu* e = (Emu*)p; out[0] = e->wb.node_count; out[1] = e->wb.prim_count; out[2] = e->wb.depth; out[3] = e->wb.bvh2_depth; out[4] = (u32)(e->wb.build_seconds * 1000); }
 
 void emu_wide_download(void* p, u32* nodes, float* prims) {

@@ -39,6 +39,32 @@ def emu():
     return L
 
 
+def test_snorm_unpack_equals_the_division_for_every_input(emu):
+    """ptb_vec.cuh unpacks snorm16 with a multiply and two fused multiply-adds; GLSL defines it as clamp(x / 32767, -1, 1)."""
+    out = np.zeros(2, np.float32)
+    x = np.arange(-32768, 32768, dtype=np.int32)
+    want = np.clip(x.astype(np.float32) / np.float32(32767.0), -1.0, 1.0).astype(np.float32)
+    got = np.zeros((65536, 2), np.float32)
+    for k, v in enumerate(x):
+        emu.emu_unpack_snorm2x16(C.c_uint32((int(v) & 0xFFFF) | ((int(-v - 1) & 0xFFFF) << 16)), out.ctypes.data_as(C.c_void_p))
+        got[k] = out
+    assert np.array_equal(got[:, 0].view(np.uint32), want.view(np.uint32))
+    assert np.array_equal(got[:, 1].view(np.uint32), want[::-1].view(np.uint32))
+
+
+def test_magic_division_is_exact(emu):
+    """udivmod (ptb_scatter.cuh): multiply-high by floor(2^32 / d) plus one correction equals n // d, n % d."""
+    rng = np.random.default_rng(4)
+    out = (C.c_uint32 * 2)()
+    ds = [1, 2, 3, 7, 16, 17, 120, 240, 256, 1920, 3840, 4096, 65535, 65536, 2**31, 2**32 - 1] + [int(x) for x in rng.integers(1, 2**32, 40)]
+    for d in ds:
+        ns = [0, 1, d - 1, d, d + 1, 2 * d - 1, 2**32 - 1, 2**32 - d] + [int(x) for x in rng.integers(0, 2**32, 200)]
+        for n in ns:
+            n &= 0xFFFFFFFF
+            emu.emu_udivmod(C.c_uint32(n), C.c_uint32(d), out)
+            assert (out[0], out[1]) == (n // d, n % d), (n, d)
+
+
 def test_packed_layouts(scenes):
     sc = scenes("terrain", 32)
     v = sc.view
