@@ -40,17 +40,24 @@ PTB_HD void coordinate_frame(f3 z, f3& x, f3& y) {
     y = cross(x, z);
 }
 
+// sin and cos of one angle with one argument reduction (the same values sinf / cosf return, CUDA math API).
+PTB_HD void sin_cos(float a, float& s, float& c) { sincosf(a, &s, &c); }
+
 // common.glsl.inc:205-218
 PTB_HD f2 random_point_on_disk(Rng& g) {
     float r = sqrtf(g.uniform());
     float theta = g.uniform() * PTB_TAU;
-    return mk2(r * cosf(theta), r * sinf(theta));
+    float sn, cs;
+    sin_cos(theta, sn, cs);
+    return mk2(r * cs, r * sn);
 }
 PTB_HD f3 random_direction(Rng& g) {
     float z = 2.0f * g.uniform() - 1.0f;
     float r = sqrtf(1.0f - z * z);
     float phi = PTB_TAU * g.uniform();
-    return mk3(r * cosf(phi), r * sinf(phi), z);
+    float sn, cs;
+    sin_cos(phi, sn, cs);
+    return mk3(r * cs, r * sn, z);
 }
 
 // common.glsl.inc:228-254 — von Mises-Fisher lobe used for sky sampling.
@@ -59,7 +66,9 @@ PTB_HD f3 random_vmf(Rng& g, float kappa, f3 mu) {
     float z = 1.0f + (1.0f / kappa) * logf(xi + (1.0f - xi) * expf(-2.0f * kappa));
     float r = sqrtf(1.0f - z * z);
     float phi = g.uniform() * PTB_TAU;
-    f3 v = mk3(r * cosf(phi), r * sinf(phi), z);
+    float sn, cs;
+    sin_cos(phi, sn, cs);
+    f3 v = mk3(r * cs, r * sn, z);
     f3 mx, my;
     coordinate_frame(mu, mx, my);
     return safe_normalize((v.x * mx + v.y * my) + v.z * mu);
@@ -82,7 +91,9 @@ PTB_HD f3 sample_hg(float aniso, float u1, float u2) {
     }
     float r = sqrtf(1.0f - z * z);
     float phi = u2 * PTB_TAU;
-    return mk3(r * cosf(phi), r * sinf(phi), z);
+    float sn, cs;
+    sin_cos(phi, sn, cs);
+    return mk3(r * cs, r * sn, z);
 }
 
 // common.glsl.inc:281-354 — GGX.
@@ -106,8 +117,10 @@ PTB_HD f3 ggx_visible_normal(f3 d, f2 alpha, float u1, float u2) {
     float r = sqrtf(u1);
     float phi = PTB_TAU * u2;
     float s = 0.5f * (1.0f + vz.z);
-    float tx = r * cosf(phi);
-    float ty = (1.0f - s) * sqrtf(1.0f - tx * tx) + (s * r) * sinf(phi);
+    float sn, cs;
+    sin_cos(phi, sn, cs);
+    float tx = r * cs;
+    float ty = (1.0f - s) * sqrtf(1.0f - tx * tx) + (s * r) * sn;
     float tz = sqrtf(fmaxf(0.0f, (1.0f - tx * tx) - ty * ty));
     f3 n = (tx * vx + ty * vy) + tz * vz;
     return safe_normalize(mk3(alpha.x * n.x, alpha.y * n.y, fmaxf(0.0f, n.z)));

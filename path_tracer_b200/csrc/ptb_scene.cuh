@@ -190,7 +190,10 @@ PTB_HDN Ray generate_camera_ray(const DeviceScene& s, u32 camera_index, f2 nsp, 
     } else if (model == 2u) {
         float phi = (nsp.x - 0.5f) * PTB_TAU;
         float theta = (0.5f - nsp.y) * PTB_PI;
-        r.velocity = mk3(cosf(theta) * sinf(phi), sinf(theta), -cosf(theta) * cosf(phi));
+        float st, ct, sp2, cp2;
+        sin_cos(theta, st, ct);
+        sin_cos(phi, sp2, cp2);
+        r.velocity = mk3(ct * sp2, st, -ct * cp2);
     }
     float to[16];
     const float4* m = (const float4*)&cam->Transform.To[0];
