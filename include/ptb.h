@@ -284,6 +284,15 @@ typedef struct {
     uint32_t trace_launches, scatter_launches, mega_launches;
 } ptb_kernel_times;
 int  ptb_renderer_profile_frames(ptb_renderer* r, uint32_t frames, ptb_kernel_times* out);
+/* Measurement aid: ONE extra launch of the default wide-BVH trace kernel, instrumented, over the renderer's current
+ * rays (the trace step is idempotent: it rewrites the same hit records).  Counts what the kernel's own data layout
+ * makes it fetch: 80-byte BVH8 nodes and 48-byte leaf primitives, plus 48 B of wavefront state per ray (16 B ray in,
+ * 2 x 16 B hit out) - the "own-layout algorithmic bytes" of bench.py's roofline - and the lane occupancy of its phases. */
+typedef struct {
+    uint64_t rays, node_steps, prim_tests, warp_iterations, flushes;
+    uint32_t node_bytes, prim_bytes, state_bytes, _pad;
+} ptb_trace_stats;
+int  ptb_renderer_trace_stats(ptb_renderer* r, ptb_trace_stats* out);
 int  ptb_renderer_stats(ptb_renderer* r, ptb_stats* out);
 /* Debug/test: download one named SoA state array (names of basic.glsl.inc:23-59). */
 int  ptb_renderer_download_state(ptb_renderer* r, const char* name, void* host, size_t bytes);
@@ -299,6 +308,54 @@ int  ptb_raycast_device(ptb_scene* scene, const ptb_ray* device_rays, size_t n, 
  * host_rgba (RenderSizeX*RenderSizeY*4 floats, alpha 1).  host_shapes (optional) receives Hit.ShapeIndex
  * per pixel, *hit_shape the shape under (MouseX, MouseY) — the reference's pick query (QuerySSBO). */
 int  ptb_preview_render(ptb_scene* scene, const ptb_preview_params* params, float* host_rgba, uint32_t* host_shapes, uint32_t* hit_shape);
+
+/* ---- multi-GPU groups: sample-split rendering of one image on several GPUs of one NVLink box -------------------
+ * No reference counterpart: the reference binds one VkPhysicalDevice (src/core/vulkan.cpp:1485-1506).  Partial
+ * films add (rgb = sum of XYZ samples, a = sample count; resolve divides by a, resolve.glsl:117-118), so every rank
+ * renders a disjoint block of RandomSeed values (basic.cpp:315,323) into its own film and ONE exchange step combines
+ * them.  A group is a communicator over NCCL (loaded with dlopen at first use: libptb.so has no NCCL dependency);
+ * every group call is enqueued on its context's stream and is collective - all ranks make the same call in the same
+ * order.  Two ways to form a group:
+ *   - one process per GPU (torchrun / mpirun): rank 0 calls ptb_group_unique_id, the launcher hands the 128 bytes to
+ *     the other ranks, every rank calls ptb_group_create;
+ *   - one process driving n GPUs (bin/ptb_headless --devices): ptb_group_create_local, then ONE HOST THREAD PER
+ *     DEVICE issues that device's calls (collectives block until every rank has joined). */
+typedef struct { char bytes[128]; } ptb_group_id;
+typedef struct ptb_group ptb_group;
+int  ptb_group_unique_id(ptb_group_id* out);
+int  ptb_group_create(ptb_context* ctx, const ptb_group_id* id, int rank, int world, ptb_group** out);
+int  ptb_group_create_local(ptb_context* const* contexts, int count, ptb_group** out_groups /* [count], rank k on contexts[k] */);
+void ptb_group_destroy(ptb_group* group);
+int  ptb_group_rank(const ptb_group* group);
+int  ptb_group_world(const ptb_group* group);
+int  ptb_group_barrier(ptb_group* group);                 /* all ranks' streams have reached this point; synchronises */
+int  ptb_group_nccl_version(int* version);
+/* Seed schedule of the sample split: first FrameIndex of `rank` when every rank renders frames_per_rank frames after
+ * its reset (rank r owns base + r * (frames_per_rank + 1) + [0, frames_per_rank]: disjoint and gap-free over ranks). */
+uint32_t ptb_group_first_frame(int rank, int world, uint32_t frames_per_rank, uint32_t base);
+
+/* The root's device scene - packed arrays, atlas layers and the flattened BVH8 - sent device-to-device over NVLink
+ * (one ncclBroadcast per array).  Ranks other than `root` pass a freshly created, never updated scene: they neither
+ * pack nor build.  (UpdateVulkanScene, scene.cpp:1704-1960, is what runs on the root only.) */
+int  ptb_scene_replicate(ptb_scene* scene, ptb_group* group, int root);
+
+/* Sum of all ranks' films into `sum` on `root` (root < 0: on every rank).  `sum` may be the rank's own film (in
+ * place) or another film of the same size; ranks that receive nothing may pass NULL. */
+int  ptb_film_reduce(ptb_film* film, ptb_group* group, int root, ptb_film* sum);
+/* The exchange step fused with the resolve that follows it (RenderSampleBuffer on the combined film).  The resolved
+ * sRGB8 frame lands in host_srgb8 (W*H*4 bytes) on the root; other ranks pass NULL.  `sum` (root only, optional)
+ * also receives the float sum.  Synchronises. */
+#define PTB_REDUCE_NCCL        0u  /* ncclReduce of the float film (16 B/pixel) to the root + k_resolve there */
+#define PTB_REDUCE_NCCL_SLICED 1u  /* ncclReduceScatter -> each rank resolves its 1/n slice -> ncclAllGather of sRGB8 (4 B/pixel
+                                      on the second leg); needs W*H divisible by the group size and no `sum`, else = NCCL */
+#define PTB_REDUCE_P2P_FUSED   2u  /* one kernel per rank over NVLink peer memory: reads its slice of every rank's film, adds in
+                                      rank order (bit-identical to a sequential sum), tone-maps, writes sRGB8 (and the float sum)
+                                      straight into the root's buffers.  Films must be library-owned (no external_device_rgba)
+                                      when the ranks are separate processes. */
+int  ptb_film_reduce_resolve(ptb_film* film, ptb_group* group, int root, uint32_t mode, const ptb_resolve_params* params,
+                             ptb_film* sum, uint8_t* host_srgb8);
+typedef struct { float exchange_ms; uint32_t mode; uint64_t bytes_in; } ptb_reduce_times;   /* device time of the last reduce_resolve on this rank */
+int  ptb_group_last_reduce(ptb_group* group, ptb_reduce_times* out);
 
 #ifdef __cplusplus
 }

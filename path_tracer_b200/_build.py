@@ -14,7 +14,7 @@ REPO = os.path.dirname(ROOT)
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
 HOST_SOURCES = ["scene.cpp", "pack.cpp", "spectrum.cpp", "procedural.cpp", "model.cpp", "serializer.cpp", "capi.cpp"]
-CUDA_SOURCES = ["ptb_api.cu", "ptb_kernels.cu", "ptb_gpu_build.cu", "ptb_spectrum.cu", "ptb_wide_build.cpp"]
+CUDA_SOURCES = ["ptb_api.cu", "ptb_kernels.cu", "ptb_gpu_build.cu", "ptb_spectrum.cu", "ptb_group.cu", "ptb_wide_build.cpp"]
 
 SPECTRUM_TABLE = os.path.join(ROOT, "data", "sRGBSpectrumTable.dat")
 
@@ -85,7 +85,7 @@ def build_cuda(force=False, verbose=False):
         if verbose:
             print(log)
     if procs or force or _newer(out, objs):
-        _run([NVCC, "-shared", "-cudart", "static", "-gencode", "arch=compute_100a,code=sm_100a", "-o", out] + objs, d)
+        _run([NVCC, "-shared", "-cudart", "static", "-gencode", "arch=compute_100a,code=sm_100a", "-o", out] + objs + ["-ldl"], d)
     return out
 
 
@@ -106,7 +106,7 @@ def build_experiment(tag, defines):
         if p.returncode != 0:
             sys.stderr.write(log)
             raise RuntimeError("build failed: " + " ".join(cmd))
-    _run([NVCC, "-shared", "-cudart", "static", "-gencode", "arch=compute_100a,code=sm_100a", "-o", out] + objs, d)
+    _run([NVCC, "-shared", "-cudart", "static", "-gencode", "arch=compute_100a,code=sm_100a", "-o", out] + objs + ["-ldl"], d)
     return out
 
 

@@ -14,8 +14,7 @@
 #include <thread>
 #include <vector>
 
-#include "ptb.h"
-#include "ptb_kernels.h"
+#include "ptb_internal.h"
 #include "ptb_preview.cuh"
 #include "ptb_wide_build.h"
 #include "ptb_gpu_build.h"
@@ -23,105 +22,22 @@
 using namespace ptb;
 
 namespace {
-
 thread_local std::string g_error;
-
 int fail(int code, const std::string& msg) { g_error = msg; return code; }
 int cuda_fail(cudaError_t e, const char* what) {
     g_error = std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
     return PTB_E_CUDA;
 }
-#define CU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return cuda_fail(e_, #x); } while (0)
-
-template <class T>
-struct DevBuf {
-    T* p = nullptr; size_t n = 0;
-    cudaError_t upload(const T* host, size_t count, cudaStream_t st) {
-        if (count != n || !p) {
-            if (p) cudaFree(p);
-            p = nullptr; n = 0;
-            if (count) { cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T)); if (e != cudaSuccess) return e; }
-            n = count;
-        }
-        if (count) return cudaMemcpyAsync(p, host, count * sizeof(T), cudaMemcpyHostToDevice, st);
-        return cudaSuccess;
-    }
-    cudaError_t alloc(size_t count) {
-        release();
-        if (count) { cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T)); if (e != cudaSuccess) return e; }
-        n = count;
-        return cudaSuccess;
-    }
-    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
-};
-
 }  // namespace
 
-struct ptb_context { int device; cudaStream_t stream; unsigned* counter; };
-
-namespace ptb {     // for the other translation units of the library (ptb_spectrum.cu)
+namespace ptb {     // for the other translation units of the library (ptb_spectrum.cu, ptb_group.cu)
 int api_fail(int code, const std::string& msg) { return fail(code, msg); }
+int api_cuda_fail(cudaError_t e, const char* what) { return cuda_fail(e, what); }
+void api_set_error(const std::string& msg) { g_error = msg; }
+const std::string& api_error() { return g_error; }
 cudaStream_t api_stream(ptb_context* ctx) { return ctx->stream; }
 int api_device(ptb_context* ctx) { return ctx->device; }
 }
-
-// PTB_BUILDER_AUTO: the tree built on the GPU is in use at once; a host thread builds the SAH tree from the device
-// copies of the packed arrays and parks it here until the next call that uses the scene swaps it in.  Any tree gives
-// bit-identical hits (leaf primitives and the canonical rank are the same), so the swap is invisible in the results.
-struct TreeUpgrade {
-    std::thread th;
-    std::mutex mu;                       // device copies of shapes / faces / mesh nodes vs. re-upload; the hand-over below
-    bool running = false;                // under mu
-    uint64_t wanted = 0;                 // under mu: generation of the scene geometry
-    std::atomic<int> ready{0};           // 1: nodes/prims below hold the tree of generation `wanted`
-    std::atomic<bool> quit{false};
-    uint32_t* nodes = nullptr; float* prims = nullptr;
-    uint32_t node_count = 0, prim_count = 0, depth = 0, bvh2_depth = 0;
-    double sah_cost = 0.0, build_seconds = 0.0;
-};
-
-struct ptb_scene {
-    ptb_context* ctx;
-    TreeUpgrade* upgrade;
-    DevBuf<ptb_packed_texture> textures;
-    DevBuf<uint32_t> materials;
-    DevBuf<ptb_packed_shape> shapes;
-    DevBuf<ptb_packed_shape_node> shape_nodes;
-    DevBuf<ptb_packed_mesh_face> faces;
-    DevBuf<ptb_packed_mesh_vertex> vertices;
-    DevBuf<ptb_packed_mesh_node> mesh_nodes;
-    DevBuf<ptb_packed_camera> cameras;
-    std::vector<DevBuf<float>> layers;
-    DevBuf<const float*> layer_table;
-    DevBuf<uint32_t> wide_nodes;
-    DevBuf<float> wide_prims;
-    DevBuf<uint32_t> wide_planes;
-    DeviceScene ds;
-    ptb_wide_info wide_info;
-    unsigned raycast_variant;
-    uint32_t builder;                // PTB_BUILDER_*
-    uint32_t material_features;      // PTB_FEAT_DIFFUSE/METAL/TRANSLUCENT bits of the uploaded material slots
-};
-
-struct ptb_film {
-    ptb_context* ctx;
-    uint32_t width, height;
-    float4* accum; bool external;
-    uchar4* srgb; float* linear;
-};
-
-struct ptb_renderer {
-    ptb_context* ctx; ptb_scene* scene; ptb_film* film;
-    ptb_render_params params;
-    uint32_t frame_index;
-    RenderConsts pc;
-    WavefrontState st;
-    void* state_block;
-    unsigned* queue[2];           // material queues of the scatter step, one per pipeline (allocated on first use)
-    cudaStream_t aux;             // second pipeline
-    cudaEvent_t ev_fork, ev_join;
-    uint64_t rays_traced, kernel_launches;
-};
 
 static void upgrade_thread(ptb_scene* s) {
     TreeUpgrade* u = s->upgrade;
@@ -157,7 +73,7 @@ static void upgrade_thread(ptb_scene* s) {
               && cudaMemcpy(d_prims, wb.prims.data(), wb.prims.size() * 4, cudaMemcpyHostToDevice) == cudaSuccess;
         }
         std::lock_guard<std::mutex> l(u->mu);
-        if (ok && !u->quit.load() && u->wanted == gen && wb.node_count) {
+        if (ok && !u->quit.load() && u->wanted == gen && u->requested == gen && wb.node_count) {
             u->nodes = d_nodes; u->prims = d_prims;
             u->node_count = wb.node_count; u->prim_count = wb.prim_count; u->depth = wb.depth; u->bvh2_depth = wb.bvh2_depth;
             u->sah_cost = wb.sah_cost; u->build_seconds = wb.build_seconds;
@@ -167,9 +83,18 @@ static void upgrade_thread(ptb_scene* s) {
         }
         if (d_nodes) cudaFree(d_nodes);
         if (d_prims) cudaFree(d_prims);
-        if (u->quit.load() || !ok || u->wanted == gen) { u->running = false; return; }      // failed or nothing to build: the GPU tree stays
-        // the geometry changed while this tree was being built: build the new one
+        // failed, nothing to build, or the geometry changed and nobody asked for a host tree of the new one
+        // (another builder was selected, or the GPU build fell back to the host builder): the tree in use stays
+        if (u->quit.load() || !ok || u->wanted == gen || u->requested != u->wanted) { u->running = false; return; }
+        // the geometry changed while this tree was being built and a tree of the new one is wanted: build it
     }
+}
+
+// Every geometry change (whatever the builder, whether or not a GPU build follows): trees of the old geometry that
+// are parked or still being built must never be installed.  Caller holds u->mu.
+static void upgrade_invalidate_locked(TreeUpgrade* u) {
+    u->wanted++;
+    if (u->ready.exchange(0)) { cudaFree(u->nodes); cudaFree(u->prims); u->nodes = nullptr; u->prims = nullptr; }
 }
 
 // Called (host thread of the API) after a GPU build has been installed for new geometry.
@@ -179,8 +104,8 @@ static void upgrade_request(ptb_scene* s) {
     bool start = false;
     {
         std::lock_guard<std::mutex> l(u->mu);
-        u->wanted++;
-        if (u->ready.exchange(0)) { cudaFree(u->nodes); cudaFree(u->prims); u->nodes = nullptr; u->prims = nullptr; }   // a tree of the old geometry
+        if (u->wanted == 0) u->wanted = 1;
+        u->requested = u->wanted;
         if (!u->running) { u->running = true; start = true; }
     }
     if (start) {
@@ -337,7 +262,10 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
     }
     // a background tree build reads the device copies of shapes / faces / mesh nodes
     std::unique_lock<std::mutex> geometry_lock;
-    if (s->upgrade && (dirty & (PTB_SCENE_DIRTY_SHAPES | PTB_SCENE_DIRTY_MESHES))) geometry_lock = std::unique_lock<std::mutex>(s->upgrade->mu);
+    if (s->upgrade && (dirty & (PTB_SCENE_DIRTY_SHAPES | PTB_SCENE_DIRTY_MESHES))) {
+        geometry_lock = std::unique_lock<std::mutex>(s->upgrade->mu);
+        upgrade_invalidate_locked(s->upgrade);
+    }
     if (dirty & PTB_SCENE_DIRTY_SHAPES) {
         CU(s->shapes.upload(v->Shapes, v->ShapeCount, st));
         CU(s->shape_nodes.upload(v->ShapeNodes, v->ShapeNodeCount, st));
@@ -352,7 +280,10 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
         s->ds.mesh_vertices = s->vertices.p;
         s->ds.mesh_nodes = s->mesh_nodes.p; s->ds.mesh_node_count = v->MeshNodeCount;
     }
-    if (geometry_lock.owns_lock()) { CU(cudaStreamSynchronize(st)); geometry_lock.unlock(); }
+    if (geometry_lock.owns_lock()) {
+        CU(cudaStreamSynchronize(st));
+        geometry_lock.unlock();
+    }
     if (dirty & PTB_SCENE_DIRTY_CAMERAS) {
         CU(s->cameras.upload(v->Cameras, v->CameraCount, st));
         s->ds.cameras = s->cameras.p; s->ds.camera_count = v->CameraCount;
@@ -368,14 +299,17 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
         int rc = PTB_E_UNSUPPORTED;
         bool built = false;
         const bool gpu_builder = s->builder == PTB_BUILDER_LBVH_GPU || s->builder == PTB_BUILDER_PLOC_GPU || s->builder == PTB_BUILDER_AUTO;
-        if (s->upgrade && s->upgrade->ready.load()) {        // a host-built tree of the previous geometry was never used
-            std::lock_guard<std::mutex> l(s->upgrade->mu);
-            if (s->upgrade->ready.exchange(0)) { cudaFree(s->upgrade->nodes); cudaFree(s->upgrade->prims); s->upgrade->nodes = nullptr; s->upgrade->prims = nullptr; }
-        }
         if (gpu_builder) {
-            // needs the device copies of the shapes and faces this very update may not have refreshed
-            if (!(dirty & PTB_SCENE_DIRTY_SHAPES)) CU(s->shapes.upload(v->Shapes, v->ShapeCount, st));
-            if (!(dirty & PTB_SCENE_DIRTY_MESHES)) CU(s->faces.upload(v->MeshFaces, v->MeshFaceCount, st));
+            // needs the device copies of the shapes, faces and (for the background host build) mesh nodes; an update that
+            // did not carry them finds them resident from the update that did - re-sent only when they are missing
+            {
+                std::unique_lock<std::mutex> l;
+                if (s->upgrade) l = std::unique_lock<std::mutex>(s->upgrade->mu);
+                if (!(dirty & PTB_SCENE_DIRTY_SHAPES) && (s->shapes.n != v->ShapeCount || !s->shapes.p)) CU(s->shapes.upload(v->Shapes, v->ShapeCount, st));
+                if (!(dirty & PTB_SCENE_DIRTY_MESHES) && (s->faces.n != v->MeshFaceCount || !s->faces.p)) CU(s->faces.upload(v->MeshFaces, v->MeshFaceCount, st));
+                if (!(dirty & PTB_SCENE_DIRTY_MESHES) && (s->mesh_nodes.n != v->MeshNodeCount || !s->mesh_nodes.p)) CU(s->mesh_nodes.upload(v->MeshNodes, v->MeshNodeCount, st));
+                CU(cudaStreamSynchronize(st));
+            }
             GpuWideBuild gb;
             rc = build_wide_bvh_gpu(v, s->shapes.p, s->faces.p, st, s->builder == PTB_BUILDER_LBVH_GPU ? 0 : 1, &gb, &err);
             if (rc == PTB_OK) {
@@ -393,11 +327,7 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
                 s->wide_info.builder = s->builder == PTB_BUILDER_LBVH_GPU ? PTB_BUILDER_LBVH_GPU : PTB_BUILDER_PLOC_GPU;
                 s->wide_info.device_build_ms = gb.device_ms;
                 built = true;
-                if (s->builder == PTB_BUILDER_AUTO && gb.node_count) {
-                    if (!(dirty & PTB_SCENE_DIRTY_MESHES)) CU(s->mesh_nodes.upload(v->MeshNodes, v->MeshNodeCount, st));
-                    CU(cudaStreamSynchronize(st));
-                    upgrade_request(s);
-                }
+                if (s->builder == PTB_BUILDER_AUTO && gb.node_count) upgrade_request(s);
             }
         }
         if (!built) {
@@ -726,6 +656,32 @@ int ptb_renderer_profile_frames(ptb_renderer* r, uint32_t frames, ptb_kernel_tim
     r->frame_index += frames;
     r->rays_traced += (uint64_t)r->film->width * r->film->height * frames;
     r->kernel_launches += (uint64_t)frames * 1u;      // trace or megakernel; scatter_step counts its own
+    return PTB_OK;
+}
+
+int ptb_renderer_trace_stats(ptb_renderer* r, ptb_trace_stats* out) {
+    if (!r || !out) return fail(PTB_E_INVALID, "ptb_renderer_trace_stats: NULL argument");
+    std::memset(out, 0, sizeof *out);
+    int rc = prepare(r);
+    if (rc) return rc;
+    if (r->params.Traversal != PTB_TRAVERSAL_WIDE || r->scene->ds.wide_tlas_root == 0xFFFFFFFFu)
+        return fail(PTB_E_UNSUPPORTED, "ptb_renderer_trace_stats: counts the wide-BVH trace kernel only");
+    CU(cudaSetDevice(r->ctx->device));
+    cudaStream_t st = r->ctx->stream;
+    unsigned long long* d = nullptr;
+    CU(cudaMalloc((void**)&d, 8 * sizeof(unsigned long long)));
+    unsigned long long h[8] = {};
+    cudaError_t e = cudaMemsetAsync(d, 0, 8 * sizeof(unsigned long long), st);
+    // the trace step is idempotent on the wavefront state (it rewrites the same hit records); scatter re-arms the ray counter
+    if (e == cudaSuccess) e = cudaMemsetAsync(r->st.ray_counter, 0, sizeof(unsigned), st);
+    if (e == cudaSuccess) e = launch_trace_stats(r->scene->ds, r->pc, r->st, d, st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(r->st.ray_counter, 0, sizeof(unsigned), st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h, d, sizeof h, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(d);
+    if (e != cudaSuccess) return cuda_fail(e, "ptb_renderer_trace_stats");
+    out->node_steps = h[0]; out->prim_tests = h[1]; out->warp_iterations = h[2]; out->flushes = h[3]; out->rays = h[4];
+    out->node_bytes = 80; out->prim_bytes = 48; out->state_bytes = 48;
     return PTB_OK;
 }
 

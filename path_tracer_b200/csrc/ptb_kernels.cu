@@ -289,7 +289,8 @@ struct CoopWarp {
 };
 
 // Tests the first min(32, queued) primitives of the group queue, one per lane.  ghead is updated.
-__device__ __forceinline__ void coop_flush(const DeviceScene& s, CoopWarp& W, u32 lane, u32& ghead, u32 gtail, u32& qprims) {
+template <bool STATS = false>
+__device__ __forceinline__ void coop_flush(const DeviceScene& s, CoopWarp& W, u32 lane, u32& ghead, u32 gtail, u32& qprims, u32* tests = nullptr) {
     __syncwarp();
     const u32 groups = min(gtail - ghead, 32u);
     uint4 g = make_uint4(0u, 0u, 0u, 0u);
@@ -311,6 +312,7 @@ __device__ __forceinline__ void coop_flush(const DeviceScene& s, CoopWarp& W, u3
     HitId h;
     h.t = 0; h.shape = PTB_SHAPE_NONE; h.prim = 0xFFFFFFFFu; h.shape_type = 0; h.coords = mk3(0, 0, 0);
     if (lane < take) {
+        if (STATS) { tests[0]++; if (lane == 0) tests[1]++; }
         const u32 start = highest_bit(start_mask & (0xFFFFFFFFu >> (31u - lane)));
         const uint4 gg = W.group[(ghead + W.starts[start]) & (PTB_COOP_QUEUE - 1)];
         u32 bits = gg.y;
@@ -361,8 +363,12 @@ __device__ __forceinline__ void coop_flush(const DeviceScene& s, CoopWarp& W, u3
     __syncwarp();
 }
 
-template <class Job, int REFILL, bool SPEC, int WAIT_T>
-__global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_trace_coop(const Job job) {
+// STATS: the same kernel with per-lane work counters, summed into job-independent device memory at exit (one extra,
+// untimed launch from ptb_renderer_trace_stats: what bench.py's own-layout byte model and lane occupancy are measured with).
+//   [0] node steps (80-byte BVH8 nodes fetched + tested)   [1] leaf primitive tests (48-byte records)
+//   [2] warp loop iterations   [3] flushes (warp-wide primitive test rounds)   [4] rays retired
+template <class Job, int REFILL, bool SPEC, int WAIT_T, bool STATS = false>
+__global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_trace_coop(const Job job, unsigned long long* __restrict__ stats = nullptr) {
     __shared__ CoopWarp warp_mem[PTB_TRACE_WARPS];
     const DeviceScene& s = job.s;
     const u32 lane = threadIdx.x & 31u;
@@ -381,8 +387,10 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
     stack.smem = &W.stack[0][lane];
     stack.sp = 0;
     { Ray z; z.origin = z.velocity = mk3(0, 0, 0); z.duration = 0; c = wide_ctx(z); }
+    u32 n_nodes = 0, n_iter = 0, n_retired = 0, n_tests[2] = {0u, 0u};
 
     for (;;) {
+        if (STATS && lane == 0) n_iter++;
         // ---- refill: whole-warp preparation of the next 32 rays into a shared-memory pool, cheap pick-up by idle lanes ----
         const u32 idle = __ballot_sync(0xFFFFFFFFu, !active);
         if (__popc(idle) >= REFILL || idle == 0xFFFFFFFFu) {
@@ -458,6 +466,7 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
         pg.base = pg.bits = pg.valid = 0u;
         if (active && ng.y > 0x00FFFFFFu && (SPEC || (int)(last_seq - ghead) <= 0)) {
             const float reach = u2f((u32)(W.key[lane] >> 32));
+            if (STATS) n_nodes++;
             wide_node_step(s, c, reach, ng, pg, stack);
             if (ng.y <= 0x00FFFFFFu && !stack.empty()) ng = stack.pop();
         }
@@ -472,7 +481,7 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
             }
             gtail += (u32)__popc(has);
             qprims += __reduce_add_sync(0xFFFFFFFFu, (u32)__popc(pg.bits));
-            while (qprims >= (u32)PTB_COOP_FLUSH_PRIMS) coop_flush(s, W, lane, ghead, gtail, qprims);
+            while (qprims >= (u32)PTB_COOP_FLUSH_PRIMS) coop_flush<STATS>(s, W, lane, ghead, gtail, qprims, n_tests);
         }
 
         // ---- partial flush when too many lanes wait for their tests ----
@@ -481,7 +490,7 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
             const bool stepper = active && ng.y > 0x00FFFFFFu && (SPEC || !pending);
             const bool waiting = active && pending && !stepper;
             const u32 votes = __reduce_add_sync(0xFFFFFFFFu, (stepper ? 1u : 0u) | (waiting ? 0x100u : 0u));      // both counts, one reduction
-            if ((votes >> 8) >= (u32)WAIT_T || (votes & 0xFFu) == 0u) coop_flush(s, W, lane, ghead, gtail, qprims);
+            if ((votes >> 8) >= (u32)WAIT_T || (votes & 0xFFu) == 0u) coop_flush<STATS>(s, W, lane, ghead, gtail, qprims, n_tests);
         }
 
         // ---- retire ----
@@ -491,6 +500,15 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
             h.coords = mk3(u2f(W.detail[4][lane]), u2f(W.detail[5][lane]), u2f(W.detail[6][lane]));
             job.store(index, h);
             active = false;
+            if (STATS) n_retired++;
+        }
+    }
+    if (STATS) {
+        const u32 v[5] = {n_nodes, n_tests[0], n_iter, n_tests[1], n_retired};
+#pragma unroll
+        for (int k = 0; k < 5; k++) {
+            const u32 t = __reduce_add_sync(0xFFFFFFFFu, v[k]);
+            if (lane == 0 && t) atomicAdd(&stats[k], (unsigned long long)t);
         }
     }
 }
@@ -751,15 +769,20 @@ cudaError_t launch_restart(const DeviceScene& s, const RenderConsts& pc, const W
     return cudaGetLastError();
 }
 
-// Persistent grid: exactly the warps that are resident at once (148 SMs x occupancy).
+// Persistent grid: exactly the blocks that are resident at once (SMs x occupancy) on the CURRENT device.  Cached per
+// kernel instantiation and per device (one process may drive several GPUs: ptb_group_create_local).
+#define PTB_MAX_DEVICES 64
 template <class K>
-static unsigned persistent_grid(K kernel) {
+static unsigned persistent_grid(K kernel, int threads, unsigned* cache /* [PTB_MAX_DEVICES] */) {
     int dev = 0, sms = 148, per_sm = 1;
     cudaGetDevice(&dev);
+    if (dev >= 0 && dev < PTB_MAX_DEVICES && cache[dev]) return cache[dev];
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 32 * PTB_TRACE_WARPS, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0);
     if (per_sm < 1) per_sm = 1;
-    return (unsigned)(sms * per_sm);
+    const unsigned grid = (unsigned)(sms * per_sm);
+    if (dev >= 0 && dev < PTB_MAX_DEVICES) cache[dev] = grid;      // racing threads write the same value
+    return grid;
 }
 
 // Variants of the wide trace kernel (TraceVariant of the render parameters; 0 = one thread per slot):
@@ -775,11 +798,11 @@ static unsigned persistent_grid(K kernel) {
 template <class Job>
 static cudaError_t launch_persistent(const Job& job, unsigned variant, cudaStream_t stream) {
     switch (variant) {
-#define X(ID, R) case ID: { static unsigned grid = 0; if (!grid) grid = persistent_grid(k_trace_persistent<Job, R>); \
+#define X(ID, R) case ID: { static unsigned cache[PTB_MAX_DEVICES]; const unsigned grid = persistent_grid(k_trace_persistent<Job, R>, 32 * PTB_TRACE_WARPS, cache); \
                             k_trace_persistent<Job, R><<<grid, 32 * PTB_TRACE_WARPS, 0, stream>>>(job); break; }
         PTB_PERSISTENT_VARIANTS(X)
 #undef X
-#define X(ID, R, S, W) case ID: { static unsigned grid = 0; if (!grid) grid = persistent_grid(k_trace_coop<Job, R, S, W>); \
+#define X(ID, R, S, W) case ID: { static unsigned cache[PTB_MAX_DEVICES]; const unsigned grid = persistent_grid(k_trace_coop<Job, R, S, W>, 32 * PTB_TRACE_WARPS, cache); \
                                   k_trace_coop<Job, R, S, W><<<grid, 32 * PTB_TRACE_WARPS, 0, stream>>>(job); break; }
         PTB_COOP_VARIANTS(X)
 #undef X
@@ -805,6 +828,16 @@ cudaError_t launch_trace(const DeviceScene& s, const RenderConsts& pc, const Wav
     return cudaGetLastError();
 }
 
+cudaError_t launch_trace_stats(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, unsigned long long* stats, cudaStream_t stream) {
+    WavefrontJob job;
+    job.s = s; job.pc = pc; job.st = st;
+    static unsigned cache[PTB_MAX_DEVICES];
+    auto kernel = k_trace_coop<WavefrontJob, 4, true, 16, true>;          // = PTB_TRACE_VARIANT_DEFAULT (14) + counters
+    const unsigned grid = persistent_grid(kernel, 32 * PTB_TRACE_WARPS, cache);
+    kernel<<<grid, 32 * PTB_TRACE_WARPS, 0, stream>>>(job, stats);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_hit_attributes(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, uint4* out, cudaStream_t stream) {
     k_hit_attributes<<<pc.slot_count / 256u, 256, 0, stream>>>(s, pc, st, out);
     return cudaGetLastError();
@@ -826,14 +859,8 @@ size_t scatter_queue_bytes(unsigned slot_count) { return ((size_t)PTB_CLASSES * 
 template <u32 F>
 static void launch_list(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, const u32* list, const u32* count,
                         cudaStream_t stream) {
-    static unsigned grid = 0;
-    if (!grid) {
-        int dev = 0, sms = 148, per_sm = 1;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_scatter_list<F>, PTB_SCATTER_THREADS, 0);
-        grid = (unsigned)(sms * (per_sm < 1 ? 1 : per_sm));
-    }
+    static unsigned cache[PTB_MAX_DEVICES];
+    const unsigned grid = persistent_grid(k_scatter_list<F>, PTB_SCATTER_THREADS, cache);
     k_scatter_list<F><<<grid, PTB_SCATTER_THREADS, 0, stream>>>(s, pc, st, accum, list, count);
 }
 

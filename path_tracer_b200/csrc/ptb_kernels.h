@@ -33,6 +33,8 @@ cudaError_t launch_restart(const DeviceScene& s, const RenderConsts& pc, const W
 // tuning point (refill threshold, postpone threshold) selected by the variant number.
 cudaError_t launch_trace(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, unsigned traversal, unsigned tie,
                          unsigned variant, cudaStream_t stream);
+// The default cooperative trace kernel with work counters (5 x u64, see k_trace_coop): same hits, not timed.
+cudaError_t launch_trace_stats(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, unsigned long long* stats, cudaStream_t stream);
 // Debug/test: closest-hit attributes of the stored hits as {packed normal, packed tangent, u, v} per slot.
 cudaError_t launch_hit_attributes(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, uint4* out, cudaStream_t stream);
 cudaError_t launch_scatter(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, cudaStream_t stream);

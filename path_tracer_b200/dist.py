@@ -1,12 +1,13 @@
 """Sample-split multi-GPU rendering: one process per GPU, scene replicated,
-one sum-reduce of the float accumulation buffers.
+one exchange step that sums the float films.
 
-The reference is single-device (src/core/vulkan.cpp:1485-1506).  Samples are
-independent given distinct RNG streams and the film is additive (rgb = sum of
-XYZ, a = count; resolve divides by a, resolve.glsl:117-118), so partial films
-simply add.  There is no per-round exchange: the only collective is the final
-reduce of 16*W*H bytes over NCCL (NVLink 5 / NVSwitch), issued through
-torch.distributed, which is plumbing here, not the product.
+The data path is in libptb.so (include/ptb.h "groups": NCCL communicators, the
+flattened-scene broadcast, ncclReduce / reduce-scatter / the fused peer-memory
+reduce+resolve kernel).  This module is the launcher-side plumbing around it for
+torchrun-style jobs: it reads RANK / WORLD_SIZE / LOCAL_RANK / MASTER_*, hands
+rank 0's 128-byte group id to the other ranks through torch.distributed, and
+offers the scalar reductions bench.py needs for its timing (max / sum over
+ranks).  The reference itself is single-device (src/core/vulkan.cpp:1485-1506).
 """
 import os
 
@@ -35,14 +36,35 @@ def init_process_group(backend=None):
 
 def frame_schedule(rank, world, frames_per_rank, base=0):
     """First FrameIndex (= RNG seed, basic.cpp:315,323) of rank `rank` when every rank
-    renders `frames_per_rank` frames: rank r owns seeds base + r*F + [0, F] (the reset
-    dispatch uses the first one).  Blocks are disjoint and gap-free over ranks."""
+    renders `frames_per_rank` frames: rank r owns seeds base + r*(F+1) + [0, F] (the reset
+    dispatch uses the first one).  Blocks are disjoint and gap-free over ranks.
+    Same rule as ptb_group_first_frame in the C ABI."""
     stride = frames_per_rank + 1
     return base + rank * stride
 
 
+def broadcast_bytes(payload, src=0, device=None):
+    """Hands a small byte string from `src` to every rank (the group id, the camera records)."""
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return payload
+    box = [payload if dist.get_rank() == src else None]
+    dist.broadcast_object_list(box, src=src, device=device)
+    return box[0]
+
+
+def create_group(ctx, device=None):
+    """The C-ABI communicator of this job (None for a single process): rank 0 draws the id, everybody joins."""
+    from . import integrator as I
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return None
+    rank, world = dist.get_rank(), dist.get_world_size()
+    gid = broadcast_bytes(I.Group.unique_id() if rank == 0 else None, 0, device)
+    return I.Group(ctx, gid, rank, world)
+
+
 def reduce_film(accum, dst=0, all_ranks=False):
-    """Sums the RGBA32F accumulators of all ranks in place (on `dst`, or everywhere)."""
+    """torch.distributed sum of RGBA32F accumulator tensors (kept for hosts that own the film as a tensor;
+    the product path is Group.reduce / Group.reduce_resolve on library-owned films)."""
     if not dist.is_initialized() or dist.get_world_size() == 1:
         return accum
     if all_ranks:
@@ -75,6 +97,5 @@ def sum_over_ranks(value, device):
 
 def shutdown():
     """Tears the process group down (no-op for a single process)."""
-    import torch.distributed as dist
     if dist.is_available() and dist.is_initialized():
         dist.destroy_process_group()

@@ -33,9 +33,15 @@ ABI_SYMBOLS = [
     "ptb_film_resolve", "ptb_film_resolve_device",
     "ptb_renderer_create", "ptb_renderer_destroy", "ptb_renderer_set_params", "ptb_renderer_set_frame_index",
     "ptb_renderer_reset", "ptb_renderer_run", "ptb_renderer_run_frames", "ptb_renderer_profile_frames", "ptb_renderer_sync", "ptb_renderer_stats",
+    "ptb_renderer_trace_stats",
     "ptb_renderer_download_state", "ptb_renderer_slot_count", "ptb_raycast", "ptb_raycast_device", "ptb_preview_render",
     "ptb_spectrum_table_build", "ptb_spectrum_upsample",
+    "ptb_group_unique_id", "ptb_group_create", "ptb_group_create_local", "ptb_group_destroy", "ptb_group_rank", "ptb_group_world",
+    "ptb_group_barrier", "ptb_group_nccl_version", "ptb_group_first_frame", "ptb_scene_replicate", "ptb_film_reduce",
+    "ptb_film_reduce_resolve", "ptb_group_last_reduce",
 ]
+
+REDUCE_NCCL, REDUCE_NCCL_SLICED, REDUCE_P2P_FUSED = 0, 1, 2
 
 STATE_ARRAYS = {
     "OriginX": "f4", "OriginY": "f4", "OriginZ": "f4", "Duration": "f4", "PackedVelocity": "u4",
@@ -98,6 +104,7 @@ def lib():
         L.ptb_renderer_run_frames.argtypes = [vp, u32]
         L.ptb_renderer_profile_frames.argtypes = [vp, u32, C.POINTER(KernelTimes)]
         L.ptb_renderer_sync.argtypes = [vp]
+        L.ptb_renderer_trace_stats.argtypes = [vp, C.POINTER(TraceStats)]
         L.ptb_renderer_stats.argtypes = [vp, C.POINTER(Stats)]
         L.ptb_renderer_download_state.argtypes = [vp, C.c_char_p, vp, sz]
         L.ptb_renderer_slot_count.argtypes = [vp]
@@ -105,6 +112,21 @@ def lib():
         L.ptb_raycast.argtypes = [vp, vp, sz, u32, u32, vp]
         L.ptb_raycast_device.argtypes = [vp, vp, sz, u32, u32, vp]
         L.ptb_preview_render.argtypes = [vp, C.POINTER(PreviewParams), vp, vp, vp]
+        L.ptb_group_unique_id.argtypes = [vp]
+        L.ptb_group_create.argtypes = [vp, vp, C.c_int, C.c_int, C.POINTER(vp)]
+        L.ptb_group_create_local.argtypes = [C.POINTER(vp), C.c_int, C.POINTER(vp)]
+        L.ptb_group_destroy.argtypes = [vp]
+        L.ptb_group_destroy.restype = None
+        L.ptb_group_rank.argtypes = [vp]
+        L.ptb_group_world.argtypes = [vp]
+        L.ptb_group_barrier.argtypes = [vp]
+        L.ptb_group_nccl_version.argtypes = [C.POINTER(C.c_int)]
+        L.ptb_group_first_frame.argtypes = [C.c_int, C.c_int, u32, u32]
+        L.ptb_group_first_frame.restype = u32
+        L.ptb_scene_replicate.argtypes = [vp, vp, C.c_int]
+        L.ptb_film_reduce.argtypes = [vp, vp, C.c_int, vp]
+        L.ptb_film_reduce_resolve.argtypes = [vp, vp, C.c_int, u32, C.POINTER(ResolveParams), vp, vp]
+        L.ptb_group_last_reduce.argtypes = [vp, C.POINTER(ReduceTimes)]
         _lib = L
     return _lib
 
@@ -162,6 +184,83 @@ def upsample_texels(ctx, table, rgba, texture_type):
     out = np.empty_like(src)
     _check(lib().ptb_spectrum_upsample(ctx.h, table.ctypes.data, table.size, src.ctypes.data, out.ctypes.data, src.size // 4, texture_type))
     return out
+
+
+class TraceStats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("rays", "node_steps", "prim_tests", "warp_iterations", "flushes")] + \
+               [(n, C.c_uint32) for n in ("node_bytes", "prim_bytes", "state_bytes", "_pad")]
+
+
+class ReduceTimes(C.Structure):
+    _fields_ = [("exchange_ms", C.c_float), ("mode", C.c_uint32), ("bytes_in", C.c_uint64)]
+
+
+class Group:
+    """Communicator of the sample-split multi-GPU job (include/ptb.h "groups"; NCCL inside libptb.so).
+
+    One process per GPU: rank 0 calls Group.unique_id(), the launcher hands the 128 bytes to the other ranks
+    (torch.distributed, MPI, a pipe ...), every rank constructs Group(ctx, id, rank, world).  Every method is
+    collective: all ranks call it in the same order."""
+
+    def __init__(self, ctx, group_id, rank, world):
+        self.ctx = ctx
+        self.h = C.c_void_p()
+        buf = C.create_string_buffer(bytes(group_id), 128)
+        _check(lib().ptb_group_create(ctx.h, buf, rank, world, C.byref(self.h)))
+        self.rank, self.world = rank, world
+
+    @staticmethod
+    def unique_id():
+        buf = C.create_string_buffer(128)
+        _check(lib().ptb_group_unique_id(buf))
+        return bytes(buf.raw)
+
+    @staticmethod
+    def first_frame(rank, world, frames_per_rank, base=0):
+        """First FrameIndex (= RNG seed, basic.cpp:315,323) of `rank`: disjoint, gap-free seed blocks."""
+        return lib().ptb_group_first_frame(rank, world, frames_per_rank, base)
+
+    def barrier(self):
+        _check(lib().ptb_group_barrier(self.h))
+
+    def replicate_scene(self, device_scene, root=0):
+        """The root's flattened device scene, device-to-device to every other rank (which passes an empty DeviceScene)."""
+        _check(lib().ptb_scene_replicate(device_scene.h, self.h, root))
+
+    def reduce(self, film, root=0, into=None):
+        """Sum of all ranks' films into `into` on root (root < 0: everywhere); in place when `into` is the film itself."""
+        _check(lib().ptb_film_reduce(film.h, self.h, root, into.h if into is not None else None))
+
+    def reduce_resolve(self, film, params, mode=REDUCE_P2P_FUSED, root=0, into=None, out_srgb8=None):
+        """Exchange + RenderSampleBuffer of the combined film; the sRGB8 frame arrives in out_srgb8 on the root."""
+        p = ResolveParams(*params)
+        if self.rank == root and out_srgb8 is None:
+            out_srgb8 = np.empty((film.Height, film.Width, 4), dtype=np.uint8)
+        _check(lib().ptb_film_reduce_resolve(film.h, self.h, root, mode, C.byref(p), into.h if into is not None else None,
+                                             out_srgb8.ctypes.data if (self.rank == root and out_srgb8 is not None) else None))
+        return out_srgb8 if self.rank == root else None
+
+    def last_reduce(self):
+        t = ReduceTimes()
+        _check(lib().ptb_group_last_reduce(self.h, C.byref(t)))
+        return {"exchange_ms": float(t.exchange_ms), "mode": int(t.mode), "bytes_in": int(t.bytes_in)}
+
+    def close(self):
+        if self.h:
+            lib().ptb_group_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def nccl_version():
+    v = C.c_int(0)
+    _check(lib().ptb_group_nccl_version(C.byref(v)))
+    return v.value
 
 
 class DeviceScene:
@@ -333,6 +432,13 @@ class BasicRenderer:
 
     def sync(self):
         _check(lib().ptb_renderer_sync(self.h))
+
+    def trace_stats(self):
+        """One instrumented launch of the default trace kernel over the current rays: what its own layout fetches."""
+        self._push()
+        t = TraceStats()
+        _check(lib().ptb_renderer_trace_stats(self.h, C.byref(t)))
+        return {n: int(getattr(t, n)) for n, _ in TraceStats._fields_ if n != "_pad"}
 
     def stats(self):
         s = Stats()

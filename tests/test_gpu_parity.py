@@ -36,10 +36,20 @@ def dev(I, gpu, scenes):
     return get
 
 
+PRODUCT, REFERENCE_LAYOUT = "product", "reference-layout"
+MODES = [PRODUCT, REFERENCE_LAYOUT]
+
+
 def render_pair(I, gpu, dev, oracle, scenes, name, params, w, h, frames, camera=0, flags=3, limit=0, term=0.0, tie=None,
-                traversal=None, integrator=None, restart_rounds=2):
-    """Reset + RunBasicRenderer(2) + `frames` steady-state frames on both sides (application.cpp:104-114)."""
+                traversal=None, integrator=None, restart_rounds=2, mode=PRODUCT):
+    """Reset + RunBasicRenderer(2) + `frames` steady-state frames on both sides (application.cpp:104-114).
+    mode PRODUCT = what ships and what bench.py times: BVH8, the default k_trace_coop variant, ScatterMode AUTO (material
+    queues where the scene mixes materials), canonical ties on both sides.  REFERENCE_LAYOUT = the packed two-level BVH2
+    walked in the reference's order with the reference's tie rules (the configuration the oracle/_ref vectors pin)."""
     sc = scenes(name, *params)
+    if mode == PRODUCT:
+        tie = oracle.TIE_CANONICAL if tie is None else tie
+        traversal = I.TRAVERSAL_WIDE if traversal is None else traversal
     tie = oracle.TIE_FAITHFUL if tie is None else tie
     o = oracle.Renderer(sc.view, w, h, camera_index=camera, render_flags=flags, path_length_limit=limit,
                         path_termination_probability=term, tie=tie)
@@ -372,11 +382,12 @@ def assert_radiance_close(a, b, tol=1e-4, max_outlier_fraction=2e-3):
     return int(bad.sum())
 
 
+@pytest.mark.parametrize("mode", MODES)
 @pytest.mark.parametrize("name,params,w,h", [("cornell", (), 160, 96), ("terrain", (64,), 160, 96), ("room", (1, 512), 128, 64),
                                              ("spherefield", (12, 2, 2), 128, 64)])
-def test_primary_and_first_bounce_radiance(I, gpu, dev, oracle, scenes, name, params, w, h):
+def test_primary_and_first_bounce_radiance(I, gpu, dev, oracle, scenes, name, params, w, h, mode):
     """Restart + RunBasicRenderer(Rounds=2) (application.cpp:104-110): identical seeding, accumulators within 1e-4."""
-    o, r, film = render_pair(I, gpu, dev, oracle, scenes, name, params, w, h, frames=0)
+    o, r, film = render_pair(I, gpu, dev, oracle, scenes, name, params, w, h, frames=0, mode=mode)
     a, b = film.download(), o.accum()
     assert np.array_equal(a[..., 3], b[..., 3])                    # same paths finished per pixel
     assert_radiance_close(a[..., :3], b[..., :3])
@@ -458,28 +469,31 @@ def test_reference_shader_vectors(I, gpu, scenes, tag):
     assert_radiance_close(b[..., :3], g["accum_frames"][..., :3], max_outlier_fraction=2e-2)
 
 
+@pytest.mark.parametrize("mode", MODES)
 @pytest.mark.parametrize("w,h", [(50, 30), (17, 33), (16, 16)])
-def test_ragged_film_sizes(I, gpu, dev, oracle, scenes, w, h):
+def test_ragged_film_sizes(I, gpu, dev, oracle, scenes, w, h, mode):
     """Widths/heights that are not multiples of the 16x16 tile (generalisation of Q5)."""
-    o, r, film = render_pair(I, gpu, dev, oracle, scenes, "cornell", (), w, h, frames=3)
+    o, r, film = render_pair(I, gpu, dev, oracle, scenes, "cornell", (), w, h, frames=3, mode=mode)
     a, b = film.download(), o.accum()
     assert np.array_equal(a[..., 3], b[..., 3])
     assert_radiance_close(a[..., :3], b[..., :3], max_outlier_fraction=5e-3)
 
 
-def test_flags_limit_and_termination(I, gpu, dev, oracle, scenes):
+@pytest.mark.parametrize("mode", MODES)
+def test_flags_limit_and_termination(I, gpu, dev, oracle, scenes, mode):
     # no jitter, no accumulate, PathLengthLimit as a real limit (D5), Russian roulette 0.25
     for flags, limit, term in ((0, 0, 0.0), (1, 3, 0.0), (3, 0, 0.25), (2, 1, 0.0)):
-        o, r, film = render_pair(I, gpu, dev, oracle, scenes, "cornell", (), 64, 48, frames=4, flags=flags, limit=limit, term=term)
+        o, r, film = render_pair(I, gpu, dev, oracle, scenes, "cornell", (), 64, 48, frames=4, flags=flags, limit=limit, term=term, mode=mode)
         a, b = film.download(), o.accum()
         assert np.array_equal(a[..., 3], b[..., 3]), (flags, limit, term)
         assert_radiance_close(a[..., :3], b[..., :3], max_outlier_fraction=5e-3)
 
 
-def test_cameras_thin_lens_and_360(I, gpu, dev, oracle, scenes):
-    o, r, film = render_pair(I, gpu, dev, oracle, scenes, "room", (1, 512), 96, 48, frames=2)            # thin lens + textures + sky lobe
+@pytest.mark.parametrize("mode", MODES)
+def test_cameras_thin_lens_and_360(I, gpu, dev, oracle, scenes, mode):
+    o, r, film = render_pair(I, gpu, dev, oracle, scenes, "room", (1, 512), 96, 48, frames=2, mode=mode)            # thin lens + textures + sky lobe
     assert_radiance_close(film.download()[..., :3], o.accum()[..., :3], max_outlier_fraction=5e-3)
-    o, r, film = render_pair(I, gpu, dev, oracle, scenes, "spherefield", (12, 2, 2), 128, 64, frames=2)  # 360 camera, mixed materials
+    o, r, film = render_pair(I, gpu, dev, oracle, scenes, "spherefield", (12, 2, 2), 128, 64, frames=2, mode=mode)  # 360 camera, mixed materials
     assert_radiance_close(film.download()[..., :3], o.accum()[..., :3], max_outlier_fraction=5e-3)
 
 
@@ -579,12 +593,14 @@ def test_scatter_material_queues_equal_direct(I, gpu, dev, scenes):
         r.reset()
 
 
+@pytest.mark.parametrize("integrator", ["wavefront", "megakernel"])
 @pytest.mark.parametrize("name,params", [("cornell", ()), ("terrain", (64,))])
-def test_converged_image_within_one_percent(I, gpu, dev, oracle, scenes, name, params):
-    """Wide BVH + megakernel on the GPU against the reference-order oracle at equal sample counts."""
+def test_converged_image_within_one_percent(I, gpu, dev, oracle, scenes, name, params, integrator):
+    """The product configuration (BVH8, wavefront, default kernels) and the megakernel against the oracle at equal
+    sample counts."""
     w, h, frames = 96, 64, 400
-    o, r, film = render_pair(I, gpu, dev, oracle, scenes, name, params, w, h, frames=frames, tie=oracle.TIE_CANONICAL,
-                             traversal=I.TRAVERSAL_WIDE, integrator=I.INTEGRATOR_MEGAKERNEL)
+    o, r, film = render_pair(I, gpu, dev, oracle, scenes, name, params, w, h, frames=frames, mode=PRODUCT,
+                             integrator=I.INTEGRATOR_MEGAKERNEL if integrator == "megakernel" else I.INTEGRATOR_WAVEFRONT)
     a, b = film.download(), o.accum()
     ia = a[..., :3] / np.maximum(a[..., 3:], 1)
     ib = b[..., :3] / np.maximum(b[..., 3:], 1)
