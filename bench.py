@@ -269,6 +269,7 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=96, help="frames of the cpu_baseline sample (about 10-30 s of CPU work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ref-port", action="store_true", help="time the oracle port instead of oracle/_ref (the reference's shaders compiled as C++)")
+    ap.add_argument("--reduce-mode", default="p2p", choices=["p2p", "nccl", "sliced"], help="N > 1: how the end-to-end loop combines the films (ptb_film_reduce_resolve mode)")
     ap.add_argument("--spp-target", type=int, default=0, help="also measure the seconds from reset until every pixel holds this many samples")
     args = ap.parse_args()
     select_workload(args)
@@ -291,14 +292,39 @@ def main():
     device = torch.device("cuda", local_rank)
     rank, world = D.init_process_group()
 
+    # ---- setup: the scene is packed and flattened ONCE (rank 0) and sent device-to-device to the other ranks ----
     S.ensure_spectrum_table()
-    scene = S.Scene.make(SCENE_NAME, *SCENE_PARAMS)
     ctx = I.Context(local_rank)
-    dscene = I.DeviceScene(ctx, scene, builder={"sah-host": I.BUILDER_SAH_HOST, "lbvh-gpu": I.BUILDER_LBVH_GPU, "ploc-gpu": I.BUILDER_PLOC_GPU, "auto": I.BUILDER_AUTO}[args.builder])
+    group = D.create_group(ctx, device)                  # NCCL communicator inside libptb.so (None for one GPU)
+    builder = {"sah-host": I.BUILDER_SAH_HOST, "lbvh-gpu": I.BUILDER_LBVH_GPU, "ploc-gpu": I.BUILDER_PLOC_GPU, "auto": I.BUILDER_AUTO}[args.builder]
+    setup = {}
+    t0 = time.perf_counter()
+    if rank == 0:
+        scene = S.Scene.make(SCENE_NAME, *SCENE_PARAMS)
+        setup["scene_make_s"] = time.perf_counter() - t0
+        t1 = time.perf_counter()
+        dscene = I.DeviceScene(ctx, scene, builder=builder)
+        setup["upload_and_flatten_s"] = time.perf_counter() - t1
+        small = (bytes(scene.cameras.tobytes()), bytes(np.asarray(scene.globals).tobytes()))
+    else:
+        scene, small = None, None
+        dscene = I.DeviceScene(ctx)
+    if group is not None:
+        t1 = time.perf_counter()
+        group.replicate_scene(dscene, 0)
+        ctx.sync()
+        setup["replicate_s"] = time.perf_counter() - t1
+        small = D.broadcast_bytes(small, 0, device)
+    setup["total_s"] = time.perf_counter() - t0
+    # the per-step host inputs of the end-to-end loop (camera + globals records) as a view of their own, on every rank
+    cam_host = np.frombuffer(small[0], dtype=np.uint8).copy()
+    glob_host = np.frombuffer(small[1], dtype=np.uint8).copy()
+    from path_tracer_b200.types import SceneView
+    step_view = SceneView()
+    step_view.Cameras, step_view.CameraCount, step_view.Globals = cam_host.ctypes.data, len(cam_host) // 160, glob_host.ctypes.data
     wide = dscene.wide_info()
-    film_t = torch.zeros((HEIGHT, WIDTH, 4), dtype=torch.float32, device=device)       # torch owns the film so NCCL can reduce it
-    torch.cuda.synchronize()
-    film = I.SampleBuffer(ctx, WIDTH, HEIGHT, external_device_ptr=film_t.data_ptr())
+    film = I.SampleBuffer(ctx, WIDTH, HEIGHT)             # library-owned: peer-addressable for the fused exchange
+    total_film = I.SampleBuffer(ctx, WIDTH, HEIGHT) if (group is not None and rank == 0) else None
     r = I.BasicRenderer(ctx, dscene, film)
     r.Integrator = I.INTEGRATOR_MEGAKERNEL if args.integrator == "megakernel" else I.INTEGRATOR_WAVEFRONT
     r.Traversal = I.TRAVERSAL_WIDE if args.traversal == "wide" else I.TRAVERSAL_BVH2_REFERENCE
@@ -309,7 +335,7 @@ def main():
     if args.trace_variant >= 0:
         r.TraceVariant = args.trace_variant
     F = args.frames
-    total_frames = F * (2 * max(3, args.warmup) + 2 * args.steps + 16)   # both timed loops, their warm-ups, the profiled frames
+    total_frames = F * (2 * max(3, args.warmup) + 2 * args.steps + 16) + max(3, args.warmup) + max(args.steps, 20) + 64   # all timed loops, their warm-ups, the profiled frames
     r.set_frame_index(D.frame_schedule(rank, world, total_frames))                      # disjoint seed block per rank
     stream = torch.cuda.ExternalStream(ctx.stream, device=device)
 
@@ -331,8 +357,8 @@ def main():
         e0.record(stream)
         for _ in range(args.steps):
             r.run_frames(F)
-        if world > 1:
-            D.reduce_film(film_t, dst=0)          # the one exchange step of the sample-split job (NCCL sum over NVLink)
+        if group is not None:
+            group.reduce(film, 0, total_film)     # the one exchange step of the sample-split job: ptb_film_reduce (ncclReduce over NVLink)
         e1.record(stream)
     e1.synchronize()
     torch.cuda.synchronize()
@@ -349,53 +375,103 @@ def main():
     paths_all = D.sum_over_ranks(float(paths), device)
     value = rays_all / (ms_max * 1e-3) / 1e6
 
-    # ---- end to end through the public API with host buffers: per step, the camera + globals records go
-    #      host -> device (ptb_scene_update) and the resolved sRGB8 frame + stats come back to the host ----
-    lin_unused = None
+    # ---- end to end through the public API with host buffers.  Per step: the camera + globals records go host -> device
+    #      (ptb_scene_update), the frames run, and ONE resolved sRGB8 frame of the whole job arrives in pinned host memory on
+    #      rank 0 - at N > 1 that is ptb_film_reduce_resolve: every rank's film summed and tone-mapped by the fused
+    #      peer-memory kernel (NCCL reduce + root resolve where peer access is unavailable) - plus the stats read-back. ----
     D.barrier()
     torch.cuda.synchronize()
-    h2d = 160 * scene.view.CameraCount + 48
+    h2d = len(cam_host) + len(glob_host)
     d2h = WIDTH * HEIGHT * 4 + 4 * (r.slot_count // 256)
     frame_host = torch.empty((HEIGHT, WIDTH, 4), dtype=torch.uint8, pin_memory=True).numpy()     # pinned destination of the resolved frame
     tone = I.TONE_HABLE if TONE == "hable" else I.TONE_ACES
-    for _ in range(max(3, args.warmup)):          # untimed warm-up of this path too (first resolve allocates and loads its kernel)
-        dscene.update(scene, 1 | 32)
-        r.run_frames(F)
-        film.resolve(1.0, tone, 1.0, want_linear=False, out_srgb8=frame_host)
-        r.stats()
-    D.barrier()
-    s2 = r.stats()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        dscene.update(scene, 1 | 32)              # SCENE_DIRTY_GLOBALS | SCENE_DIRTY_CAMERAS (synchronises, like the reference)
-        r.run_frames(F)
-        lin_unused, srgb = film.resolve(1.0, tone, 1.0, want_linear=False, out_srgb8=frame_host)
-        s3 = r.stats()
-    e2e_s = time.perf_counter() - t0
-    e2e_s = D.max_over_ranks(e2e_s, device)
-    e2e_rays = D.sum_over_ranks(float(s3["rays_traced"] - s2["rays_traced"]), device)
-    e2e_value = e2e_rays / e2e_s / 1e6
+    exchange = {"mode": None, "ms": None}
+    reduce_mode = {"p2p": I.REDUCE_P2P_FUSED, "nccl": I.REDUCE_NCCL, "sliced": I.REDUCE_NCCL_SLICED}[args.reduce_mode]
+
+    def deliver_frame():
+        nonlocal reduce_mode
+        if group is None:
+            film.resolve(1.0, tone, 1.0, want_linear=False, out_srgb8=frame_host)
+            return
+        try:
+            group.reduce_resolve(film, (1.0, tone, 1.0), mode=reduce_mode, root=0, out_srgb8=frame_host if rank == 0 else None)
+        except I.PtbError as e:              # the verdict is collective: every rank lands here together
+            if reduce_mode == I.REDUCE_NCCL or e.code != -4:
+                raise
+            sys.stderr.write("bench.py: %s; falling back to ncclReduce + root resolve\n" % e)
+            reduce_mode = I.REDUCE_NCCL
+            group.reduce_resolve(film, (1.0, tone, 1.0), mode=reduce_mode, root=0, out_srgb8=frame_host if rank == 0 else None)
+
+    def e2e_loop(frames, steps):
+        for _ in range(max(3, args.warmup)):          # untimed warm-up of this path too (first resolve allocates and loads its kernel)
+            dscene.update(step_view, 1 | 32)
+            r.run_frames(frames)
+            deliver_frame()
+            r.stats()
+        D.barrier()
+        a = r.stats()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            dscene.update(step_view, 1 | 32)          # SCENE_DIRTY_GLOBALS | SCENE_DIRTY_CAMERAS (synchronises, like the reference)
+            r.run_frames(frames)
+            deliver_frame()
+            b = r.stats()
+        dt = D.max_over_ranks(time.perf_counter() - t0, device)
+        return D.sum_over_ranks(float(b["rays_traced"] - a["rays_traced"]), device) / dt / 1e6
+
+    e2e_value = e2e_loop(F, args.steps)
+    if group is not None:
+        t = group.last_reduce()
+        exchange = {"mode": {0: "ncclReduce + root resolve", 1: "reduce-scatter + sliced resolve + all-gather of sRGB8", 2: "fused peer-memory reduce + resolve kernel"}[t["mode"]],
+                    "ms": D.max_over_ranks(t["exchange_ms"], device), "film_bytes": t["bytes_in"]}
+    e2e_one = e2e_loop(1, max(args.steps, 20))        # what the reference does: present after EVERY frame (application.cpp:114)
 
     # ---- per-kernel device time (events around every launch) for the roofline of the trace kernel ----
     kt = r.profile_frames(F)
     trace_ms = (kt["trace_ms"] / max(1, kt["trace_launches"])) if kt["trace_launches"] else (kt["mega_ms"] / max(1, kt["mega_launches"]))
 
-    # ---- optional: wall time from reset until min-over-pixels alpha >= target ----
+    # ---- instrumented launch of the default trace kernel over the current rays: what its own layout fetches ----
+    tstats = None
+    if args.integrator == "wavefront" and args.traversal == "wide":
+        try:
+            tstats = r.trace_stats()
+        except I.PtbError:
+            tstats = None
+
+    # ---- optional: seconds from reset until every pixel of the COMBINED film holds >= target samples and the resolved frame
+    #      is in rank 0's host memory (BASELINE config 5 at N > 1: strong scaling, the exchange inside) ----
     spp = None
-    if args.spp_target > 0 and world == 1:
-        r.reset()
-        r.sync()
+    if args.spp_target > 0:
+        class _Cai:                               # the library-owned film as a torch tensor (no copy), for min() on the device
+            def __init__(self, ptr, shape):
+                self.__cuda_array_interface__ = {"shape": shape, "typestr": "<f4", "data": (ptr, False), "version": 2}
+        film_t = torch.as_tensor(_Cai(film.device_ptr, (HEIGHT, WIDTH, 4)), device=device)
+        per_rank = -(-args.spp_target // world)   # min over pixels of a sum >= sum of the per-rank minima
+        chunk = 64
+        r.set_frame_index(rank << 22)             # disjoint seed blocks of 4 Mi frames
+        D.barrier()
+        torch.cuda.synchronize()
         t0 = time.perf_counter()
+        r.reset()
         frames_done = 0
         while True:
-            r.run_frames(64)
+            r.run_frames(chunk)
+            frames_done += chunk
             r.sync()
-            frames_done += 64
-            if float(film_t[..., 3].min()) >= args.spp_target or frames_done > 64 * 4096:
+            if float(film_t[..., 3].min()) >= per_rank or frames_done >= (1 << 22) - chunk:
                 break
-        spp = {"target": args.spp_target, "seconds": time.perf_counter() - t0, "frames": frames_done,
-               "min_alpha": float(film_t[..., 3].min()), "mean_alpha": float(film_t[..., 3].mean())}
+        t_render = time.perf_counter() - t0
+        deliver_frame()
+        seconds = D.max_over_ranks(time.perf_counter() - t0, device)
+        spp = {"target": args.spp_target, "per_rank_target": per_rank, "seconds": seconds, "render_seconds_this_rank": t_render,
+               "frames_this_rank": frames_done, "frames_max": int(D.max_over_ranks(float(frames_done), device)),
+               "min_alpha_this_rank": float(film_t[..., 3].min()), "mean_alpha_this_rank": float(film_t[..., 3].mean()),
+               "exchange_ms": (D.max_over_ranks(group.last_reduce()["exchange_ms"], device) if group is not None else 0.0),
+               "what": "reset -> frames until min-over-pixels alpha >= ceil(target / n_gpus) on every rank -> exchange + resolve -> sRGB8 frame in rank 0's pinned host memory"}
+        del film_t
 
+    if group is not None:
+        group.close()
     D.shutdown()
     if rank != 0:
         return
@@ -425,29 +501,60 @@ def main():
         # workload in the committed full run (profiles/r01_v1_bench.json: 82.5 nodes, 7.05 faces, 1.92 shapes per ray)
         seg_bytes, trace_bytes = 3522.405, 3314.405
         bytes_source = "oracle traversal counters recorded in profiles/r01_v1_bench.json (same workload)"
+    from path_tracer_b200 import _build
+    build_hash = _build.source_hash()
+    live = WIDTH * HEIGHT
+    trace_s = trace_ms * 1e-3
+    issue_peak = 148 * 4 * sm_max * 1e6 / 1e9            # G warp-instructions / s: 148 SMs x 4 schedulers x one issue per clock
+    # ncu counters of the dominant kernels, per launch: accepted only from a capture of THIS build (source hash) of THIS workload
+    ncu, ncu_note = None, "no ncu capture of this build for this workload in profiles/traffic.json"
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f).get(args.workload)
+        default_path = args.integrator == "wavefront" and args.traversal == "wide" and args.trace_variant < 0 and args.builder == "sah-host"
+        if t and not default_path:
+            ncu_note = "profiles/traffic.json describes the default kernels; this run selected others"
+        elif t and t.get("build_hash") != build_hash:
+            ncu_note = "profiles/traffic.json was captured from build %s, this is build %s: not quoted" % (t.get("build_hash"), build_hash)
+        elif t:
+            ncu, ncu_note = t, t.get("source")
+    except Exception:
+        pass
     roofline = None
-    if trace_bytes is not None:
-        live = WIDTH * HEIGHT
-        achieved = live * trace_bytes / (trace_ms * 1e-3) / 1e9
-        traffic, issue = None, None
-        try:        # ncu figures of the committed capture of this command (per launch of the trace kernel)
-            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-                t = json.load(f).get(args.workload)
-            if t and args.integrator == "wavefront" and args.traversal == "wide" and args.trace_variant < 0:
-                traffic = t["dram_bytes_per_launch"]
-                issue = {"warp_instructions_per_launch": t["warp_instructions_per_launch"], "lanes_per_instruction": t["lanes_per_instruction"],
-                         "frac_of_issue_peak": t["warp_instructions_per_launch"] / (trace_ms * 1e-3 * 148 * 4 * sm_max * 1e6),
-                         "peak": "148 SMs x 4 schedulers x %.0f MHz" % sm_max, "source": t["source"]}
-        except Exception:
-            pass
-        roofline = {"bound": "hbm", "kernel": "k_trace" if kt["trace_launches"] else "k_mega", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                    "frac": achieved / hbm_peak, "traffic": traffic, "sm_issue": issue, "peak_source": peak_src,
-                    "algorithmic_bytes_per_ray": trace_bytes, "bytes_source": bytes_source, "rays_per_launch": live, "kernel_ms": trace_ms,
-                    "segment_bytes_model": seg_bytes, "whole_segment_achieved_gbs": value * 1e6 * seg_bytes / 1e9,
-                    "whole_segment_frac": value * 1e6 * seg_bytes / 1e9 / hbm_peak,
-                    "note": "achieved uses the SURVEY 8(d) per-ray bytes of the REFERENCE layout (BVH2 walk), so it can exceed the HBM peak: the BVH8 "
-                            "moves about a third of those bytes and most of them hit in L2 (traffic = ncu dram bytes per launch); "
-                            "the kernel is bound by SM issue (sm_issue), see profiles/"}
+    if kt["trace_launches"]:
+        own = None
+        if tstats and tstats["rays"]:
+            own_bytes = tstats["node_bytes"] * tstats["node_steps"] + tstats["prim_bytes"] * tstats["prim_tests"] + tstats["state_bytes"] * tstats["rays"]
+            own = {"bytes_per_launch": own_bytes, "bytes_per_ray": own_bytes / tstats["rays"], "node_steps_per_ray": tstats["node_steps"] / tstats["rays"],
+                   "prim_tests_per_ray": tstats["prim_tests"] / tstats["rays"], "achieved_gbs": own_bytes / trace_s / 1e9, "frac_of_hbm_peak": own_bytes / trace_s / 1e9 / hbm_peak,
+                   "lanes_per_node_step": tstats["node_steps"] / max(1, tstats["warp_iterations"]), "lanes_per_primitive_flush": tstats["prim_tests"] / max(1, tstats["flushes"]),
+                   "what": "80 B x BVH8 node steps + 48 B x leaf primitive tests + 48 B wavefront state per ray, counted by one instrumented launch of the "
+                           "same kernel over this run's rays (ptb_renderer_trace_stats); most of it is served by L1/L2, which is why it may exceed the HBM peak"}
+        inst = ncu["trace"]["warp_instructions_per_launch"] if ncu else None
+        achieved = inst / trace_s / 1e9 if inst else None
+        roofline = {"bound": "sm_issue", "kernel": "k_trace_coop", "achieved": achieved, "peak": issue_peak, "unit": "Gwarp-inst/s",
+                    "frac": achieved / issue_peak if achieved else None,
+                    "traffic": ncu["trace"]["dram_bytes_per_launch"] if ncu else None,
+                    "warp_instructions_per_launch": inst, "lanes_per_instruction": ncu["trace"]["lanes_per_instruction"] if ncu else None,
+                    "frac_of_lane_issue_peak": (achieved / issue_peak * ncu["trace"]["lanes_per_instruction"] / 32.0) if achieved else None,
+                    "kernel_ms": trace_ms, "rays_per_launch": live, "peak_source": "148 SMs x 4 schedulers x %.0f MHz (MEASURED_PEAKS.json sm_max_mhz)" % sm_max,
+                    "counters_source": ncu_note, "build_hash": build_hash,
+                    "own_layout": own,
+                    "reference_layout_model": None if trace_bytes is None else {
+                        "bytes_per_ray": trace_bytes, "achieved_gbs": live * trace_bytes / trace_s / 1e9, "bytes_source": bytes_source,
+                        "what": "SURVEY 8(d): what the REFERENCE's uncached BVH2 walk would fetch for these rays (32 B nodes, 48 B faces, 144 B shapes); "
+                                "a comparison figure, not this kernel's traffic"},
+                    "note": "software BVH traversal on the SMs is bound by instruction issue, not by HBM (DRAM traffic per launch is a few % of what HBM could move in the "
+                            "kernel's time); frac = warp instructions (ncu, this build) / (kernel time measured in this run x issue peak)"}
+    roofline_scatter = None
+    if kt["scatter_launches"]:
+        scatter_s = kt["scatter_ms"] / kt["scatter_launches"] * 1e-3
+        finished = paths / max(1, args.steps * F)            # paths finished per round in the timed loop (this rank)
+        sb = 208.0 * live + 32.0 * finished                    # 7 x 16 B in, 5 x 16 B out... per slot: hit0, hit1, ray, path0-3 in; ray, path0-3 out (+ the pixel RMW of a finished path)
+        roofline_scatter = {"bound": "hbm", "kernel": "k_scatter (direct) or k_classify + k_scatter_list per material queue", "achieved": sb / scatter_s / 1e9, "peak": hbm_peak,
+                            "unit": "GB/s", "frac": sb / scatter_s / 1e9 / hbm_peak, "traffic": ncu["scatter"]["dram_bytes_per_launch"] if (ncu and ncu.get("scatter")) else None,
+                            "kernel_ms": scatter_s * 1e3, "algorithmic_bytes_per_slot": 208, "algorithmic_bytes_per_finished_path": 32, "finished_paths_per_round": finished,
+                            "peak_source": peak_src}
     out = {
         "metric": "Mrays/s (ray segments traced, whole job)", "value": value, "unit": "Mrays/s",
         "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_max / args.steps,
@@ -464,9 +571,14 @@ def main():
         "kernel_ms": {"trace": kt["trace_ms"] / max(1, kt["trace_launches"]), "scatter": kt["scatter_ms"] / max(1, kt["scatter_launches"]),
                       "mega": kt["mega_ms"] / max(1, kt["mega_launches"])},
         "clocks": clocks,
-        "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "what": "per step: ptb_scene_update(camera+globals from host) + run_frames + ptb_film_resolve to a pinned host sRGB8 frame + stats"},
+        "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "frames_per_step": F,
+                "frames_per_step_1": {"value": e2e_one, "unit": "Mrays/s", "what": "the same loop with ONE frame per step: a resolved frame on the host after every frame, as the reference presents (application.cpp:114)"},
+                "exchange": exchange,
+                "what": "per step: ptb_scene_update(camera+globals from host) + run_frames + ONE resolved sRGB8 frame of the whole job in pinned host memory on rank 0 "
+                        "(ptb_film_resolve; at N > 1 ptb_film_reduce_resolve over all ranks' films) + stats; d2h is rank 0's"},
+        "setup_seconds": setup,
         "roofline": roofline,
+        "roofline_scatter": roofline_scatter,
         "cpu_baseline": cpu,
     }
     _emit(out)

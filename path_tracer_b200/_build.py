@@ -62,6 +62,20 @@ def _includes(path, seen):
                     _includes(os.path.normpath(os.path.join(base, name)), seen)
 
 
+def source_hash():
+    """sha256 (12 hex digits) over the CUDA sources, their headers and the compile flags: names the build that
+    profiles/traffic.json's ncu figures were captured from, so bench.py never quotes counters of another kernel."""
+    import hashlib
+    d = os.path.join(ROOT, "csrc")
+    h = hashlib.sha256(" ".join(cuda_flags()).encode())
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh", ".h", ".cpp")):
+            h.update(f.encode())
+            with open(os.path.join(d, f), "rb") as fh:
+                h.update(fh.read())
+    return h.hexdigest()[:12]
+
+
 def build_cuda(force=False, verbose=False):
     """One object per source (rebuilt only when it or a header it includes changed), then one link."""
     d = os.path.join(ROOT, "csrc")

@@ -96,7 +96,7 @@ def test_shipped_configuration_matches_oracle_at_full_size(I, gpu, oracle, key):
     sa, sb = a[m][:, :3].sum(axis=0, dtype=np.float64), b[m][:, :3].sum(axis=0, dtype=np.float64)
     assert (np.abs(sa - sb) <= 2e-3 * np.abs(sb)).all(), (sa, sb)
     st = r.stats()
-    assert st["rays_traced"] == (2 + frames) * w * h and int(a[..., 3].sum()) == st["paths_finished"]
+    assert st["rays_traced"] == (2 + frames) * w * h and int(a[..., 3].sum(dtype=np.float64)) == st["paths_finished"]
     lin, srgb = film.resolve(1.0, I.TONE_HABLE if tone == "hable" else I.TONE_ACES, 1.0)
     assert np.isfinite(lin).all()
 

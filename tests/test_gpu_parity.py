@@ -397,7 +397,7 @@ def test_primary_and_first_bounce_radiance(I, gpu, dev, oracle, scenes, name, pa
         live = r.state("ImagePosition") == o.state("ImagePosition")
         assert (bits(ga)[live] == bits(oa)[live]).mean() > 0.995, arr
     st = r.stats()
-    assert st["rays_traced"] == 2 * w * h and st["paths_finished"] == int(b[..., 3].sum()) == o.stats()["paths"]
+    assert st["rays_traced"] == 2 * w * h and st["paths_finished"] == int(b[..., 3].sum(dtype=np.float64)) == o.stats()["paths"]
 
 
 def test_first_bounce_golden(I, gpu, dev, scenes):
@@ -741,7 +741,7 @@ def test_full_size_c2_properties(I, gpu, oracle):
     st = r.stats()
     a = film.download()
     assert st["rays_traced"] == 16 * w * h
-    assert int(a[..., 3].sum()) == st["paths_finished"] > w * h
+    assert int(a[..., 3].sum(dtype=np.float64)) == st["paths_finished"] > w * h
     assert np.isfinite(a).all() and (a[..., 3] >= 0).all() and (a[..., 1] >= 0).all()
     lin, srgb = film.resolve(1.0, I.TONE_ACES, 1.0)
     assert np.isfinite(lin).all() and srgb[..., :3].std() > 5      # an actual picture
@@ -777,7 +777,7 @@ def test_medium_size_c4_properties(I, gpu, oracle):
         r.run_frames(10)
         st = r.stats()
         a = film.download()
-        assert st["rays_traced"] == 12 * w * h and int(a[..., 3].sum()) == st["paths_finished"] > 0
+        assert st["rays_traced"] == 12 * w * h and int(a[..., 3].sum(dtype=np.float64)) == st["paths_finished"] > 0
         assert np.isfinite(a).all()
         films.append(a)
     assert np.array_equal(films[0], films[1])

@@ -59,14 +59,14 @@ def test_sample_split_films_sum_exactly(I, gpu, scenes, world, scene_spec):
     own = [res[r]["own"] for r in range(world)]
     # Sigma alpha == Sigma paths_finished, per rank and in total
     for r in range(world):
-        assert int(own[r][..., 3].sum()) == res[r]["paths"] > 0
+        assert int(own[r][..., 3].sum(dtype=np.float64)) == res[r]["paths"] > 0
         assert res[r]["rays"] == Wk.FRAMES * Wk.W * Wk.H
         assert np.array_equal(res[r]["own_after"], own[r])
     seq = own[0].copy()
     for r in range(1, world):
         seq = seq + own[r]                                    # rank order, float32: what the peer-memory kernel computes
     total = np.sum(np.stack(own).astype(np.float64), axis=0)
-    assert int(seq[..., 3].sum()) == sum(res[r]["paths"] for r in range(world))
+    assert int(seq[..., 3].sum(dtype=np.float64)) == sum(res[r]["paths"] for r in range(world))
     root = res[0]
     assert np.array_equal(root["sum_p2p"], seq)               # bit for bit, any world size
     for key in ("sum_nccl", "sum_nccl"):
