@@ -371,6 +371,19 @@ def test_imported_obj_model_renders_like_the_oracle(I, gpu, oracle, tmp_path):
 
 
 # ---------------------------------------------------------------- radiance
+def assert_alpha_equal(a, b, mode, what=None):
+    """Paths finished per pixel.  The reference-layout traversal must agree with the oracle everywhere.  The product's BVH8
+    returns the brute-force closest hit, which the oracle's walk of the reference BVH2 misses for a few rays in 1e5 (its slab
+    test culls its own closest primitive on grazing / axis-parallel rays, Q19): bounded here, adjudicated ray by ray in
+    test_first_bounce_rays_product_traversal_is_the_brute_force_hit and measured per config in test_baseline_configs.py."""
+    if mode == REFERENCE_LAYOUT:
+        assert np.array_equal(a, b), what
+        return 0
+    differ = int((a != b).sum())
+    assert differ <= max(1, int(2e-4 * a.size)), (what, differ, a.size)
+    return differ
+
+
 def assert_radiance_close(a, b, tol=1e-4, max_outlier_fraction=2e-3):
     """|a-b| <= tol * max(|b|, 1) per channel; a path whose random branch flips on an ulp
     (libdevice vs glibc transcendentals) changes a whole sample, so a small fraction of
@@ -389,7 +402,7 @@ def test_primary_and_first_bounce_radiance(I, gpu, dev, oracle, scenes, name, pa
     """Restart + RunBasicRenderer(Rounds=2) (application.cpp:104-110): identical seeding, accumulators within 1e-4."""
     o, r, film = render_pair(I, gpu, dev, oracle, scenes, name, params, w, h, frames=0, mode=mode)
     a, b = film.download(), o.accum()
-    assert np.array_equal(a[..., 3], b[..., 3])                    # same paths finished per pixel
+    differ = assert_alpha_equal(a[..., 3], b[..., 3], mode)        # same paths finished per pixel
     assert_radiance_close(a[..., :3], b[..., :3])
     # wavefront state after the second round: origins bit-equal wherever the path history is equal
     for arr in ("PackedVelocity", "OriginX", "ImagePosition", "NormalizedLambda0", "ShapeAndMaterialIndex"):
@@ -397,7 +410,31 @@ def test_primary_and_first_bounce_radiance(I, gpu, dev, oracle, scenes, name, pa
         live = r.state("ImagePosition") == o.state("ImagePosition")
         assert (bits(ga)[live] == bits(oa)[live]).mean() > 0.995, arr
     st = r.stats()
-    assert st["rays_traced"] == 2 * w * h and st["paths_finished"] == int(b[..., 3].sum(dtype=np.float64)) == o.stats()["paths"]
+    assert st["rays_traced"] == 2 * w * h and int(b[..., 3].sum(dtype=np.float64)) == o.stats()["paths"]
+    assert st["paths_finished"] == int(a[..., 3].sum(dtype=np.float64)) and abs(st["paths_finished"] - o.stats()["paths"]) <= differ
+
+
+@pytest.mark.parametrize("name,params,w,h", [("terrain", (64,), 256, 160), ("spherefield", (12, 2, 2), 192, 96), ("room", (1, 512), 192, 96)])
+def test_first_bounce_rays_product_traversal_is_the_brute_force_hit(I, gpu, dev, oracle, scenes, name, params, w, h):
+    """The extension rays the oracle holds after reset + one round (first-bounce rays: grazing, starting 1e-3 off a surface)
+    cast through the product's BVH8 kernel and through the oracle's walk of the reference BVH2.  Where the two differ the
+    product's hit must be the oracle's brute-force closest hit - i.e. the reference traversal lost it, not the product."""
+    from util import unpack_unit_vectors
+    sc = scenes(name, *params)
+    o = oracle.Renderer(sc.view, w, h, tie=oracle.TIE_CANONICAL)
+    o.set_frame_index(0)
+    o.reset()
+    o.run(1)
+    n = w * h
+    origins = np.stack([o.state("OriginX"), o.state("OriginY"), o.state("OriginZ")], axis=1)[:n]
+    rays = oracle.make_rays(origins, unpack_unit_vectors(oracle, o.state("PackedVelocity")[:n]))
+    out = dev(name, *params).raycast(rays)
+    ref = oracle.raycast(sc.view, rays, tie=oracle.TIE_CANONICAL)
+    bad = np.nonzero(~(ids_equal(out, ref) & (bits(out["t"]) == bits(ref["t"]))))[0]
+    assert len(bad) <= max(2, int(2e-4 * n)), len(bad)
+    sample = np.concatenate([bad, np.arange(0, n, 211)]).astype(np.int64)
+    bf = oracle.raycast_bruteforce(sc.view, rays[sample])
+    assert ids_equal(out[sample], bf).all() and (bits(out["t"][sample]) == bits(bf["t"])).all()
 
 
 def test_first_bounce_golden(I, gpu, dev, scenes):
@@ -475,7 +512,7 @@ def test_ragged_film_sizes(I, gpu, dev, oracle, scenes, w, h, mode):
     """Widths/heights that are not multiples of the 16x16 tile (generalisation of Q5)."""
     o, r, film = render_pair(I, gpu, dev, oracle, scenes, "cornell", (), w, h, frames=3, mode=mode)
     a, b = film.download(), o.accum()
-    assert np.array_equal(a[..., 3], b[..., 3])
+    assert_alpha_equal(a[..., 3], b[..., 3], mode)
     assert_radiance_close(a[..., :3], b[..., :3], max_outlier_fraction=5e-3)
 
 
@@ -485,7 +522,7 @@ def test_flags_limit_and_termination(I, gpu, dev, oracle, scenes, mode):
     for flags, limit, term in ((0, 0, 0.0), (1, 3, 0.0), (3, 0, 0.25), (2, 1, 0.0)):
         o, r, film = render_pair(I, gpu, dev, oracle, scenes, "cornell", (), 64, 48, frames=4, flags=flags, limit=limit, term=term, mode=mode)
         a, b = film.download(), o.accum()
-        assert np.array_equal(a[..., 3], b[..., 3]), (flags, limit, term)
+        assert_alpha_equal(a[..., 3], b[..., 3], mode, (flags, limit, term))
         assert_radiance_close(a[..., :3], b[..., :3], max_outlier_fraction=5e-3)
 
 
