@@ -303,6 +303,18 @@ int  ptb_raycast(ptb_scene* scene, const ptb_ray* host_rays, size_t n, uint32_t 
 /* Same with both buffers already in device memory; enqueued on the context stream, no synchronisation. */
 int  ptb_raycast_device(ptb_scene* scene, const ptb_ray* device_rays, size_t n, uint32_t traversal, uint32_t tie_mode, ptb_hit* device_hits);
 
+/* ptb_raycast without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same kernel and bit-identical hits as ptb_raycast; the device staging of the rays and hits and the kernel's ray-fetch
+ * counter live in one file-scope static __device__ array (csrc/ptb_noalloc.cu) of PTB_NOALLOC_MAX_RAYS rays = 5.75 MiB,
+ * resident on every GPU that loads the library until the process exits.  n > PTB_NOALLOC_MAX_RAYS fails with
+ * PTB_E_INVALID.  Calls no cudaMalloc / cudaFree / allocating library routine.  All calls on a device share the array:
+ * the counter is cleared on the stream before each launch, the hits of the call's n rays are overwritten; calls that
+ * overlap on the GPU (two contexts or two host threads on one device) race - serialise them.  Synchronises. */
+#define PTB_NOALLOC_MAX_RAYS 65536
+int    ptb_raycast_noalloc(ptb_scene* scene, const ptb_ray* host_rays, size_t n, uint32_t traversal, uint32_t tie_mode, ptb_hit* host_hits);
+size_t ptb_raycast_noalloc_max_rays(void);
+
 /* ---- preview visualiser (src/application/preview_render.glsl:96-178; application.cpp preview pass) ----
  * One camera ray per pixel, closest hit, colour by RenderMode; no graphics API: the image is written to
  * host_rgba (RenderSizeX*RenderSizeY*4 floats, alpha 1).  host_shapes (optional) receives Hit.ShapeIndex

@@ -35,6 +35,7 @@ ABI_SYMBOLS = [
     "ptb_renderer_reset", "ptb_renderer_run", "ptb_renderer_run_frames", "ptb_renderer_profile_frames", "ptb_renderer_sync", "ptb_renderer_stats",
     "ptb_renderer_trace_stats",
     "ptb_renderer_download_state", "ptb_renderer_slot_count", "ptb_raycast", "ptb_raycast_device", "ptb_preview_render",
+    "ptb_raycast_noalloc", "ptb_raycast_noalloc_max_rays",
     "ptb_spectrum_table_build", "ptb_spectrum_upsample",
     "ptb_group_unique_id", "ptb_group_create", "ptb_group_create_local", "ptb_group_destroy", "ptb_group_rank", "ptb_group_world",
     "ptb_group_barrier", "ptb_group_nccl_version", "ptb_group_first_frame", "ptb_scene_replicate", "ptb_film_reduce",
@@ -111,6 +112,9 @@ def lib():
         L.ptb_renderer_slot_count.restype = u32
         L.ptb_raycast.argtypes = [vp, vp, sz, u32, u32, vp]
         L.ptb_raycast_device.argtypes = [vp, vp, sz, u32, u32, vp]
+        L.ptb_raycast_noalloc.argtypes = [vp, vp, sz, u32, u32, vp]
+        L.ptb_raycast_noalloc_max_rays.argtypes = []
+        L.ptb_raycast_noalloc_max_rays.restype = sz
         L.ptb_preview_render.argtypes = [vp, C.POINTER(PreviewParams), vp, vp, vp]
         L.ptb_group_unique_id.argtypes = [vp]
         L.ptb_group_create.argtypes = [vp, vp, C.c_int, C.c_int, C.POINTER(vp)]
@@ -302,6 +306,14 @@ class DeviceScene:
         rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
         out = np.zeros(len(rays), dtype=HIT_DTYPE)
         _check(lib().ptb_raycast(self.h, rays.ctypes.data, len(rays), traversal, tie, out.ctypes.data))
+        return out
+
+    def raycast_noalloc(self, rays, traversal=TRAVERSAL_WIDE, tie=TIE_CANONICAL):
+        """ptb_raycast_noalloc: the same query through the library's static device scratch (no cudaMalloc anywhere on the
+        path; at most ptb_raycast_noalloc_max_rays() rays per call; calls on one device must not overlap)."""
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        out = np.zeros(len(rays), dtype=HIT_DTYPE)
+        _check(lib().ptb_raycast_noalloc(self.h, rays.ctypes.data, len(rays), traversal, tie, out.ctypes.data))
         return out
 
     def preview(self, camera_to, camera_from, mode, width, height, brightness=1.0, selected=0xFFFFFFFF, mouse=(0, 0),
