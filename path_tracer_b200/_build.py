@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(ROOT)
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
-HOST_SOURCES = ["scene.cpp", "pack.cpp", "spectrum.cpp", "procedural.cpp", "model.cpp", "serializer.cpp", "capi.cpp"]
+HOST_SOURCES = ["scene.cpp", "pack.cpp", "spectrum.cpp", "procedural.cpp", "model.cpp", "image.cpp", "serializer.cpp", "capi.cpp"]
 CUDA_SOURCES = ["ptb_api.cu", "ptb_kernels.cu", "ptb_gpu_build.cu", "ptb_spectrum.cu", "ptb_group.cu", "ptb_noalloc.cu", "ptb_wide_build.cpp"]
 
 SPECTRUM_TABLE = os.path.join(ROOT, "data", "sRGBSpectrumTable.dat")

@@ -156,6 +156,13 @@ uint32_t ptbh_prefab_mesh_count(void* prefab_) {
     return E->Type == ENTITY_TYPE_MESH_INSTANCE ? 1u : (uint32_t)E->Children.size();
 }
 void* ptbh_load_texture(void* s, const char* path, int type, const char* name) { return LoadTexture((scene*)s, path, (texture_type)type, name && name[0] ? name : nullptr); }
+// DecodeImageFile (image.cpp): 0 and the size on success; pixels (w*h*4 floats) are copied when `out` holds `capacity` floats.
+int ptbh_decode_image(const char* path, int* w, int* h, float* out, size_t capacity) {
+    std::vector<vec4> px;
+    if (!DecodeImageFile(path, *w, *h, px)) return -1;
+    if (out && capacity >= px.size() * 4) std::memcpy(out, px.data(), px.size() * sizeof(vec4));
+    return 0;
+}
 int ptbh_write_png(const char* path, uint32_t w, uint32_t h, const uint8_t* rgba) { return WriteImagePNG(path, w, h, rgba) ? 0 : -1; }
 int ptbh_write_pfm(const char* path, uint32_t w, uint32_t h, const float* rgb) { return WriteImagePFM(path, w, h, rgb) ? 0 : -1; }
 uint32_t ptbh_mesh_vertex_count(void* m) { return (uint32_t)((mesh*)m)->Vertices.size(); }

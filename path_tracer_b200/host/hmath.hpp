@@ -42,8 +42,14 @@ struct mat4 {
     static mat4 identity() { mat4 m; m.c[0] = {1, 0, 0, 0}; m.c[1] = {0, 1, 0, 0}; m.c[2] = {0, 0, 1, 0}; m.c[3] = {0, 0, 0, 1}; return m; }
 };
 
-inline vec4 mul(const mat4& m, vec4 v) { return ((m.c[0] * v.x + m.c[1] * v.y) + m.c[2] * v.z) + m.c[3] * v.w; }
-inline mat4 mul(const mat4& a, const mat4& b) { mat4 r; for (int j = 0; j < 4; j++) r.c[j] = mul(a, b.c[j]); return r; }
+// glm 1.0.1's association: a matrix-vector product sums its four column terms in pairs, a matrix-matrix product sums
+// them left to right (both pinned against the reference's own PackSceneData, tests/test_reference_host.py).
+inline vec4 mul(const mat4& m, vec4 v) { return (m.c[0] * v.x + m.c[1] * v.y) + (m.c[2] * v.z + m.c[3] * v.w); }
+inline mat4 mul(const mat4& a, const mat4& b) {
+    mat4 r;
+    for (int j = 0; j < 4; j++) r.c[j] = ((a.c[0] * b.c[j].x + a.c[1] * b.c[j].y) + a.c[2] * b.c[j].z) + a.c[3] * b.c[j].w;
+    return r;
+}
 
 // Rz(rz) * Ry(ry) * Rx(rx)  — role of glm::eulerAngleZYX(Rotation.z, Rotation.y, Rotation.x)
 // in /root/reference/src/core/common.hpp:62-82.
@@ -69,28 +75,36 @@ inline mat4 make_transform(vec3 position, vec3 rotation, vec3 scale) {
     return m;
 }
 
-// General 4x4 inverse by cofactors (role of glm::inverse at scene.hpp:405).
+// glm::inverse(mat4) as the reference calls it (scene.hpp:403-406 PackTransform), in glm 1.0.1's operation order:
+// eighteen 2x2 minors of rows 1..3, four cofactor columns as sums of three products, signs by multiplication,
+// the determinant from column 0 with pairwise association, and one reciprocal.  Pinned bit for bit against the
+// reference's own PackTransform compiled in oracle/_ref/libref_host.so (tests/test_reference_host.py).
 inline mat4 inverse(const mat4& m) {
-    const float a00 = m.c[0].x, a01 = m.c[0].y, a02 = m.c[0].z, a03 = m.c[0].w;
-    const float a10 = m.c[1].x, a11 = m.c[1].y, a12 = m.c[1].z, a13 = m.c[1].w;
-    const float a20 = m.c[2].x, a21 = m.c[2].y, a22 = m.c[2].z, a23 = m.c[2].w;
-    const float a30 = m.c[3].x, a31 = m.c[3].y, a32 = m.c[3].z, a33 = m.c[3].w;
-    const float b00 = a00 * a11 - a01 * a10, b01 = a00 * a12 - a02 * a10, b02 = a00 * a13 - a03 * a10;
-    const float b03 = a01 * a12 - a02 * a11, b04 = a01 * a13 - a03 * a11, b05 = a02 * a13 - a03 * a12;
-    const float b06 = a20 * a31 - a21 * a30, b07 = a20 * a32 - a22 * a30, b08 = a20 * a33 - a23 * a30;
-    const float b09 = a21 * a32 - a22 * a31, b10 = a21 * a33 - a23 * a31, b11 = a22 * a33 - a23 * a32;
-    const float det = ((b00 * b11 - b01 * b10) + (b02 * b09 + b03 * b08)) - (b04 * b07 - b05 * b06);
-    const float id = 1.0f / det;
-    mat4 r;
-    r.c[0] = {(a11 * b11 - a12 * b10 + a13 * b09) * id, (a02 * b10 - a01 * b11 - a03 * b09) * id,
-              (a31 * b05 - a32 * b04 + a33 * b03) * id, (a22 * b04 - a21 * b05 - a23 * b03) * id};
-    r.c[1] = {(a12 * b08 - a10 * b11 - a13 * b07) * id, (a00 * b11 - a02 * b08 + a03 * b07) * id,
-              (a32 * b02 - a30 * b05 - a33 * b01) * id, (a20 * b05 - a22 * b02 + a23 * b01) * id};
-    r.c[2] = {(a10 * b10 - a11 * b08 + a13 * b06) * id, (a01 * b08 - a00 * b10 - a03 * b06) * id,
-              (a30 * b04 - a31 * b02 + a33 * b00) * id, (a21 * b02 - a20 * b04 - a23 * b00) * id};
-    r.c[3] = {(a11 * b07 - a10 * b09 - a12 * b06) * id, (a00 * b09 - a01 * b07 + a02 * b06) * id,
-              (a31 * b01 - a30 * b03 - a32 * b00) * id, (a20 * b03 - a21 * b01 + a22 * b00) * id};
-    return r;
+    auto e = [&](int col, int row) { return m.c[col][row]; };
+    auto minor2 = [&](int c0, int c1, int r0, int r1) { return e(c0, r0) * e(c1, r1) - e(c1, r0) * e(c0, r1); };
+    // minors named by (columns, rows): the pairs glm calls Coef00..Coef23
+    const float k00 = minor2(2, 3, 2, 3), k02 = minor2(1, 3, 2, 3), k03 = minor2(1, 2, 2, 3);
+    const float k04 = minor2(2, 3, 1, 3), k06 = minor2(1, 3, 1, 3), k07 = minor2(1, 2, 1, 3);
+    const float k08 = minor2(2, 3, 1, 2), k10 = minor2(1, 3, 1, 2), k11 = minor2(1, 2, 1, 2);
+    const float k12 = minor2(2, 3, 0, 3), k14 = minor2(1, 3, 0, 3), k15 = minor2(1, 2, 0, 3);
+    const float k16 = minor2(2, 3, 0, 2), k18 = minor2(1, 3, 0, 2), k19 = minor2(1, 2, 0, 2);
+    const float k20 = minor2(2, 3, 0, 1), k22 = minor2(1, 3, 0, 1), k23 = minor2(1, 2, 0, 1);
+    const float f0[4] = {k00, k00, k02, k03}, f1[4] = {k04, k04, k06, k07}, f2[4] = {k08, k08, k10, k11};
+    const float f3[4] = {k12, k12, k14, k15}, f4[4] = {k16, k16, k18, k19}, f5[4] = {k20, k20, k22, k23};
+    float v[4][4];                                       // v[r][i]: element of row r taken from column (i == 0 ? 1 : 0)
+    for (int r = 0; r < 4; r++) { v[r][0] = e(1, r); v[r][1] = v[r][2] = v[r][3] = e(0, r); }
+    mat4 adj;
+    for (int i = 0; i < 4; i++) {
+        const float sa = (i & 1) ? -1.0f : 1.0f, sb = -sa;
+        adj.c[0][i] = (v[1][i] * f0[i] - v[2][i] * f1[i] + v[3][i] * f2[i]) * sa;
+        adj.c[1][i] = (v[0][i] * f0[i] - v[2][i] * f3[i] + v[3][i] * f4[i]) * sb;
+        adj.c[2][i] = (v[0][i] * f1[i] - v[1][i] * f3[i] + v[3][i] * f5[i]) * sa;
+        adj.c[3][i] = (v[0][i] * f2[i] - v[1][i] * f4[i] + v[2][i] * f5[i]) * sb;
+    }
+    const float d0 = e(0, 0) * adj.c[0][0], d1 = e(0, 1) * adj.c[1][0], d2 = e(0, 2) * adj.c[2][0], d3 = e(0, 3) * adj.c[3][0];
+    const float inv_det = 1.0f / ((d0 + d1) + (d2 + d3));
+    for (int c = 0; c < 4; c++) for (int r = 0; r < 4; r++) adj.c[c][r] = adj.c[c][r] * inv_det;
+    return adj;
 }
 
 // ---- pack helpers (common.hpp:90-114, scene.cpp:1297) ----

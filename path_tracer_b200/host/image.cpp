@@ -1,0 +1,1012 @@
+// Host scene layer, part 5: image decoding for LoadTexture.
+//
+// The reference loads every texture and skybox through `stbi_loadf(Path, &W, &H, &N, 4)`
+// (/root/reference/src/scene/scene.cpp:294-297; model import :718), i.e. whatever stb_image
+// decodes, delivered as linear RGBA32F.  This file restates the parts of that contract the
+// reference's assets use, from the published formats, with stb_image's conversions:
+//   * PNG  (ISO/IEC 15948): all colour types and bit depths, tRNS, Adam7 interlace; inflate by zlib.
+//          16-bit samples are reduced to their high byte, sub-byte grey is scaled to 0..255,
+//          a tRNS colour key gives alpha 0 where the pixel equals it (stb_image.h: "convert_16_to_8",
+//          "depth_scale_table", "compute_transparency").
+//   * Radiance .hdr (RGBE, "#?RADIANCE" / "#?RGBE", FORMAT=32-bit_rle_rgbe, "-Y h +X w"):
+//          new-style per-channel run-length scanlines and flat pixels; rgb = mantissa * 2^(e-136), alpha 1.
+//   * JPEG (ITU T.81) baseline and progressive Huffman, 8-bit, 1 or 3 components, any sampling factors the
+//          decoder below can upsample (1x1, 2x1, 1x2, 2x2 and generic integer factors).  stb_image's integer
+//          IDCT, its triangle-filter chroma upsampling and its 20-bit fixed-point YCbCr conversion are
+//          followed so that 8-bit output is identical with the reference's.
+//   * PPM (P6) and PFM (PF) kept from round 1 (not stb formats with this contract: P6 is read as
+//          sRGB-encoded, PFM as linear float, rows bottom to top).
+// 8-bit sources become float the way stbi_loadf does it (stb_image.h "ldr_to_hdr"): colour channels
+// pow(v / 255, 2.2), alpha v / 255.
+// Pinned against the reference's own vendored stb_image.h compiled into oracle/_ref
+// (tests/test_image_decode.py; golden files written by tests/golden/make_image_golden.py).
+#include "scene.hpp"
+
+#include <zlib.h>
+
+#include <algorithm>
+#include <cctype>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+namespace ptb { namespace host {
+
+namespace {
+
+typedef unsigned char u8;
+typedef unsigned short u16;
+
+bool read_file(const char* path, std::vector<u8>& out) {
+    FILE* f = std::fopen(path, "rb");
+    if (!f) return false;
+    std::fseek(f, 0, SEEK_END);
+    long n = std::ftell(f);
+    std::fseek(f, 0, SEEK_SET);
+    if (n < 0) { std::fclose(f); return false; }
+    out.resize((size_t)n);
+    bool ok = n == 0 || std::fread(out.data(), 1, (size_t)n, f) == (size_t)n;
+    std::fclose(f);
+    return ok;
+}
+
+// 8-bit RGBA -> linear float RGBA as stbi_loadf delivers it.
+void ldr_to_float(const std::vector<u8>& rgba, std::vector<vec4>& px) {
+    float lut[256];
+    for (int v = 0; v < 256; v++) lut[v] = (float)(std::pow((double)(v / 255.0f), (double)2.2f) * (double)1.0f);
+    px.resize(rgba.size() / 4);
+    for (size_t i = 0; i < px.size(); i++)
+        px[i] = {lut[rgba[4 * i]], lut[rgba[4 * i + 1]], lut[rgba[4 * i + 2]], rgba[4 * i + 3] / 255.0f};
+}
+
+// ------------------------------------------------------------------ PNG
+uint32_t be32(const u8* p) { return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3]; }
+
+int paeth(int a, int b, int c) {
+    int p = a + b - c, pa = std::abs(p - a), pb = std::abs(p - b), pc = std::abs(p - c);
+    return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
+}
+
+// Unfilters one (sub)image of w x h pixels from `raw` and writes native-depth samples (channels per pixel) to `out`.
+bool png_unfilter(const u8*& raw, const u8* end, uint32_t w, uint32_t h, int channels, int depth, std::vector<u16>& out) {
+    const size_t bits = (size_t)channels * depth;
+    const size_t stride = (w * bits + 7) / 8, bpp = bits >= 8 ? bits / 8 : 1;
+    std::vector<u8> prev(stride, 0), cur(stride);
+    out.resize((size_t)w * h * channels);
+    for (uint32_t y = 0; y < h; y++) {
+        if (raw + 1 + stride > end) return false;
+        const int filter = *raw++;
+        if (filter > 4) return false;
+        for (size_t i = 0; i < stride; i++) {
+            const int a = i >= bpp ? cur[i - bpp] : 0, b = prev[i], c = i >= bpp ? prev[i - bpp] : 0;
+            int x = raw[i];
+            switch (filter) {
+                case 1: x += a; break;
+                case 2: x += b; break;
+                case 3: x += (a + b) >> 1; break;
+                case 4: x += paeth(a, b, c); break;
+                default: break;
+            }
+            cur[i] = (u8)x;
+        }
+        raw += stride;
+        u16* o = &out[(size_t)y * w * channels];
+        const size_t n = (size_t)w * channels;
+        if (depth == 8) for (size_t i = 0; i < n; i++) o[i] = cur[i];
+        else if (depth == 16) for (size_t i = 0; i < n; i++) o[i] = (u16)((cur[2 * i] << 8) | cur[2 * i + 1]);
+        else for (size_t i = 0; i < n; i++) {                      // 1, 2, 4 bits: most significant bits first
+            const size_t bit = i * depth;
+            o[i] = (u16)((cur[bit >> 3] >> (8 - depth - (bit & 7))) & ((1 << depth) - 1));
+        }
+        prev.swap(cur);
+    }
+    return true;
+}
+
+bool decode_png(const std::vector<u8>& file, int& W, int& H, std::vector<u8>& rgba) {
+    static const u8 sig[8] = {137, 80, 78, 71, 13, 10, 26, 10};
+    if (file.size() < 8 || std::memcmp(file.data(), sig, 8)) return false;
+    uint32_t w = 0, h = 0;
+    int depth = 0, ctype = 0, interlace = 0;
+    u8 palette[256][4];
+    for (auto& p : palette) { p[0] = p[1] = p[2] = 0; p[3] = 255; }
+    bool has_key = false, seen_ihdr = false;
+    u16 key[3] = {0, 0, 0};
+    std::vector<u8> idat;
+    size_t pos = 8;
+    while (pos + 8 <= file.size()) {
+        const uint32_t len = be32(&file[pos]);
+        const u8* type = &file[pos + 4];
+        const u8* data = &file[pos + 8];
+        if (pos + 12 + (size_t)len > file.size()) return false;
+        if (!std::memcmp(type, "IHDR", 4)) {
+            if (len != 13) return false;
+            w = be32(data); h = be32(data + 4);
+            depth = data[8]; ctype = data[9]; interlace = data[12];
+            if (data[10] != 0 || data[11] != 0 || interlace > 1) return false;
+            if (w == 0 || h == 0 || w > (1u << 24) || h > (1u << 24)) return false;
+            if (depth != 1 && depth != 2 && depth != 4 && depth != 8 && depth != 16) return false;
+            if (ctype != 0 && ctype != 2 && ctype != 3 && ctype != 4 && ctype != 6) return false;
+            if (ctype == 3 && depth == 16) return false;
+            if ((ctype == 2 || ctype == 4 || ctype == 6) && depth < 8) return false;
+            seen_ihdr = true;
+        } else if (!seen_ihdr) {
+            return false;
+        } else if (!std::memcmp(type, "PLTE", 4)) {
+            if (len > 768 || len % 3) return false;
+            for (uint32_t i = 0; i < len / 3; i++) { palette[i][0] = data[3 * i]; palette[i][1] = data[3 * i + 1]; palette[i][2] = data[3 * i + 2]; }
+        } else if (!std::memcmp(type, "tRNS", 4)) {
+            if (ctype == 3) { for (uint32_t i = 0; i < len && i < 256; i++) palette[i][3] = data[i]; }
+            else if (ctype == 0 && len >= 2) { key[0] = (u16)((data[0] << 8) | data[1]); has_key = true; }
+            else if (ctype == 2 && len >= 6) { for (int k = 0; k < 3; k++) key[k] = (u16)((data[2 * k] << 8) | data[2 * k + 1]); has_key = true; }
+        } else if (!std::memcmp(type, "IDAT", 4)) {
+            idat.insert(idat.end(), data, data + len);
+        } else if (!std::memcmp(type, "IEND", 4)) {
+            break;
+        }
+        pos += 12 + (size_t)len;
+    }
+    if (!seen_ihdr || idat.empty()) return false;
+    const int channels = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 3 ? 1 : ctype == 4 ? 2 : 4;
+
+    // inflate: the exact decompressed size follows from the header
+    static const int xorig[7] = {0, 4, 0, 2, 0, 1, 0}, yorig[7] = {0, 0, 4, 0, 2, 0, 1};
+    static const int xspc[7] = {8, 8, 4, 4, 2, 2, 1}, yspc[7] = {8, 8, 8, 4, 4, 2, 2};
+    size_t need = 0;
+    if (!interlace) need = (size_t)h * (1 + ((size_t)w * channels * depth + 7) / 8);
+    else for (int p = 0; p < 7; p++) {
+        const size_t pw = (w - xorig[p] + xspc[p] - 1) / xspc[p], ph = (h - yorig[p] + yspc[p] - 1) / yspc[p];
+        if (pw && ph) need += ph * (1 + (pw * channels * depth + 7) / 8);
+    }
+    std::vector<u8> raw(need);
+    {
+        z_stream zs;
+        std::memset(&zs, 0, sizeof zs);
+        if (inflateInit(&zs) != Z_OK) return false;
+        zs.next_in = idat.data(); zs.avail_in = (uInt)idat.size();
+        zs.next_out = raw.data(); zs.avail_out = (uInt)raw.size();
+        const int rc = inflate(&zs, Z_FINISH);
+        const size_t got = zs.total_out;
+        inflateEnd(&zs);
+        if ((rc != Z_STREAM_END && rc != Z_BUF_ERROR && rc != Z_OK) || got < need) return false;
+    }
+
+    std::vector<u16> samples((size_t)w * h * channels);
+    const u8* rp = raw.data();
+    const u8* rend = raw.data() + raw.size();
+    if (!interlace) {
+        if (!png_unfilter(rp, rend, w, h, channels, depth, samples)) return false;
+    } else {
+        std::vector<u16> sub;
+        for (int p = 0; p < 7; p++) {
+            const uint32_t pw = (w - xorig[p] + xspc[p] - 1) / xspc[p], ph = (h - yorig[p] + yspc[p] - 1) / yspc[p];
+            if (!pw || !ph) continue;
+            if (!png_unfilter(rp, rend, pw, ph, channels, depth, sub)) return false;
+            for (uint32_t j = 0; j < ph; j++)
+                for (uint32_t i = 0; i < pw; i++)
+                    std::memcpy(&samples[(((size_t)j * yspc[p] + yorig[p]) * w + (size_t)i * xspc[p] + xorig[p]) * channels],
+                                &sub[((size_t)j * pw + i) * channels], sizeof(u16) * channels);
+        }
+    }
+
+    // to 8-bit RGBA
+    static const int depth_scale[9] = {0, 0xff, 0x55, 0, 0x11, 0, 0, 0, 0x01};
+    W = (int)w; H = (int)h;
+    rgba.resize((size_t)w * h * 4);
+    const size_t n = (size_t)w * h;
+    auto to8 = [&](u16 v) -> u8 { return depth == 16 ? (u8)(v >> 8) : depth == 8 ? (u8)v : (u8)(v * depth_scale[depth]); };
+    // the colour key is compared at 16 bits for 16-bit files and on the scaled 8-bit values otherwise
+    u16 k8[3];
+    for (int k = 0; k < 3; k++) k8[k] = depth == 16 ? key[k] : (u16)((key[k] & 255) * depth_scale[depth]);
+    for (size_t i = 0; i < n; i++) {
+        const u16* s = &samples[i * channels];
+        u8* o = &rgba[4 * i];
+        switch (ctype) {
+            case 0: {
+                o[0] = o[1] = o[2] = to8(s[0]);
+                const u16 cmp = depth == 16 ? s[0] : (u16)to8(s[0]);
+                o[3] = (has_key && cmp == k8[0]) ? 0 : 255;
+                break;
+            }
+            case 2: {
+                for (int k = 0; k < 3; k++) o[k] = to8(s[k]);
+                bool eq = has_key;
+                for (int k = 0; k < 3 && eq; k++) eq = (depth == 16 ? s[k] : (u16)to8(s[k])) == k8[k];
+                o[3] = eq ? 0 : 255;
+                break;
+            }
+            case 3: std::memcpy(o, palette[s[0] & 255], 4); break;
+            case 4: o[0] = o[1] = o[2] = to8(s[0]); o[3] = to8(s[1]); break;
+            default: for (int k = 0; k < 4; k++) o[k] = to8(s[k]); break;
+        }
+    }
+    return true;
+}
+
+// ------------------------------------------------------------------ Radiance HDR
+bool hdr_line(const std::vector<u8>& f, size_t& pos, std::string& line) {
+    line.clear();
+    if (pos >= f.size()) return false;
+    while (pos < f.size() && f[pos] != '\n') { if (line.size() < 1023) line.push_back((char)f[pos]); pos++; }
+    pos++;
+    return true;
+}
+
+void rgbe_to_float(const u8* in, vec4& out) {
+    if (in[3] != 0) {
+        const float f1 = (float)std::ldexp(1.0f, (int)in[3] - (128 + 8));
+        out = {in[0] * f1, in[1] * f1, in[2] * f1, 1.0f};
+    } else {
+        out = {0.0f, 0.0f, 0.0f, 1.0f};
+    }
+}
+
+bool decode_hdr(const std::vector<u8>& file, int& W, int& H, std::vector<vec4>& px) {
+    size_t pos = 0;
+    std::string line;
+    if (!hdr_line(file, pos, line) || (line != "#?RADIANCE" && line != "#?RGBE")) return false;
+    bool format_ok = false;
+    for (;;) {
+        if (!hdr_line(file, pos, line)) return false;
+        if (line.empty()) break;
+        if (line == "FORMAT=32-bit_rle_rgbe") format_ok = true;
+    }
+    if (!format_ok || !hdr_line(file, pos, line)) return false;
+    long h = 0, w = 0;
+    {
+        if (line.compare(0, 3, "-Y ")) return false;
+        char* end = nullptr;
+        h = std::strtol(line.c_str() + 3, &end, 10);
+        while (*end == ' ') end++;
+        if (std::strncmp(end, "+X ", 3)) return false;
+        w = std::strtol(end + 3, nullptr, 10);
+    }
+    if (w <= 0 || h <= 0 || w > (1 << 24) || h > (1 << 24)) return false;
+    W = (int)w; H = (int)h;
+    px.resize((size_t)w * h);
+    auto flat_from = [&](size_t first_pixel) -> bool {
+        for (size_t i = first_pixel; i < (size_t)w * h; i++) {
+            if (pos + 4 > file.size()) return false;
+            rgbe_to_float(&file[pos], px[i]);
+            pos += 4;
+        }
+        return true;
+    };
+    if (w < 8 || w >= 32768) return flat_from(0);
+    std::vector<u8> scan((size_t)w * 4);
+    for (long j = 0; j < h; j++) {
+        if (pos + 4 > file.size()) return false;
+        const u8 c1 = file[pos], c2 = file[pos + 1], len = file[pos + 2];
+        if (c1 != 2 || c2 != 2 || (len & 0x80)) {
+            // not run-length encoded: these four bytes are a pixel, and the rest of the file is flat
+            if (j != 0) return false;
+            return flat_from(0);
+        }
+        if ((((long)len << 8) | file[pos + 3]) != w) return false;
+        pos += 4;
+        for (int k = 0; k < 4; k++) {
+            long i = 0;
+            while (i < w) {
+                if (pos >= file.size()) return false;
+                int count = file[pos++];
+                if (count > 128) {
+                    if (pos >= file.size()) return false;
+                    const u8 value = file[pos++];
+                    count -= 128;
+                    if (count == 0 || count > w - i) return false;
+                    for (int z = 0; z < count; z++) scan[(size_t)(i++) * 4 + k] = value;
+                } else {
+                    if (count == 0 || count > w - i || pos + (size_t)count > file.size()) return false;
+                    for (int z = 0; z < count; z++) scan[(size_t)(i++) * 4 + k] = file[pos++];
+                }
+            }
+        }
+        for (long i = 0; i < w; i++) rgbe_to_float(&scan[(size_t)i * 4], px[(size_t)j * w + i]);
+    }
+    return true;
+}
+
+// ------------------------------------------------------------------ JPEG (baseline + progressive Huffman)
+// Follows ITU T.81 for the entropy decoding and stb_image's integer arithmetic for everything after it
+// (dequantise, IDCT with 12-bit constants, triangle-filter upsampling, fixed-point YCbCr -> RGB).
+struct jpeg_huff {
+    u8 size[257];
+    u16 code[256];
+    u8 values[256];
+    int maxcode[18];
+    int delta[17];
+    int count = 0;
+    bool build(const int* counts) {
+        int k = 0;
+        for (int i = 0; i < 16; i++)
+            for (int j = 0; j < counts[i]; j++) { if (k >= 256) return false; size[k++] = (u8)(i + 1); }
+        size[k] = 0;
+        count = k;
+        int c = 0;
+        k = 0;
+        for (int j = 1; j <= 16; j++) {
+            delta[j] = k - c;
+            if (size[k] == j) {
+                while (size[k] == j) code[k++] = (u16)(c++);
+                if (c - 1 >= (1 << j)) return false;
+            }
+            maxcode[j] = c << (16 - j);
+            c <<= 1;
+        }
+        maxcode[17] = 0x7fffffff;
+        return true;
+    }
+};
+
+struct jpeg_component {
+    int id = 0, h = 1, v = 1, tq = 0, hd = 0, ha = 0, dc_pred = 0;
+    int w2 = 0, h2 = 0;                    // padded plane size in pixels
+    int coeff_w = 0, coeff_h = 0;          // blocks
+    std::vector<u8> plane;
+    std::vector<short> coeff;              // progressive only
+};
+
+struct jpeg_decoder {
+    const u8* p; const u8* end;
+    jpeg_huff huff_dc[4], huff_ac[4];
+    u16 dequant[4][64];
+    jpeg_component comp[4];
+    int ncomp = 0, width = 0, height = 0, hmax = 1, vmax = 1, mcu_x = 0, mcu_y = 0, mcu_w = 0, mcu_h = 0;
+    bool progressive = false;
+    int restart_interval = 0, todo = 0;
+    int spec_start = 0, spec_end = 0, succ_high = 0, succ_low = 0, eob_run = 0;
+    int scan_n = 0, order[4];
+    int app14_transform = -1;
+    bool jfif = false;
+    // bit reader
+    uint32_t code_buffer = 0; int code_bits = 0; int marker = 0xff; bool nomore = false;
+
+    int get8() { return p < end ? *p++ : 0; }
+    int get16() { int a = get8(); return (a << 8) | get8(); }
+
+    void grow() {
+        do {
+            unsigned b = nomore ? 0 : (unsigned)get8();
+            if (b == 0xff) {
+                int c = get8();
+                while (c == 0xff) c = get8();
+                if (c != 0) { marker = c; nomore = true; return; }
+            }
+            code_buffer |= b << (24 - code_bits);
+            code_bits += 8;
+        } while (code_bits <= 24);
+    }
+    int huff_decode(const jpeg_huff& h) {
+        if (code_bits < 16) grow();
+        const unsigned temp = code_buffer >> 16;
+        int k;
+        for (k = 1; ; k++) if ((int)temp < h.maxcode[k]) break;
+        if (k == 17) { code_bits -= 16; return -1; }
+        if (k > code_bits) return -1;
+        const int c = (int)((code_buffer >> (32 - k)) & ((1u << k) - 1)) + h.delta[k];
+        if (c < 0 || c >= 256) return -1;
+        code_bits -= k;
+        code_buffer <<= k;
+        return h.values[c];
+    }
+    int extend_receive(int n) {              // n bits, sign-extended per T.81 F.2.2.1
+        if (n == 0) return 0;
+        if (code_bits < n) grow();
+        if (code_bits < n) return 0;
+        const int sgn = (int)(code_buffer >> 31);
+        const unsigned k = (code_buffer << n) | (code_buffer >> (32 - n));      // rotate left
+        const unsigned mask = (1u << n) - 1;
+        code_buffer = k & ~mask;
+        code_bits -= n;
+        return (int)(k & mask) + ((sgn - 1) & (int)((~0u << n) + 1));
+    }
+    int get_bits(int n) {
+        if (n == 0) return 0;
+        if (code_bits < n) grow();
+        if (code_bits < n) return 0;
+        const unsigned k = (code_buffer << n) | (code_buffer >> (32 - n));
+        const unsigned mask = (1u << n) - 1;
+        code_buffer = k & ~mask;
+        code_bits -= n;
+        return (int)(k & mask);
+    }
+    int get_bit() {
+        if (code_bits < 1) grow();
+        if (code_bits < 1) return 0;
+        const unsigned k = code_buffer;
+        code_buffer <<= 1;
+        --code_bits;
+        return (int)(k & 0x80000000u);
+    }
+    void reset() {
+        code_bits = 0; code_buffer = 0; nomore = false;
+        for (int i = 0; i < 4; i++) comp[i].dc_pred = 0;
+        marker = 0xff;
+        todo = restart_interval ? restart_interval : 0x7fffffff;
+        eob_run = 0;
+    }
+};
+
+const u8 jpeg_dezigzag[64 + 15] = {
+    0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28,
+    35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63,
+    63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63};
+
+bool jpeg_block_baseline(jpeg_decoder& j, short data[64], const jpeg_huff& hdc, const jpeg_huff& hac, int b, const u16* dq) {
+    if (j.code_bits < 16) j.grow();
+    const int t = j.huff_decode(hdc);
+    if (t < 0 || t > 15) return false;
+    std::memset(data, 0, 64 * sizeof(short));
+    const int diff = t ? j.extend_receive(t) : 0;
+    const int dc = j.comp[b].dc_pred + diff;
+    j.comp[b].dc_pred = dc;
+    data[0] = (short)(dc * dq[0]);
+    int k = 1;
+    do {
+        const int rs = j.huff_decode(hac);
+        if (rs < 0) return false;
+        const int s = rs & 15, r = rs >> 4;
+        if (s == 0) {
+            if (rs != 0xf0) break;
+            k += 16;
+        } else {
+            k += r;
+            const unsigned zig = jpeg_dezigzag[k++];
+            data[zig] = (short)(j.extend_receive(s) * dq[zig]);
+        }
+    } while (k < 64);
+    return true;
+}
+
+bool jpeg_block_prog_dc(jpeg_decoder& j, short data[64], const jpeg_huff& hdc, int b) {
+    if (j.spec_end != 0) return false;
+    if (j.code_bits < 16) j.grow();
+    if (j.succ_high == 0) {
+        std::memset(data, 0, 64 * sizeof(short));
+        const int t = j.huff_decode(hdc);
+        if (t < 0 || t > 15) return false;
+        const int diff = t ? j.extend_receive(t) : 0;
+        const int dc = j.comp[b].dc_pred + diff;
+        j.comp[b].dc_pred = dc;
+        data[0] = (short)(dc * (1 << j.succ_low));
+    } else {
+        if (j.get_bit()) data[0] += (short)(1 << j.succ_low);
+    }
+    return true;
+}
+
+bool jpeg_block_prog_ac(jpeg_decoder& j, short data[64], const jpeg_huff& hac) {
+    if (j.spec_start == 0) return false;
+    if (j.succ_high == 0) {
+        const int shift = j.succ_low;
+        if (j.eob_run) { --j.eob_run; return true; }
+        int k = j.spec_start;
+        do {
+            const int rs = j.huff_decode(hac);
+            if (rs < 0) return false;
+            const int s = rs & 15, r = rs >> 4;
+            if (s == 0) {
+                if (r < 15) {
+                    j.eob_run = 1 << r;
+                    if (r) j.eob_run += j.get_bits(r);
+                    --j.eob_run;
+                    break;
+                }
+                k += 16;
+            } else {
+                k += r;
+                const unsigned zig = jpeg_dezigzag[k++];
+                data[zig] = (short)(j.extend_receive(s) * (1 << shift));
+            }
+        } while (k <= j.spec_end);
+    } else {
+        const short bit = (short)(1 << j.succ_low);
+        if (j.eob_run) {
+            --j.eob_run;
+            for (int k = j.spec_start; k <= j.spec_end; k++) {
+                short* p = &data[jpeg_dezigzag[k]];
+                if (*p != 0 && j.get_bit() && (*p & bit) == 0) { if (*p > 0) *p += bit; else *p -= bit; }
+            }
+        } else {
+            int k = j.spec_start;
+            do {
+                const int rs = j.huff_decode(hac);
+                if (rs < 0) return false;
+                int s = rs & 15, r = rs >> 4;
+                if (s == 0) {
+                    if (r < 15) {
+                        j.eob_run = (1 << r) - 1;
+                        if (r) j.eob_run += j.get_bits(r);
+                        r = 64;            // force the end of the block
+                    }
+                } else {
+                    if (s != 1) return false;
+                    s = j.get_bit() ? bit : -bit;
+                }
+                while (k <= j.spec_end) {
+                    short* p = &data[jpeg_dezigzag[k++]];
+                    if (*p != 0) {
+                        if (j.get_bit() && (*p & bit) == 0) { if (*p > 0) *p += bit; else *p -= bit; }
+                    } else {
+                        if (r == 0) { *p = (short)s; break; }
+                        --r;
+                    }
+                }
+            } while (k <= j.spec_end);
+        }
+    }
+    return true;
+}
+
+inline u8 jpeg_clamp(int x) { return (unsigned)x > 255 ? (x < 0 ? 0 : 255) : (u8)x; }
+
+#define PTB_F2F(x) ((int)(((x) * 4096 + 0.5)))
+#define PTB_FSH(x) ((x) * 4096)
+#define PTB_IDCT_1D(s0, s1, s2, s3, s4, s5, s6, s7)            \
+    int t0, t1, t2, t3, p1, p2, p3, p4, p5, x0, x1, x2, x3;     \
+    p2 = s2; p3 = s6;                                           \
+    p1 = (p2 + p3) * PTB_F2F(0.5411961f);                       \
+    t2 = p1 + p3 * PTB_F2F(-1.847759065f);                      \
+    t3 = p1 + p2 * PTB_F2F(0.765366865f);                       \
+    p2 = s0; p3 = s4;                                           \
+    t0 = PTB_FSH(p2 + p3);                                      \
+    t1 = PTB_FSH(p2 - p3);                                      \
+    x0 = t0 + t3; x3 = t0 - t3; x1 = t1 + t2; x2 = t1 - t2;     \
+    t0 = s7; t1 = s5; t2 = s3; t3 = s1;                         \
+    p3 = t0 + t2; p4 = t1 + t3; p1 = t0 + t3; p2 = t1 + t2;     \
+    p5 = (p3 + p4) * PTB_F2F(1.175875602f);                     \
+    t0 = t0 * PTB_F2F(0.298631336f);                            \
+    t1 = t1 * PTB_F2F(2.053119869f);                            \
+    t2 = t2 * PTB_F2F(3.072711026f);                            \
+    t3 = t3 * PTB_F2F(1.501321110f);                            \
+    p1 = p5 + p1 * PTB_F2F(-0.899976223f);                      \
+    p2 = p5 + p2 * PTB_F2F(-2.562915447f);                      \
+    p3 = p3 * PTB_F2F(-1.961570560f);                           \
+    p4 = p4 * PTB_F2F(-0.390180644f);                           \
+    t3 += p1 + p4; t2 += p2 + p3; t1 += p2 + p4; t0 += p1 + p3;
+
+void jpeg_idct(u8* out, int out_stride, short data[64]) {
+    int val[64], *v = val;
+    short* d = data;
+    for (int i = 0; i < 8; ++i, ++d, ++v) {
+        if (d[8] == 0 && d[16] == 0 && d[24] == 0 && d[32] == 0 && d[40] == 0 && d[48] == 0 && d[56] == 0) {
+            const int dcterm = d[0] * 4;
+            v[0] = v[8] = v[16] = v[24] = v[32] = v[40] = v[48] = v[56] = dcterm;
+        } else {
+            PTB_IDCT_1D(d[0], d[8], d[16], d[24], d[32], d[40], d[48], d[56])
+            x0 += 512; x1 += 512; x2 += 512; x3 += 512;
+            v[0] = (x0 + t3) >> 10; v[56] = (x0 - t3) >> 10;
+            v[8] = (x1 + t2) >> 10; v[48] = (x1 - t2) >> 10;
+            v[16] = (x2 + t1) >> 10; v[40] = (x2 - t1) >> 10;
+            v[24] = (x3 + t0) >> 10; v[32] = (x3 - t0) >> 10;
+        }
+    }
+    v = val;
+    u8* o = out;
+    for (int i = 0; i < 8; ++i, v += 8, o += out_stride) {
+        PTB_IDCT_1D(v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7])
+        x0 += 65536 + (128 << 17); x1 += 65536 + (128 << 17); x2 += 65536 + (128 << 17); x3 += 65536 + (128 << 17);
+        o[0] = jpeg_clamp((x0 + t3) >> 17); o[7] = jpeg_clamp((x0 - t3) >> 17);
+        o[1] = jpeg_clamp((x1 + t2) >> 17); o[6] = jpeg_clamp((x1 - t2) >> 17);
+        o[2] = jpeg_clamp((x2 + t1) >> 17); o[5] = jpeg_clamp((x2 - t1) >> 17);
+        o[3] = jpeg_clamp((x3 + t0) >> 17); o[4] = jpeg_clamp((x3 - t0) >> 17);
+    }
+}
+
+// markers between scans; returns false on a malformed segment
+bool jpeg_segment(jpeg_decoder& j, int m) {
+    switch (m) {
+        case 0xDD:
+            if (j.get16() != 4) return false;
+            j.restart_interval = j.get16();
+            return true;
+        case 0xDB: {
+            int L = j.get16() - 2;
+            while (L > 0) {
+                const int q = j.get8(), prec = q >> 4, t = q & 15;
+                if ((prec != 0 && prec != 1) || t > 3) return false;
+                for (int i = 0; i < 64; i++) j.dequant[t][jpeg_dezigzag[i]] = (u16)(prec ? j.get16() : j.get8());
+                L -= prec ? 129 : 65;
+            }
+            return L == 0;
+        }
+        case 0xC4: {
+            int L = j.get16() - 2;
+            while (L > 0) {
+                int sizes[16], n = 0;
+                const int q = j.get8(), tc = q >> 4, th = q & 15;
+                if (tc > 1 || th > 3) return false;
+                for (int i = 0; i < 16; i++) { sizes[i] = j.get8(); n += sizes[i]; }
+                if (n > 256) return false;
+                L -= 17;
+                jpeg_huff& h = tc == 0 ? j.huff_dc[th] : j.huff_ac[th];
+                if (!h.build(sizes)) return false;
+                for (int i = 0; i < n; i++) h.values[i] = (u8)j.get8();
+                L -= n;
+            }
+            return L == 0;
+        }
+        default: break;
+    }
+    if ((m >= 0xE0 && m <= 0xEF) || m == 0xFE) {
+        int L = j.get16();
+        if (L < 2) return false;
+        L -= 2;
+        if (m == 0xE0 && L >= 5) {
+            static const u8 tag[5] = {'J', 'F', 'I', 'F', 0};
+            bool ok = true;
+            for (int i = 0; i < 5; i++) if (j.get8() != tag[i]) ok = false;
+            L -= 5;
+            if (ok) j.jfif = true;
+        } else if (m == 0xEE && L >= 12) {
+            static const u8 tag[6] = {'A', 'd', 'o', 'b', 'e', 0};
+            bool ok = true;
+            for (int i = 0; i < 6; i++) if (j.get8() != tag[i]) ok = false;
+            L -= 6;
+            if (ok) { j.get8(); j.get16(); j.get16(); j.app14_transform = j.get8(); L -= 6; }
+        }
+        j.p += L;
+        if (j.p > j.end) j.p = j.end;
+        return true;
+    }
+    return false;
+}
+
+bool jpeg_frame_header(jpeg_decoder& j) {
+    const int Lf = j.get16();
+    if (Lf < 11) return false;
+    if (j.get8() != 8) return false;
+    j.height = j.get16(); j.width = j.get16();
+    if (j.height == 0 || j.width == 0) return false;
+    const int c = j.get8();
+    if (c != 1 && c != 3) return false;           // CMYK / YCCK are not texture formats the reference's scenes use
+    j.ncomp = c;
+    if (Lf != 8 + 3 * c) return false;
+    for (int i = 0; i < c; i++) {
+        j.comp[i].id = j.get8();
+        const int q = j.get8();
+        j.comp[i].h = q >> 4; j.comp[i].v = q & 15;
+        if (j.comp[i].h < 1 || j.comp[i].h > 4 || j.comp[i].v < 1 || j.comp[i].v > 4) return false;
+        j.comp[i].tq = j.get8();
+        if (j.comp[i].tq > 3) return false;
+    }
+    j.hmax = j.vmax = 1;
+    for (int i = 0; i < c; i++) { j.hmax = std::max(j.hmax, j.comp[i].h); j.vmax = std::max(j.vmax, j.comp[i].v); }
+    for (int i = 0; i < c; i++) if (j.hmax % j.comp[i].h || j.vmax % j.comp[i].v) return false;
+    j.mcu_w = j.hmax * 8; j.mcu_h = j.vmax * 8;
+    j.mcu_x = (j.width + j.mcu_w - 1) / j.mcu_w;
+    j.mcu_y = (j.height + j.mcu_h - 1) / j.mcu_h;
+    for (int i = 0; i < c; i++) {
+        jpeg_component& k = j.comp[i];
+        k.w2 = j.mcu_x * k.h * 8; k.h2 = j.mcu_y * k.v * 8;
+        k.plane.assign((size_t)k.w2 * k.h2, 0);
+        if (j.progressive) {
+            k.coeff_w = k.w2 / 8; k.coeff_h = k.h2 / 8;
+            k.coeff.assign((size_t)k.w2 * k.h2, 0);
+        }
+    }
+    return true;
+}
+
+bool jpeg_scan_header(jpeg_decoder& j) {
+    const int Ls = j.get16();
+    j.scan_n = j.get8();
+    if (j.scan_n < 1 || j.scan_n > 4 || j.scan_n > j.ncomp) return false;
+    if (Ls != 6 + 2 * j.scan_n) return false;
+    for (int i = 0; i < j.scan_n; i++) {
+        const int id = j.get8(), q = j.get8();
+        int which = 0;
+        for (; which < j.ncomp; which++) if (j.comp[which].id == id) break;
+        if (which == j.ncomp) return false;
+        j.comp[which].hd = q >> 4; j.comp[which].ha = q & 15;
+        if (j.comp[which].hd > 3 || j.comp[which].ha > 3) return false;
+        j.order[i] = which;
+    }
+    j.spec_start = j.get8(); j.spec_end = j.get8();
+    const int aa = j.get8();
+    j.succ_high = aa >> 4; j.succ_low = aa & 15;
+    if (j.progressive) {
+        if (j.spec_start > 63 || j.spec_end > 63 || j.spec_start > j.spec_end || j.succ_high > 13 || j.succ_low > 13) return false;
+    } else {
+        if (j.spec_start != 0 || j.succ_high != 0 || j.succ_low != 0) return false;
+        j.spec_end = 63;
+    }
+    return true;
+}
+
+bool jpeg_restart(jpeg_decoder& j) {          // at the end of a restart interval: expect RSTn
+    if (j.code_bits < 24) j.grow();
+    if (!(j.marker >= 0xD0 && j.marker <= 0xD7)) return false;       // the scan ends here
+    j.reset();
+    return true;
+}
+
+bool jpeg_entropy_scan(jpeg_decoder& j) {
+    j.reset();
+    short data[64];
+    if (!j.progressive) {
+        if (j.scan_n == 1) {
+            jpeg_component& k = j.comp[j.order[0]];
+            const int n = j.order[0], w = (((j.width * k.h + j.hmax - 1) / j.hmax) + 7) >> 3,
+                      h = (((j.height * k.v + j.vmax - 1) / j.vmax) + 7) >> 3;
+            for (int y = 0; y < h; y++)
+                for (int x = 0; x < w; x++) {
+                    if (!jpeg_block_baseline(j, data, j.huff_dc[k.hd], j.huff_ac[k.ha], n, j.dequant[k.tq])) return false;
+                    jpeg_idct(&k.plane[(size_t)k.w2 * y * 8 + x * 8], k.w2, data);
+                    if (--j.todo <= 0) { if (!jpeg_restart(j)) return true; }
+                }
+            return true;
+        }
+        for (int my = 0; my < j.mcu_y; my++)
+            for (int mx = 0; mx < j.mcu_x; mx++) {
+                for (int c = 0; c < j.scan_n; c++) {
+                    const int n = j.order[c];
+                    jpeg_component& k = j.comp[n];
+                    for (int y = 0; y < k.v; y++)
+                        for (int x = 0; x < k.h; x++) {
+                            const int x2 = (mx * k.h + x) * 8, y2 = (my * k.v + y) * 8;
+                            if (!jpeg_block_baseline(j, data, j.huff_dc[k.hd], j.huff_ac[k.ha], n, j.dequant[k.tq])) return false;
+                            jpeg_idct(&k.plane[(size_t)k.w2 * y2 + x2], k.w2, data);
+                        }
+                }
+                if (--j.todo <= 0) { if (!jpeg_restart(j)) return true; }
+            }
+        return true;
+    }
+    if (j.scan_n == 1) {
+        const int n = j.order[0];
+        jpeg_component& k = j.comp[n];
+        const int w = (((j.width * k.h + j.hmax - 1) / j.hmax) + 7) >> 3, h = (((j.height * k.v + j.vmax - 1) / j.vmax) + 7) >> 3;
+        for (int y = 0; y < h; y++)
+            for (int x = 0; x < w; x++) {
+                short* blk = &k.coeff[64 * ((size_t)x + (size_t)y * k.coeff_w)];
+                if (j.spec_start == 0) { if (!jpeg_block_prog_dc(j, blk, j.huff_dc[k.hd], n)) return false; }
+                else if (!jpeg_block_prog_ac(j, blk, j.huff_ac[k.ha])) return false;
+                if (--j.todo <= 0) { if (!jpeg_restart(j)) return true; }
+            }
+        return true;
+    }
+    for (int my = 0; my < j.mcu_y; my++)
+        for (int mx = 0; mx < j.mcu_x; mx++) {
+            for (int c = 0; c < j.scan_n; c++) {
+                const int n = j.order[c];
+                jpeg_component& k = j.comp[n];
+                for (int y = 0; y < k.v; y++)
+                    for (int x = 0; x < k.h; x++) {
+                        const int x2 = mx * k.h + x, y2 = my * k.v + y;
+                        short* blk = &k.coeff[64 * ((size_t)x2 + (size_t)y2 * k.coeff_w)];
+                        if (!jpeg_block_prog_dc(j, blk, j.huff_dc[k.hd], n)) return false;
+                    }
+            }
+            if (--j.todo <= 0) { if (!jpeg_restart(j)) return true; }
+        }
+    return true;
+}
+
+void jpeg_finish_progressive(jpeg_decoder& j) {
+    for (int n = 0; n < j.ncomp; n++) {
+        jpeg_component& k = j.comp[n];
+        const int w = (((j.width * k.h + j.hmax - 1) / j.hmax) + 7) >> 3, h = (((j.height * k.v + j.vmax - 1) / j.vmax) + 7) >> 3;
+        for (int y = 0; y < h; y++)
+            for (int x = 0; x < w; x++) {
+                short* blk = &k.coeff[64 * ((size_t)x + (size_t)y * k.coeff_w)];
+                const u16* dq = j.dequant[k.tq];
+                for (int i = 0; i < 64; i++) blk[i] = (short)(blk[i] * dq[i]);
+                jpeg_idct(&k.plane[(size_t)k.w2 * y * 8 + x * 8], k.w2, blk);
+            }
+    }
+}
+
+// Row resamplers: `near` is the row closer to the output row, `far` the other one; w = input samples.
+typedef u8* (*jpeg_resample_fn)(u8* out, u8* near, u8* far, int w, int hs);
+u8* jpeg_resample_1(u8*, u8* near, u8*, int, int) { return near; }
+u8* jpeg_resample_v2(u8* out, u8* near, u8* far, int w, int) {
+    for (int i = 0; i < w; i++) out[i] = (u8)((3 * near[i] + far[i] + 2) >> 2);
+    return out;
+}
+u8* jpeg_resample_h2(u8* out, u8* in, u8*, int w, int) {
+    if (w == 1) { out[0] = out[1] = in[0]; return out; }
+    out[0] = in[0];
+    out[1] = (u8)((in[0] * 3 + in[1] + 2) >> 2);
+    int i;
+    for (i = 1; i < w - 1; i++) {
+        const int n = 3 * in[i] + 2;
+        out[i * 2 + 0] = (u8)((n + in[i - 1]) >> 2);
+        out[i * 2 + 1] = (u8)((n + in[i + 1]) >> 2);
+    }
+    out[i * 2 + 0] = (u8)((in[w - 2] * 3 + in[w - 1] + 2) >> 2);
+    out[i * 2 + 1] = in[w - 1];
+    return out;
+}
+u8* jpeg_resample_hv2(u8* out, u8* near, u8* far, int w, int) {
+    if (w == 1) { out[0] = out[1] = (u8)((3 * near[0] + far[0] + 2) >> 2); return out; }
+    int t1 = 3 * near[0] + far[0], t0;
+    out[0] = (u8)((t1 + 2) >> 2);
+    for (int i = 1; i < w; i++) {
+        t0 = t1;
+        t1 = 3 * near[i] + far[i];
+        out[i * 2 - 1] = (u8)((3 * t0 + t1 + 8) >> 4);
+        out[i * 2] = (u8)((3 * t1 + t0 + 8) >> 4);
+    }
+    out[w * 2 - 1] = (u8)((t1 + 2) >> 2);
+    return out;
+}
+u8* jpeg_resample_generic(u8* out, u8* near, u8*, int w, int hs) {
+    for (int i = 0; i < w; i++) for (int k = 0; k < hs; k++) out[i * hs + k] = near[i];
+    return out;
+}
+
+bool decode_jpeg(const std::vector<u8>& file, int& W, int& H, std::vector<u8>& rgba) {
+    if (file.size() < 4 || file[0] != 0xFF || file[1] != 0xD8) return false;
+    jpeg_decoder* jp = new jpeg_decoder();
+    struct guard { jpeg_decoder* p; ~guard() { delete p; } } g{jp};
+    jpeg_decoder& j = *jp;
+    j.p = file.data() + 2; j.end = file.data() + file.size();
+    std::memset(j.dequant, 0, sizeof j.dequant);
+    auto next_marker = [&]() -> int {
+        if (j.marker != 0xff) { const int m = j.marker; j.marker = 0xff; return m; }
+        int x = j.get8();
+        if (x != 0xff) return 0xff;
+        while (x == 0xff) x = j.get8();
+        return x;
+    };
+    int m = next_marker();
+    bool have_frame = false;
+    while (!(m == 0xC0 || m == 0xC1 || m == 0xC2)) {
+        if (!jpeg_segment(j, m)) return false;
+        m = next_marker();
+        while (m == 0xff) { if (j.p >= j.end) return false; m = next_marker(); }
+    }
+    j.progressive = m == 0xC2;
+    if (!jpeg_frame_header(j)) return false;
+    have_frame = true;
+    m = next_marker();
+    while (m != 0xD9) {
+        if (m == 0xDA) {
+            if (!jpeg_scan_header(j)) return false;
+            if (!jpeg_entropy_scan(j)) return false;
+            if (j.marker == 0xff) {
+                // skip padding / garbage up to the next marker
+                while (j.p < j.end) {
+                    const int x = j.get8();
+                    if (x == 0xff) { j.marker = j.get8(); break; }
+                }
+            }
+        } else if (m == 0xDC) {
+            const int Ld = j.get16(), NL = j.get16();
+            if (Ld != 4 || NL != j.height) return false;
+        } else if (m == 0xff) {
+            if (j.p >= j.end) break;
+        } else if (!jpeg_segment(j, m)) {
+            return false;
+        }
+        m = next_marker();
+    }
+    if (!have_frame) return false;
+    if (j.progressive) jpeg_finish_progressive(j);
+
+    // upsample to full resolution and convert to RGB
+    W = j.width; H = j.height;
+    rgba.resize((size_t)W * H * 4);
+    struct resample { jpeg_resample_fn fn; u8 *line0, *line1; int hs, vs, w_lores, ystep, ypos; std::vector<u8> buf; } rs[3];
+    for (int k = 0; k < j.ncomp; k++) {
+        resample& r = rs[k];
+        r.buf.assign((size_t)W + 3, 0);
+        r.hs = j.hmax / j.comp[k].h; r.vs = j.vmax / j.comp[k].v;
+        r.ystep = r.vs >> 1;
+        r.w_lores = (W + r.hs - 1) / r.hs;
+        r.ypos = 0;
+        r.line0 = r.line1 = j.comp[k].plane.data();
+        if (r.hs == 1 && r.vs == 1) r.fn = jpeg_resample_1;
+        else if (r.hs == 1 && r.vs == 2) r.fn = jpeg_resample_v2;
+        else if (r.hs == 2 && r.vs == 1) r.fn = jpeg_resample_h2;
+        else if (r.hs == 2 && r.vs == 2) r.fn = jpeg_resample_hv2;
+        else r.fn = jpeg_resample_generic;
+    }
+    const bool is_rgb = j.ncomp == 3 && (j.app14_transform == 0 || (j.app14_transform < 0 && !j.jfif &&
+                                          j.comp[0].id == 'R' && j.comp[1].id == 'G' && j.comp[2].id == 'B'));
+    for (int y = 0; y < H; y++) {
+        u8* rows[3] = {nullptr, nullptr, nullptr};
+        for (int k = 0; k < j.ncomp; k++) {
+            resample& r = rs[k];
+            const bool y_bot = r.ystep >= (r.vs >> 1);
+            rows[k] = r.fn(r.buf.data(), y_bot ? r.line1 : r.line0, y_bot ? r.line0 : r.line1, r.w_lores, r.hs);
+            if (++r.ystep >= r.vs) {
+                r.ystep = 0;
+                r.line0 = r.line1;
+                if (++r.ypos < ((j.height * j.comp[k].v + j.vmax - 1) / j.vmax)) r.line1 += j.comp[k].w2;
+            }
+        }
+        u8* o = &rgba[(size_t)y * W * 4];
+        if (j.ncomp == 1) {
+            for (int x = 0; x < W; x++) { o[4 * x] = o[4 * x + 1] = o[4 * x + 2] = rows[0][x]; o[4 * x + 3] = 255; }
+        } else if (is_rgb) {
+            for (int x = 0; x < W; x++) { o[4 * x] = rows[0][x]; o[4 * x + 1] = rows[1][x]; o[4 * x + 2] = rows[2][x]; o[4 * x + 3] = 255; }
+        } else {
+            for (int x = 0; x < W; x++) {
+                const int yf = (rows[0][x] << 20) + (1 << 19);
+                const int cr = rows[2][x] - 128, cb = rows[1][x] - 128;
+                int r = yf + cr * (int)(1.40200f * 4096.0f + 0.5f) * 256;
+                int gch = yf + cr * -((int)(0.71414f * 4096.0f + 0.5f) * 256) + ((cb * -((int)(0.34414f * 4096.0f + 0.5f) * 256)) & 0xffff0000);
+                int b = yf + cb * (int)(1.77200f * 4096.0f + 0.5f) * 256;
+                r >>= 20; gch >>= 20; b >>= 20;
+                o[4 * x] = jpeg_clamp(r); o[4 * x + 1] = jpeg_clamp(gch); o[4 * x + 2] = jpeg_clamp(b); o[4 * x + 3] = 255;
+            }
+        }
+    }
+    return true;
+}
+
+// ------------------------------------------------------------------ PPM / PFM (round 1)
+bool pnm_token(const std::vector<u8>& f, size_t& pos, std::string& tok) {
+    tok.clear();
+    while (pos < f.size()) {
+        if (f[pos] == '#') { while (pos < f.size() && f[pos] != '\n') pos++; }
+        else if (std::isspace(f[pos])) pos++;
+        else break;
+    }
+    while (pos < f.size() && !std::isspace(f[pos])) tok.push_back((char)f[pos++]);
+    return !tok.empty();
+}
+
+bool decode_pnm(const std::vector<u8>& file, int& W, int& H, std::vector<vec4>& px) {
+    size_t pos = 0;
+    std::string magic, a, b, c;
+    if (!pnm_token(file, pos, magic) || !pnm_token(file, pos, a) || !pnm_token(file, pos, b) || !pnm_token(file, pos, c)) return false;
+    const int w = std::atoi(a.c_str()), h = std::atoi(b.c_str());
+    if (w <= 0 || h <= 0) return false;
+    pos++;                                   // the single whitespace byte that ends the header
+    if (magic == "P6") {
+        const int maxv = std::atoi(c.c_str());
+        if (maxv <= 0 || maxv >= 256 || pos + (size_t)w * h * 3 > file.size()) return false;
+        px.resize((size_t)w * h);
+        for (size_t i = 0; i < px.size(); i++) {
+            float v[3];
+            for (int k = 0; k < 3; k++) {
+                const float s = file[pos + 3 * i + k] / (float)maxv;          // 8-bit PPM holds sRGB-encoded values
+                v[k] = s <= 0.04045f ? s / 12.92f : std::pow((s + 0.055f) / 1.055f, 2.4f);
+            }
+            px[i] = {v[0], v[1], v[2], 1.0f};
+        }
+    } else if (magic == "PF") {
+        const float scale = (float)std::atof(c.c_str());
+        if (!(scale < 0) || pos + (size_t)w * h * 12 > file.size()) return false;      // little-endian only
+        px.resize((size_t)w * h);
+        for (int y = 0; y < h; y++)                                           // PFM rows run bottom to top
+            for (int x = 0; x < w; x++) {
+                float s[3];
+                std::memcpy(s, &file[pos + ((size_t)(h - 1 - y) * w + x) * 12], 12);
+                px[(size_t)y * w + x] = {s[0], s[1], s[2], 1.0f};
+            }
+    } else {
+        return false;
+    }
+    W = w; H = h;
+    return true;
+}
+
+}  // namespace
+
+// What stbi_loadf(Path, &W, &H, &N, 4) returns for the formats above: linear RGBA32F, row 0 at the top.
+bool DecodeImageFile(char const* Path, int& Width, int& Height, std::vector<vec4>& Pixels) {
+    std::vector<u8> file;
+    if (!read_file(Path, file) || file.size() < 4) return false;
+    std::vector<u8> rgba;
+    if (file[0] == 137 && file[1] == 'P') {
+        if (!decode_png(file, Width, Height, rgba)) return false;
+        ldr_to_float(rgba, Pixels);
+        return true;
+    }
+    if (file[0] == 0xFF && file[1] == 0xD8) {
+        if (!decode_jpeg(file, Width, Height, rgba)) return false;
+        ldr_to_float(rgba, Pixels);
+        return true;
+    }
+    if (file[0] == '#' && file[1] == '?') return decode_hdr(file, Width, Height, Pixels);
+    if (file[0] == 'P' && (file[1] == '6' || file[1] == 'F')) return decode_pnm(file, Width, Height, Pixels);
+    return false;
+}
+
+}}  // namespace ptb::host

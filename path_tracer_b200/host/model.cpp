@@ -15,7 +15,7 @@
 //     empty or uses two materials);
 //   * material groups of a shape are ordered by first use (the reference iterates an
 //     unordered_set, scene.cpp:773-778);
-//   * textures load from PPM (P6) and PFM files only — there is no stb_image here.
+//   * textures are decoded by host/image.cpp (PNG, JPEG, Radiance HDR with stb_image's conversions; PPM, PFM).
 // The reference has no image writer; the headless replacement for its swapchain is a file:
 // PNG (8-bit sRGB, stored deflate blocks) and PFM (linear float).
 #include "scene.hpp"
@@ -126,64 +126,16 @@ void delete_tree(entity* E) {
 
 }  // namespace
 
-// LoadTexture (scene.cpp:294-318) for the two formats available without stb_image.
+// LoadTexture (scene.cpp:294-318): stbi_loadf's contract (linear RGBA32F, row 0 first) through host/image.cpp
+// (PNG, JPEG, Radiance HDR; plus PPM / PFM).  The default name is the file name, as in the reference.
 texture* LoadTexture(scene* Scene, char const* Path, texture_type Type, char const* Name) {
-    FILE* f = std::fopen(Path, "rb");
-    if (!f) return nullptr;
-    char magic[3] = {0, 0, 0};
     int w = 0, h = 0;
     std::vector<vec4> px;
-    bool ok = false;
-    if (std::fscanf(f, "%2s", magic) == 1) {
-        auto skip = [&]() {                           // whitespace and # comments between header fields
-            int c;
-            while ((c = std::fgetc(f)) != EOF) {
-                if (c == '#') { while ((c = std::fgetc(f)) != EOF && c != '\n') {} }
-                else if (!std::isspace(c)) { std::ungetc(c, f); break; }
-            }
-        };
-        if (!std::strcmp(magic, "P6")) {
-            int maxv = 0;
-            skip(); if (std::fscanf(f, "%d", &w) != 1) w = 0;
-            skip(); if (std::fscanf(f, "%d", &h) != 1) h = 0;
-            skip(); if (std::fscanf(f, "%d", &maxv) != 1) maxv = 0;
-            std::fgetc(f);
-            if (w > 0 && h > 0 && maxv > 0 && maxv < 256) {
-                std::vector<unsigned char> raw((size_t)w * h * 3);
-                if (std::fread(raw.data(), 1, raw.size(), f) == raw.size()) {
-                    px.resize((size_t)w * h);
-                    for (size_t i = 0; i < px.size(); i++) {
-                        float c[3];
-                        for (int k = 0; k < 3; k++) {
-                            // 8-bit files hold sRGB-encoded values; textures are linear (scene.cpp:300-309 via stbi_loadf)
-                            float s = raw[3 * i + k] / (float)maxv;
-                            c[k] = s <= 0.04045f ? s / 12.92f : std::pow((s + 0.055f) / 1.055f, 2.4f);
-                        }
-                        px[i] = {c[0], c[1], c[2], 1.0f};
-                    }
-                    ok = true;
-                }
-            }
-        } else if (!std::strcmp(magic, "PF")) {
-            float scale = 0;
-            if (std::fscanf(f, "%d %d %f", &w, &h, &scale) == 3 && w > 0 && h > 0 && scale < 0) {     // little-endian only
-                std::fgetc(f);
-                std::vector<float> raw((size_t)w * h * 3);
-                if (std::fread(raw.data(), 4, raw.size(), f) == raw.size()) {
-                    px.resize((size_t)w * h);
-                    for (int y = 0; y < h; y++)                       // PFM rows run bottom to top
-                        for (int x = 0; x < w; x++) {
-                            const float* s = &raw[((size_t)(h - 1 - y) * w + x) * 3];
-                            px[(size_t)y * w + x] = {s[0], s[1], s[2], 1.0f};
-                        }
-                    ok = true;
-                }
-            }
-        }
-    }
-    std::fclose(f);
-    if (!ok) return nullptr;
-    return CreateTexture(Scene, Name ? Name : stem_of(Path).c_str(), Type, (uint32_t)w, (uint32_t)h, px.data());
+    if (!DecodeImageFile(Path, w, h, px)) return nullptr;
+    const std::string p = Path;
+    const size_t slash = p.find_last_of("/\\");
+    const std::string file_name = slash == std::string::npos ? p : p.substr(slash + 1);
+    return CreateTexture(Scene, Name ? Name : file_name.c_str(), Type, (uint32_t)w, (uint32_t)h, px.data());
 }
 
 prefab* LoadModelAsPrefab(scene* Scene, char const* Path, load_model_options* Options) {

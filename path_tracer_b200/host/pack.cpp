@@ -4,7 +4,9 @@
 // :1115-1621 (PackSceneData); material packers follow basic_diffuse.hpp:17-28,
 // basic_metal.hpp:26-52, basic_translucent.hpp:26-61.
 #include "scene.hpp"
+#include <algorithm>
 #include <cassert>
+#include <unordered_map>
 #include <functional>
 
 namespace ptb { namespace host {
@@ -70,16 +72,39 @@ void pack_material(scene* S, material const* M, uint32_t* A) {
 inline uint32_t material_words(material_type T) { return T == MATERIAL_TYPE_OPENPBR ? 64u : 32u; }   // scene.hpp:468-483
 
 // ---- texture atlas (scene.cpp:1120-1233) ----
-// The reference places rectangles with stb_rect_pack's skyline heuristic; any
-// non-overlapping placement is equivalent for rendering, so a simple shelf
-// packer is used here (placements are therefore not byte-comparable).
-struct shelf_packer {
-    uint32_t W, H, x = 0, y = 0, row_h = 0;
+// The reference places the rectangles of one atlas layer with stb_rect_pack (stbrp_init_target with one skyline node
+// per atlas column, stbrp_pack_rects with the default heuristic, scene.cpp:1144-1147).  That algorithm, restated:
+// rectangles are taken by height descending, then width descending (ties: input order); the skyline is a list of
+// (x, height) steps; a rectangle of width w is tried with its left edge on every step whose x + w fits, resting at
+// the highest skyline point under it, and goes where it rests LOWEST, leftmost among equals ("bottom-left");
+// a rectangle that would rise above the atlas stays unplaced for the next layer.  Placements are equal to the
+// reference's (tests/test_reference_host.py compares them with the reference's own PackSceneData).
+struct skyline_packer {
+    struct step { uint32_t x, y; };
+    uint32_t W, H;
+    std::vector<step> line;                        // ascending x; the last entry is the sentinel {W, 65535}
+    skyline_packer(uint32_t w, uint32_t h) : W(w), H(h) { line.push_back({0u, 0u}); line.push_back({w, 65535u}); }
     bool place(uint32_t w, uint32_t h, uint32_t& ox, uint32_t& oy) {
         if (w > W || h > H) return false;
-        if (x + w > W) { y += row_h; x = 0; row_h = 0; }
-        if (y + h > H) return false;
-        ox = x; oy = y; x += w; row_h = std::max(row_h, h);
+        size_t best = line.size();
+        uint32_t best_y = 1u << 30;
+        for (size_t i = 0; i + 1 < line.size() && line[i].x + w <= W; i++) {
+            const uint32_t x1 = line[i].x + w;
+            uint32_t y = 0;
+            for (size_t j = i; line[j].x < x1; j++) y = std::max(y, line[j].y);
+            if (y < best_y) { best_y = y; best = i; }
+        }
+        if (best == line.size() || best_y + h > H) return false;
+        ox = line[best].x; oy = best_y;
+        // the new step replaces every step it covers; the first step reaching beyond it is cut back to its right edge
+        const uint32_t x1 = ox + w;
+        size_t k = best;
+        while (k + 1 < line.size() && line[k + 1].x <= x1) k++;      // line[k]: the last step starting at or before the right edge
+        std::vector<step> next(line.begin(), line.begin() + best);
+        next.push_back({ox, best_y + h});
+        next.push_back({std::max(line[k].x, x1), line[k].y});       // it survives, cut back to the right edge if it started inside
+        next.insert(next.end(), line.begin() + k + 1, line.end());
+        line.swap(next);
         return true;
     }
 };
@@ -90,14 +115,24 @@ void pack_textures(scene* S) {
     std::vector<texture*> Pending(S->Textures.begin(), S->Textures.end());
     const uint32_t AW = S->AtlasWidth, AH = S->AtlasHeight;
     while (!Pending.empty()) {
-        shelf_packer P{AW, AH};
+        skyline_packer P(AW, AH);
+        // stbrp_pack_rects: by height, then width, both descending; unplaced rectangles wait for the next layer
+        std::vector<texture*> Order(Pending);
+        std::stable_sort(Order.begin(), Order.end(), [](texture const* A, texture const* B) {
+            return A->Height != B->Height ? A->Height > B->Height : A->Width > B->Width; });
+        std::unordered_map<texture const*, std::pair<uint32_t, uint32_t>> Spot;
+        for (texture* T : Order) {
+            uint32_t rx = 0, ry = 0;
+            if (T->Width == 0 || T->Height == 0 || P.place(T->Width, T->Height, rx, ry)) Spot[T] = {rx, ry};
+        }
         std::vector<float> Layer((size_t)AW * AH * 4, 0.0f);
         const uint32_t ImageIndex = (uint32_t)S->Images.size();
         std::vector<texture*> Left;
         bool any = false;
         for (texture* T : Pending) {
-            uint32_t rx, ry;
-            if (!P.place(T->Width, T->Height, rx, ry)) { Left.push_back(T); continue; }
+            auto Found = Spot.find(T);
+            if (Found == Spot.end()) { Left.push_back(T); continue; }
+            const uint32_t rx = Found->second.first, ry = Found->second.second;
             any = true;
             T->PackedTextureIndex = (uint32_t)S->TexturePack.size();
             ptb_packed_texture K{};

@@ -170,7 +170,9 @@ mesh* CreateMesh(scene* Scene, char const* Name, std::vector<mesh_vertex>&& Vert
 // CreateMesh in two steps, so that independent meshes can be built on several threads and attached in order.
 mesh* BuildMesh(char const* Name, std::vector<mesh_vertex>&& Vertices, std::vector<mesh_face>&& Faces);
 mesh* AttachMesh(scene* Scene, mesh* M);
-// Model import and prefabs (scene.hpp:415,428-429; model.cpp).  Wavefront OBJ + MTL; textures from PPM/PFM files.
+// Model import and prefabs (scene.hpp:415,428-429; model.cpp).  Wavefront OBJ + MTL; textures through DecodeImageFile.
+// DecodeImageFile (image.cpp) = stbi_loadf(Path, &W, &H, &N, 4) for PNG, JPEG and Radiance HDR (plus PPM / PFM).
+bool DecodeImageFile(char const* Path, int& Width, int& Height, std::vector<vec4>& Pixels);
 texture* LoadTexture(scene* Scene, char const* Path, texture_type Type, char const* Name = nullptr);
 prefab* LoadModelAsPrefab(scene* Scene, char const* Path, load_model_options* Options = nullptr);
 entity* CreateEntity(scene* Scene, prefab* Prefab, entity* Parent = nullptr);

@@ -81,6 +81,7 @@ def lib():
         L.ptbh_prefab_mesh_count.argtypes = [vp]
         L.ptbh_load_texture.restype = vp
         L.ptbh_load_texture.argtypes = [vp, C.c_char_p, C.c_int, C.c_char_p]
+        L.ptbh_decode_image.argtypes = [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int), vp, C.c_size_t]
         L.ptbh_write_png.argtypes = [C.c_char_p, u32, u32, vp]
         L.ptbh_write_pfm.argtypes = [C.c_char_p, u32, u32, vp]
         L.ptbh_mesh_vertex_count.restype = u32
@@ -131,6 +132,18 @@ def fit_spectrum(rgb):
     out = (C.c_float * 3)()
     lib().ptbh_fit_spectrum(_f3(rgb), out)
     return np.array(out[:], dtype=np.float32)
+
+
+def decode_image(path):
+    """What LoadTexture reads from an image file (the reference: stbi_loadf(path, ..., 4), scene.cpp:294-297):
+    linear RGBA32F (H, W, 4) from PNG, JPEG, Radiance HDR (or PPM / PFM); None when the file cannot be decoded."""
+    L = lib()
+    w, h = C.c_int(0), C.c_int(0)
+    if L.ptbh_decode_image(os.fsencode(path), C.byref(w), C.byref(h), None, 0) != 0:
+        return None
+    out = np.zeros((h.value, w.value, 4), dtype=np.float32)
+    L.ptbh_decode_image(os.fsencode(path), C.byref(w), C.byref(h), out.ctypes.data, out.size)
+    return out
 
 
 def write_png(path, srgb8):
@@ -283,7 +296,7 @@ class Scene:
         return self._L.ptbh_prefab_mesh_count(prefab)
 
     def load_texture(self, path, ttype, name=None):
-        """LoadTexture for PPM (P6, sRGB-encoded) and PFM (linear float) files."""
+        """LoadTexture (scene.cpp:294-318): PNG, JPEG, Radiance HDR as stbi_loadf delivers them; also PPM / PFM."""
         t = self._L.ptbh_load_texture(self.h, os.fsencode(path), ttype, (name or "").encode())
         if not t:
             raise OSError("cannot load texture " + str(path))

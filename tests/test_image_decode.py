@@ -1,0 +1,245 @@
+"""Image decoding for LoadTexture: host/image.cpp against the reference's own vendored stb_image.h
+(stbi_loadf(path, &w, &h, &n, 4), scene.cpp:294-297) compiled into oracle/_ref/libref_host.so - bit for bit on the float
+pixels, for PNG (every colour type / depth, tRNS, Adam7), JPEG (baseline, progressive, subsampling, restart intervals,
+greyscale) and Radiance HDR (run-length and flat).  Files are written here with Pillow or by hand.  CPU only."""
+import struct
+import zlib
+
+import numpy as np
+import pytest
+
+from oracle.ref import host_binding as H
+from path_tracer_b200 import scene as S
+
+PIL = pytest.importorskip("PIL.Image")
+pytestmark = pytest.mark.skipif(not H.available(), reason="oracle/_ref/libref_host.so cannot be built here")
+
+
+def picture(w, h, seed=0):
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:h, 0:w]
+    base = np.stack([128 + 100 * np.sin(x / 7.0), 128 + 100 * np.cos(y / 5.0), (x * 3 + y * 5) % 256, 255 * ((x // 4 + y // 4) % 2)], -1)
+    return np.clip(base + rng.integers(-20, 20, size=(h, w, 4)), 0, 255).astype(np.uint8)
+
+
+def same(path):
+    ours, ref = S.decode_image(str(path)), H.stbi_loadf(str(path))
+    assert ref is not None, "the reference's stb_image cannot read %s" % path
+    assert ours is not None, "host/image.cpp cannot read %s" % path
+    assert ours.shape == ref.shape
+    if ours.tobytes() != ref.tobytes():
+        d = np.argwhere((ours.view(np.uint32) != ref.view(np.uint32)).any(axis=-1))
+        raise AssertionError("%s: %d of %d pixels differ, first at %s: %s vs %s" % (path, len(d), ours.shape[0] * ours.shape[1], d[0], ours[tuple(d[0])], ref[tuple(d[0])]))
+    return ours
+
+
+@pytest.mark.parametrize("mode", ["L", "LA", "RGB", "RGBA", "P", "P-trns", "1", "I;16", "RGB-trns", "L-trns"])
+@pytest.mark.parametrize("size", [(37, 23), (1, 1), (8, 300)])
+def test_png_matches_stb_image(tmp_path, mode, size):
+    w, h = size
+    a = picture(w, h, 1)
+    f = tmp_path / "t.png"
+    if mode == "P":
+        PIL.fromarray(a[..., :3]).quantize(17).save(f)
+    elif mode == "P-trns":
+        im = PIL.fromarray(a[..., :3]).quantize(5)
+        im.save(f, transparency=bytes([0, 128, 255, 7, 200]))
+    elif mode == "1":
+        PIL.fromarray(a[..., 0] > 128).save(f)
+    elif mode == "I;16":
+        PIL.fromarray((a[..., 0].astype(np.uint16) * 257 + a[..., 1]) & 0xFFFF).save(f)
+    elif mode == "RGB-trns":
+        b = a[..., :3].copy()
+        b[::3, ::2] = (10, 20, 30)
+        PIL.fromarray(b).save(f, transparency=(10, 20, 30))
+    elif mode == "L-trns":
+        b = a[..., 0].copy()
+        b[::2, ::3] = 77
+        PIL.fromarray(b).save(f, transparency=77)
+    else:
+        PIL.fromarray(a if mode == "RGBA" else a[..., :3] if mode == "RGB" else a[..., 0] if mode == "L" else a[..., [0, 3]], mode).save(f)
+    px = same(f)
+    assert px.shape == (h, w, 4)
+
+
+def png_chunk(tag, data):
+    return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+
+
+def write_png_raw(path, w, h, depth, ctype, rows_of, interlace, extra=b"", idat_split=1):
+    """rows_of(pw, ph, xs, ys) -> list of raw scanlines (bytes, no filter byte); a random filter type is applied here."""
+    rng = np.random.default_rng(w * 131 + h)
+    channels = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[ctype]
+    bpp = max(1, channels * depth // 8)
+
+    def filt(rows):
+        out, prev = b"", None
+        for r in rows:
+            r = bytearray(r)
+            t = int(rng.integers(0, 5))
+            p = prev if prev is not None else bytearray(len(r))
+            f = bytearray(len(r))
+            for i in range(len(r)):
+                a = r[i - bpp] if i >= bpp else 0
+                b = p[i]
+                c = p[i - bpp] if i >= bpp else 0
+                if t == 0:
+                    pr = 0
+                elif t == 1:
+                    pr = a
+                elif t == 2:
+                    pr = b
+                elif t == 3:
+                    pr = (a + b) >> 1
+                else:
+                    pa, pb, pc = abs(b - c), abs(a - c), abs(a + b - 2 * c)
+                    pr = a if (pa <= pb and pa <= pc) else (b if pb <= pc else c)
+                f[i] = (r[i] - pr) & 255
+            out += bytes([t]) + bytes(f)
+            prev = r
+        return out
+    raw = b""
+    if not interlace:
+        raw = filt(rows_of(w, h, lambda i: i, lambda j: j))
+    else:
+        for xo, yo, xs, ys in ((0, 0, 8, 8), (4, 0, 8, 8), (0, 4, 4, 8), (2, 0, 4, 4), (0, 2, 2, 4), (1, 0, 2, 2), (0, 1, 1, 2)):
+            pw, ph = (w - xo + xs - 1) // xs, (h - yo + ys - 1) // ys
+            if pw > 0 and ph > 0:
+                raw += filt(rows_of(pw, ph, lambda i, xo=xo, xs=xs: xo + i * xs, lambda j, yo=yo, ys=ys: yo + j * ys))
+    z = zlib.compress(raw, 6)
+    cut = [len(z) * k // idat_split for k in range(idat_split + 1)]
+    with open(path, "wb") as o:
+        o.write(b"\x89PNG\r\n\x1a\n" + png_chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, ctype, 0, 0, 1 if interlace else 0)) + extra)
+        for k in range(idat_split):
+            o.write(png_chunk(b"IDAT", z[cut[k]:cut[k + 1]]))
+        o.write(png_chunk(b"IEND", b""))
+
+
+@pytest.mark.parametrize("interlace", [False, True])
+@pytest.mark.parametrize("depth,ctype", [(1, 0), (2, 0), (4, 0), (8, 0), (16, 0), (8, 2), (16, 2), (1, 3), (2, 3), (4, 3), (8, 3), (8, 4), (16, 4), (8, 6), (16, 6)])
+def test_png_every_type_and_depth_with_filters_and_adam7(tmp_path, depth, ctype, interlace):
+    w, h = 21, 13
+    rng = np.random.default_rng(depth * 10 + ctype)
+    channels = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[ctype]
+    samples = rng.integers(0, 1 << depth, size=(h, w, channels))
+
+    def rows_of(pw, ph, xs, ys):
+        rows = []
+        for j in range(ph):
+            vals = [int(samples[ys(j), xs(i), c]) for i in range(pw) for c in range(channels)]
+            if depth == 16:
+                rows.append(b"".join(struct.pack(">H", v) for v in vals))
+            elif depth == 8:
+                rows.append(bytes(vals))
+            else:
+                bits = "".join(format(v, "0%db" % depth) for v in vals)
+                bits += "0" * (-len(bits) % 8)
+                rows.append(bytes(int(bits[k:k + 8], 2) for k in range(0, len(bits), 8)))
+        return rows
+    extra = b""
+    if ctype == 3:
+        n = 1 << depth
+        extra = png_chunk(b"PLTE", bytes(rng.integers(0, 256, size=3 * n).tolist())) + png_chunk(b"tRNS", bytes(rng.integers(0, 256, size=n // 2 + 1).tolist()))
+    elif ctype == 0:
+        extra = png_chunk(b"tRNS", struct.pack(">H", int(samples[0, 0, 0])))
+    elif ctype == 2:
+        extra = png_chunk(b"tRNS", struct.pack(">HHH", *[int(v) for v in samples[1, 2]]))
+    f = tmp_path / "t.png"
+    write_png_raw(f, w, h, depth, ctype, rows_of, interlace, extra, idat_split=3)
+    px = same(f)
+    if ctype in (0, 2):
+        assert px[..., 3].min() == 0.0                      # the colour key made something transparent
+
+
+@pytest.mark.parametrize("kind", ["444", "420", "422", "grey", "progressive", "progressive-420", "restart", "odd-size", "q30"])
+def test_jpeg_matches_stb_image(tmp_path, kind):
+    w, h = (67, 45) if kind == "odd-size" else (96, 64)
+    a = picture(w, h, 3)[..., :3]
+    f = tmp_path / "t.jpg"
+    im = PIL.fromarray(a)
+    kw = dict(quality=30 if kind == "q30" else 88)
+    if kind == "grey":
+        im = im.convert("L")
+    elif kind in ("444", "restart", "progressive"):
+        kw["subsampling"] = 0
+    elif kind == "422":
+        kw["subsampling"] = 1
+    else:
+        kw["subsampling"] = 2
+    if kind.startswith("progressive"):
+        kw["progressive"] = True
+    if kind == "restart":
+        kw["restart_marker_blocks"] = 5
+    try:
+        im.save(f, "JPEG", **kw)
+    except TypeError:
+        kw.pop("restart_marker_blocks", None)
+        im.save(f, "JPEG", **kw)
+    px = same(f)
+    assert px.shape == (h, w, 4) and (px[..., 3] == 1.0).all()
+
+
+def write_hdr(path, rgbe, rle, magic=b"#?RADIANCE"):
+    h, w = rgbe.shape[:2]
+    with open(path, "wb") as o:
+        o.write(magic + b"\n# made by a test\nFORMAT=32-bit_rle_rgbe\nEXPOSURE=1.0\n\n-Y %d +X %d\n" % (h, w))
+        for j in range(h):
+            if not rle or w < 8:                            # scanlines shorter than 8 pixels are never run-length coded
+                o.write(rgbe[j].tobytes())
+                continue
+            o.write(bytes([2, 2, w >> 8, w & 255]))
+            for c in range(4):
+                row = rgbe[j, :, c]
+                i = 0
+                while i < w:
+                    run = 1
+                    while i + run < w and run < 127 and row[i + run] == row[i]:
+                        run += 1
+                    if run >= 3:
+                        o.write(bytes([128 + run, int(row[i])]))
+                        i += run
+                    else:
+                        k = i
+                        while k < w and k - i < 128 and not (k + 2 < w and row[k] == row[k + 1] == row[k + 2]):
+                            k += 1
+                        k = max(k, i + 1)
+                        o.write(bytes([k - i]) + row[i:k].tobytes())
+                        i = k
+
+
+@pytest.mark.parametrize("w,h,rle,magic", [(40, 17, True, b"#?RADIANCE"), (40, 17, False, b"#?RADIANCE"), (5, 9, True, b"#?RGBE"), (300, 4, True, b"#?RADIANCE")])
+def test_radiance_hdr_matches_stb_image(tmp_path, w, h, rle, magic):
+    rng = np.random.default_rng(w)
+    rgbe = rng.integers(0, 256, size=(h, w, 4)).astype(np.uint8)
+    rgbe[..., 3] = rng.integers(100, 150, size=(h, w))
+    rgbe[:, : w // 3, 0] = 200                              # runs for the run-length coder
+    rgbe[0, 0, 3] = 0                                       # exponent 0: black
+    f = tmp_path / "t.hdr"
+    write_hdr(f, rgbe, rle, magic)
+    px = same(f)
+    assert px[0, 0, :3].max() == 0.0 and (px[..., 3] == 1.0).all() and px.max() > 100.0
+
+
+def test_load_texture_and_mtl_maps(tmp_path):
+    """LoadTexture / LoadModelAsPrefab take PNG, JPEG and HDR files: a textured OBJ and an HDR sky end up in the atlas."""
+    S.ensure_spectrum_table()
+    a = picture(32, 16, 5)
+    PIL.fromarray(a[..., :3]).save(tmp_path / "kd.png")
+    rgbe = np.full((8, 16, 4), 128, np.uint8)
+    rgbe[..., 0] = np.arange(16, dtype=np.uint8) * 10
+    write_hdr(tmp_path / "sky.hdr", rgbe, True)
+    with open(tmp_path / "m.mtl", "w") as o:
+        o.write("newmtl tex\nKd 1 1 1\nmap_Kd kd.png\n")
+    with open(tmp_path / "m.obj", "w") as o:
+        o.write("mtllib m.mtl\no quad\nv 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nvt 0 0\nvt 1 0\nvt 1 1\nvt 0 1\nusemtl tex\nf 1/1 2/2 3/3\nf 1/1 3/3 4/4\n")
+    sc = S.Scene()
+    sc.set_atlas_size(64, 64)
+    prefab = sc.load_model(str(tmp_path / "m.obj"))
+    sc.create_prefab_instance(prefab)
+    sky = sc.load_texture(str(tmp_path / "sky.hdr"), S.TEXTURE_RADIANCE)
+    sc.set_root(sky_texture=sky)
+    sc.create_camera((0, -3, 1), (0, 0, 0))
+    sc.pack()
+    assert len(sc.textures) == 2 and sc.globals["SkyboxTextureIndex"] != 0xFFFFFFFF
+    with pytest.raises(OSError):
+        sc.load_texture(str(tmp_path / "m.obj"), S.TEXTURE_RAW)
