@@ -101,4 +101,36 @@ void RunBasicRenderer(device*, basic_renderer* Renderer, uint Rounds) {
     Renderer->FrameIndex += 1;                    // basic.cpp:315
 }
 
+device_group* CreateDeviceGroup(std::vector<device*> const& Devices) {
+    device_group* G = new device_group;
+    G->Devices = Devices;
+    G->Handles.assign(Devices.size(), nullptr);
+    std::vector<ptb_context*> Contexts;
+    for (device* D : Devices) Contexts.push_back(D->Context);
+    if (ptb_group_create_local(Contexts.data(), (int)Contexts.size(), G->Handles.data()) != PTB_OK) { Errorf("CreateDeviceGroup"); delete G; return nullptr; }
+    return G;
+}
+
+void DestroyDeviceGroup(device_group* Group) {
+    if (!Group) return;
+    for (ptb_group* H : Group->Handles) ptb_group_destroy(H);
+    delete Group;
+}
+
+uint FirstFrameIndex(device_group* Group, int Rank, uint FramesPerRank) {
+    return ptb_group_first_frame(Rank, (int)Group->Handles.size(), FramesPerRank, 0);
+}
+
+bool ReplicateDeviceScene(device_group* Group, int Rank, device_scene* DeviceScene) {
+    if (ptb_scene_replicate(DeviceScene->Handle, Group->Handles[Rank], 0) != PTB_OK) { Errorf("ReplicateDeviceScene"); return false; }
+    return true;
+}
+
+bool RenderCombinedSampleBuffer(device_group* Group, int Rank, sample_buffer* SampleBuffer, resolve_parameters* Parameters, sample_buffer* Sum) {
+    ptb_resolve_params P = {Parameters->Brightness, (uint32_t)Parameters->ToneMappingMode, Parameters->ToneMappingWhiteLevel};
+    if (ptb_film_reduce_resolve(SampleBuffer->Film, Group->Handles[Rank], 0, PTB_REDUCE_P2P_FUSED, &P, (Rank == 0 && Sum) ? Sum->Film : nullptr,
+                                Rank == 0 ? SampleBuffer->Frame.data() : nullptr) != PTB_OK) { Errorf("RenderCombinedSampleBuffer"); return false; }
+    return true;
+}
+
 }}  // namespace ptb::host

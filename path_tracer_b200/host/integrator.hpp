@@ -92,4 +92,23 @@ void DestroyBasicRenderer(device* Device, basic_renderer* Renderer);
 void ResetBasicRenderer(device* Device, basic_renderer* Renderer);
 void RunBasicRenderer(device* Device, basic_renderer* Renderer, uint Rounds);
 
+// ---- several GPUs of one box (no reference counterpart: it binds one VkPhysicalDevice, core/vulkan.cpp:1485-1506) ----
+// One process drives every device: ONE HOST THREAD PER DEVICE makes that device's calls (the two functions below are
+// collective: they return when every rank has joined).  The scene is packed and flattened once, on rank 0, and sent
+// device-to-device; every rank renders its own block of RandomSeed values into its own sample buffer; one exchange
+// step sums the films and resolves the combined frame into rank 0's SampleBuffer->Frame.
+struct device_group {
+    std::vector<device*>    Devices;              // rank k renders on Devices[k]
+    std::vector<ptb_group*> Handles;
+};
+device_group* CreateDeviceGroup(std::vector<device*> const& Devices);
+void DestroyDeviceGroup(device_group* Group);
+// First FrameIndex of `Rank` when every rank renders at most FramesPerRank frames after its reset (disjoint seed blocks).
+uint FirstFrameIndex(device_group* Group, int Rank, uint FramesPerRank);
+// Rank 0's device scene (after UpdateDeviceScene) to every other rank's freshly created one.  Collective.
+bool ReplicateDeviceScene(device_group* Group, int Rank, device_scene* DeviceScene);
+// RenderSampleBuffer on the SUM of all ranks' sample buffers: the frame lands in rank 0's SampleBuffer->Frame; Sum
+// (rank 0 only, optional) also receives the float film.  Collective.
+bool RenderCombinedSampleBuffer(device_group* Group, int Rank, sample_buffer* SampleBuffer, resolve_parameters* Parameters, sample_buffer* Sum = nullptr);
+
 }}  // namespace ptb::host

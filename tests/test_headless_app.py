@@ -57,3 +57,42 @@ def test_headless_renders_what_the_python_binding_renders(exe, gpu, scenes, tmp_
         assert f.read(8) == b"\x89PNG\r\n\x1a\n"
     lin, srgb = film.resolve(1.5, I.TONE_HABLE, 1.0)
     assert os.path.getsize(png_path) > srgb.size // 2            # stored (uncompressed) deflate blocks
+
+
+@pytest.mark.gpu
+def test_headless_renders_one_image_on_two_devices(exe, gpu, scenes, tmp_path):
+    """--devices 0,1: scene packed once and replicated, one host thread and one seed block per GPU, fused peer-memory
+    reduce + resolve (host/integrator.hpp device_group over ptb_group_create_local).  The combined film is the sum of what
+    each GPU renders alone from its own first frame index."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from path_tracer_b200 import _build, integrator as I
+    sc = scenes("cornell")
+    w, h, spp, max_frames = 96, 64, 8, 2000
+    film_path, png_path = str(tmp_path / "film.bin"), str(tmp_path / "frame.png")
+    log_path = str(tmp_path / "stderr.txt")
+    with open(log_path, "wb") as log:
+        out = subprocess.run([exe, "--scene", "cornell", "--size", "%dx%d" % (w, h), "--spp", str(spp), "--max-frames", str(max_frames), "--devices", "0,1",
+                              "--table", _build.SPECTRUM_TABLE, "--film", film_path, "--out", png_path], stdout=subprocess.PIPE, stderr=log, text=True, timeout=300)
+    with open(log_path, "rb") as log:
+        assert out.returncode == 0, log.read(4000).decode(errors="replace")
+    info = json.loads(out.stdout.strip().splitlines()[-1])
+    assert info["devices"] == 2 and info["paths_finished"] >= spp * w * h
+    a = np.fromfile(film_path, dtype=np.float32).reshape(h, w, 4)
+    assert a[..., 3].sum() == info["paths_finished"]
+    total = np.zeros_like(a)
+    d = I.DeviceScene(gpu, sc)
+    for rank in range(2):
+        film = I.SampleBuffer(gpu, w, h)
+        r = I.BasicRenderer(gpu, d, film)
+        r.set_frame_index(I.Group.first_frame(rank, 2, max_frames + 64))
+        r.reset()
+        r.run(2)
+        for _ in range(info["frames_by_device"][rank] - 1):
+            r.run(1)
+        total = total + film.download()
+    # sums agree up to float addition order
+    assert np.array_equal(a[..., 3], total[..., 3]) and np.allclose(a, total, rtol=1e-6, atol=1e-7)
+    with open(png_path, "rb") as f:
+        assert f.read(8) == b"\x89PNG\r\n\x1a\n"
