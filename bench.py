@@ -270,7 +270,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ref-port", action="store_true", help="time the oracle port instead of oracle/_ref (the reference's shaders compiled as C++)")
     ap.add_argument("--reduce-mode", default="p2p", choices=["p2p", "nccl", "sliced"], help="N > 1: how the end-to-end loop combines the films (ptb_film_reduce_resolve mode)")
-    ap.add_argument("--spp-target", type=int, default=0, help="also measure the seconds from reset until every pixel holds this many samples")
+    ap.add_argument("--spp-target", type=int, default=0, help="also measure the seconds from reset until the combined film holds this many samples per pixel")
+    ap.add_argument("--spp-criterion", default="mean", choices=["mean", "min"], help="samples per pixel on average (finished paths / pixels: what 'N spp' means "
+                    "for a progressive renderer, and what bin/ptb_headless --spp uses) or in the least-sampled pixel")
     args = ap.parse_args()
     select_workload(args)
 
@@ -446,7 +448,8 @@ def main():
             def __init__(self, ptr, shape):
                 self.__cuda_array_interface__ = {"shape": shape, "typestr": "<f4", "data": (ptr, False), "version": 2}
         film_t = torch.as_tensor(_Cai(film.device_ptr, (HEIGHT, WIDTH, 4)), device=device)
-        per_rank = -(-args.spp_target // world)   # min over pixels of a sum >= sum of the per-rank minima
+        per_rank = -(-args.spp_target // world)   # mean: the means add up; min: min over pixels of a sum >= sum of the per-rank minima
+        reached = (lambda: float(film_t[..., 3].mean())) if args.spp_criterion == "mean" else (lambda: float(film_t[..., 3].min()))
         chunk = 64
         r.set_frame_index(rank << 22)             # disjoint seed blocks of 4 Mi frames
         D.barrier()
@@ -458,16 +461,16 @@ def main():
             r.run_frames(chunk)
             frames_done += chunk
             r.sync()
-            if float(film_t[..., 3].min()) >= per_rank or frames_done >= (1 << 22) - chunk:
+            if reached() >= per_rank or frames_done >= (1 << 22) - chunk:
                 break
         t_render = time.perf_counter() - t0
         deliver_frame()
         seconds = D.max_over_ranks(time.perf_counter() - t0, device)
-        spp = {"target": args.spp_target, "per_rank_target": per_rank, "seconds": seconds, "render_seconds_this_rank": t_render,
+        spp = {"target": args.spp_target, "criterion": args.spp_criterion, "per_rank_target": per_rank, "seconds": seconds, "render_seconds_this_rank": t_render,
                "frames_this_rank": frames_done, "frames_max": int(D.max_over_ranks(float(frames_done), device)),
                "min_alpha_this_rank": float(film_t[..., 3].min()), "mean_alpha_this_rank": float(film_t[..., 3].mean()),
                "exchange_ms": (D.max_over_ranks(group.last_reduce()["exchange_ms"], device) if group is not None else 0.0),
-               "what": "reset -> frames until min-over-pixels alpha >= ceil(target / n_gpus) on every rank -> exchange + resolve -> sRGB8 frame in rank 0's pinned host memory"}
+               "what": "reset -> frames until the %s-over-pixels alpha >= ceil(target / n_gpus) on every rank -> exchange + resolve -> sRGB8 frame in rank 0's pinned host memory" % args.spp_criterion}
         del film_t
 
     if group is not None:

@@ -63,16 +63,19 @@ def _includes(path, seen):
 
 
 def source_hash():
-    """sha256 (12 hex digits) over the CUDA sources, their headers and the compile flags: names the build that
-    profiles/traffic.json's ncu figures were captured from, so bench.py never quotes counters of another kernel."""
+    """sha256 (12 hex digits) over the sources the trace / scatter kernels are compiled from (ptb_kernels.cu and every
+    header it includes, transitively) and the compile flags: names the build that profiles/traffic.json's ncu figures
+    were captured from, so bench.py never quotes counters of another kernel.  (Host-side files of the library - the API,
+    the group code, the builders - do not change those kernels and are not part of it.)"""
     import hashlib
     d = os.path.join(ROOT, "csrc")
+    deps = set()
+    _includes(os.path.join(d, "ptb_kernels.cu"), deps)
     h = hashlib.sha256(" ".join(cuda_flags()).encode())
-    for f in sorted(os.listdir(d)):
-        if f.endswith((".cu", ".cuh", ".h", ".cpp")):
-            h.update(f.encode())
-            with open(os.path.join(d, f), "rb") as fh:
-                h.update(fh.read())
+    for f in sorted(deps):
+        h.update(os.path.relpath(f, REPO).encode())
+        with open(f, "rb") as fh:
+            h.update(fh.read())
     return h.hexdigest()[:12]
 
 

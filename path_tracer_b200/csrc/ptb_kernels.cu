@@ -277,6 +277,9 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_TRACE_MIN_BLOCKS) k_
 #ifndef PTB_COOP_MIN_BLOCKS
 #define PTB_COOP_MIN_BLOCKS 6
 #endif
+#ifndef PTB_COOP_DEFER_STORE
+#define PTB_COOP_DEFER_STORE 0
+#endif
 
 struct CoopWarp {
     uint2 stack[PTB_SMEM_STACK][32];
@@ -381,6 +384,9 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
     u32 index = 0;
     u32 ghead = 0, gtail = 0, qprims = 0;      // group queue sequence numbers and queued primitive count (warp-uniform)
     u32 last_seq = 0;                          // one past this lane's newest group: its tests are pending while last_seq > ghead
+#if PTB_COOP_DEFER_STORE
+    bool unsaved = false;                      // this lane's finished ray still has its hit in W.detail: stored when the lane picks up its next ray
+#endif
     WideCtx c;
     uint2 ng = make_uint2(0u, 0u);
     WarpStack stack;
@@ -435,6 +441,15 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
             const u32 rank = (u32)__popc(idle & lt_mask);
             if (!active && rank < avail) {
                 const u32 e = pool_next + rank;
+#if PTB_COOP_DEFER_STORE
+                if (unsaved) {
+                    HitId h;
+                    h.t = u2f(W.detail[0][lane]); h.shape = W.detail[1][lane]; h.prim = W.detail[2][lane]; h.shape_type = W.detail[3][lane];
+                    h.coords = mk3(u2f(W.detail[4][lane]), u2f(W.detail[5][lane]), u2f(W.detail[6][lane]));
+                    job.store(index, h);
+                    unsaved = false;
+                }
+#endif
                 Ray ray;
                 ray.origin = mk3(u2f(W.pool[0][e]), u2f(W.pool[1][e]), u2f(W.pool[2][e]));
                 ray.velocity = mk3(u2f(W.pool[3][e]), u2f(W.pool[4][e]), u2f(W.pool[5][e]));
@@ -495,14 +510,26 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
 
         // ---- retire ----
         if (active && ng.y <= 0x00FFFFFFu && (int)(last_seq - ghead) <= 0) {
+#if PTB_COOP_DEFER_STORE
+            unsaved = true;                    // retiring lanes are few per iteration (3.5 of 32): the stores wait for the pick-up, where >= REFILL lanes act together
+#else
             HitId h;
             h.t = u2f(W.detail[0][lane]); h.shape = W.detail[1][lane]; h.prim = W.detail[2][lane]; h.shape_type = W.detail[3][lane];
             h.coords = mk3(u2f(W.detail[4][lane]), u2f(W.detail[5][lane]), u2f(W.detail[6][lane]));
             job.store(index, h);
+#endif
             active = false;
             if (STATS) n_retired++;
         }
     }
+#if PTB_COOP_DEFER_STORE
+    if (unsaved) {
+        HitId h;
+        h.t = u2f(W.detail[0][lane]); h.shape = W.detail[1][lane]; h.prim = W.detail[2][lane]; h.shape_type = W.detail[3][lane];
+        h.coords = mk3(u2f(W.detail[4][lane]), u2f(W.detail[5][lane]), u2f(W.detail[6][lane]));
+        job.store(index, h);
+    }
+#endif
     if (STATS) {
         const u32 v[5] = {n_nodes, n_tests[0], n_iter, n_tests[1], n_retired};
 #pragma unroll

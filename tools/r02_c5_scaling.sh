@@ -8,7 +8,7 @@ if [ "$3" = tests ]; then
   tail -4 gpurun_out/r02_e_multigpu_tests_${N}gpu.log
 fi
 timeout 1500 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N \
-  --workload C5 --no-cpu-baseline --steps 5 --warmup 3 --spp-target $SPP > gpurun_out/r02_e_bench_C5_${N}gpu_spp${SPP}.json 2> gpurun_out/r02_e_bench_C5_${N}gpu.err
+  --workload C5 --no-cpu-baseline --steps 5 --warmup 3 --spp-target $SPP $SPPARGS > gpurun_out/r02_e_bench_C5_${N}gpu_spp${SPP}.json 2> gpurun_out/r02_e_bench_C5_${N}gpu.err
 python - <<PY
 import json
 try:
