@@ -280,10 +280,24 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_TRACE_MIN_BLOCKS) k_
 #ifndef PTB_COOP_DEFER_STORE
 #define PTB_COOP_DEFER_STORE 0
 #endif
+// 1: the closest-hit key {t bits, canonical rank} is kept as two 32-bit words and published with two native shared-memory
+// atomicMin (ATOMS.MIN) instead of one 64-bit atomicMin, which compiles to a compare-and-swap spin loop (ATOMS.CAST.SPIN.64).
+#ifndef PTB_COOP_ATOMIC32
+#define PTB_COOP_ATOMIC32 0
+#endif
+#if PTB_COOP_ATOMIC32
+#define PTB_COOP_REACH(W, l) u2f((W).tkey[l])
+#else
+#define PTB_COOP_REACH(W, l) u2f((u32)((W).key[l] >> 32))
+#endif
 
 struct CoopWarp {
     uint2 stack[PTB_SMEM_STACK][32];
+#if PTB_COOP_ATOMIC32
+    u32 tkey[32], rkey[32];           // closest hit so far: t bits (+0 canonical) and tag; tag 0xFFFFFFFF = none
+#else
     unsigned long long key[32];       // closest hit so far: {t bits (+0 canonical), tag}; tag 0xFFFFFFFF = none
+#endif
     float ray[6][32];                 // world-space origin, velocity of each lane's ray
     u32 detail[7][32];                // t, shape, face, shape type, coords of the hit `key` names
     uint4 group[PTB_COOP_QUEUE];      // {owner lane << 27 | primitive base, pending bits, valid bits, -}
@@ -311,7 +325,11 @@ __device__ __forceinline__ void coop_flush(const DeviceScene& s, CoopWarp& W, u3
 
     bool won = false;
     u32 owner = 0;
+#if PTB_COOP_ATOMIC32
+    u32 tb = 0, t_seen = 0, rank_tag = 0;
+#else
     unsigned long long key = 0;
+#endif
     HitId h;
     h.t = 0; h.shape = PTB_SHAPE_NONE; h.prim = 0xFFFFFFFFu; h.shape_type = 0; h.coords = mk3(0, 0, 0);
     if (lane < take) {
@@ -328,7 +346,7 @@ __device__ __forceinline__ void coop_flush(const DeviceScene& s, CoopWarp& W, u3
         Ray w;
         w.origin = mk3(W.ray[0][owner], W.ray[1][owner], W.ray[2][owner]);
         w.velocity = mk3(W.ray[3][owner], W.ray[4][owner], W.ray[5][owner]);
-        h.t = w.duration = u2f((u32)(W.key[owner] >> 32));
+        h.t = w.duration = PTB_COOP_REACH(W, owner);
         Ray o;
         if (tag & 4u) {
             // identity transform: ((1*x + 0*y) + 0*z) + 0 of mat_mul_point / mat_mul_vector is x + 0.0f for every
@@ -341,6 +359,27 @@ __device__ __forceinline__ void coop_flush(const DeviceScene& s, CoopWarp& W, u3
         }
         if ((tag & 3u) == 0u) test_triangle<true>(o, mk3(v0.x, v0.y, v0.z), mk3(v1.x, v1.y, v1.z), mk3(v2.x, v2.y, v2.z), shape, face, h);
         else test_analytic<true>(o, tag & 3u, shape, h);
+#if PTB_COOP_ATOMIC32
+        if (h.shape != PTB_SHAPE_NONE) {
+            tb = f2u(h.t);
+            if (tb == 0x80000000u) tb = 0u;         // -0 == +0 in the reference's comparisons
+            t_seen = f2u(w.duration);
+            rank_tag = tag;
+            atomicMin(&W.tkey[owner], tb);
+            won = true;
+        }
+    }
+    __syncwarp();
+    // the lowest t is known; candidates at that t settle the tie by rank.  When t improved, the rank of the old hit goes first:
+    // the first lane that wrote this t read a larger one before (t_seen > best), so at least one candidate sees the improvement.
+    const u32 best = won ? W.tkey[owner] : 0u;
+    won = won && tb == best;
+    if (won && best < t_seen) W.rkey[owner] = 0xFFFFFFFFu;
+    __syncwarp();
+    if (won) atomicMin(&W.rkey[owner], rank_tag);
+    __syncwarp();
+    if (won && W.rkey[owner] == rank_tag) {
+#else
         if (h.shape != PTB_SHAPE_NONE) {
             u32 tb = f2u(h.t);
             if (tb == 0x80000000u) tb = 0u;         // -0 == +0 in the reference's comparisons
@@ -351,6 +390,7 @@ __device__ __forceinline__ void coop_flush(const DeviceScene& s, CoopWarp& W, u3
     }
     __syncwarp();
     if (won && W.key[owner] == key) {
+#endif
         W.detail[0][owner] = f2u(h.t); W.detail[1][owner] = h.shape; W.detail[2][owner] = h.prim; W.detail[3][owner] = h.shape_type;
         W.detail[4][owner] = f2u(h.coords.x); W.detail[5][owner] = f2u(h.coords.y); W.detail[6][owner] = f2u(h.coords.z);
     }
@@ -462,7 +502,11 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
                 active = true;
                 W.ray[0][lane] = ray.origin.x; W.ray[1][lane] = ray.origin.y; W.ray[2][lane] = ray.origin.z;
                 W.ray[3][lane] = ray.velocity.x; W.ray[4][lane] = ray.velocity.y; W.ray[5][lane] = ray.velocity.z;
+#if PTB_COOP_ATOMIC32
+                W.tkey[lane] = W.pool[7][e]; W.rkey[lane] = W.pool[6][e];
+#else
                 W.key[lane] = ((unsigned long long)W.pool[7][e] << 32) | W.pool[6][e];
+#endif
                 const u32 hs = W.pool[10][e];
                 W.detail[0][lane] = W.pool[9][e]; W.detail[1][lane] = hs; W.detail[2][lane] = hs == PTB_SHAPE_NONE ? 0xFFFFFFFFu : 0u;
                 W.detail[3][lane] = W.pool[11][e];
@@ -480,7 +524,7 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_t
         PrimGroup pg;
         pg.base = pg.bits = pg.valid = 0u;
         if (active && ng.y > 0x00FFFFFFu && (SPEC || (int)(last_seq - ghead) <= 0)) {
-            const float reach = u2f((u32)(W.key[lane] >> 32));
+            const float reach = PTB_COOP_REACH(W, lane);
             if (STATS) n_nodes++;
             wide_node_step(s, c, reach, ng, pg, stack);
             if (ng.y <= 0x00FFFFFFu && !stack.empty()) ng = stack.pop();
