@@ -277,13 +277,16 @@ __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_TRACE_MIN_BLOCKS) k_
 #ifndef PTB_COOP_MIN_BLOCKS
 #define PTB_COOP_MIN_BLOCKS 6
 #endif
+// 1: a finished lane keeps its hit in shared memory and stores it when it picks up its next ray (>= REFILL lanes act together
+// there; retiring lanes are ~3.5 per iteration).  Together with PTB_COOP_ATOMIC32: C2 trace 0.605 -> 0.598 ms, whole job +1.3 %
+// (profiles/r02_f_ab_defer_store_atomic32.txt; each alone: -0.8 % / +0.3 %).
 #ifndef PTB_COOP_DEFER_STORE
-#define PTB_COOP_DEFER_STORE 0
+#define PTB_COOP_DEFER_STORE 1
 #endif
 // 1: the closest-hit key {t bits, canonical rank} is kept as two 32-bit words and published with two native shared-memory
 // atomicMin (ATOMS.MIN) instead of one 64-bit atomicMin, which compiles to a compare-and-swap spin loop (ATOMS.CAST.SPIN.64).
 #ifndef PTB_COOP_ATOMIC32
-#define PTB_COOP_ATOMIC32 0
+#define PTB_COOP_ATOMIC32 1
 #endif
 #if PTB_COOP_ATOMIC32
 #define PTB_COOP_REACH(W, l) u2f((W).tkey[l])
