@@ -259,7 +259,7 @@ def main():
     ap.add_argument("--integrator", default="wavefront", choices=["wavefront", "megakernel"])
     ap.add_argument("--traversal", default="wide", choices=["wide", "bvh2"])
     ap.add_argument("--trace-variant", type=int, default=-1, help="PTB_TRACE_VARIANT_* (default: the library's)")
-    ap.add_argument("--scatter-mode", default="auto", choices=["auto", "direct", "queues"])
+    ap.add_argument("--scatter-mode", default="auto", choices=["auto", "direct", "queues", "direct-staged"])
     ap.add_argument("--pipelines", type=int, default=0, choices=[0, 1, 2], help="0 = the library's choice")
     ap.add_argument("--builder", default="sah-host", choices=["sah-host", "lbvh-gpu", "ploc-gpu", "auto"], help="who flattens the scene into the BVH8 (ptb_scene_set_builder)")
     ap.add_argument("--grid", type=int, default=GRID)
@@ -333,7 +333,7 @@ def main():
     r.TieMode = I.TIE_CANONICAL
     r.PathLengthLimit = PATH_LIMIT
     r.Pipelines = args.pipelines
-    r.ScatterMode = {"auto": I.SCATTER_AUTO, "direct": I.SCATTER_DIRECT, "queues": I.SCATTER_QUEUES}[args.scatter_mode]
+    r.ScatterMode = {"auto": I.SCATTER_AUTO, "direct": I.SCATTER_DIRECT, "queues": I.SCATTER_QUEUES, "direct-staged": I.SCATTER_DIRECT_STAGED}[args.scatter_mode]
     if args.trace_variant >= 0:
         r.TraceVariant = args.trace_variant
     F = args.frames

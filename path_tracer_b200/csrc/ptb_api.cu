@@ -149,13 +149,13 @@ static void upgrade_shutdown(ptb_scene* s) {
 // PTB_SCATTER_AUTO: material queues pay when a warp would otherwise meet several materials' code.
 static bool use_queues(const ptb_renderer* r) {
     if (r->params.ScatterMode == PTB_SCATTER_QUEUES) return true;
-    if (r->params.ScatterMode == PTB_SCATTER_DIRECT) return false;
+    if (r->params.ScatterMode == PTB_SCATTER_DIRECT || r->params.ScatterMode == PTB_SCATTER_DIRECT_STAGED) return false;
     const uint32_t f = r->scene->ds.features;
     const uint32_t types = f & (PTB_FEAT_DIFFUSE | PTB_FEAT_METAL | PTB_FEAT_TRANSLUCENT);
     return (types & (types - 1u)) != 0u || (f & (PTB_FEAT_TRANSLUCENT | PTB_FEAT_SCENE_SCATTER)) != 0u;
 }
 static int scatter_step(ptb_renderer* r, const RenderConsts& pc, const WavefrontState& wst, unsigned pipe, cudaStream_t st) {
-    if (!use_queues(r)) { CU(launch_scatter(r->scene->ds, pc, wst, r->film->accum, st)); r->kernel_launches += 1; return PTB_OK; }
+    if (!use_queues(r)) { CU(launch_scatter(r->scene->ds, pc, wst, r->film->accum, r->params.ScatterMode == PTB_SCATTER_DIRECT_STAGED, st)); r->kernel_launches += 1; return PTB_OK; }
     if (!r->queue[pipe]) {
         cudaError_t e = cudaMalloc((void**)&r->queue[pipe], scatter_queue_bytes(r->pc.slot_count));
         if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc(material queues)");
@@ -506,7 +506,7 @@ void ptb_renderer_destroy(ptb_renderer* r) {
 }
 int ptb_renderer_set_params(ptb_renderer* r, const ptb_render_params* p) {
     if (!r || !p) return fail(PTB_E_INVALID, "ptb_renderer_set_params: NULL argument");
-    if (p->Integrator > PTB_INTEGRATOR_MEGAKERNEL || p->Traversal > PTB_TRAVERSAL_WIDE || p->TieMode > PTB_TIE_CANONICAL || p->TraceVariant > PTB_TRACE_VARIANT_MAX || p->ScatterMode > PTB_SCATTER_QUEUES || p->Pipelines > 2u)
+    if (p->Integrator > PTB_INTEGRATOR_MEGAKERNEL || p->Traversal > PTB_TRAVERSAL_WIDE || p->TieMode > PTB_TIE_CANONICAL || p->TraceVariant > PTB_TRACE_VARIANT_MAX || p->ScatterMode > PTB_SCATTER_DIRECT_STAGED || p->Pipelines > 2u)
         return fail(PTB_E_INVALID, "ptb_renderer_set_params: unknown enum value");
     if (p->Traversal == PTB_TRAVERSAL_WIDE && p->TieMode != PTB_TIE_CANONICAL)
         return fail(PTB_E_INVALID, "ptb_renderer_set_params: the wide traversal is order-free and needs PTB_TIE_CANONICAL");
@@ -564,7 +564,7 @@ static int run_rounds(ptb_renderer* r, uint32_t rounds, uint32_t seed_stride) {
             const uint32_t half = (r->pc.slot_count / 512u) * 256u;
             pc[0].slot_count = half;
             pc[1].slot_base = half; pc[1].slot_count = r->pc.slot_count - half;
-            wst[1].ray_counter = r->st.ray_counter + 1;
+            wst[1].ray_counter = r->st.ray_counter + 1;      // and its scatter tile counter at [+2] = base + 3
             str[1] = r->aux;
             CU(cudaEventRecord(r->ev_fork, st));
             CU(cudaStreamWaitEvent(r->aux, r->ev_fork, 0));

@@ -9,6 +9,8 @@
 //
 // Compiled with --fmad=false (see ptb_vec.cuh).
 #include "ptb_kernels.h"
+#include <cstdio>
+#include <cstdlib>
 #include "ptb_resolve.cuh"
 #include "ptb_wide.cuh"
 #include "ptb_preview.cuh"
@@ -72,6 +74,28 @@ __device__ __forceinline__ void store_path(const WavefrontState& st, u32 slot, c
     st.path3[slot] = make_float4(path.sample.x, path.sample.y, path.sample.z, __uint_as_float(path.length));
 }
 
+// The same conversions on records already in registers (the staged scatter kernel reads them from shared memory).
+__device__ __forceinline__ Ray ray_of(const float4 r) {
+    Ray ray;
+    ray.origin = mk3(r.x, r.y, r.z);
+    ray.velocity = unpack_unit_vector(__float_as_uint(r.w));
+    ray.duration = PTB_HIT_TIME_LIMIT;
+    return ray;
+}
+__device__ __forceinline__ float4 record_of(const Ray& ray) {
+    return make_float4(ray.origin.x, ray.origin.y, ray.origin.z, __uint_as_float(pack_unit_vector(ray.velocity)));
+}
+__device__ __forceinline__ PathState path_of(const uint4 a, const float4 t, const float4 p, const float4 c) {
+    PathState path;
+    path.pixel = a.x; path.lambda0 = __uint_as_float(a.y);
+    unpack_active(a.z, a.w, path.active);
+    path.throughput = mk4(t.x, t.y, t.z, t.w);
+    path.probability = mk4(p.x, p.y, p.z, p.w);
+    path.sample = mk3(c.x, c.y, c.z);
+    path.length = __float_as_uint(c.w);
+    return path;
+}
+
 // Compact closest-hit record written by the trace kernels.
 __device__ __forceinline__ void store_hit(const DeviceScene& s, const WavefrontState& st, u32 slot, const HitId& h) {
     if (h.shape == PTB_SHAPE_NONE) {
@@ -108,13 +132,14 @@ __global__ void __launch_bounds__(256) k_restart(const DeviceScene s, const Rend
     store_path(st, slot, path);
     accum[y * pc.width + x] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (threadIdx.x == 0) st.tile_paths[blockIdx.x] = 0u;
-    if (slot < 2) st.ray_counter[slot] = 0u;        // one counter per pipeline
+    if (slot < 4) st.ray_counter[slot] = 0u;        // ray fetch [0,1] and scatter tile fetch [2,3] counters, one of each per pipeline
 }
 
 // ---- K1: trace ----
 template <int MODE>
 __global__ void __launch_bounds__(128) k_trace(const DeviceScene s, const RenderConsts pc, const WavefrontState st) {
     const u32 slot = pc.slot_base + blockIdx.x * 128u + threadIdx.x;
+    if (slot == pc.slot_base) st.ray_counter[2] = 0u;       // tile fetch counter of the staged scatter kernel that follows
     u32 x, y;
     if (!slot_pixel(pc, slot, x, y)) return;
     const Ray ray = load_ray(st, slot);
@@ -166,6 +191,7 @@ struct WavefrontJob {
     __device__ __forceinline__ unsigned* counter() const { return st.ray_counter; }
     __device__ __forceinline__ bool load(u32 i, Ray& r) const { u32 x, y; if (!slot_pixel(pc, pc.slot_base + i, x, y)) return false; r = load_ray(st, pc.slot_base + i); return true; }
     __device__ __forceinline__ void store(u32 i, const HitId& h) const { store_hit(s, st, pc.slot_base + i, h); }
+    __device__ __forceinline__ void begin() const { if (blockIdx.x == 0 && threadIdx.x == 0) st.ray_counter[2] = 0u; }   // tile fetch counter of the staged scatter kernel that follows
 };
 // Caller rays (parity harness).
 struct RaycastJob {
@@ -178,11 +204,13 @@ struct RaycastJob {
         return true;
     }
     __device__ __forceinline__ void store(u32 i, const HitId& h) const;
+    __device__ __forceinline__ void begin() const {}
 };
 
 template <class Job, int REFILL>
 __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_TRACE_MIN_BLOCKS) k_trace_persistent(const Job job) {
     __shared__ uint2 stack_mem[PTB_TRACE_WARPS][PTB_SMEM_STACK][32];
+    job.begin();
     const DeviceScene& s = job.s;
     const u32 lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const u32 lt_mask = (1u << lane) - 1u;
@@ -416,6 +444,7 @@ __device__ __forceinline__ void coop_flush(const DeviceScene& s, CoopWarp& W, u3
 template <class Job, int REFILL, bool SPEC, int WAIT_T, bool STATS = false>
 __global__ void __launch_bounds__(32 * PTB_TRACE_WARPS, PTB_COOP_MIN_BLOCKS) k_trace_coop(const Job job, unsigned long long* __restrict__ stats = nullptr) {
     __shared__ CoopWarp warp_mem[PTB_TRACE_WARPS];
+    job.begin();
     const DeviceScene& s = job.s;
     const u32 lane = threadIdx.x & 31u;
     CoopWarp& W = warp_mem[threadIdx.x >> 5];
@@ -681,6 +710,153 @@ k_scatter(const DeviceScene scene, const RenderConsts pc, const WavefrontState s
     if (first + threadIdx.x == pc.slot_base) *st.ray_counter = 0u;       // re-arm the dynamic ray fetch of the next trace launch
 }
 
+
+// ---- K2, staged through shared memory by the TMA unit (ScatterMode DIRECT_STAGED: measured, NOT the default) ----
+// The direct kernel above waits on memory more than it moves bytes or issues instructions (C2: 57 % of issue slots, 46 % of the
+// measured HBM rate, 3.6 long-scoreboard stall cycles per issue): every block loads hit0, sorts hits first behind two barriers,
+// and only then issues its 7 x 16-byte loads per slot.  This kernel tries the remedy the hardware offers: the state of a
+// 256-slot tile - six contiguous 4 KB runs (ray, hit0, path0..3) - is brought into shared memory by six bulk asynchronous
+// copies (cp.async.bulk + mbarrier, no registers, issued by one thread), two tiles deep: resident blocks take tile numbers from
+// a counter (fetched one iteration early, so nobody waits for the atomic), and while a block shades tile i the copies of its
+// tile i+1 are in flight.  Threads read the records of whichever slot the hits-first order deals them from shared memory (the
+// permutation is free there) and store the new ray and path records themselves.  hit1 (hits only) stays a direct load from a
+// run prefetched into L2 when the tile's copies are issued.  Same per-slot arithmetic: films and state are bit-identical
+// (test_scatter_staged_equals_direct).
+// RESULT (profiles/r02_g_ab_scatter_staged*.txt, C2): 0.180 ms against 0.151 ms for k_scatter, at the same 4 blocks per SM; storing
+// through shared memory with bulk copies as well (a proxy fence and a third barrier per tile): 0.176 ms.  The 48 KB of staging
+// per block take 200 KB of the SM's 256 KB away from L1, which the dependent fetches of finish_hit (shape transforms, face,
+// vertices, material words: 56 % L1 hits in k_scatter) and the film pixels need more than the state loads need hiding - those
+// already find their lines in L2 thanks to the bulk L2 prefetch 296 blocks ahead.  k_scatter stays the default.
+#define PTB_STAGE_RECORDS 6u            // ray, hit0, path0, path1, path2, path3
+#define PTB_STAGE_BYTES (PTB_STAGE_RECORDS * 256u * 16u)
+
+__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, u32 count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, u32 bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, u32 parity) {
+    u32 done;
+    do {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src, u32 bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* dst, const void* src_smem, u32 bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(dst), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+template <u32 FEATURES>
+__global__ void __launch_bounds__(256, 4)
+k_scatter_staged(const DeviceScene scene, const RenderConsts pc, const WavefrontState st, float4* __restrict__ accum) {
+    extern __shared__ __align__(128) unsigned char stage_mem[];          // 2 stages x 6 records x 256 slots x 16 B
+    __shared__ unsigned long long full[2];
+    __shared__ u32 next_tile[2];
+    __shared__ u32 order[256];
+    __shared__ u32 warp_hits[8], warp_rest[8];
+    DeviceScene s = scene;
+    s.features = FEATURES;
+    const u32 tiles = pc.slot_count >> 8;
+    unsigned* const tile_counter = st.ray_counter + 2;                   // zeroed by the trace kernel of this round
+    const u32 lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+
+    auto issue = [&](u32 tile, u32 k) {                                   // thread 0: the six runs of `tile` into stage k
+        const size_t first = (size_t)pc.slot_base + (size_t)tile * 256u;
+        uint4* dst = (uint4*)(stage_mem + (size_t)k * PTB_STAGE_BYTES);
+        mbar_expect_tx(&full[k], PTB_STAGE_BYTES);
+        bulk_load(dst + 0 * 256, st.ray + first, 4096u, &full[k]);
+        bulk_load(dst + 1 * 256, st.hit0 + first, 4096u, &full[k]);
+        bulk_load(dst + 2 * 256, st.path0 + first, 4096u, &full[k]);
+        bulk_load(dst + 3 * 256, st.path1 + first, 4096u, &full[k]);
+        bulk_load(dst + 4 * 256, st.path2 + first, 4096u, &full[k]);
+        bulk_load(dst + 5 * 256, st.path3 + first, 4096u, &full[k]);
+        prefetch_l2_bulk(st.hit1 + first, 4096u);
+    };
+
+    u32 ahead = 0;                                                         // thread 0: the tile number fetched one iteration early
+    if (threadIdx.x == 0) {
+        mbar_init(&full[0], 1u);
+        mbar_init(&full[1], 1u);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        if (blockIdx.x == 0) *st.ray_counter = 0u;                        // re-arm the dynamic ray fetch of the next trace launch
+        const u32 a = atomicAdd(tile_counter, 1u);
+        next_tile[0] = a;
+        if (a < tiles) issue(a, 0u);
+        ahead = atomicAdd(tile_counter, 1u);                              // not needed before the first barrier of iteration 0
+    }
+    __syncthreads();
+
+    for (u32 it = 0;; it++) {
+        const u32 k = it & 1u;
+        const u32 tile = next_tile[k];
+        if (tile >= tiles) break;
+        mbar_wait(&full[k], (it >> 1) & 1u);
+
+        const uint4* rec = (const uint4*)(stage_mem + (size_t)k * PTB_STAGE_BYTES);
+        const u32 first = pc.slot_base + tile * 256u;
+        u32 x, y;
+        u32 j = threadIdx.x;
+        {
+            // hits first (see k_scatter): all but one warp of the block run uniform code
+            const bool hit = slot_pixel(pc, first + j, x, y) && rec[1 * 256 + j].y != 0xFFFFFFFFu;
+            const u32 hb = __ballot_sync(0xFFFFFFFFu, hit);
+            if (lane == 0) { warp_hits[warp] = (u32)__popc(hb); warp_rest[warp] = 32u - (u32)__popc(hb); }
+            __syncthreads();
+            // every thread is past the tile before this one: its stage is free, and the copies of the next tile go there now.
+            // The tile number after that is fetched here as well and read one iteration later, so nobody waits for the atomic.
+            if (threadIdx.x == 0) {
+                next_tile[k ^ 1u] = ahead;
+                if (ahead < tiles) issue(ahead, k ^ 1u);
+                ahead = atomicAdd(tile_counter, 1u);
+            }
+            u32 hits_before = 0, rest_before = 0, hits_total = 0;
+#pragma unroll
+            for (u32 w = 0; w < 8; w++) {
+                if (w < warp) { hits_before += warp_hits[w]; rest_before += warp_rest[w]; }
+                hits_total += warp_hits[w];
+            }
+            const u32 below = (1u << lane) - 1u;
+            const u32 pos = hit ? hits_before + (u32)__popc(hb & below) : hits_total + rest_before + (u32)__popc(~hb & below);
+            order[pos] = threadIdx.x;
+            __syncthreads();
+            j = order[threadIdx.x];
+        }
+        const u32 slot = first + j;
+        bool finished = false;
+        if (slot_pixel(pc, slot, x, y)) {
+            const uint4 h0 = rec[1 * 256 + j];
+            Ray ray = ray_of(*(const float4*)&rec[0 * 256 + j]);
+            PathState path = path_of(rec[2 * 256 + j], *(const float4*)&rec[3 * 256 + j], *(const float4*)&rec[4 * 256 + j], *(const float4*)&rec[5 * 256 + j]);
+            PackedHit p = packed_miss();
+            if (h0.y != 0xFFFFFFFFu) {
+                const uint4 h1 = st.hit1[slot];
+                HitId h;
+                h.t = __uint_as_float(h0.x); h.shape = h0.y >> 16; h.prim = h0.z; h.shape_type = h0.w;
+                h.coords = mk3(__uint_as_float(h1.x), __uint_as_float(h1.y), __uint_as_float(h1.z));
+                const Surface sf = finish_hit(s, h);
+                p = pack_hit(h, sf);
+            }
+            const SurfaceHit hit = unpack_hit(p, ray);
+            finished = scatter_invocation(s, pc, x, y, path, ray, hit, accum);
+            store_ray(st, slot, ray);
+            store_path(st, slot, path);
+        }
+        // finished-path counters per 256-slot tile; no block barrier here, so warps go on to the next tile as they finish
+        const u32 c = (u32)__popc(__ballot_sync(0xFFFFFFFFu, finished));
+        if (lane == 0u && c != 0u) atomicAdd(&st.tile_paths[first >> 8], c);
+    }
+}
+
 // ---- material queues ----
 // Class of a slot for this round: what its scatter invocation can execute.
 //   0 miss, 1 diffuse hit, 2 metal hit (all three: no enclosing medium), 3 everything else.
@@ -917,9 +1093,39 @@ cudaError_t launch_hit_attributes(const DeviceScene& s, const RenderConsts& pc, 
     return cudaGetLastError();
 }
 
-cudaError_t launch_scatter(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, cudaStream_t stream) {
+template <u32 F>
+static cudaError_t launch_staged(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, cudaStream_t stream) {
+    static unsigned cache[PTB_MAX_DEVICES];
+    const size_t smem = 2u * (size_t)PTB_STAGE_BYTES;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= PTB_MAX_DEVICES || !cache[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(k_scatter_staged<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+#ifdef PTB_STAGED_CARVEOUT
+        cudaFuncSetAttribute(k_scatter_staged<F>, cudaFuncAttributePreferredSharedMemoryCarveout, PTB_STAGED_CARVEOUT);
+#endif
+        int sms = 148, per_sm = 1;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_scatter_staged<F>, 256, smem);
+        if (per_sm < 1) per_sm = 1;
+        if (getenv("PTB_DEBUG_OCCUPANCY")) fprintf(stderr, "k_scatter_staged<%u>: %d blocks/SM, %d SMs, %zu B dynamic smem\n", F, per_sm, sms, smem);
+        if (dev >= 0 && dev < PTB_MAX_DEVICES) cache[dev] = (unsigned)(sms * per_sm);
+    }
+    const unsigned resident = (dev >= 0 && dev < PTB_MAX_DEVICES) ? cache[dev] : 148u;
+    const unsigned tiles = pc.slot_count >> 8;
+    k_scatter_staged<F><<<tiles < resident ? tiles : resident, 256, smem, stream>>>(s, pc, st, accum);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_scatter(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, bool staged, cudaStream_t stream) {
     const unsigned grid = pc.slot_count / (unsigned)PTB_SCATTER_THREADS;
     const u32 opaque = PTB_FEAT_DIFFUSE | PTB_FEAT_METAL | PTB_FEAT_TEXTURES | PTB_FEAT_SKY_TEXTURE;
+    if (staged) {
+        if ((s.features & ~PTB_FEAT_DIFFUSE) == 0u) return launch_staged<PTB_FEAT_DIFFUSE>(s, pc, st, accum, stream);
+        if ((s.features & ~opaque) == 0u) return launch_staged<opaque>(s, pc, st, accum, stream);
+        return launch_staged<PTB_FEAT_ALL>(s, pc, st, accum, stream);
+    }
     if ((s.features & ~PTB_FEAT_DIFFUSE) == 0u) k_scatter<PTB_FEAT_DIFFUSE><<<grid, PTB_SCATTER_THREADS, 0, stream>>>(s, pc, st, accum);
     else if ((s.features & ~opaque) == 0u) k_scatter<opaque><<<grid, PTB_SCATTER_THREADS, 0, stream>>>(s, pc, st, accum);
     else k_scatter<PTB_FEAT_ALL><<<grid, PTB_SCATTER_THREADS, 0, stream>>>(s, pc, st, accum);

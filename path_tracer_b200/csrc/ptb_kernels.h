@@ -37,7 +37,8 @@ cudaError_t launch_trace(const DeviceScene& s, const RenderConsts& pc, const Wav
 cudaError_t launch_trace_stats(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, unsigned long long* stats, cudaStream_t stream);
 // Debug/test: closest-hit attributes of the stored hits as {packed normal, packed tangent, u, v} per slot.
 cudaError_t launch_hit_attributes(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, uint4* out, cudaStream_t stream);
-cudaError_t launch_scatter(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, cudaStream_t stream);
+// staged: the TMA-staged persistent kernel (k_scatter_staged, an experiment kept for A/B); else k_scatter
+cudaError_t launch_scatter(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, bool staged, cudaStream_t stream);
 // Scatter through per-material queues (classify + one specialised kernel per class); `queue` holds scatter_queue_bytes().
 size_t scatter_queue_bytes(unsigned slot_count);
 unsigned scatter_queue_launches(const DeviceScene& s);

@@ -21,7 +21,7 @@ from . import _build
 from .types import (KernelTimes, PreviewParams, PREVIEW_MODES, RenderParams, ResolveParams, SceneView, Stats, WideInfo, HIT_DTYPE, RAY_DTYPE,
                     RENDER_FLAG_ACCUMULATE, RENDER_FLAG_SAMPLE_JITTER, INTEGRATOR_WAVEFRONT, INTEGRATOR_MEGAKERNEL,
                     TRAVERSAL_BVH2_REFERENCE, TRAVERSAL_WIDE, TIE_FAITHFUL, TIE_CANONICAL, SCENE_DIRTY_ALL, BUILDER_SAH_HOST, BUILDER_LBVH_GPU, BUILDER_PLOC_GPU, BUILDER_AUTO,
-                    TRACE_VARIANT_SIMPLE, TRACE_VARIANT_DEFAULT, TRACE_VARIANT_MAX, SCATTER_AUTO, SCATTER_DIRECT, SCATTER_QUEUES,
+                    TRACE_VARIANT_SIMPLE, TRACE_VARIANT_DEFAULT, TRACE_VARIANT_MAX, SCATTER_AUTO, SCATTER_DIRECT, SCATTER_QUEUES, SCATTER_DIRECT_STAGED,
                     TONE_CLAMP, TONE_REINHARD, TONE_HABLE, TONE_ACES)
 
 # every symbol include/ptb.h declares (checked by tests/test_abi.py)

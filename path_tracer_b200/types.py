@@ -97,5 +97,5 @@ INTEGRATOR_WAVEFRONT, INTEGRATOR_MEGAKERNEL = 0, 1
 TRAVERSAL_BVH2_REFERENCE, TRAVERSAL_WIDE = 0, 1
 TIE_FAITHFUL, TIE_CANONICAL = 0, 1
 TRACE_VARIANT_SIMPLE, TRACE_VARIANT_DEFAULT, TRACE_VARIANT_MAX = 0, 14, 19
-SCATTER_AUTO, SCATTER_DIRECT, SCATTER_QUEUES = 0, 1, 2
+SCATTER_AUTO, SCATTER_DIRECT, SCATTER_QUEUES, SCATTER_DIRECT_STAGED = 0, 1, 2, 3
 SCENE_DIRTY_ALL = 0xFFFFFFFF

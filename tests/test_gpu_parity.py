@@ -630,6 +630,34 @@ def test_scatter_material_queues_equal_direct(I, gpu, dev, scenes):
         r.reset()
 
 
+def test_scatter_staged_equals_direct(I, gpu, dev, scenes):
+    """The TMA-staged scatter kernel (ScatterMode DIRECT_STAGED: resident blocks, 256-slot tiles brought into shared memory by bulk
+    asynchronous copies two tiles deep, tile numbers from a counter) against the default direct kernel: the same
+    per-slot arithmetic, so film, every wavefront state array and the counters are identical - on films with ragged last tile
+    rows, on a film smaller than one wave of resident blocks, over many rounds (the counter is re-armed by every trace
+    launch, whichever trace kernel runs), and with two half-film pipelines."""
+    names = ("OriginX", "OriginY", "OriginZ", "PackedVelocity", "ImagePosition", "NormalizedLambda0", "Throughput0", "Throughput3",
+             "Probability1", "SampleR", "SampleB", "ActiveShapeIndex01", "ActiveShapeIndex23", "PathLength")
+    for (name, params), (w, h), variant, pipes in ((("cornell", ()), (144, 80), I.TRACE_VARIANT_DEFAULT, 1), (("terrain", (64,)), (100, 70), I.TRACE_VARIANT_DEFAULT, 1),
+                                                   (("room", (1, 512)), (640, 368), I.TRACE_VARIANT_DEFAULT, 2), (("terrain", (48,)), (1936, 1096), I.TRACE_VARIANT_SIMPLE, 1),
+                                                   (("cornell", ()), (16, 16), 3, 1)):
+        outs = []
+        for mode in (I.SCATTER_DIRECT, I.SCATTER_DIRECT_STAGED):
+            film = I.SampleBuffer(gpu, w, h)
+            r = I.BasicRenderer(gpu, dev(name, *params), film)
+            r.ScatterMode, r.TraceVariant, r.Pipelines = mode, variant, pipes
+            r.set_frame_index(11)
+            r.reset()
+            r.run(2)
+            r.run_frames(13)
+            outs.append((film.download(), [r.state(n) for n in names], r.stats()))
+        a, b = outs
+        assert np.array_equal(a[0], b[0]), (name, w, h)
+        for n, x, y in zip(names, a[1], b[1]):
+            assert np.array_equal(bits(x), bits(y)), (name, n)
+        assert a[2]["paths_finished"] == b[2]["paths_finished"] > 0 and a[2]["rays_traced"] == b[2]["rays_traced"]
+
+
 @pytest.mark.parametrize("integrator", ["wavefront", "megakernel"])
 @pytest.mark.parametrize("name,params", [("cornell", ()), ("terrain", (64,))])
 def test_converged_image_within_one_percent(I, gpu, dev, oracle, scenes, name, params, integrator):
