@@ -17,7 +17,13 @@ sys.path.insert(0, ROOT)
 
 
 def rows_of(path):
-    raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv", "--print-units", "base"], stdout=subprocess.PIPE, text=True).stdout
+    """An .ncu-rep, or the CSV that `ncu -i REP --page raw --csv --print-units base` printed from it (the reports of five
+    workloads together are too big to bring back from the GPU box; the CSVs are not)."""
+    if path.endswith(".csv"):
+        with open(path) as f:
+            raw = f.read()
+    else:
+        raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv", "--print-units", "base"], stdout=subprocess.PIPE, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     hdr = rows[0]
     return hdr, rows[2:]
