@@ -15,7 +15,7 @@ ctx = I.Context(0)
 for name, params in (("cornell", ()), ("terrain", (24,)), ("spherefield", (6, 1, 2))):
     sc = S.Scene.make(name, *params)
     dev = I.DeviceScene(ctx, sc)
-    for mode in (I.SCATTER_DIRECT, I.SCATTER_QUEUES):
+    for mode in (I.SCATTER_DIRECT, I.SCATTER_QUEUES, I.SCATTER_DIRECT_STAGED):
         film = I.SampleBuffer(ctx, 80, 48)
         r = I.BasicRenderer(ctx, dev, film)
         r.ScatterMode = mode
@@ -33,6 +33,7 @@ for name, params in (("cornell", ()), ("terrain", (24,)), ("spherefield", (6, 1,
     rays["d"] = d / np.linalg.norm(d, axis=1, keepdims=True)
     rays["duration"] = 1048576.0
     dev.raycast(rays)
+    dev.raycast_noalloc(rays)
     cam = sc.cameras[0]
     dev.preview(cam["To"].ravel(), cam["From"].ravel(), 1, 64, 40)
 print("sanitize_smoke ok")
