@@ -318,6 +318,8 @@ struct jpeg_huff {
     int maxcode[18];
     int delta[17];
     int count = 0;
+    jpeg_huff() { std::memset(size, 0, sizeof size); std::memset(code, 0, sizeof code); std::memset(values, 0, sizeof values);
+                  std::memset(maxcode, 0, sizeof maxcode); std::memset(delta, 0, sizeof delta); maxcode[17] = 0x7fffffff; }
     bool build(const int* counts) {
         int k = 0;
         for (int i = 0; i < 16; i++)
@@ -382,7 +384,7 @@ struct jpeg_decoder {
         if (code_bits < 16) grow();
         const unsigned temp = code_buffer >> 16;
         int k;
-        for (k = 1; ; k++) if ((int)temp < h.maxcode[k]) break;
+        for (k = 1; k < 17; k++) if ((int)temp < h.maxcode[k]) break;       // (a table the file never defined has no codes: k ends at 17)
         if (k == 17) { code_bits -= 16; return -1; }
         if (k > code_bits) return -1;
         const int c = (int)((code_buffer >> (32 - k)) & ((1u << k) - 1)) + h.delta[k];
@@ -540,12 +542,13 @@ bool jpeg_block_prog_ac(jpeg_decoder& j, short data[64], const jpeg_huff& hac) {
     return true;
 }
 
-inline u8 jpeg_clamp(int x) { return (unsigned)x > 255 ? (x < 0 ? 0 : 255) : (u8)x; }
+// (64-bit intermediates: identical results for every valid coefficient range, and no signed overflow on a corrupt file)
+inline u8 jpeg_clamp(long long x) { return x < 0 ? 0 : x > 255 ? 255 : (u8)x; }
 
 #define PTB_F2F(x) ((int)(((x) * 4096 + 0.5)))
 #define PTB_FSH(x) ((x) * 4096)
 #define PTB_IDCT_1D(s0, s1, s2, s3, s4, s5, s6, s7)            \
-    int t0, t1, t2, t3, p1, p2, p3, p4, p5, x0, x1, x2, x3;     \
+    long long t0, t1, t2, t3, p1, p2, p3, p4, p5, x0, x1, x2, x3; \
     p2 = s2; p3 = s6;                                           \
     p1 = (p2 + p3) * PTB_F2F(0.5411961f);                       \
     t2 = p1 + p3 * PTB_F2F(-1.847759065f);                      \
@@ -568,11 +571,11 @@ inline u8 jpeg_clamp(int x) { return (unsigned)x > 255 ? (x < 0 ? 0 : 255) : (u8
     t3 += p1 + p4; t2 += p2 + p3; t1 += p2 + p4; t0 += p1 + p3;
 
 void jpeg_idct(u8* out, int out_stride, short data[64]) {
-    int val[64], *v = val;
+    long long val[64], *v = val;
     short* d = data;
     for (int i = 0; i < 8; ++i, ++d, ++v) {
         if (d[8] == 0 && d[16] == 0 && d[24] == 0 && d[32] == 0 && d[40] == 0 && d[48] == 0 && d[56] == 0) {
-            const int dcterm = d[0] * 4;
+            const long long dcterm = d[0] * 4;
             v[0] = v[8] = v[16] = v[24] = v[32] = v[40] = v[48] = v[56] = dcterm;
         } else {
             PTB_IDCT_1D(d[0], d[8], d[16], d[24], d[32], d[40], d[48], d[56])
