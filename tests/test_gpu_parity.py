@@ -370,6 +370,63 @@ def test_imported_obj_model_renders_like_the_oracle(I, gpu, oracle, tmp_path):
     assert (tmp_path / "torus.png").stat().st_size > w * h * 4 and srgb[..., :3].std() > 5
 
 
+def test_textured_obj_with_png_jpeg_and_hdr_sky_renders_like_the_oracle(I, gpu, oracle, tmp_path):
+    """The asset class SURVEY 8(f) N4 exists for: an OBJ whose MTL names a PNG (map_Kd) and a JPEG texture, under a Radiance
+    .hdr skybox - decoded by host/image.cpp (bit-identical with the reference's stb_image, tests/test_image_decode.py), packed
+    into the atlas, rendered by the shipped configuration: ray casts bit-exact, first-bounce radiance within 1e-4."""
+    PIL = pytest.importorskip("PIL.Image")
+    from path_tracer_b200 import scene as S
+    from test_image_decode import picture, write_hdr
+    a = picture(64, 32, 2)
+    PIL.fromarray(a[..., :3]).save(tmp_path / "kd.png")
+    PIL.fromarray(picture(48, 48, 3)[..., :3]).save(tmp_path / "kd2.jpg", quality=90, subsampling=2)
+    y, x = np.mgrid[0:32, 0:64]
+    rgbe = np.zeros((32, 64, 4), np.uint8)
+    rgbe[..., 0] = 90 + 60 * np.sin(x / 9.0)
+    rgbe[..., 1] = 120 + 50 * np.cos(y / 5.0)
+    rgbe[..., 2] = 200
+    rgbe[..., 3] = 128 + (y < 8) * 3                          # a bright band near the top of the sky
+    write_hdr(tmp_path / "sky.hdr", rgbe, True)
+    (tmp_path / "m.mtl").write_text("newmtl png\nKd 1 1 1\nmap_Kd kd.png\nnewmtl jpg\nKd 1 1 1\nmap_Kd kd2.jpg\n")
+    lines = ["mtllib m.mtl", "o A", "v -1 -1 0", "v 1 -1 0", "v 1 1 0", "v -1 1 0", "v -1 1 1.5", "v 1 1 1.5",
+             "vt 0 0", "vt 1 0", "vt 1 1", "vt 0 1", "usemtl png", "f 1/1 2/2 3/3", "f 1/1 3/3 4/4", "usemtl jpg", "f 4/1 3/2 6/3", "f 4/1 6/3 5/4"]
+    (tmp_path / "m.obj").write_text("\n".join(lines) + "\n")
+    sc = S.Scene()
+    sc.set_atlas_size(256, 256)
+    prefab = sc.load_model(str(tmp_path / "m.obj"))
+    assert sc.prefab_mesh_count(prefab) == 2
+    sc.create_prefab_instance(prefab, position=(0, 0, 0.2))
+    sky = sc.load_texture(str(tmp_path / "sky.hdr"), S.TEXTURE_RADIANCE)
+    sc.set_root(sky_brightness=1.0, sky_sampling_probability=0.3, sky_texture=sky)
+    glass = sc.create_material(S.MATERIAL_BASIC_TRANSLUCENT, "glass", IOR=1.5, Roughness=0.0)
+    sc.create_entity(S.ENTITY_SPHERE, position=(0.2, -0.3, 0.8), scale=(0.35, 0.35, 0.35), material=glass)
+    sc.create_camera((0.3, -4.0, 1.6), (0, 0, 0.6), params=(55.0, 0.0))
+    sc.pack()
+    assert len(sc.textures) == 3 and sc.globals["SkyboxTextureIndex"] != 0xFFFFFFFF
+    d = I.DeviceScene(gpu, sc)
+    rays = random_rays(sc, 50000, 6, oracle)
+    out = d.raycast(rays, I.TRAVERSAL_WIDE, I.TIE_CANONICAL)
+    bf = oracle.raycast_bruteforce(sc.view, rays[::17])
+    assert ids_equal(out[::17], bf).all() and (bits(out["t"][::17]) == bits(bf["t"])).all()
+    w, h = 160, 96
+    o = oracle.Renderer(sc.view, w, h, tie=oracle.TIE_CANONICAL)
+    film = I.SampleBuffer(gpu, w, h)
+    r = I.BasicRenderer(gpu, d, film)
+    for side in (o, r):
+        side.set_frame_index(3)
+        side.reset()
+        side.run(2)
+    a, b = film.download(), o.accum()
+    assert_alpha_equal(a[..., 3], b[..., 3], PRODUCT)
+    assert_radiance_close(a[..., :3], b[..., :3])
+    assert b[..., :3].max() > 0.05                            # the sky texture and the textured quads contribute
+    r.run_frames(6)
+    o.run_frames(6)
+    a, b = film.download(), o.accum()
+    sa, sb = a[..., :3].sum(axis=(0, 1), dtype=np.float64), b[..., :3].sum(axis=(0, 1), dtype=np.float64)
+    assert (np.abs(sa - sb) <= 5e-3 * np.abs(sb)).all(), (sa, sb)
+
+
 # ---------------------------------------------------------------- radiance
 def assert_alpha_equal(a, b, mode, what=None):
     """Paths finished per pixel.  The reference-layout traversal must agree with the oracle everywhere.  The product's BVH8
