@@ -279,6 +279,7 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
         s->ds.mesh_faces = s->faces.p; s->ds.mesh_face_count = v->MeshFaceCount;
         s->ds.mesh_vertices = s->vertices.p;
         s->ds.mesh_nodes = s->mesh_nodes.p; s->ds.mesh_node_count = v->MeshNodeCount;
+        { int rc = ptb_scene_build_face_attrs(s); if (rc) return rc; }
     }
     if (geometry_lock.owns_lock()) {
         CU(cudaStreamSynchronize(st));
@@ -362,13 +363,26 @@ int ptb_scene_update(ptb_scene* s, const ptb_scene_view* v, uint32_t dirty) {
     return PTB_OK;
 }
 
+int ptb_scene_build_face_attrs(ptb_scene* s) {
+    s->ds.face_attrs = nullptr;
+    const size_t n = s->faces.n;
+    static const bool off = std::getenv("PTB_NO_FACE_ATTRS") != nullptr;      // A/B switch
+    if (n == 0 || !s->faces.p || !s->vertices.p || off) { s->face_attrs.release(); return PTB_OK; }
+    if (s->face_attrs.n != 2 * n || !s->face_attrs.p) {
+        if (s->face_attrs.alloc(2 * n) != cudaSuccess) { cudaGetLastError(); s->face_attrs.release(); return PTB_OK; }     // indexed path stays
+    }
+    CU(launch_face_attrs(s->faces.p, s->vertices.p, s->face_attrs.p, (unsigned)n, s->ctx->stream));
+    s->ds.face_attrs = s->face_attrs.p;
+    return PTB_OK;
+}
+
 void ptb_scene_destroy(ptb_scene* s) {
     if (!s) return;
     cudaSetDevice(s->ctx->device);
     cudaStreamSynchronize(s->ctx->stream);
     upgrade_shutdown(s);
     s->textures.release(); s->materials.release(); s->shapes.release(); s->shape_nodes.release();
-    s->faces.release(); s->vertices.release(); s->mesh_nodes.release(); s->cameras.release();
+    s->faces.release(); s->vertices.release(); s->mesh_nodes.release(); s->cameras.release(); s->face_attrs.release();
     for (auto& l : s->layers) l.release();
     s->layer_table.release(); s->wide_nodes.release(); s->wide_prims.release(); s->wide_planes.release();
     delete s;

@@ -495,6 +495,7 @@ int ptb_scene_replicate(ptb_scene* s, ptb_group* g, int root) {
         d.atlas_layers = s->layer_table.p;
         d.wide_nodes = (const uint4*)s->wide_nodes.p; d.wide_tris = (const float4*)s->wide_prims.p; d.wide_planes = s->wide_planes.p;
         s->wide_info = h.info; s->material_features = h.material_features; s->builder = h.builder;
+        if ((rc = ptb_scene_build_face_attrs(s))) return rc;      // gathered here from the arrays that just arrived (not broadcast)
     }
     CU(cudaStreamSynchronize(st));
     return PTB_OK;

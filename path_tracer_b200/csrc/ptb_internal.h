@@ -72,6 +72,7 @@ struct ptb_scene {
     ptb::DevBuf<ptb_packed_mesh_face> faces;
     ptb::DevBuf<ptb_packed_mesh_vertex> vertices;
     ptb::DevBuf<ptb_packed_mesh_node> mesh_nodes;
+    ptb::DevBuf<uint4> face_attrs;   // per-face vertex attributes gathered on the device (DeviceScene::face_attrs)
     ptb::DevBuf<ptb_packed_camera> cameras;
     std::vector<ptb::DevBuf<float>> layers;
     ptb::DevBuf<const float*> layer_table;
@@ -84,6 +85,10 @@ struct ptb_scene {
     uint32_t builder;                // PTB_BUILDER_*
     uint32_t material_features;      // PTB_FEAT_DIFFUSE/METAL/TRANSLUCENT bits of the uploaded material slots
 };
+
+// (Re)builds s->face_attrs from the device copies of faces and vertices; on an allocation failure the scene keeps working
+// through the indexed path (ds.face_attrs = null).  Enqueued on the context's stream.
+extern "C" int ptb_scene_build_face_attrs(ptb_scene* s);
 
 struct ptb_film {
     ptb_context* ctx;

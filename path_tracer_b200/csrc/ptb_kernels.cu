@@ -119,6 +119,27 @@ __device__ __forceinline__ PackedHit load_packed_hit(const DeviceScene& s, const
     return pack_hit(h, sf);
 }
 
+// ---- per-face vertex attributes, gathered once per mesh upload ----
+// finish_hit needs the packed normal and uv of a hit face's three vertices.  Through the reference's arrays that is a
+// dependent chain - face record (48 B, for three indices) -> three 8-byte vertex records anywhere in the vertex array - i.e.
+// five 32-byte sectors and two memory round trips per hit; on the 10 M-triangle scenes, whose 520 MB of faces and vertices
+// do not fit in L2, that is most of what the scatter kernels wait for.  One 32-byte record per face, indexed by the face
+// index the hit already carries, makes it one sector and one round trip.  Same bits, so results are unchanged.
+__global__ void __launch_bounds__(256) k_face_attrs(const ptb_packed_mesh_face* __restrict__ faces, const ptb_packed_mesh_vertex* __restrict__ vertices,
+                                                     uint4* __restrict__ out, u32 n) {
+    const u32 i = blockIdx.x * 256u + threadIdx.x;
+    if (i >= n) return;
+    const ptb_packed_mesh_face* f = &faces[i];
+    const uint2 v0 = *(const uint2*)&vertices[f->VertexIndex0], v1 = *(const uint2*)&vertices[f->VertexIndex1], v2 = *(const uint2*)&vertices[f->VertexIndex2];
+    out[2 * (size_t)i] = make_uint4(v0.x, v0.y, v1.x, v1.y);
+    out[2 * (size_t)i + 1] = make_uint4(v2.x, v2.y, 0u, 0u);
+}
+cudaError_t launch_face_attrs(const ptb_packed_mesh_face* faces, const ptb_packed_mesh_vertex* vertices, uint4* out, unsigned n, cudaStream_t stream) {
+    if (n == 0) return cudaSuccess;
+    k_face_attrs<<<(n + 255u) / 256u, 256, 0, stream>>>(faces, vertices, out, n);
+    return cudaGetLastError();
+}
+
 // ---- K3: restart ----
 __global__ void __launch_bounds__(256) k_restart(const DeviceScene s, const RenderConsts pc, const WavefrontState st, float4* __restrict__ accum) {
     const u32 slot = blockIdx.x * 256u + threadIdx.x;

@@ -28,6 +28,8 @@ struct WavefrontState {
 
 struct LaunchStats { unsigned int launches; };
 
+// 2 x uint4 per face = {n0, uv0, n1, uv1}, {n2, uv2, 0, 0} (DeviceScene::face_attrs)
+cudaError_t launch_face_attrs(const ptb_packed_mesh_face* faces, const ptb_packed_mesh_vertex* vertices, uint4* out, unsigned n, cudaStream_t stream);
 cudaError_t launch_restart(const DeviceScene& s, const RenderConsts& pc, const WavefrontState& st, float4* accum, cudaStream_t stream);
 // variant 0: one thread per slot; variant >= 1: persistent warps with dynamic ray fetch (wide traversal only),
 // tuning point (refill threshold, postpone threshold) selected by the variant number.

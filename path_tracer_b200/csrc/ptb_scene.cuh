@@ -24,6 +24,9 @@ struct DeviceScene {
     const ptb_packed_mesh_face*    mesh_faces;
     const ptb_packed_mesh_vertex*  mesh_vertices;
     const ptb_packed_mesh_node*    mesh_nodes;
+    const uint4*                   face_attrs;        // 2 x uint4 per face: the three vertices' {packed normal, packed uv} gathered once
+                                                      // (k_face_attrs), so that deriving a hit's attributes is one 32-byte fetch by face
+                                                      // index instead of face -> 3 indices -> 3 scattered vertex records; null = not built
     const ptb_packed_camera*       cameras;
     const float* const*            atlas_layers;      // device array of device pointers, RGBA32F
     u32 atlas_width, atlas_height;

@@ -248,11 +248,17 @@ PTB_HD Surface finish_hit(const DeviceScene& s, const HitId& h) {
         for (int c = 0; c < 4; c++) { float4 col = PTB_LDG(&m[4 + c]); from[4 * c] = col.x; from[4 * c + 1] = col.y; from[4 * c + 2] = col.z; from[4 * c + 3] = col.w; }
     }
     if (h.shape_type == PTB_SHAPE_MESH) {
-        const ptb_packed_mesh_face* f = &s.mesh_faces[h.prim];
-        u32 i0 = PTB_LDG(&f->VertexIndex0), i1 = PTB_LDG(&f->VertexIndex1), i2 = PTB_LDG(&f->VertexIndex2);
-        uint2 v0 = PTB_LDG((const uint2*)&s.mesh_vertices[i0]);
-        uint2 v1 = PTB_LDG((const uint2*)&s.mesh_vertices[i1]);
-        uint2 v2 = PTB_LDG((const uint2*)&s.mesh_vertices[i2]);
+        uint2 v0, v1, v2;
+        if (s.face_attrs) {
+            const uint4 a = PTB_LDG(&s.face_attrs[2 * (size_t)h.prim]), b = PTB_LDG(&s.face_attrs[2 * (size_t)h.prim + 1]);
+            v0 = make_uint2(a.x, a.y); v1 = make_uint2(a.z, a.w); v2 = make_uint2(b.x, b.y);
+        } else {
+            const ptb_packed_mesh_face* f = &s.mesh_faces[h.prim];
+            u32 i0 = PTB_LDG(&f->VertexIndex0), i1 = PTB_LDG(&f->VertexIndex1), i2 = PTB_LDG(&f->VertexIndex2);
+            v0 = PTB_LDG((const uint2*)&s.mesh_vertices[i0]);
+            v1 = PTB_LDG((const uint2*)&s.mesh_vertices[i1]);
+            v2 = PTB_LDG((const uint2*)&s.mesh_vertices[i2]);
+        }
         f3 c = h.coords;
         f3 n = safe_normalize((unpack_unit_vector(v0.x) * c.x + unpack_unit_vector(v1.x) * c.y) + unpack_unit_vector(v2.x) * c.z);
         out.normal = normalize(vector_mul_mat(n, from));
