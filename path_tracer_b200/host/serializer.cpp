@@ -249,8 +249,15 @@ void save_texture(context& C, json& J, texture& T) {
     write_compressed(f, T.Pixels.data(), sizeof(vec4) * T.Pixels.size());
     if (!f) throw std::runtime_error("scene file: cannot write texture " + T.Name);
 }
+// An enumerator read from a file must be one the packer knows (a corrupt file otherwise reaches PackSceneData with it).
+// Counts: scene.hpp:10-46,230-240 (TEXTURE_TYPE__COUNT 3, MATERIAL_TYPE__COUNT 4, CAMERA_MODEL__COUNT 3, ENTITY_TYPE__COUNT 7).
+int checked_enum(const json& J, int count, const char* what) {
+    const int v = (int)J.i();
+    if (v < 0 || v >= count) throw std::runtime_error(std::string("scene file: unknown ") + what);
+    return v;
+}
 void load_texture(context& C, const json& J, texture& T) {
-    T.Type = (texture_type)J.at("Type").i(); T.Name = J.at("Name").str; T.EnableNearestFiltering = J.at("EnableNearestFiltering").boolean();
+    T.Type = (texture_type)checked_enum(J.at("Type"), 3, "texture type"); T.Name = J.at("Name").str; T.EnableNearestFiltering = J.at("EnableNearestFiltering").boolean();
     std::ifstream f(C.Dir + "/" + make_file_name(T.Name, "texture"), std::ios::binary);
     if (!f) throw std::runtime_error("scene file: missing texture file for " + T.Name);
     const size_t fs = file_size_of(f);
@@ -349,14 +356,14 @@ void save_entity(context& C, json& J, entity& E) {
 }
 void load_entity(context& C, const json& J, entity& E) {
     entity D;
-    E.Type = (entity_type)J.at("Type").i();
+    E.Type = (entity_type)checked_enum(J.at("Type"), 7, "entity type");
     E.Transform.Position = J.at("Position").v3(); E.Transform.Rotation = J.at("Rotation").v3(); E.Transform.Scale = J.at("Scale").v3({1, 1, 1});
     E.Name = J.at("Name").str; E.Active = J.at("Active").boolean(true); E.Material = C.mat(J.at("Material"));
     if (E.Type == ENTITY_TYPE_ROOT) {
         E.ScatterRate = J.at("ScatterRate").f(); E.SkyboxBrightness = J.at("SkyboxBrightness").f(1.0f); E.SkyboxTexture = C.tex(J.at("SkyboxTexture"));
         E.SkyboxSamplingProbability = J.at("SkyboxSamplingProbability").f(0.0f);
     } else if (E.Type == ENTITY_TYPE_CAMERA) {
-        E.CameraModel = (camera_model)J.at("CameraModel").i();
+        E.CameraModel = (camera_model)checked_enum(J.at("CameraModel"), 3, "camera model");
         E.Pinhole.FieldOfViewInDegrees = J.at("Pinhole").at("FieldOfViewInDegrees").f(D.Pinhole.FieldOfViewInDegrees);
         E.Pinhole.ApertureDiameterInMM = J.at("Pinhole").at("ApertureDiameterInMM").f(D.Pinhole.ApertureDiameterInMM);
         E.ThinLens.SensorSizeInMM = J.at("ThinLens").at("SensorSizeInMM").v2(D.ThinLens.SensorSizeInMM);
@@ -430,7 +437,7 @@ scene* LoadScene(char const* Path, std::string* Error) {
         context C{S, dir_of(Path), false, {}, {}, {}};
         const json &JT = J.at("Textures"), &JM = J.at("Materials"), &JG = J.at("Meshes"), &JP = J.at("Prefabs");
         for (size_t n = 0; n < JT.size(); n++) { texture* T = new texture; S->Textures.push_back(T); load_texture(C, JT.at(n), *T); }
-        for (size_t n = 0; n < JM.size(); n++) CreateMaterial(S, (material_type)JM.at(n).at("Type").i(), "");
+        for (size_t n = 0; n < JM.size(); n++) CreateMaterial(S, (material_type)checked_enum(JM.at(n).at("Type"), 4, "material type"), "");
         for (size_t n = 0; n < JM.size(); n++) load_material(C, JM.at(n), *S->Materials[n]);
         for (size_t n = 0; n < JG.size(); n++) { mesh* M = new mesh; S->Meshes.push_back(M); load_mesh(C, JG.at(n), *M); }
         for (size_t n = 0; n < JP.size(); n++) { prefab* R = new prefab; R->Entity = new entity; S->Prefabs.push_back(R); load_entity(C, JP.at(n), *R->Entity); }
