@@ -14,6 +14,8 @@
 //          decoder below can upsample (1x1, 2x1, 1x2, 2x2 and generic integer factors).  stb_image's integer
 //          IDCT, its triangle-filter chroma upsampling and its 20-bit fixed-point YCbCr conversion are
 //          followed so that 8-bit output is identical with the reference's.
+//   * TGA (types 1/2/3 and run-length 9/10/11; 8/15/16/24/32 bits) and BMP (1/4/8-bit paletted, 16/24/32-bit, BITFIELDS; no RLE),
+//          with stb_image's conversions (5-5-5 scaling, bit-field replication, the "all alpha zero means opaque" rule).
 //   * PPM (P6) and PFM (PF) kept from round 1 (not stb formats with this contract: P6 is read as
 //          sRGB-encoded, PFM as linear float, rows bottom to top).
 // 8-bit sources become float the way stbi_loadf does it (stb_image.h "ldr_to_hdr"): colour channels
@@ -942,6 +944,227 @@ bool decode_jpeg(const std::vector<u8>& file, int& W, int& H, std::vector<u8>& r
     return true;
 }
 
+// ------------------------------------------------------------------ TGA (Truevision, as stb_image reads it)
+// Types 1 / 2 / 3 (colour-mapped, true colour, grey) and their run-length forms 9 / 10 / 11; 8, 15, 16, 24, 32 bits per pixel or
+// palette entry; 15/16-bit colour is 5-5-5 scaled by 255/31; 16-bit grey is grey + alpha; rows bottom-up unless bit 5 of the
+// descriptor is set.  One stb quirk is kept because files depend on it: the palette's "first entry" field is skipped as BYTES.
+uint32_t le16(const u8* p) { return (uint32_t)p[0] | ((uint32_t)p[1] << 8); }
+
+bool tga_header_ok(const std::vector<u8>& f) {
+    if (f.size() < 18) return false;
+    const int cmap = f[1], type = f[2], pal_bits = f[7], bpp = f[16];
+    if (cmap > 1) return false;
+    if (cmap == 1) {
+        if (type != 1 && type != 9) return false;
+        if (pal_bits != 8 && pal_bits != 15 && pal_bits != 16 && pal_bits != 24 && pal_bits != 32) return false;
+    } else if (type != 2 && type != 3 && type != 10 && type != 11) return false;
+    if (le16(&f[12]) < 1 || le16(&f[14]) < 1) return false;
+    if (cmap == 1 && bpp != 8 && bpp != 16) return false;
+    return bpp == 8 || bpp == 15 || bpp == 16 || bpp == 24 || bpp == 32;
+}
+
+int tga_components(int bits, bool grey, bool& rgb16) {
+    rgb16 = false;
+    switch (bits) {
+        case 8: return 1;
+        case 16: if (grey) return 2;   // fall through: 5-5-5 colour
+        case 15: rgb16 = true; return 3;
+        case 24: case 32: return bits / 8;
+        default: return 0;
+    }
+}
+
+bool decode_tga(const std::vector<u8>& f, int& W, int& H, std::vector<u8>& rgba) {
+    if (!tga_header_ok(f)) return false;
+    const int id_len = f[0], cmap = f[1];
+    int type = f[2];
+    const uint32_t pal_start = le16(&f[3]), pal_len = le16(&f[5]);
+    const int pal_bits = f[7], bpp = f[16];
+    const uint32_t w = le16(&f[12]), h = le16(&f[14]);
+    const bool bottom_up = !((f[17] >> 5) & 1);
+    const bool rle = type >= 8;
+    if (rle) type -= 8;
+    const bool indexed = cmap == 1;
+    bool rgb16 = false;
+    const int comp = indexed ? tga_components(pal_bits, false, rgb16) : tga_components(bpp, type == 3, rgb16);
+    if (!comp) return false;
+    size_t pos = 18 + (size_t)id_len;
+    auto need = [&](size_t n) { return pos + n <= f.size(); };
+    auto read_555 = [&](u8* out) {
+        const uint32_t px = le16(&f[pos]); pos += 2;
+        out[0] = (u8)((((px >> 10) & 31) * 255) / 31); out[1] = (u8)((((px >> 5) & 31) * 255) / 31); out[2] = (u8)(((px & 31) * 255) / 31);
+    };
+    std::vector<u8> palette;
+    if (indexed) {
+        if (pal_len == 0) return false;
+        pos += pal_start;
+        palette.resize((size_t)pal_len * comp);
+        if (rgb16) { if (!need((size_t)pal_len * 2)) return false; for (uint32_t i = 0; i < pal_len; i++) read_555(&palette[(size_t)i * comp]); }
+        else { if (!need(palette.size())) return false; std::memcpy(palette.data(), &f[pos], palette.size()); pos += palette.size(); }
+    }
+    std::vector<u8> px((size_t)w * h * comp);
+    u8 cur[4] = {0, 0, 0, 0};
+    int count = 0;
+    bool run = false, fetch = true;
+    for (size_t i = 0; i < (size_t)w * h; i++) {
+        if (rle) {
+            if (count == 0) { if (!need(1)) return false; const int cmd = f[pos++]; count = 1 + (cmd & 127); run = (cmd >> 7) != 0; fetch = true; }
+            else if (!run) fetch = true;
+        } else fetch = true;
+        if (fetch) {
+            if (indexed) {
+                if (!need(bpp == 8 ? 1 : 2)) return false;
+                uint32_t idx = bpp == 8 ? f[pos] : le16(&f[pos]);
+                pos += bpp == 8 ? 1 : 2;
+                if (idx >= pal_len) idx = 0;
+                for (int k = 0; k < comp; k++) cur[k] = palette[(size_t)idx * comp + k];
+            } else if (rgb16) { if (!need(2)) return false; read_555(cur); }
+            else { if (!need((size_t)comp)) return false; for (int k = 0; k < comp; k++) cur[k] = f[pos++]; }
+            fetch = false;
+        }
+        for (int k = 0; k < comp; k++) px[i * comp + k] = cur[k];
+        --count;
+    }
+    W = (int)w; H = (int)h;
+    rgba.resize((size_t)w * h * 4);
+    for (uint32_t y = 0; y < h; y++) {
+        const u8* src = &px[(size_t)(bottom_up ? h - 1 - y : y) * w * comp];
+        u8* o = &rgba[(size_t)y * w * 4];
+        for (uint32_t x = 0; x < w; x++, src += comp, o += 4) {
+            if (comp == 1) { o[0] = o[1] = o[2] = src[0]; o[3] = 255; }
+            else if (comp == 2) { o[0] = o[1] = o[2] = src[0]; o[3] = src[1]; }
+            else {
+                const bool swap = !rgb16;                         // 24 / 32-bit pixels are stored blue first
+                o[0] = src[swap ? 2 : 0]; o[1] = src[1]; o[2] = src[swap ? 0 : 2]; o[3] = comp == 4 ? src[3] : 255;
+            }
+        }
+    }
+    return true;
+}
+
+// ------------------------------------------------------------------ BMP (Windows / OS2 bitmaps, uncompressed or BITFIELDS)
+int bmp_high_bit(uint32_t z) { int n = -1; while (z) { n++; z >>= 1; } return n; }
+int bmp_bit_count(uint32_t a) { int n = 0; while (a) { n += a & 1; a >>= 1; } return n; }
+// a masked field of `bits` bits scaled to 0..255 by bit replication
+int bmp_field(uint32_t v, int shift, int bits) {
+    static const uint32_t mul[9] = {0, 0xff, 0x55, 0x49, 0x11, 0x21, 0x41, 0x81, 0x01};
+    static const uint32_t shr[9] = {0, 0, 0, 1, 0, 2, 4, 6, 0};
+    if (shift < 0) v <<= -shift; else v >>= shift;
+    if (bits < 1 || bits > 8) return 0;
+    v >>= (8 - bits);
+    return (int)((v * mul[bits]) >> shr[bits]);
+}
+
+bool decode_bmp(const std::vector<u8>& f, int& W, int& H, std::vector<u8>& rgba) {
+    if (f.size() < 26 || f[0] != 'B' || f[1] != 'M') return false;
+    auto r16 = [&](size_t p) -> uint32_t { return p + 2 <= f.size() ? le16(&f[p]) : 0u; };
+    auto r32 = [&](size_t p) -> uint32_t { return p + 4 <= f.size() ? (le16(&f[p]) | (le16(&f[p + 2]) << 16)) : 0u; };
+    const uint32_t offset = r32(10), hsz = r32(14);
+    if (hsz != 12 && hsz != 40 && hsz != 56 && hsz != 108 && hsz != 124) return false;
+    int width, height;
+    uint32_t bpp, compress = 0;
+    uint32_t mr = 0, mg = 0, mb = 0, ma = 0;
+    bool all_alpha_unknown = false;                    // 32 bits without masks: alpha counts only if some pixel has any
+    if (hsz == 12) { width = (int)r16(18); height = (int)r16(20); if (r16(22) != 1) return false; bpp = r16(24); }
+    else {
+        width = (int)r32(18); height = (int)r32(22);
+        if (r16(26) != 1) return false;
+        bpp = r16(28); compress = r32(30);
+        if (compress == 1 || compress == 2) return false;                       // run-length forms
+        if (compress >= 4) return false;
+        if (compress == 3 && bpp != 16 && bpp != 32) return false;
+        if (hsz == 40 || hsz == 56) {
+            if (bpp == 16 || bpp == 32) {
+                if (compress == 0) {
+                    if (bpp == 32) { mr = 0xffu << 16; mg = 0xffu << 8; mb = 0xffu; ma = 0xffu << 24; all_alpha_unknown = true; }
+                    else { mr = 31u << 10; mg = 31u << 5; mb = 31u; }
+                } else {
+                    const size_t m = hsz == 56 ? 54 : 54;
+                    mr = r32(m); mg = r32(m + 4); mb = r32(m + 8);
+                    if (mr == mg && mg == mb) return false;
+                }
+            }
+        } else {
+            mr = r32(54); mg = r32(58); mb = r32(62); ma = r32(66);
+            if (compress != 3 && (bpp == 16 || bpp == 32)) {
+                if (bpp == 32) { mr = 0xffu << 16; mg = 0xffu << 8; mb = 0xffu; ma = 0xffu << 24; all_alpha_unknown = true; }
+                else { mr = 31u << 10; mg = 31u << 5; mb = 31u; ma = 0; }
+            }
+        }
+    }
+    if (width <= 0 || height == 0 || width > (1 << 24)) return false;
+    const bool flip = height > 0;
+    const uint32_t h = (uint32_t)(height < 0 ? -(long long)height : height), w = (uint32_t)width;
+    if (h > (1u << 24)) return false;
+    // header bytes consumed before the palette / pixel data: 14 + hsz (+ 12 for the masks that follow a 40-byte BITFIELDS header)
+    size_t header_end = 14 + (size_t)hsz + ((hsz == 40 && compress == 3) ? 12 : 0);
+    int psize = 0;
+    if (hsz == 12) { if (bpp < 24) psize = (int)((offset - header_end) / 3); }
+    else if (bpp < 16) psize = (int)((offset - header_end) >> 2);
+    if (offset < header_end || offset > f.size()) return false;
+    W = (int)w; H = (int)h;
+    rgba.assign((size_t)w * h * 4, 255);
+    bool any_alpha = false;
+    if (bpp < 16) {
+        if (psize == 0 || psize > 256) return false;
+        u8 pal[256][4];
+        size_t pos = header_end;
+        for (int i = 0; i < psize; i++) {
+            if (pos + 3 > f.size()) return false;
+            pal[i][2] = f[pos]; pal[i][1] = f[pos + 1]; pal[i][0] = f[pos + 2]; pal[i][3] = 255;
+            pos += hsz == 12 ? 3 : 4;
+        }
+        if (bpp != 1 && bpp != 4 && bpp != 8) return false;
+        const size_t row = (((size_t)w * bpp + 7) / 8 + 3) & ~(size_t)3;
+        if (offset + row * h > f.size()) return false;
+        for (uint32_t y = 0; y < h; y++) {
+            const u8* src = &f[offset + row * y];
+            u8* o = &rgba[(size_t)(flip ? h - 1 - y : y) * w * 4];
+            for (uint32_t x = 0; x < w; x++) {
+                int v;
+                if (bpp == 8) v = src[x];
+                else if (bpp == 4) v = (src[x >> 1] >> ((x & 1) ? 0 : 4)) & 15;
+                else v = (src[x >> 3] >> (7 - (x & 7))) & 1;
+                if (v >= psize) v = 0;
+                o[4 * x] = pal[v][0]; o[4 * x + 1] = pal[v][1]; o[4 * x + 2] = pal[v][2]; o[4 * x + 3] = 255;
+            }
+        }
+        return true;
+    }
+    if (bpp != 16 && bpp != 24 && bpp != 32) return false;
+    const size_t bytes = bpp / 8, row = ((size_t)w * bytes + 3) & ~(size_t)3;
+    if (offset + (row * (h - 1) + (size_t)w * bytes) > f.size()) return false;
+    const bool bgr24 = bpp == 24, bgra32 = bpp == 32 && mb == 0xffu && mg == 0xff00u && mr == 0x00ff0000u && ma == 0xff000000u;
+    int rs = 0, gs = 0, bs = 0, as = 0, rc = 0, gc = 0, bc = 0, ac = 0;
+    if (!bgr24 && !bgra32) {
+        if (!mr || !mg || !mb) return false;
+        rs = bmp_high_bit(mr) - 7; rc = bmp_bit_count(mr); gs = bmp_high_bit(mg) - 7; gc = bmp_bit_count(mg);
+        bs = bmp_high_bit(mb) - 7; bc = bmp_bit_count(mb); as = bmp_high_bit(ma) - 7; ac = bmp_bit_count(ma);
+        if (rc > 8 || gc > 8 || bc > 8 || ac > 8) return false;
+    }
+    const bool has_alpha = ma != 0;
+    for (uint32_t y = 0; y < h; y++) {
+        const u8* src = &f[offset + row * y];
+        u8* o = &rgba[(size_t)(flip ? h - 1 - y : y) * w * 4];
+        for (uint32_t x = 0; x < w; x++, src += bytes, o += 4) {
+            if (bgr24 || bgra32) {
+                o[0] = src[2]; o[1] = src[1]; o[2] = src[0];
+                const u8 a = bgra32 ? src[3] : 255;
+                any_alpha |= a != 0;
+                o[3] = has_alpha ? a : 255;
+            } else {
+                const uint32_t v = bpp == 16 ? le16(src) : (le16(src) | (le16(src + 2) << 16));
+                o[0] = (u8)bmp_field(v & mr, rs, rc); o[1] = (u8)bmp_field(v & mg, gs, gc); o[2] = (u8)bmp_field(v & mb, bs, bc);
+                const int a = ma ? bmp_field(v & ma, as, ac) : 255;
+                any_alpha |= a != 0;
+                o[3] = has_alpha ? (u8)a : 255;
+            }
+        }
+    }
+    if (has_alpha && all_alpha_unknown && !any_alpha) for (size_t i = 3; i < rgba.size(); i += 4) rgba[i] = 255;
+    return true;
+}
+
 // ------------------------------------------------------------------ PPM / PFM (round 1)
 bool pnm_token(const std::vector<u8>& f, size_t& pos, std::string& tok) {
     tok.clear();
@@ -1009,6 +1232,15 @@ bool DecodeImageFile(char const* Path, int& Width, int& Height, std::vector<vec4
     }
     if (file[0] == '#' && file[1] == '?') return decode_hdr(file, Width, Height, Pixels);
     if (file[0] == 'P' && (file[1] == '6' || file[1] == 'F')) return decode_pnm(file, Width, Height, Pixels);
+    if (file[0] == 'B' && file[1] == 'M') {
+        if (!decode_bmp(file, Width, Height, rgba)) return false;
+        ldr_to_float(rgba, Pixels);
+        return true;
+    }
+    if (decode_tga(file, Width, Height, rgba)) {               // no magic number: tried last, as stb_image does
+        ldr_to_float(rgba, Pixels);
+        return true;
+    }
     return false;
 }
 

@@ -243,3 +243,99 @@ def test_load_texture_and_mtl_maps(tmp_path):
     assert len(sc.textures) == 2 and sc.globals["SkyboxTextureIndex"] != 0xFFFFFFFF
     with pytest.raises(OSError):
         sc.load_texture(str(tmp_path / "m.obj"), S.TEXTURE_RAW)
+
+
+@pytest.mark.parametrize("mode", ["L", "LA", "RGB", "RGBA", "P"])
+@pytest.mark.parametrize("rle", [False, True])
+@pytest.mark.parametrize("top_down", [False, True])
+def test_tga_matches_stb_image(tmp_path, mode, rle, top_down):
+    w, h = 37, 23
+    a = picture(w, h, 4)
+    a[:, :9] = a[0, 0]                                        # runs for the run-length coder
+    f = tmp_path / "t.tga"
+    if mode == "P":
+        im = PIL.fromarray(a[..., :3]).quantize(19)
+    else:
+        im = PIL.fromarray(a if mode == "RGBA" else a[..., :3] if mode == "RGB" else a[..., 0] if mode == "L" else a[..., [0, 3]], mode)
+    im.save(f, compression="tga_rle" if rle else None, orientation=1 if top_down else -1)
+    px = same(f)
+    assert px.shape == (h, w, 4)
+
+
+def test_tga_16_bit_colour_and_16_bit_indices(tmp_path):
+    """5-5-5 true colour (type 2, 16 bits; and run-length type 10) and a colour-mapped file with 16-bit indices and a 15-bit
+    palette: written by hand."""
+    rng = np.random.default_rng(5)
+    w, h = 11, 7
+    px16 = rng.integers(0, 1 << 15, size=(h, w)).astype("<u2")
+    hdr = struct.pack("<BBBHHBHHHHBB", 0, 0, 2, 0, 0, 0, 0, 0, w, h, 16, 0)
+    (tmp_path / "a.tga").write_bytes(hdr + px16.tobytes())
+    same(tmp_path / "a.tga")
+    body = b""
+    for row in px16:                                          # one raw packet per row (w <= 128)
+        body += bytes([w - 1]) + row.tobytes()
+    hdr = struct.pack("<BBBHHBHHHHBB", 3, 0, 10, 0, 0, 0, 0, 0, w, h, 15, 0x20)
+    (tmp_path / "b.tga").write_bytes(hdr + b"abc" + body)
+    same(tmp_path / "b.tga")
+    pal = rng.integers(0, 1 << 15, size=300).astype("<u2")
+    idx = rng.integers(0, 300, size=(h, w)).astype("<u2")
+    hdr = struct.pack("<BBBHHBHHHHBB", 0, 1, 1, 0, 300, 15, 0, 0, w, h, 16, 0)
+    (tmp_path / "c.tga").write_bytes(hdr + pal.tobytes() + idx.tobytes())
+    same(tmp_path / "c.tga")
+
+
+@pytest.mark.parametrize("mode", ["RGB", "RGBA", "P", "L", "1"])
+@pytest.mark.parametrize("size", [(37, 23), (5, 3), (64, 1)])
+def test_bmp_matches_stb_image(tmp_path, mode, size):
+    w, h = size
+    a = picture(w, h, 6)
+    f = tmp_path / "t.bmp"
+    if mode == "P":
+        PIL.fromarray(a[..., :3]).quantize(23).save(f)
+    elif mode == "1":
+        PIL.fromarray(a[..., 0] > 128).save(f)
+    else:
+        PIL.fromarray(a if mode == "RGBA" else a[..., :3] if mode == "RGB" else a[..., 0], mode).save(f)
+    px = same(f)
+    assert px.shape == (h, w, 4)
+
+
+def test_bmp_16_bit_bitfields_4_bit_and_top_down(tmp_path):
+    """Forms Pillow does not write: 16-bit 5-5-5 (BI_RGB) and 5-6-5 (BITFIELDS), 32-bit BI_RGB whose alpha bytes are all zero
+    (means opaque) or not, 4-bit palettes, negative height (rows top-down), an OS/2 12-byte header."""
+    rng = np.random.default_rng(8)
+    w, h = 13, 6
+
+    def bmp(bpp, pixels_rows, compress=0, masks=b"", palette=b"", height=None, hsz=40):
+        rows = b"".join(r + b"\0" * (-len(r) % 4) for r in pixels_rows)
+        off = 14 + hsz + len(masks) + len(palette)
+        if hsz == 12:
+            info = struct.pack("<IHHHH", 12, w, h if height is None else height, 1, bpp)
+        else:
+            info = struct.pack("<IiiHHIIiiII", hsz, w, h if height is None else height, 1, bpp, compress, len(rows), 2835, 2835, 0, 0)
+            info += b"\0" * (hsz - len(info))
+        return b"BM" + struct.pack("<IHHI", off + len(rows), 0, 0, off) + info + masks + palette + rows
+    v16 = rng.integers(0, 1 << 16, size=(h, w)).astype("<u2")
+    (tmp_path / "a.bmp").write_bytes(bmp(16, [r.tobytes() for r in v16]))
+    same(tmp_path / "a.bmp")
+    (tmp_path / "b.bmp").write_bytes(bmp(16, [r.tobytes() for r in v16], compress=3, masks=struct.pack("<III", 0xF800, 0x07E0, 0x001F)))
+    same(tmp_path / "b.bmp")
+    v32 = rng.integers(0, 256, size=(h, w, 4)).astype(np.uint8)
+    (tmp_path / "c.bmp").write_bytes(bmp(32, [r.tobytes() for r in v32]))
+    same(tmp_path / "c.bmp")
+    v32[..., 3] = 0
+    (tmp_path / "d.bmp").write_bytes(bmp(32, [r.tobytes() for r in v32], height=-h))
+    px = same(tmp_path / "d.bmp")
+    assert (px[..., 3] == 1.0).all()
+    pal = rng.integers(0, 256, size=(16, 4)).astype(np.uint8)
+    idx = rng.integers(0, 16, size=(h, w + (w & 1)))
+    rows4 = [bytes(int(r[i]) << 4 | int(r[i + 1]) for i in range(0, len(r), 2)) for r in idx]
+    (tmp_path / "e.bmp").write_bytes(bmp(4, rows4, palette=pal.tobytes()))
+    same(tmp_path / "e.bmp")
+    v24 = rng.integers(0, 256, size=(h, w, 3)).astype(np.uint8)
+    (tmp_path / "f.bmp").write_bytes(bmp(24, [r.tobytes() for r in v24], hsz=12))
+    same(tmp_path / "f.bmp")
+    pal3 = rng.integers(0, 256, size=(256, 3)).astype(np.uint8)
+    idx8 = rng.integers(0, 252, size=(h, w)).astype(np.uint8)      # (stb_image reads only 252 entries of a 12-byte-header file's palette)
+    (tmp_path / "g.bmp").write_bytes(bmp(8, [r.tobytes() for r in idx8], palette=pal3.tobytes(), hsz=12))
+    same(tmp_path / "g.bmp")

@@ -1,8 +1,8 @@
 #!/usr/bin/env python
-"""Mutation fuzz of host/image.cpp (PNG / JPEG / Radiance HDR decoders) under AddressSanitizer + UBSan.  CPU only.
+"""Mutation fuzz of host/image.cpp (PNG / JPEG / Radiance HDR / TGA / BMP decoders) under AddressSanitizer + UBSan.  CPU only.
     cd path_tracer_b200/host && g++ -std=c++17 -O1 -g -fsanitize=address,undefined -I . -I ../../include -o /tmp/asan_img ../../tools/fuzz_image_decoders_main.cpp image.cpp -lz
     python tools/fuzz_image_decoders.py
-Round 2: 12 000 mutated files, no sanitizer report (two findings on the way, fixed: signed overflow in the IDCT on absurd
+Round 2: 12 000 + 8 000 (TGA / BMP seeds) mutated files, no sanitizer report (two findings on the way, fixed: signed overflow in the IDCT on absurd
 coefficients, a scan that names a Huffman table the file never defined)."""
 import sys, os, numpy as np, tempfile, subprocess
 sys.path.insert(0,"/root/repo"); sys.path.insert(0,"/root/repo/tests")
@@ -17,8 +17,14 @@ for name,kw in (("a.png",{}),("b.jpg",dict(quality=80)),("c.jpg",dict(quality=60
 Image.fromarray(a[...,:3]).quantize(16).save(os.path.join(d,"p.png")); seeds.append(open(os.path.join(d,"p.png"),"rb").read())
 Image.fromarray((a[...,0].astype(np.uint16)*257)).save(os.path.join(d,"s.png")); seeds.append(open(os.path.join(d,"s.png"),"rb").read())
 rgbe=rng.integers(0,256,size=(9,40,4)).astype(np.uint8); T.write_hdr(os.path.join(d,"h.hdr"),rgbe,True); seeds.append(open(os.path.join(d,"h.hdr"),"rb").read())
+b=T.picture(40,30,1)
+def add(name, im, **kw):
+    p=os.path.join(d,name); im.save(p,**kw); seeds.append(open(p,"rb").read())
+add("a.tga", Image.fromarray(b[...,:3])); add("b.tga", Image.fromarray(b), compression="tga_rle")
+add("c.tga", Image.fromarray(b[...,:3]).quantize(17), compression="tga_rle"); add("d.tga", Image.fromarray(b[...,[0,3]],"LA"))
+add("a.bmp", Image.fromarray(b[...,:3])); add("b.bmp", Image.fromarray(b)); add("c.bmp", Image.fromarray(b[...,:3]).quantize(17)); add("d.bmp", Image.fromarray(b[...,0]>128))
 files=[]
-for it in range(8000):
+for it in range(16000):
     s=bytearray(seeds[it%len(seeds)])
     for _ in range(rng.integers(1,6)):
         m=rng.integers(0,3)
@@ -30,7 +36,7 @@ for it in range(8000):
 bad=0
 for k in range(0,len(files),400):
     r=subprocess.run(["/tmp/asan_img"]+files[k:k+400],stdout=subprocess.PIPE,stderr=subprocess.PIPE,text=True)
-    if r.returncode!=0 or "runtime error" in r.stderr:
+    if r.returncode!=0 or "runtime error" in r.stderr or "AddressSanitizer" in r.stderr:
         bad+=1; print(r.stderr[:1500])
         break
     print(r.stdout.strip())
