@@ -5,7 +5,9 @@
 // basic_metal.hpp:26-52, basic_translucent.hpp:26-61.
 #include "scene.hpp"
 #include <algorithm>
+#include <atomic>
 #include <cassert>
+#include <thread>
 #include <unordered_map>
 #include <functional>
 
@@ -284,33 +286,70 @@ uint32_t PackSceneData(scene* Scene) {
     // Meshes (scene.cpp:1266-1343): global vertex / face / node index bases.
     if (Dirty & SCENE_DIRTY_MESHES) {
         auto& VP = Scene->MeshVertexPack; auto& FP = Scene->MeshFacePack; auto& NP = Scene->MeshNodePack;
+        // Index bases first (a prefix sum over the meshes, in order), then every record is a pure function of its
+        // source and its mesh's bases: the arrays are filled in pieces on all host threads and come out as the
+        // reference's sequential push_backs do.
+        struct base { uint32_t V, F, N; };
+        std::vector<base> Bases(Scene->Meshes.size());
         size_t nv = 0, nf = 0, nn = 0;
-        for (mesh* M : Scene->Meshes) { nv += M->Vertices.size(); nf += M->Faces.size(); nn += M->Nodes.size(); }
-        VP.clear(); VP.reserve(nv); FP.clear(); FP.reserve(nf); NP.clear(); NP.reserve(nn);
-        for (mesh* M : Scene->Meshes) {
-            const uint32_t VB = (uint32_t)VP.size(), FB = (uint32_t)FP.size(), NB = (uint32_t)NP.size();
-            for (mesh_vertex const& V : M->Vertices)
-                VP.push_back({pack_unit_vector(V.Normal), pack_half2x16(V.UV.x, V.UV.y)});
-            for (mesh_face const& F : M->Faces) {
-                ptb_packed_mesh_face K;
-                vec3 const& p0 = M->Vertices[F.VertexIndex[0]].Position;
-                vec3 const& p1 = M->Vertices[F.VertexIndex[1]].Position;
-                vec3 const& p2 = M->Vertices[F.VertexIndex[2]].Position;
-                K.Position0[0] = p0.x; K.Position0[1] = p0.y; K.Position0[2] = p0.z; K.VertexIndex0 = VB + F.VertexIndex[0];
-                K.Position1[0] = p1.x; K.Position1[1] = p1.y; K.Position1[2] = p1.z; K.VertexIndex1 = VB + F.VertexIndex[1];
-                K.Position2[0] = p2.x; K.Position2[1] = p2.y; K.Position2[2] = p2.z; K.VertexIndex2 = VB + F.VertexIndex[2];
-                FP.push_back(K);
-            }
-            for (mesh_node const& N : M->Nodes) {
-                ptb_packed_mesh_node K;
-                K.Minimum[0] = N.Bounds.Minimum.x; K.Minimum[1] = N.Bounds.Minimum.y; K.Minimum[2] = N.Bounds.Minimum.z;
-                K.Maximum[0] = N.Bounds.Maximum.x; K.Maximum[1] = N.Bounds.Maximum.y; K.Maximum[2] = N.Bounds.Maximum.z;
-                if (N.ChildNodeIndex > 0) { K.FaceBeginOrNodeIndex = NB + N.ChildNodeIndex; K.FaceEndIndex = 0; }
-                else { K.FaceBeginOrNodeIndex = FB + N.FaceBeginIndex; K.FaceEndIndex = FB + N.FaceEndIndex; }
-                NP.push_back(K);
-            }
-            M->PackedRootNodeIndex = NB;
+        for (size_t m = 0; m < Scene->Meshes.size(); m++) {
+            mesh* M = Scene->Meshes[m];
+            Bases[m] = {(uint32_t)nv, (uint32_t)nf, (uint32_t)nn};
+            M->PackedRootNodeIndex = (uint32_t)nn;
+            nv += M->Vertices.size(); nf += M->Faces.size(); nn += M->Nodes.size();
         }
+        VP.resize(nv); FP.resize(nf); NP.resize(nn);
+        struct piece { uint32_t Mesh, Kind, Begin, End; };
+        std::vector<piece> Pieces;
+        constexpr uint32_t PIECE = 32768;
+        for (size_t m = 0; m < Scene->Meshes.size(); m++) {
+            mesh* M = Scene->Meshes[m];
+            const size_t Counts[3] = {M->Vertices.size(), M->Faces.size(), M->Nodes.size()};
+            for (uint32_t k = 0; k < 3; k++)
+                for (size_t b = 0; b < Counts[k]; b += PIECE)
+                    Pieces.push_back({(uint32_t)m, k, (uint32_t)b, (uint32_t)std::min(Counts[k], b + PIECE)});
+        }
+        std::atomic<size_t> Next(0);
+        auto Work = [&]() {
+            for (size_t i = Next.fetch_add(1); i < Pieces.size(); i = Next.fetch_add(1)) {
+                piece const& W = Pieces[i];
+                mesh const* M = Scene->Meshes[W.Mesh];
+                const uint32_t VB = Bases[W.Mesh].V, FB = Bases[W.Mesh].F, NB = Bases[W.Mesh].N;
+                if (W.Kind == 0) {
+                    for (uint32_t v = W.Begin; v < W.End; v++) {
+                        mesh_vertex const& V = M->Vertices[v];
+                        VP[VB + v] = {pack_unit_vector(V.Normal), pack_half2x16(V.UV.x, V.UV.y)};
+                    }
+                } else if (W.Kind == 1) {
+                    for (uint32_t f = W.Begin; f < W.End; f++) {
+                        mesh_face const& F = M->Faces[f];
+                        ptb_packed_mesh_face K;
+                        vec3 const& p0 = M->Vertices[F.VertexIndex[0]].Position;
+                        vec3 const& p1 = M->Vertices[F.VertexIndex[1]].Position;
+                        vec3 const& p2 = M->Vertices[F.VertexIndex[2]].Position;
+                        K.Position0[0] = p0.x; K.Position0[1] = p0.y; K.Position0[2] = p0.z; K.VertexIndex0 = VB + F.VertexIndex[0];
+                        K.Position1[0] = p1.x; K.Position1[1] = p1.y; K.Position1[2] = p1.z; K.VertexIndex1 = VB + F.VertexIndex[1];
+                        K.Position2[0] = p2.x; K.Position2[1] = p2.y; K.Position2[2] = p2.z; K.VertexIndex2 = VB + F.VertexIndex[2];
+                        FP[FB + f] = K;
+                    }
+                } else {
+                    for (uint32_t n = W.Begin; n < W.End; n++) {
+                        mesh_node const& N = M->Nodes[n];
+                        ptb_packed_mesh_node K;
+                        K.Minimum[0] = N.Bounds.Minimum.x; K.Minimum[1] = N.Bounds.Minimum.y; K.Minimum[2] = N.Bounds.Minimum.z;
+                        K.Maximum[0] = N.Bounds.Maximum.x; K.Maximum[1] = N.Bounds.Maximum.y; K.Maximum[2] = N.Bounds.Maximum.z;
+                        if (N.ChildNodeIndex > 0) { K.FaceBeginOrNodeIndex = NB + N.ChildNodeIndex; K.FaceEndIndex = 0; }
+                        else { K.FaceBeginOrNodeIndex = FB + N.FaceBeginIndex; K.FaceEndIndex = FB + N.FaceEndIndex; }
+                        NP[NB + n] = K;
+                    }
+                }
+            }
+        };
+        const unsigned T = (unsigned)std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), std::max<size_t>(1, Pieces.size() / 4));
+        std::vector<std::thread> Pool;
+        for (unsigned t = 1; t < T; t++) Pool.emplace_back(Work);
+        Work();
+        for (auto& Th : Pool) Th.join();
         Dirty |= SCENE_DIRTY_SHAPES;
     }
 

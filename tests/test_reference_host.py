@@ -223,6 +223,26 @@ def test_build_mesh_node_edge_cases(Ref, faces):
     assert mesh_faces_of(packs[0], 0).tobytes() == mesh_faces_of(packs[1], 0).tobytes()
 
 
+@pytest.mark.parametrize("kind", ["field", "torus"])
+def test_threaded_mesh_build_equals_the_references_sequential_one(Ref, kind):
+    """Large meshes are built on several threads here (host/scene.cpp: subtrees as tasks from 2048 faces per side, the
+    passes of a node cut into pieces from 131 072 faces); nodes, their numbering and the face permutation must still
+    be the reference's, whose BuildMeshNode is one sequential recursion."""
+    p, nrm, uv, f = heightfield(300, 4) if kind == "field" else torus(400, 170)
+    assert len(f) >= 131072
+    packs = []
+    for sc in (S.Scene(), Ref()):
+        m = sc.create_mesh("m", p, nrm, uv, f)
+        sc.create_entity(S.ENTITY_MESH_INSTANCE, mesh=m, position=(0, 0, 1))
+        sc.create_entity(S.ENTITY_CAMERA, position=(0, -3, 1), rotation=(1.5, 0, 0))
+        sc.pack()
+        packs.append(sc)
+    rows_equal("MeshNodePack", packs[0].mesh_nodes, packs[1].mesh_nodes)
+    rows_equal("MeshFacePack", packs[0].mesh_faces, packs[1].mesh_faces)
+    assert packs[0].mesh_info() == packs[1].mesh_info()
+    assert mesh_faces_of(packs[0], 0).tobytes() == mesh_faces_of(packs[1], 0).tobytes()
+
+
 def write_obj(path, two_materials_in_one_shape):
     p, n, uv, f = torus(16, 8)
     q, _, quv, g = heightfield(9, 1)
