@@ -98,6 +98,39 @@ def test_mesh_bvh2_invariants(scenes):
     assert (seen == 1).all()
 
 
+def test_wide_flattening_of_a_large_mesh_on_several_threads(emu, oracle, scenes):
+    """Above 262 144 primitives the host builder cuts the passes of a node into pieces, hands subtrees to other threads
+    and emits the wide tree level by level on all threads (csrc/ptb_wide_build.cpp).  The tree must not depend on the
+    thread schedule, must contain everything below every slot, and its closest hits must be the brute-force ones."""
+    sc = scenes("terrain", 370)                               # 273 800 triangles + the ground plane
+    trees = []
+    for _ in range(2):
+        e = emu.emu_create(C.addressof(sc.view), 16, 16)
+        assert e
+        info = (C.c_uint32 * 5)()
+        emu.emu_wide_info(e, info)
+        assert info[1] == 2 * 370 * 370 and info[2] <= 30
+        nodes, prims = np.zeros((info[0], 20), np.uint32), np.zeros((info[1], 12), np.float32)
+        emu.emu_wide_download(e, nodes.ctypes.data, prims.ctypes.data)
+        trees.append((e, nodes, prims, info[2]))
+    assert trees[0][1].tobytes() == trees[1][1].tobytes() and trees[0][2].tobytes() == trees[1][2].tobytes()
+    from util import check_wide_tree
+    e, nodes, prims, depth = trees[0]
+    assert check_wide_tree(nodes, prims, sc.shapes) == depth
+    rank = prims[:, 11].view(np.uint32) >> 3                  # canonical (shape, face) order, the plane ranked among them
+    key = (prims[:, 7].view(np.uint32).astype(np.uint64) << np.uint64(32)) | prims[:, 3].view(np.uint32).astype(np.uint64)
+    assert len(np.unique(rank)) == len(rank) and np.array_equal(np.argsort(rank), np.argsort(key))
+    n = 400
+    rays = random_rays(sc, n, 33, oracle)
+    from path_tracer_b200.types import HIT_DTYPE
+    out = np.zeros(n, dtype=HIT_DTYPE)
+    emu.emu_raycast(e, rays.ctypes.data, n, 2, out.ctypes.data)
+    bf = oracle.raycast_bruteforce(sc.view, rays)
+    assert ids_equal(out, bf).all() and (out["t"].view(np.uint32) == bf["t"].view(np.uint32)).all()
+    for t in trees:
+        emu.emu_destroy(t[0])
+
+
 @pytest.mark.parametrize("name,params", [("cornell", ()), ("terrain", (48,)), ("room", (1, 256)), ("spherefield", (10, 2, 2))])
 def test_wide_flattening_equals_brute_force(emu, oracle, scenes, name, params):
     """The wide BVH is only a culling structure: its closest hit must be the brute-force
