@@ -131,6 +131,16 @@ def test_wide_flattening_of_a_large_mesh_on_several_threads(emu, oracle, scenes)
         emu.emu_destroy(t[0])
 
 
+def test_random_scenes_traverse_like_brute_force(emu):
+    """A slice of tools/fuzz_traversal.py: random shapes, nested non-uniform transforms, triangle soups, slivers, duplicate
+    and zero-area faces; uniform, axis-parallel, signed-zero and vertex-aimed rays.  The BVH8 hit must be the brute-force
+    hit unless the reference's own traversal loses it too; the reference-layout traversals must equal the oracle's."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import fuzz_traversal
+    assert fuzz_traversal.main(["--scenes", "150", "--rays", "1000", "--seed", "7"]) == 0
+
+
 @pytest.mark.parametrize("name,params", [("cornell", ()), ("terrain", (48,)), ("room", (1, 256)), ("spherefield", (10, 2, 2))])
 def test_wide_flattening_equals_brute_force(emu, oracle, scenes, name, params):
     """The wide BVH is only a culling structure: its closest hit must be the brute-force
