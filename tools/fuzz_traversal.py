@@ -18,11 +18,13 @@ the BVH8 with the product's per-thread device functions compiled for the host (t
 
 A difference from brute force is not fatal when the reference's own traversal (the oracle's, canonical ties) returns
 what we return - its box tests round too, and reject boxes whose exit is <= 0 - or when the brute-force hit is a
-zero-area face accepted on rounding noise; both are counted.  With --extreme (specks of 1e-6 seen from 50 units away:
+zero-area face accepted on rounding noise; both are counted.  With --extreme (specks of 1e-6 seen from 50 units away,
+slivers of aspect 5e5 under nested scales:
 the object-space ray origin is ~1e7 primitive sizes from the primitive, and whether it hits is decided by rounding in
 the reference as well) nothing is fatal and everything is counted.  Otherwise: exit code 1 and the seed of the scene on
-the first difference.  Round 2: 900 000 rays over 600 scenes, 28 differences from brute force (27 shared with the
-reference's traversal, 1 zero-area face) against 1872 for the reference's own traversal; no other difference."""
+the first difference.  Round 2 (seeds 7, 8, 9, 400 scenes x 1000 rays each): 1 200 000 rays, 29 differences from brute
+force (26 shared with the reference's traversal, 3 zero-area faces) against 1866 for the reference's own traversal; no
+other difference."""
 import argparse
 import ctypes as C
 import os
@@ -56,7 +58,7 @@ def load_emu():
     return L
 
 
-def random_mesh(rng):
+def random_mesh(rng, extreme):
     kind = rng.integers(0, 5)
     if kind == 0:                                             # triangle soup
         n = int(rng.integers(1, 400))
@@ -85,7 +87,7 @@ def random_mesh(rng):
     elif kind == 3:                                           # long thin slivers along one axis
         n = int(rng.integers(1, 120))
         base = rng.uniform(-1, 1, size=(n, 3)).astype(np.float32)
-        p = np.concatenate([base, base + np.float32([50, 0, 0]), base + np.float32([50, 1e-4, 0])]).astype(np.float32)
+        p = np.concatenate([base, base + np.float32([50, 0, 0]), base + np.float32([50, 1e-4 if extreme else 1e-2, 0])]).astype(np.float32)
         f = np.stack([np.arange(n), np.arange(n) + n, np.arange(n) + 2 * n], -1).astype(np.uint32)
     else:                                                     # one triangle
         p = rng.normal(size=(3, 3)).astype(np.float32)
@@ -110,14 +112,14 @@ def random_transform(rng, extreme):
     if rng.random() < 0.3:
         scale[:] = s
     if rng.random() < 0.15:
-        scale[rng.integers(0, 3)] *= 1e-3 if extreme else 0.05   # almost flat
+        scale[rng.integers(0, 3)] *= 1e-3 if extreme else 0.2    # flattened
     return tuple(pos), tuple(rot), tuple(scale)
 
 
 def random_scene(S, rng, extreme=False):
     sc = S.Scene()
     mats = [sc.create_material(S.MATERIAL_BASIC_DIFFUSE, "d%d" % k, BaseColor=tuple(rng.uniform(0, 1, 3))) for k in range(3)]
-    meshes = [sc.create_mesh("m%d" % k, *random_mesh(rng)) for k in range(int(rng.integers(0, 4)))]
+    meshes = [sc.create_mesh("m%d" % k, *random_mesh(rng, extreme)) for k in range(int(rng.integers(0, 4)))]
     n = int(rng.integers(0, 14))
     if n == 0 and rng.random() < 0.5:
         n = 1
@@ -127,6 +129,8 @@ def random_scene(S, rng, extreme=False):
         t = rng.integers(0, 6)
         pos, rot, scale = random_transform(rng, extreme)
         if t == 0:
+            if not extreme:                                   # scales multiply down the hierarchy: keep the product in range
+                scale = tuple(rng.uniform(0.5, 2.0, size=3))
             parents.append(sc.create_entity(S.ENTITY_CONTAINER, parent=parent, position=pos, rotation=rot, scale=scale))
         elif t == 1:
             sc.create_entity(S.ENTITY_PLANE, parent=parent, position=pos, rotation=rot, material=mats[k % 3])
