@@ -184,8 +184,10 @@ def main(argv=None):
     ap.add_argument("--scenes", type=int, default=200)
     ap.add_argument("--rays", type=int, default=1500)
     ap.add_argument("--seed", type=int, default=1)
-    ap.add_argument("--near-tie-ulps", type=int, default=16)
+    ap.add_argument("--near-tie-ulps", type=int, default=64)
     ap.add_argument("--extreme", action="store_true", help="include ill-conditioned scenes (see DESIGN section 3): differences are counted, not fatal")
+    ap.add_argument("--gpu", action="store_true", help="on a GPU box: the shipped library through the C ABI (ptb_raycast: the cooperative trace kernel) on the trees "
+                    "of all three builders, instead of the host build of the device functions")
     args = ap.parse_args(argv)
     from oracle import binding as oracle
     from path_tracer_b200 import scene as S
@@ -193,9 +195,11 @@ def main(argv=None):
     from util import check_wide_tree, ids_equal
     oracle.lib()
     S.ensure_spectrum_table()
-    emu = load_emu()
     total_rays = total_hits = 0
     counts = {}
+    if args.gpu:
+        return main_gpu(args, oracle, S, counts)
+    emu = load_emu()
     for k in range(args.scenes):
         seed = args.seed * 100003 + k
         rng = np.random.default_rng(seed)
@@ -278,6 +282,115 @@ def main(argv=None):
         if (k + 1) % 20 == 0:
             print("%d scenes, %d rays (%d hits): all equal" % (k + 1, total_rays, total_hits), flush=True)
     print("done: %d scenes, %d rays (%d hits); beyond exact equality:" % (args.scenes, total_rays, total_hits), counts or "nothing")
+    return 0
+
+
+def zero_area_hit(sc, hits):
+    """Hits on mesh faces of zero area: rounding noise in the reference's triangle test (see the module docstring)."""
+    out = np.zeros(len(hits), bool)
+    if not len(sc.mesh_faces):
+        return out
+    m = (hits["shape"] != 0xFFFFFFFF) & (hits["prim"] < len(sc.mesh_faces))
+    m[m] &= sc.shapes["Type"][hits["shape"][m]] == 0
+    fp = sc.mesh_faces[hits["prim"][m]]
+    e1 = fp["Position1"].astype(np.float64) - fp["Position0"].astype(np.float64)
+    e2 = fp["Position2"].astype(np.float64) - fp["Position0"].astype(np.float64)
+    out[np.flatnonzero(m)] = (np.cross(e1, e2) == 0).all(axis=1)
+    return out
+
+
+def main_gpu(args, oracle, S, counts):
+    """The same scenes and rays through libptb.so on cuda:0."""
+    from path_tracer_b200 import integrator as I
+    from util import check_wide_tree, ids_equal
+    ctx = I.Context(0)
+    total_rays = total_hits = 0
+    builders = (("host SAH", I.BUILDER_SAH_HOST), ("GPU LBVH", I.BUILDER_LBVH_GPU), ("GPU PLOC", I.BUILDER_PLOC_GPU))
+    for k in range(args.scenes):
+        seed = args.seed * 100003 + k
+        rng = np.random.default_rng(seed)
+        sc = random_scene(S, rng, args.extreme)
+        rays = make_rays(sc, rng, oracle, args.rays)
+        bf = oracle.raycast_bruteforce(sc.view, rays)
+        ref_canonical = oracle.raycast(sc.view, rays, tie=oracle.TIE_CANONICAL)
+        ref_faithful = oracle.raycast(sc.view, rays, tie=oracle.TIE_FAITHFUL)
+        first = None
+        for label, which in builders:
+            dev = I.DeviceScene(ctx, sc, builder=which)
+            info = dev.wide_info()
+            if info["status"] != 0:
+                counts[label + ": tree refused"] = counts.get(label + ": tree refused", 0) + 1
+                dev.close()
+                continue
+            if info["node_count"]:
+                nodes, prims = dev.wide_download()
+                try:
+                    check_wide_tree(nodes, prims, sc.shapes)
+                except AssertionError as ex:
+                    print("seed", seed, label, "STRUCTURE", ex)
+                    return 1
+            out = dev.raycast(rays, I.TRAVERSAL_WIDE, I.TIE_CANONICAL)
+            bad = ~(ids_equal(out, bf) & (out["t"].view(np.uint32) == bf["t"].view(np.uint32)))
+            as_reference = bad & ids_equal(out, ref_canonical) & (out["t"].view(np.uint32) == ref_canonical["t"].view(np.uint32))
+            counts[label + ": as the reference's traversal"] = counts.get(label + ": as the reference's traversal", 0) + int(as_reference.sum())
+            bad &= ~as_reference
+            mesh = bad & (bf["shape"] != 0xFFFFFFFF) & (bf["prim"] < max(1, len(sc.mesh_faces)))
+            if mesh.any() and len(sc.mesh_faces):
+                fp = sc.mesh_faces[bf["prim"][mesh]]
+                e1 = fp["Position1"].astype(np.float64) - fp["Position0"].astype(np.float64)
+                e2 = fp["Position2"].astype(np.float64) - fp["Position0"].astype(np.float64)
+                flat = (np.cross(e1, e2) == 0).all(axis=1) & (sc.shapes["Type"][bf["shape"][mesh]] == 0)
+                idx = np.flatnonzero(mesh)[flat]
+                counts[label + ": their hit is a zero-area face"] = counts.get(label + ": their hit is a zero-area face", 0) + len(idx)
+                bad[idx] = False
+            both = bad & (out["shape"] != 0xFFFFFFFF) & (bf["shape"] != 0xFFFFFFFF)
+            ulps = np.abs(out["t"].view(np.int32).astype(np.int64) - bf["t"].view(np.int32).astype(np.int64))
+            near = both & (ulps <= args.near_tie_ulps)
+            if near.any():                                      # printed: these are the cases worth reading
+                counts[label + ": near-ties"] = counts.get(label + ": near-ties", 0) + int(near.sum())
+                for i in np.flatnonzero(near)[:3]:
+                    print("seed", seed, label, "near-tie at ray", int(i), "(%d ulp of t)" % int(ulps[i]), "ours", (out[i]["t"], out[i]["shape"], out[i]["prim"]),
+                          "brute force", (bf[i]["t"], bf[i]["shape"], bf[i]["prim"]))
+                bad &= ~near
+            if bad.any():
+                if args.extreme:
+                    counts[label + ": other"] = counts.get(label + ": other", 0) + int(bad.sum())
+                else:
+                    i = int(np.flatnonzero(bad)[0])
+                    print("seed", seed, label, "vs brute force differs at ray", i, "of", int(bad.sum()), "\n ray", rays[i], "\n ours", out[i], "\n theirs", bf[i])
+                    return 1
+            if first is None:
+                first = out
+            elif first.tobytes() != out.tobytes():
+                # Hits must not depend on who built the tree - except where brute force and the reference's traversal
+                # already disagree (a hit that only a loose enough box lets through: either answer is "the reference's").
+                d = first != out
+                split = ~(ids_equal(bf, ref_canonical) & (bf["t"].view(np.uint32) == ref_canonical["t"].view(np.uint32)))
+                split |= zero_area_hit(sc, first) | zero_area_hit(sc, out) | zero_area_hit(sc, bf)
+                u2 = np.abs(out["t"].view(np.int32).astype(np.int64) - first["t"].view(np.int32).astype(np.int64))
+                split |= (out["shape"] != 0xFFFFFFFF) & (first["shape"] != 0xFFFFFFFF) & (u2 <= args.near_tie_ulps) & (u2 > 0)
+                counts[label + ": differs from the host-built tree's where brute force and the reference's traversal differ or on zero-area faces"] = \
+                    counts.get(label + ": differs from the host-built tree's where brute force and the reference's traversal differ or on zero-area faces", 0) + int((d & split).sum())
+                if (d & ~split).any():
+                    counts[label + ": differs from the host-built tree's"] = counts.get(label + ": differs from the host-built tree's", 0) + int((d & ~split).sum())
+                    if not args.extreme:
+                        i = int(np.flatnonzero(d & ~split)[0])
+                        print("seed", seed, label, "hits differ from the host-built tree's at ray", i, "\n ray", rays[i], "\n host tree", first[i], "\n this tree", out[i], "\n brute", bf[i])
+                        return 1
+            if which == I.BUILDER_SAH_HOST:
+                for trav_tie, ref in ((I.TIE_FAITHFUL, ref_faithful), (I.TIE_CANONICAL, ref_canonical)):
+                    got = dev.raycast(rays, I.TRAVERSAL_BVH2_REFERENCE, trav_tie)
+                    b2 = ~(ids_equal(got, ref) & (got["t"].view(np.uint32) == ref["t"].view(np.uint32)))
+                    if b2.any():
+                        i = int(np.flatnonzero(b2)[0])
+                        print("seed", seed, "REFERENCE-LAYOUT kernel differs from the oracle at ray", i, "of", int(b2.sum()), "\n ray", rays[i], "\n ours", got[i], "\n oracle", ref[i])
+                        return 1
+            dev.close()
+        total_rays += len(rays)
+        total_hits += int((bf["shape"] != 0xFFFFFFFF).sum())
+        if (k + 1) % 20 == 0:
+            print("%d scenes, %d rays (%d hits) x 3 builders" % (k + 1, total_rays, total_hits), flush=True)
+    print("done (GPU, C ABI): %d scenes, %d rays (%d hits), three builders; beyond exact equality:" % (args.scenes, total_rays, total_hits), counts or "nothing")
     return 0
 
 
