@@ -131,6 +131,16 @@ def test_wide_flattening_of_a_large_mesh_on_several_threads(emu, oracle, scenes)
         emu.emu_destroy(t[0])
 
 
+def test_random_scenes_scatter_like_the_oracle(emu):
+    """A slice of tools/fuzz_scatter.py: random materials over their whole parameter range, nested and overlapping
+    dielectrics, media, textured sky, three cameras, every flag combination, path-length limits and termination
+    probabilities - the product's scatter code (host build, same libm) must leave the accumulator the oracle leaves."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import fuzz_scatter
+    assert fuzz_scatter.main(["--scenes", "40", "--seed", "11"]) == 0
+
+
 def test_random_scenes_traverse_like_brute_force(emu):
     """A slice of tools/fuzz_traversal.py: random shapes, nested non-uniform transforms, triangle soups, slivers, duplicate
     and zero-area faces; uniform, axis-parallel, signed-zero and vertex-aimed rays.  The BVH8 hit must be the brute-force

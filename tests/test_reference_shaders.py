@@ -186,3 +186,12 @@ def test_oracle_reproduces_reference_resolve_and_preview_vectors(oracle, case_sc
             img, _, pick = oracle.preview(sc.view, cam["To"].ravel(), cam["From"].ravel(), mode, w, h, brightness=1.25, selected=2, mouse=(20, 17),
                                           tie=oracle.TIE_FAITHFUL)
             assert np.allclose(img, g["%s_mode%d" % (tag, mode)], rtol=1e-6, atol=1e-7) and pick == int(g[tag + "_pick"][0]), (tag, mode)
+
+
+def test_oracle_equals_the_reference_shaders_on_random_scenes(ref):
+    """A slice of tools/fuzz_scatter.py --reference: scenes nobody designed (see its docstring), film and all wavefront
+    state arrays after every round, up to where the reference's medium of a non-dielectric shape becomes undefined."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import fuzz_scatter
+    assert fuzz_scatter.main(["--scenes", "40", "--seed", "12", "--width", "48", "--height", "32", "--reference"]) == 0
