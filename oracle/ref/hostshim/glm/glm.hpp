@@ -306,7 +306,7 @@ inline vec2 unpackSnorm2x16(uint p) {
     const int16_t a = (int16_t)(p & 0xFFFFu), b = (int16_t)(p >> 16);
     return clamp(vec2((float)a, (float)b) * 3.0518509475997192297128208258309e-5f, -1.0f, 1.0f);
 }
-inline uint16_t shim_float_to_half(float f) {            // glm::detail::toFloat16: round to nearest even, overflow to infinity
+inline uint16_t shim_float_to_half(float f) {            // glm::detail::toFloat16: round to nearest, ties away from zero; overflow to infinity
     uint32_t i; std::memcpy(&i, &f, 4);
     int s = (i >> 16) & 0x00008000;
     int e = ((i >> 23) & 0x000000ff) - (127 - 15);

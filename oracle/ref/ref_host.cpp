@@ -121,7 +121,14 @@ double refh_spectrum_lab_error(const float* rgb, const float* beta) {
 }
 
 void* ptbh_scene_create(int with_defaults) { return create_scene(with_defaults != 0); }
-void ptbh_scene_destroy(void* s) { g_views.erase((scene*)s); /* the table is shared: not DestroyScene */ }
+// The table is shared, so not DestroyScene; but the atlas layers (256 MiB each, never freed by the reference: scene.cpp:1140
+// clears the vector of a previous pack without deleting) go, or a fuzz over hundreds of scenes runs out of memory.
+void ptbh_scene_destroy(void* s) {
+    scene* S = (scene*)s;
+    g_views.erase(S);
+    for (image const& I : S->Images) delete[] (glm::vec4*)I.Pixels;
+    S->Images.clear();
+}
 uint32_t ptbh_scene_pack(void* s) { return PackSceneData((scene*)s); }
 void ptbh_scene_mark_dirty(void* s, uint32_t flags) { ((scene*)s)->DirtyFlags |= flags; }
 void ptbh_scene_view(void* s, ptb_scene_view* out) {

@@ -64,15 +64,17 @@ inline mat4 euler_zyx(float rz, float ry, float rx) {
     return m;
 }
 
-// T(position) * R(rotation) * S(scale)   (common.hpp:72-82)
+// T(position) * R(rotation) * S(scale)   (common.hpp:72-82), as the reference computes it: glm::translate and glm::scale of the
+// identity, then two full matrix products.  The values are those of "columns of R times the scale, position in column 3"; what the
+// products add is the SIGN OF ZEROS: a -0 of R (sin of a zero angle, negated) or of a negative scale meets the +0 terms of the sums
+// and comes out +0.  Found by tools/fuzz_pack.py against the reference's own PackSceneData (byte for byte, zeros included).
 inline mat4 make_transform(vec3 position, vec3 rotation, vec3 scale) {
-    mat4 r = euler_zyx(rotation.z, rotation.y, rotation.x);
-    mat4 m;
-    m.c[0] = r.c[0] * scale.x;
-    m.c[1] = r.c[1] * scale.y;
-    m.c[2] = r.c[2] * scale.z;
-    m.c[3] = {position.x, position.y, position.z, 1.0f};
-    return m;
+    const mat4 I = mat4::identity();
+    mat4 t = I;                                              // glm::translate: m[0] v[0] + m[1] v[1] + m[2] v[2] + m[3]
+    t.c[3] = ((I.c[0] * position.x + I.c[1] * position.y) + I.c[2] * position.z) + I.c[3];
+    mat4 sc;                                                 // glm::scale: columns times the factors
+    sc.c[0] = I.c[0] * scale.x; sc.c[1] = I.c[1] * scale.y; sc.c[2] = I.c[2] * scale.z; sc.c[3] = I.c[3];
+    return mul(mul(t, euler_zyx(rotation.z, rotation.y, rotation.x)), sc);
 }
 
 // glm::inverse(mat4) as the reference calls it (scene.hpp:403-406 PackTransform), in glm 1.0.1's operation order:
@@ -124,20 +126,29 @@ inline uint32_t pack_unit_vector(vec3 v) {
     return pack_snorm2x16(px, py);
 }
 // binary32 -> binary16, round to nearest even (glm::packHalf2x16 role).
+// glm::packHalf2x16 (scene.cpp:1297) converts with glm::detail::toFloat16 (glm 1.0.1, detail/type_half.inl): round to nearest with
+// TIES AWAY FROM ZERO ("round 0.5 up" on the magnitude), values below 2^-25 flushed to zero, overflow to infinity - not IEEE
+// round-to-nearest-even.  A tie needs the 13 dropped bits to be exactly 0x1000: one texture coordinate in 8192 for arbitrary floats,
+// every one of the form (2k + 1) / 4096 in [0.5, 1).  Found by tools/fuzz_pack.py against the reference's own PackSceneData.
 inline uint16_t float_to_half(float f) {
-    uint32_t x; std::memcpy(&x, &f, 4);
-    uint32_t s = (x >> 16) & 0x8000u, ax = x & 0x7FFFFFFFu;
-    if (ax >= 0x7F800000u) return (uint16_t)(s | 0x7C00u | (ax > 0x7F800000u ? 0x200u : 0u));
-    if (ax >= 0x477FF000u) return (uint16_t)(s | 0x7C00u);
-    if (ax < 0x33000001u) return (uint16_t)s;
-    int e = (int)(ax >> 23) - 127;
-    uint32_t m = (ax & 0x7FFFFFu) | 0x800000u;
-    int shift = e < -14 ? 13 + (-14 - e) : 13;
-    uint32_t he = e < -14 ? 0u : (uint32_t)(e + 15);
-    uint32_t hm = m >> shift, rem = m & ((1u << shift) - 1u), half = 1u << (shift - 1);
-    if (rem > half || (rem == half && (hm & 1u))) hm++;
-    uint32_t h = he == 0 ? hm : ((he << 10) + (hm - 0x400u));
-    return (uint16_t)(s | h);
+    uint32_t i; std::memcpy(&i, &f, 4);
+    int s = (int)((i >> 16) & 0x00008000u);
+    int e = (int)((i >> 23) & 0x000000ffu) - (127 - 15);
+    int m = (int)(i & 0x007fffffu);
+    if (e <= 0) {
+        if (e < -10) return (uint16_t)s;
+        m = (m | 0x00800000) >> (1 - e);
+        if (m & 0x00001000) m += 0x00002000;
+        return (uint16_t)(s | (m >> 13));
+    }
+    if (e == 0xff - (127 - 15)) {
+        if (m == 0) return (uint16_t)(s | 0x7c00);
+        m >>= 13;
+        return (uint16_t)(s | 0x7c00 | m | (m == 0));
+    }
+    if (m & 0x00001000) { m += 0x00002000; if (m & 0x00800000) { m = 0; e += 1; } }
+    if (e > 30) return (uint16_t)(s | 0x7c00);
+    return (uint16_t)(s | (e << 10) | (m >> 13));
 }
 inline uint32_t pack_half2x16(float x, float y) { return (uint32_t)float_to_half(x) | ((uint32_t)float_to_half(y) << 16); }
 

@@ -356,3 +356,29 @@ def test_spectrum_lookup_and_table_columns(Ref):
             assert e_ours <= e_ref + 1e-3, (i, j, l, k, e_ours, e_ref)      # measured: within 1.6e-4 of the reference's own fit
             worst = max(worst, e_ours - e_ref)
     assert worst <= 1e-3
+
+
+def test_random_scenes_pack_like_the_reference(Ref):
+    """A slice of tools/fuzz_pack.py: the random scenes of the traversal and scatter fuzzers (nested non-uniform transforms,
+    degenerate meshes, every material, odd-sized textures, three cameras) through both host layers, every packed array
+    byte for byte.  It found glm's half conversion (ties away from zero) and the zero signs of T * R * S."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import fuzz_pack
+    assert fuzz_pack.main(["--scenes", "25", "--seed", "3"]) == 0
+
+
+def test_half_conversion_is_glms(Ref):
+    """glm::detail::toFloat16 rounds ties away from zero; IEEE (numpy) rounds them to even."""
+    import ctypes as C
+    L = S.Scene()._L
+    L.ptbh_pack_half2.restype = C.c_uint32
+    L.ptbh_pack_half2.argtypes = [C.c_float, C.c_float]
+    tie_down = np.uint32(0x3F001000).view(np.float32)        # 0.5 + half an ulp of binary16, even mantissa below: IEEE keeps 0x3800
+    tie_up = np.uint32(0x3F003000).view(np.float32)          # odd mantissa below: both go up
+    assert L.ptbh_pack_half2(float(tie_down), float(tie_up)) == (0x3801 | (0x3802 << 16))
+    assert int(np.float16(tie_down).view(np.uint16)) == 0x3800
+    rng = np.random.default_rng(1)
+    for v in rng.uniform(-3, 3, 2000).astype(np.float32):    # away from ties the two agree
+        if (int(v.view(np.uint32)) & 0x1FFF) != 0x1000:
+            assert (L.ptbh_pack_half2(float(v), 0.0) & 0xFFFF) == int(np.float16(v).view(np.uint16))

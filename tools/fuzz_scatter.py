@@ -73,9 +73,9 @@ def random_material(sc, S, rng, k, tex_r, tex_raw, unit_ior=True):
                               ScatteringAnisotropy=float(rng.choice([0.0, -0.8, 0.3, 0.9])), textures=tx or None)
 
 
-def random_scene(S, rng, unit_ior=True):
+def random_scene(S, rng, unit_ior=True, make=None):
     import fuzz_traversal as FT
-    sc = S.Scene()
+    sc = (make or S.Scene)()
     tex_r = [random_texture(sc, S, rng, k, S.TEXTURE_REFLECTANCE_WITH_ALPHA) for k in range(int(rng.integers(0, 3)))]
     tex_raw = [random_texture(sc, S, rng, 10 + k, S.TEXTURE_RAW) for k in range(int(rng.integers(0, 3)))]
     sky = random_texture(sc, S, rng, 20, S.TEXTURE_RADIANCE) if rng.random() < 0.5 else None

@@ -116,8 +116,8 @@ def random_transform(rng, extreme):
     return tuple(pos), tuple(rot), tuple(scale)
 
 
-def random_scene(S, rng, extreme=False):
-    sc = S.Scene()
+def random_scene(S, rng, extreme=False, make=None):
+    sc = (make or S.Scene)()
     mats = [sc.create_material(S.MATERIAL_BASIC_DIFFUSE, "d%d" % k, BaseColor=tuple(rng.uniform(0, 1, 3))) for k in range(3)]
     meshes = [sc.create_mesh("m%d" % k, *random_mesh(rng, extreme)) for k in range(int(rng.integers(0, 4)))]
     n = int(rng.integers(0, 14))
