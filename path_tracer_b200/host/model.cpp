@@ -5,7 +5,7 @@
 // pair, shapes recentred on their bounding-box centre, exact-match vertex welding,
 // BuildMeshNode per mesh, single mesh entity or container prefab).  The reference reads
 // the file with tinyobjloader (un-vendored dependency semantics: 1-based / negative
-// indices, `v/vt/vn` corners, polygons split as a fan, `o`/`g` start a shape, `usemtl`
+// indices, `v/vt/vn` corners, polygons triangulated as tinyobjloader does (triangulate() below), `o`/`g` start a shape, `usemtl`
 // selects the material, `mtllib` names the material file); the subset of that format
 // meshes actually use is parsed here directly.  Differences, all deliberate:
 //   * materials become BasicDiffuse (BaseColor = Kd, BaseTexture = map_Kd): the reference
@@ -39,6 +39,82 @@ namespace {
 struct corner { int v = -1, vt = -1, vn = -1; };
 struct obj_shape { std::string name; std::vector<corner> corners; std::vector<int> material_ids; };   // 3 corners per face
 struct obj_material { std::string name; float kd[3] = {0.6f, 0.6f, 0.6f}; float ke[3] = {0, 0, 0}; std::string map_kd, map_ke; };
+
+// Polygons become triangles the way the reference's loader makes them (tinyobjloader 2.0.0rc, "simple" method,
+// tiny_obj_loader.h:1509-1964; float arithmetic): which triangles come out decides face numbering and shading, so a fan is
+// not good enough.  Found by tools/fuzz_obj.py against the reference's own LoadModelAsPrefab.
+//  * a quad is cut along its SHORTER diagonal: (0,1,2)(0,2,3) if |p2-p0|^2 < |p3-p1|^2, else (0,1,3)(1,2,3);
+//  * a larger polygon is ear-clipped in the plane of the two axes other than the dominant one of its first non-degenerate
+//    corner: starting at vertex 0, a corner (g, g+1, g+2) is an ear if its turn has the sign of the "area" term
+//    x0*y1 - y0*x1 (the loader's test, kept literally) and no other remaining vertex is inside it (crossing-number test);
+//    an ear is emitted and its middle vertex removed, otherwise g advances; the search gives up after one fruitless
+//    round, so a polygon can yield FEWER than n - 2 triangles; the last three vertices are emitted as they are.
+int crossing_number(const float* vx, const float* vy, float tx, float ty) {
+    int c = 0;
+    for (int i = 0, j = 2; i < 3; j = i++)
+        if (((vy[i] > ty) != (vy[j] > ty)) && (tx < (vx[j] - vx[i]) * (ty - vy[i]) / (vy[j] - vy[i]) + vx[i])) c = !c;
+    return c;
+}
+
+void triangulate(const std::vector<corner>& poly, const std::vector<float>& P, std::vector<corner>& out) {
+    const size_t n = poly.size();
+    auto pos = [&](const corner& c, int a) { return P[3 * (size_t)c.v + a]; };
+    if (n == 3) { out.insert(out.end(), poly.begin(), poly.end()); return; }
+    if (n == 4) {
+        float d02 = 0.0f, d13 = 0.0f;
+        for (int a = 0; a < 3; a++) {
+            const float e02 = pos(poly[2], a) - pos(poly[0], a), e13 = pos(poly[3], a) - pos(poly[1], a);
+            d02 = a == 0 ? e02 * e02 : d02 + e02 * e02;
+            d13 = a == 0 ? e13 * e13 : d13 + e13 * e13;
+        }
+        const int pick[2][6] = {{0, 1, 2, 0, 2, 3}, {0, 1, 3, 1, 2, 3}};
+        for (int k = 0; k < 6; k++) out.push_back(poly[pick[d02 < d13 ? 0 : 1][k]]);
+        return;
+    }
+    // the two working axes
+    int ax0 = 1, ax1 = 2;
+    for (size_t k = 0; k < n; k++) {
+        const corner &a = poly[k % n], &b = poly[(k + 1) % n], &c = poly[(k + 2) % n];
+        const float e0x = pos(b, 0) - pos(a, 0), e0y = pos(b, 1) - pos(a, 1), e0z = pos(b, 2) - pos(a, 2);
+        const float e1x = pos(c, 0) - pos(b, 0), e1y = pos(c, 1) - pos(b, 1), e1z = pos(c, 2) - pos(b, 2);
+        const float cx = std::fabs(e0y * e1z - e0z * e1y), cy = std::fabs(e0z * e1x - e0x * e1z), cz = std::fabs(e0x * e1y - e0y * e1x);
+        const float eps = std::numeric_limits<float>::epsilon();
+        if (cx > eps || cy > eps || cz > eps) {
+            if (!(cx > cy && cx > cz)) {
+                ax0 = 0;
+                if (cz > cx && cz > cy) ax1 = 1;
+            }
+            break;
+        }
+    }
+    std::vector<corner> rest = poly;
+    size_t guess = 0, tries = n, last_count = n;
+    while (rest.size() > 3 && tries > 0) {
+        const size_t m = rest.size();
+        if (guess >= m) guess -= m;
+        if (last_count != m) { last_count = m; tries = m; } else tries--;
+        corner tri[3];
+        float vx[3], vy[3];
+        for (int k = 0; k < 3; k++) {
+            tri[k] = rest[(guess + k) % m];
+            vx[k] = pos(tri[k], ax0);
+            vy[k] = pos(tri[k], ax1);
+        }
+        const float e0x = vx[1] - vx[0], e0y = vy[1] - vy[0], e1x = vx[2] - vx[1], e1y = vy[2] - vy[1];
+        const float turn = e0x * e1y - e0y * e1x;
+        const float area = (vx[0] * vy[1] - vy[0] * vx[1]) * 0.5f;
+        if (turn * area < 0.0f) { guess++; continue; }
+        bool inside = false;
+        for (size_t o = 3; o < m && !inside; o++) {
+            const corner& q = rest[(guess + o) % m];
+            inside = crossing_number(vx, vy, pos(q, ax0), pos(q, ax1)) != 0;
+        }
+        if (inside) { guess++; continue; }
+        out.insert(out.end(), tri, tri + 3);
+        rest.erase(rest.begin() + (std::ptrdiff_t)((guess + 1) % m));
+    }
+    if (rest.size() == 3) out.insert(out.end(), rest.begin(), rest.end());
+}
 
 std::string dir_of(const std::string& p) {
     size_t s = p.find_last_of("/\\");
@@ -171,10 +247,9 @@ prefab* LoadModelAsPrefab(scene* Scene, char const* Path, load_model_options* Op
             }
             if (!good || poly.size() < 3) continue;
             obj_shape& S = Shapes.back();
-            for (size_t k = 1; k + 1 < poly.size(); k++) {            // triangle fan
-                S.corners.push_back(poly[0]); S.corners.push_back(poly[k]); S.corners.push_back(poly[k + 1]);
-                S.material_ids.push_back(CurrentMaterial);
-            }
+            const size_t before = S.corners.size();
+            triangulate(poly, Positions, S.corners);
+            for (size_t k = before; k < S.corners.size(); k += 3) S.material_ids.push_back(CurrentMaterial);
         } else if (key == "o" || key == "g") {
             std::string name = rest_of(ss);
             if (Shapes.back().corners.empty()) Shapes.back().name = name;
@@ -195,8 +270,8 @@ prefab* LoadModelAsPrefab(scene* Scene, char const* Path, load_model_options* Op
                 vec3 P[3];
                 for (int j = 0; j < 3; j++) { const float* p = &Positions[3 * (size_t)S.corners[i + j].v]; P[j] = {p[0], p[1], p[2]}; }
                 vec3 C = cross3(P[1] - P[0], P[2] - P[0]);
-                float L = length3(C);
-                vec3 N = C / L;                                        // glm::normalize: NaN for a degenerate face, like the reference
+                vec3 N = C * (1.0f / std::sqrt(dot3(C, C)));           // glm::normalize is v * inversesqrt(dot(v, v)), not v / length: NaN for a
+                                                                       // degenerate face, like the reference
                 for (int j = 0; j < 3; j++) {
                     corner& K = S.corners[i + j];
                     K.vn = K.v;

@@ -382,3 +382,30 @@ def test_half_conversion_is_glms(Ref):
     for v in rng.uniform(-3, 3, 2000).astype(np.float32):    # away from ties the two agree
         if (int(v.view(np.uint32)) & 0x1FFF) != 0x1000:
             assert (L.ptbh_pack_half2(float(v), 0.0) & 0xFFFF) == int(np.float16(v).view(np.uint16))
+
+
+def test_random_obj_files_import_like_the_reference(Ref):
+    """A slice of tools/fuzz_obj.py: random Wavefront files (quads, larger polygons, relative indices, several shapes and
+    materials, with and without normals) through both importers.  It found tinyobjloader's triangulation (quads along the
+    shorter diagonal, ear clipping beyond) and glm's normalize (v * inversesqrt) in the generated normals."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import fuzz_obj
+    assert fuzz_obj.main(["--files", "60", "--seed", "2"]) == 0
+
+
+def test_quad_is_cut_along_its_shorter_diagonal(tmp_path):
+    """tiny_obj_loader.h:1510-1602: (0,1,2)(0,2,3) if |p2-p0|^2 < |p3-p1|^2, else (0,1,3)(1,2,3)."""
+    for k, (p3, want) in enumerate((((0.0, 1.0, 0.0), [(0, 1, 3), (1, 2, 3)]),          # square: equal diagonals -> second form
+                                    ((-2.0, 1.0, 0.0), [(0, 1, 2), (0, 2, 3)]))):         # p3 far away: diagonal 1-3 is the long one
+        path = str(tmp_path / ("q%d.obj" % k))
+        with open(path, "w") as o:
+            o.write("v 0 0 0\nv 1 0 0\nv 1 1 0\nv %g %g %g\nvn 0 0 1\nf 1//1 2//1 3//1 4//1\n" % p3)
+        sc = S.Scene()
+        sc.load_model(path)
+        v = sc.source_mesh_vertices(0)[:, :3]
+        src = np.array([[0, 0, 0], [1, 0, 0], [1, 1, 0], p3], np.float32)
+        centre = (src.min(0) + src.max(0)) / 2                 # shapes are recentred (scene.cpp:742-768)
+        index_of = {tuple(np.round(p - centre, 5)): i for i, p in enumerate(src)}
+        faces = sorted(tuple(sorted(index_of[tuple(np.round(v[i], 5))] for i in f)) for f in mesh_faces_of(sc, 0))
+        assert faces == sorted(tuple(sorted(f)) for f in want), (k, faces)
