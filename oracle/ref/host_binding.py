@@ -32,18 +32,21 @@ def build(force=False):
         if os.path.exists(LIB):
             return LIB
         raise RuntimeError("oracle/_ref: %s is not here and no prebuilt libref_host.so travelled with the repository" % REFERENCE_SRC)
-    deps = [os.path.join(HERE, "ref_host.cpp"), os.path.join(HERE, "hostgen.py"), os.path.join(HERE, "hostshim", "glm", "glm.hpp"),
+    deps = [os.path.join(HERE, "ref_host.cpp"), os.path.join(HERE, "ref_serializer.cpp"), os.path.join(HERE, "hostgen.py"), os.path.join(HERE, "hostshim", "glm", "glm.hpp"),
             os.path.join(HERE, "hostshim", "core", "vulkan.hpp"), os.path.join(ROOT, "include", "ptb.h")]
     if force or not os.path.exists(LIB) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in deps):
         gen = os.path.join(OUT, "gen")
         os.makedirs(gen, exist_ok=True)
         subprocess.check_call([sys.executable, os.path.join(HERE, "hostgen.py"), REFERENCE_SRC, gen])
-        cmd = ["g++", "-std=c++20", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared", "-fpermissive", "-w",
-               "-I", os.path.join(HERE, "hostshim"), "-I", gen, "-I", REFERENCE_SRC, "-I", os.path.join(ROOT, "include"),
-               "-o", LIB, os.path.join(HERE, "ref_host.cpp")]
-        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
-        if r.returncode != 0:
-            raise RuntimeError("oracle/_ref host build failed:\n" + r.stdout)
+        flags = ["-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-fpermissive", "-w", "-I", os.path.join(HERE, "hostshim"), "-I", gen, "-I", REFERENCE_SRC,
+                 "-I", os.path.join(ROOT, "include")]
+        miniz, ser = os.path.join(gen, "miniz.o"), os.path.join(gen, "ref_serializer.o")
+        for cmd in (["gcc", "-O2", "-fPIC", "-w", "-c", "-o", miniz, os.path.join(REFERENCE_SRC, "core", "miniz.c")],
+                    ["g++", "-std=c++20"] + flags + ["-c", "-o", ser, os.path.join(HERE, "ref_serializer.cpp")],
+                    ["g++", "-std=c++20"] + flags + ["-shared", "-o", LIB, os.path.join(HERE, "ref_host.cpp"), ser, miniz]):
+            r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+            if r.returncode != 0:
+                raise RuntimeError("oracle/_ref host build failed:\n" + r.stdout)
     return LIB
 
 
@@ -85,6 +88,21 @@ def ref_scene_class():
             if not self.h:
                 raise RuntimeError("reference scene creation failed")
             self._view = None
+
+        @classmethod
+        def load(cls, path):
+            """The reference's LoadScene (serializer.cpp:501-516)."""
+            h = lib().ptbh_load_scene(os.fsencode(path))
+            if not h:
+                raise OSError("the reference's LoadScene failed on " + str(path))
+            sc = cls.__new__(cls)
+            sc._L, sc.h, sc._view = lib(), h, None
+            return sc
+
+        def save(self, path):
+            """The reference's SaveScene (serializer.cpp:518-529)."""
+            if self._L.ptbh_save_scene(self.h, os.fsencode(path)) != 0:
+                raise OSError("the reference's SaveScene failed on " + str(path))
 
         def set_atlas_size(self, w, h):
             assert (w, h) == (4096, 4096), "the reference's atlas size is a constant (scene.cpp:1122-1123)"

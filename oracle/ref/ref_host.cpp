@@ -28,6 +28,8 @@ static inline int fopen_s(FILE** f, const char* path, const char* mode) { *f = s
 #include "core/stb_rect_pack.h"
 #define TINYOBJLOADER_IMPLEMENTATION
 #include "core/tiny_obj_loader.h"
+// LoadScene / SaveScene come from ref_serializer.cpp (the reference's serializer.cpp wants scene.hpp with
+// SERIALIZER_IMPLEMENTATION defined: its own translation unit), miniz from the reference's miniz.c compiled as C.
 
 #include "ptb.h"
 
@@ -118,6 +120,15 @@ double refh_spectrum_lab_error(const float* rgb, const float* beta) {
     dvec3 lab0 = XYZToLab(ObserveSpectrumUnderD65(dvec3(B0, B1, B2)));
     dvec3 lab1 = XYZToLab(dvec3(SRGBToXYZ(vec3(rgb[0], rgb[1], rgb[2]))));
     return glm::length(lab0 - lab1);
+}
+
+// LoadScene / SaveScene of the reference (serializer.cpp:501-529).  A loaded scene brings its own spectrum table (spectrum.dat
+// beside the scene file); everything else here shares g_table, so the loaded copy replaces nothing and is simply kept.
+void* ptbh_load_scene(const char* path) {
+    try { return LoadScene(path); } catch (...) { return nullptr; }
+}
+int ptbh_save_scene(void* s, const char* path) {
+    try { SaveScene(path, (scene*)s); return 0; } catch (...) { return -1; }
 }
 
 void* ptbh_scene_create(int with_defaults) { return create_scene(with_defaults != 0); }

@@ -13,7 +13,7 @@
 //     scene it saved cannot be rendered after loading.  Here a third block {u32 count, vertices}
 //     follows the two the reference reads; a file without it fails to load with a clear error.
 //   * the size prefix is `mz_ulong` = unsigned long (:18,27): 4 bytes where the reference builds
-//     (MSVC), 8 on LP64.  Written as 4 bytes, read as either (told apart by plausibility).
+//     (MSVC), 8 on LP64.  Written as 4 bytes (8 with PTB_SCENE_FILE_SIZE_PREFIX=8), read as either (told apart by plausibility).
 //   * Root.SkyboxSamplingProbability is not saved (:342-349); written here as an extra key.
 #include "scene.hpp"
 
@@ -24,6 +24,7 @@
 #include <charconv>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <map>
@@ -189,8 +190,10 @@ void write_compressed(std::ostream& out, const void* data, size_t size) {
     uLongf n = compressBound((uLong)size);
     std::vector<unsigned char> buf(n);
     if (compress(buf.data(), &n, (const Bytef*)data, (uLong)size) != Z_OK) throw std::runtime_error("scene file: compression failed");
-    const uint32_t n32 = (uint32_t)n;
-    out.write((const char*)&n32, 4);
+    // PTB_SCENE_FILE_SIZE_PREFIX=8: the prefix an LP64 build of the reference writes and expects (tests exchange files with one).
+    const char* width = std::getenv("PTB_SCENE_FILE_SIZE_PREFIX");
+    if (width && std::atoi(width) == 8) { const uint64_t n64 = (uint64_t)n; out.write((const char*)&n64, 8); }
+    else { const uint32_t n32 = (uint32_t)n; out.write((const char*)&n32, 4); }
     out.write((const char*)buf.data(), n);
 }
 void read_compressed(std::istream& in, void* data, size_t size, size_t file_size) {

@@ -409,3 +409,54 @@ def test_quad_is_cut_along_its_shorter_diagonal(tmp_path):
         index_of = {tuple(np.round(p - centre, 5)): i for i, p in enumerate(src)}
         faces = sorted(tuple(sorted(index_of[tuple(np.round(v[i], 5))] for i in f)) for f in mesh_faces_of(sc, 0))
         assert faces == sorted(tuple(sorted(f)) for f in want), (k, faces)
+
+
+def test_scene_files_are_interchangeable_with_the_reference(Ref, tmp_path, monkeypatch):
+    """LoadScene / SaveScene (serializer.cpp:501-529) of the reference itself - its serializer.cpp, json.hpp and miniz compiled
+    into oracle/_ref/libref_host.so - against host/serializer.cpp: a scene saved by either is loaded by both, and all four
+    packed results equal the original's, byte for byte.  Three limits, all the reference's: it does not save mesh vertices
+    (serializer.cpp:294-295), so scenes with meshes cannot go through it at all; it does not save SkyboxSamplingProbability
+    (:342-349); and its size prefix is `unsigned long`, 8 bytes in this LP64 build and 4 where the reference is built (MSVC) -
+    the product writes 4 by default and 8 on request, and reads both."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import fuzz_pack
+    import fuzz_scatter
+    monkeypatch.setenv("PTB_SCENE_FILE_SIZE_PREFIX", "8")
+    Ours, Theirs = fuzz_pack.plain_cameras(S.Scene, S), fuzz_pack.plain_cameras(Ref, S)
+    done = 0
+    for seed in range(40):
+        pair = []
+        for make in (Ours, Theirs):
+            sc, _ = fuzz_scatter.random_scene(S, np.random.default_rng(900 + seed), make=make, with_meshes=False)
+            pair.append(sc)
+        if float(pair[0].globals["SkyboxSamplingProbability"]) != 0.0:
+            continue
+        compare_packs(*pair)
+        d = tmp_path / ("s%d" % seed)
+        (d / "ours").mkdir(parents=True)
+        (d / "theirs").mkdir(parents=True)
+        pair[0].save(str(d / "ours" / "scene.json"))
+        pair[1].save(str(d / "theirs" / "scene.json"))
+        for written_by in ("ours", "theirs"):
+            a = S.Scene.load(str(d / written_by / "scene.json"))
+            b = Ref.load(str(d / written_by / "scene.json"))
+            a.pack(), b.pack()
+            compare_packs(a, pair[1])
+            compare_packs(pair[0], b)
+            for sc in (a, b):
+                sc.close()
+        for sc in pair:
+            sc.close()
+        done += 1
+        if done == 8:
+            break
+    assert done == 8
+    # the default prefix is the 4-byte one of the reference's own platform; the product reads it back
+    monkeypatch.delenv("PTB_SCENE_FILE_SIZE_PREFIX")
+    sc, _ = fuzz_scatter.random_scene(S, np.random.default_rng(5), make=Ours, with_meshes=True)
+    sc.save(str(tmp_path / "four" / "scene.json"))
+    back = S.Scene.load(str(tmp_path / "four" / "scene.json"))
+    back.pack()
+    for name in ("shapes", "shape_nodes", "mesh_faces", "mesh_vertices", "mesh_nodes", "cameras", "materials"):
+        assert getattr(back, name).tobytes() == getattr(sc, name).tobytes(), name

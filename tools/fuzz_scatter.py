@@ -73,7 +73,7 @@ def random_material(sc, S, rng, k, tex_r, tex_raw, unit_ior=True):
                               ScatteringAnisotropy=float(rng.choice([0.0, -0.8, 0.3, 0.9])), textures=tx or None)
 
 
-def random_scene(S, rng, unit_ior=True, make=None):
+def random_scene(S, rng, unit_ior=True, make=None, with_meshes=True):
     import fuzz_traversal as FT
     sc = (make or S.Scene)()
     tex_r = [random_texture(sc, S, rng, k, S.TEXTURE_REFLECTANCE_WITH_ALPHA) for k in range(int(rng.integers(0, 3)))]
@@ -83,7 +83,7 @@ def random_scene(S, rng, unit_ior=True, make=None):
                 sky_sampling_probability=float(rng.choice([0.0, 0.0, 0.3, 0.9])) if sky is not None else float(rng.choice([0.0, 0.5])), sky_texture=sky)
     mats = [random_material(sc, S, rng, k, tex_r, tex_raw, unit_ior) for k in range(int(rng.integers(1, 6)))]
     mat = lambda: mats[rng.integers(0, len(mats))]
-    meshes = [sc.create_mesh("m%d" % k, *FT.random_mesh(rng, False)) for k in range(int(rng.integers(0, 3)))]
+    meshes = [sc.create_mesh("m%d" % k, *FT.random_mesh(rng, False)) for k in range(int(rng.integers(0, 3)) if with_meshes else 0)]
     if rng.random() < 0.7:
         sc.create_entity(S.ENTITY_PLANE, position=(0, 0, float(rng.uniform(-2, 0))), material=mat())
     for k in range(int(rng.integers(1, 9))):
