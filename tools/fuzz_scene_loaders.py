@@ -3,7 +3,7 @@
     cd path_tracer_b200/host && g++ -std=c++17 -O1 -g -fsanitize=address,undefined -pthread -I . -I ../../include -o /tmp/asan_host \
         ../../tools/fuzz_scene_loaders_main.cpp scene.cpp pack.cpp spectrum.cpp procedural.cpp model.cpp image.cpp serializer.cpp -lz
     python tools/fuzz_scene_loaders.py
-Round 2: 2000 mutated OBJ files and 1500 mutated scene files, no sanitizer report (one finding fixed: enumerators read from a
+Round 2: 2000 + 2100 (polygon-rich seeds) mutated OBJ files and 1500 mutated scene files, no sanitizer report (one finding fixed: enumerators read from a
 scene file are range-checked now)."""
 import sys, os, numpy as np, tempfile, subprocess
 sys.path.insert(0,"/root/repo"); sys.path.insert(0,"/root/repo/tests")
@@ -40,5 +40,11 @@ def run(kind, seed, ext, n, textual):
         print(kind, r.stdout.strip())
     return bad
 b1=run("obj",obj,".obj",2000,True)
+# quads and larger polygons (the triangulation of host/model.cpp), relative indices, several shapes and materials
+sys.path.insert(0,"/root/repo/tools")
+import fuzz_obj
+for k in range(3):
+    fuzz_obj.write_random_obj(os.path.join(d,"p%d.obj"%k), np.random.default_rng(40+k))
+    b1+=run("obj",open(os.path.join(d,"p%d.obj"%k),"rb").read(),".obj",700,True)
 b2=run("scene",js,".json",1500,True)
 print("bad",b1,b2)
