@@ -10,7 +10,7 @@
 //          "depth_scale_table", "compute_transparency").
 //   * Radiance .hdr (RGBE, "#?RADIANCE" / "#?RGBE", FORMAT=32-bit_rle_rgbe, "-Y h +X w"):
 //          new-style per-channel run-length scanlines and flat pixels; rgb = mantissa * 2^(e-136), alpha 1.
-//   * JPEG (ITU T.81) baseline and progressive Huffman, 8-bit, 1 or 3 components, any sampling factors the
+//   * JPEG (ITU T.81) baseline and progressive Huffman, 8-bit, 1, 3 or 4 (CMYK / YCCK) components, any sampling factors the
 //          decoder below can upsample (1x1, 2x1, 1x2, 2x2 and generic integer factors).  stb_image's integer
 //          IDCT, its triangle-filter chroma upsampling and its 20-bit fixed-point YCbCr conversion are
 //          followed so that 8-bit output is identical with the reference's.
@@ -666,7 +666,7 @@ bool jpeg_frame_header(jpeg_decoder& j) {
     j.height = j.get16(); j.width = j.get16();
     if (j.height == 0 || j.width == 0) return false;
     const int c = j.get8();
-    if (c != 1 && c != 3) return false;           // CMYK / YCCK are not texture formats the reference's scenes use
+    if (c != 1 && c != 3 && c != 4) return false;   // 4: CMYK / YCCK with the Adobe marker, combined as stb_image combines them
     j.ncomp = c;
     if (Lf != 8 + 3 * c) return false;
     for (int i = 0; i < c; i++) {
@@ -895,7 +895,7 @@ bool decode_jpeg(const std::vector<u8>& file, int& W, int& H, std::vector<u8>& r
     // upsample to full resolution and convert to RGB
     W = j.width; H = j.height;
     rgba.resize((size_t)W * H * 4);
-    struct resample { jpeg_resample_fn fn; u8 *line0, *line1; int hs, vs, w_lores, ystep, ypos; std::vector<u8> buf; } rs[3];
+    struct resample { jpeg_resample_fn fn; u8 *line0, *line1; int hs, vs, w_lores, ystep, ypos; std::vector<u8> buf; } rs[4];
     for (int k = 0; k < j.ncomp; k++) {
         resample& r = rs[k];
         r.buf.assign((size_t)W + 3, 0);
@@ -910,10 +910,24 @@ bool decode_jpeg(const std::vector<u8>& file, int& W, int& H, std::vector<u8>& r
         else if (r.hs == 2 && r.vs == 2) r.fn = jpeg_resample_hv2;
         else r.fn = jpeg_resample_generic;
     }
-    const bool is_rgb = j.ncomp == 3 && (j.app14_transform == 0 || (j.app14_transform < 0 && !j.jfif &&
-                                          j.comp[0].id == 'R' && j.comp[1].id == 'G' && j.comp[2].id == 'B'));
+    // stb_image: three components are RGB as they are if their ids spell "RGB", or if an Adobe marker says "no transform" and
+    // there is no JFIF marker; four are CMYK (transform 0), YCCK (transform 2) or YCbCr plus a channel that is ignored.
+    const bool ids_rgb = j.ncomp == 3 && j.comp[0].id == 'R' && j.comp[1].id == 'G' && j.comp[2].id == 'B';
+    const bool is_rgb = j.ncomp == 3 && (ids_rgb || (j.app14_transform == 0 && !j.jfif));
+    auto blinn = [](int x, int m) { const unsigned t = (unsigned)x * (unsigned)m + 128u; return (u8)((t + (t >> 8)) >> 8); };
+    auto ycbcr_row = [](u8* o, const u8* yr, const u8* cbr, const u8* crr, int count) {
+        for (int x = 0; x < count; x++) {
+            const int yf = (yr[x] << 20) + (1 << 19);
+            const int cr = crr[x] - 128, cb = cbr[x] - 128;
+            int r = yf + cr * (int)(1.40200f * 4096.0f + 0.5f) * 256;
+            int gch = yf + cr * -((int)(0.71414f * 4096.0f + 0.5f) * 256) + ((cb * -((int)(0.34414f * 4096.0f + 0.5f) * 256)) & 0xffff0000);
+            int b = yf + cb * (int)(1.77200f * 4096.0f + 0.5f) * 256;
+            r >>= 20; gch >>= 20; b >>= 20;
+            o[4 * x] = jpeg_clamp(r); o[4 * x + 1] = jpeg_clamp(gch); o[4 * x + 2] = jpeg_clamp(b); o[4 * x + 3] = 255;
+        }
+    };
     for (int y = 0; y < H; y++) {
-        u8* rows[3] = {nullptr, nullptr, nullptr};
+        u8* rows[4] = {nullptr, nullptr, nullptr, nullptr};
         for (int k = 0; k < j.ncomp; k++) {
             resample& r = rs[k];
             const bool y_bot = r.ystep >= (r.vs >> 1);
@@ -929,16 +943,18 @@ bool decode_jpeg(const std::vector<u8>& file, int& W, int& H, std::vector<u8>& r
             for (int x = 0; x < W; x++) { o[4 * x] = o[4 * x + 1] = o[4 * x + 2] = rows[0][x]; o[4 * x + 3] = 255; }
         } else if (is_rgb) {
             for (int x = 0; x < W; x++) { o[4 * x] = rows[0][x]; o[4 * x + 1] = rows[1][x]; o[4 * x + 2] = rows[2][x]; o[4 * x + 3] = 255; }
-        } else {
+        } else if (j.ncomp == 4 && j.app14_transform == 0) {             // CMYK: each ink times black
             for (int x = 0; x < W; x++) {
-                const int yf = (rows[0][x] << 20) + (1 << 19);
-                const int cr = rows[2][x] - 128, cb = rows[1][x] - 128;
-                int r = yf + cr * (int)(1.40200f * 4096.0f + 0.5f) * 256;
-                int gch = yf + cr * -((int)(0.71414f * 4096.0f + 0.5f) * 256) + ((cb * -((int)(0.34414f * 4096.0f + 0.5f) * 256)) & 0xffff0000);
-                int b = yf + cb * (int)(1.77200f * 4096.0f + 0.5f) * 256;
-                r >>= 20; gch >>= 20; b >>= 20;
-                o[4 * x] = jpeg_clamp(r); o[4 * x + 1] = jpeg_clamp(gch); o[4 * x + 2] = jpeg_clamp(b); o[4 * x + 3] = 255;
+                const int m = rows[3][x];
+                o[4 * x] = blinn(rows[0][x], m); o[4 * x + 1] = blinn(rows[1][x], m); o[4 * x + 2] = blinn(rows[2][x], m); o[4 * x + 3] = 255;
             }
+        } else {
+            ycbcr_row(o, rows[0], rows[1], rows[2], W);
+            if (j.ncomp == 4 && j.app14_transform == 2)                 // YCCK: the complement of the converted colour times black
+                for (int x = 0; x < W; x++) {
+                    const int m = rows[3][x];
+                    o[4 * x] = blinn(255 - o[4 * x], m); o[4 * x + 1] = blinn(255 - o[4 * x + 1], m); o[4 * x + 2] = blinn(255 - o[4 * x + 2], m);
+                }
         }
     }
     return true;

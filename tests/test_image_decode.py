@@ -339,3 +339,61 @@ def test_bmp_16_bit_bitfields_4_bit_and_top_down(tmp_path):
     idx8 = rng.integers(0, 252, size=(h, w)).astype(np.uint8)      # (stb_image reads only 252 entries of a 12-byte-header file's palette)
     (tmp_path / "g.bmp").write_bytes(bmp(8, [r.tobytes() for r in idx8], palette=pal3.tobytes(), hsz=12))
     same(tmp_path / "g.bmp")
+
+
+def patch_adobe_transform(data, value):
+    """Sets (or inserts, after SOI) an Adobe APP14 marker with the given colour-transform byte."""
+    at = data.find(b"\xff\xee")
+    if at >= 0 and data[at + 4:at + 9] == b"Adobe":
+        return data[:at + 15] + bytes([value]) + data[at + 16:]
+    return data[:2] + b"\xff\xee\x00\x0eAdobe\x00\x64\x00\x00\x00\x00" + bytes([value]) + data[2:]
+
+
+def strip_jfif(data):
+    at = data.find(b"\xff\xe0")
+    if at < 0 or data[at + 4:at + 8] != b"JFIF":
+        return data
+    n = struct.unpack(">H", data[at + 2:at + 4])[0]
+    return data[:at] + data[at + 2 + n:]
+
+
+@pytest.mark.parametrize("case", ["cmyk", "ycck", "four-unknown-transform", "rgb-by-adobe-no-jfif", "adobe-0-with-jfif", "adobe-1", "ids-RGB"])
+def test_jpeg_adobe_marker_and_four_components(tmp_path, case):
+    """stb_image: 4 components are CMYK (Adobe transform 0), YCCK (2) or YCbCr + an ignored channel; 3 components are taken as RGB
+    when their ids spell RGB or when an Adobe marker says 0 and there is no JFIF marker (stb_image.h:3878, 3955-3975)."""
+    a = picture(45, 31, 3)
+    f = tmp_path / "t.jpg"
+    if case in ("cmyk", "ycck", "four-unknown-transform"):
+        PIL.fromarray(a, "CMYK").save(f, quality=85)
+        data = f.read_bytes()
+        data = patch_adobe_transform(data, {"cmyk": 0, "ycck": 2, "four-unknown-transform": 1}[case])
+    else:
+        PIL.fromarray(a[..., :3]).save(f, quality=85, subsampling=0)
+        data = f.read_bytes()
+        if case == "rgb-by-adobe-no-jfif":
+            data = patch_adobe_transform(strip_jfif(data), 0)
+        elif case == "adobe-0-with-jfif":
+            data = patch_adobe_transform(data, 0)
+            assert b"JFIF" in data
+        elif case == "adobe-1":
+            data = patch_adobe_transform(strip_jfif(data), 1)
+        else:                                                  # component ids 1, 2, 3 -> 'R', 'G', 'B' in SOF0 and SOS
+            sof = data.find(b"\xff\xc0")
+            sos = data.find(b"\xff\xda")
+            d = bytearray(data)
+            for k, c in enumerate(b"RGB"):
+                assert d[sof + 10 + 3 * k] == k + 1 and d[sos + 5 + 2 * k] == k + 1
+                d[sof + 10 + 3 * k] = c
+                d[sos + 5 + 2 * k] = c
+            data = bytes(d)
+    f.write_bytes(data)
+    same(f)
+
+
+def test_random_valid_files_decode_like_stb_image():
+    """A slice of tools/fuzz_image_files.py: random pictures written with random encoder settings (PNG, JPEG incl. CMYK, TGA, BMP)."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import fuzz_image_files
+    assert fuzz_image_files.main(["--files", "300", "--seed", "5"]) == 0
