@@ -168,7 +168,9 @@ void ptbh_root_set(void* s, float scatter_rate, float sky_brightness, float sky_
 }
 
 void* ptbh_create_entity(void* s, int type, void* parent) { return CreateEntity((scene*)s, (entity_type)type, (entity*)parent); }
-void ptbh_destroy_entity(void* s, void* e) { DestroyEntity((scene*)s, (entity*)e); }
+// The reference's DestroyEntity leaves the dirty flags to its caller (imgui_main.cpp:525 sets SCENE_DIRTY_SHAPES); the product's sets
+// shapes and cameras itself, and so does this wrapper.
+void ptbh_destroy_entity(void* s, void* e) { DestroyEntity((scene*)s, (entity*)e); ((scene*)s)->DirtyFlags |= SCENE_DIRTY_SHAPES | SCENE_DIRTY_CAMERAS; }
 void ptbh_entity_set_transform(void* s, void* e, const float* pos, const float* rot, const float* scale) {
     entity* E = (entity*)e;
     E->Transform.Position = {pos[0], pos[1], pos[2]};

@@ -201,6 +201,8 @@ bounds shape_bounds(scene const* S, ptb_packed_shape const& O) {
 void build_shape_nodes(scene* S) {
     auto& Nodes = S->ShapeNodePack;
     Nodes.resize(1);
+    // Node 0 of a scene without shapes: the reference's resize(1) keeps whatever its previous pack left there (scene.cpp:1349), a
+    // root whose children no longer exist; here it is an empty leaf (found by tools/fuzz_pack.py's edit rounds).
     std::memset(&Nodes[0], 0, sizeof(Nodes[0]));
     std::vector<uint16_t> Map;
     for (uint32_t s = 0; s < S->ShapePack.size(); s++) {

@@ -35,7 +35,58 @@ def plain_cameras(cls, S):
             p = list(params) + [0.0] * 5
             self._L.ptbh_camera_set(self.h, e, model, S._f3(p))
             return e
+
+        # handles of what the generators create, for the edit rounds
+        def create_entity(self, etype, parent=None, **kw):
+            e = super().create_entity(etype, parent=parent, **kw)
+            made = self.__dict__.setdefault("made_entities", [])
+            owner = next((r for r in reversed(made) if r["handle"] == parent and not r["gone"]), None) if parent is not None else None
+            made.append({"handle": e, "type": etype, "owner": owner, "gone": False})      # handles are addresses: a freed one can come back
+            return e
+
+        def create_material(self, mtype, name="Material", textures=None, **fields):
+            m = super().create_material(mtype, name, textures=textures, **fields)
+            self.__dict__.setdefault("made_materials", []).append((m, mtype))
+            return m
     return Scene
+
+
+def edit_round(sc, S, rng):
+    """Random edits through the scene API (the dirty flags are the ones the reference's editor sets for the same edits)."""
+    ents = sc.__dict__.setdefault("made_entities", [])
+    mats = sc.__dict__.setdefault("made_materials", [])
+
+    def living():
+        return [r for r in ents if not r["gone"] and not (r["owner"] is not None and r["owner"]["gone"])]
+    alive = living()
+    for _ in range(int(rng.integers(1, 5))):
+        what = rng.integers(0, 6)
+        if what == 0 and alive:
+            e = alive[rng.integers(0, len(alive))]["handle"]
+            sc.set_transform(e, position=tuple(rng.normal(size=3) * 3), rotation=tuple(rng.uniform(-3, 3, 3)), scale=tuple(rng.uniform(0.3, 2.0, 3)))
+        elif what == 1 and alive:
+            sc.set_active(alive[rng.integers(0, len(alive))]["handle"], bool(rng.integers(0, 2)))
+        elif what == 2 and alive:
+            leaves = [r for r in alive if r["type"] != S.ENTITY_CONTAINER]
+            if leaves:
+                r = leaves[rng.integers(0, len(leaves))]
+                sc.destroy_entity(r["handle"])
+                r["gone"] = True
+                alive = living()
+        elif what == 3:
+            parents = [None] + [r["handle"] for r in alive if r["type"] == S.ENTITY_CONTAINER]
+            sc.create_entity((S.ENTITY_SPHERE, S.ENTITY_CUBE, S.ENTITY_PLANE)[rng.integers(0, 3)], parent=parents[rng.integers(0, len(parents))],
+                             position=tuple(rng.normal(size=3) * 2), rotation=tuple(rng.uniform(-3, 3, 3)), scale=tuple(rng.uniform(0.3, 2.0, 3)),
+                             material=mats[rng.integers(0, len(mats))][0] if mats else None)
+            alive = living()
+        elif what == 4 and mats:
+            m, mtype = mats[rng.integers(0, len(mats))]
+            if mtype in (S.MATERIAL_BASIC_DIFFUSE, S.MATERIAL_BASIC_METAL):
+                sc._L.ptbh_material_set(sc.h, m, b"BaseColor", S._f3(rng.uniform(0, 1, 3)))
+            else:
+                sc._L.ptbh_material_set(sc.h, m, b"Roughness", S._f3([float(rng.uniform(0, 1)), 0, 0]))
+        else:
+            sc.set_root(scatter_rate=float(rng.choice([0.0, 0.1])), sky_brightness=float(rng.uniform(0.5, 2)), sky_sampling_probability=0.0, sky_texture=None)
 
 
 def main(argv=None):
@@ -74,6 +125,18 @@ def main(argv=None):
             except AssertionError as ex:
                 print("seed", seed, which, "PACKED ARRAYS DIFFER:", str(ex)[:1500])
                 return 1
+            # edit rounds: only what the dirty flags select is repacked, and it must still agree
+            for r in range(3):
+                flags = []
+                for sc in pair:
+                    edit_round(sc, S, np.random.default_rng(seed * 7 + r))
+                    flags.append(sc.pack())
+                try:
+                    assert flags[0] == flags[1], ("dirty flags reported by PackSceneData", flags)
+                    T.compare_packs(*pair)
+                except AssertionError as ex:
+                    print("seed", seed, which, "after edit round", r, "PACKED ARRAYS DIFFER:", str(ex)[:1500])
+                    return 1
             faces += len(pair[0].mesh_faces)
             shapes += len(pair[0].shapes)
             for sc in pair:
