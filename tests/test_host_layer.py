@@ -131,6 +131,44 @@ def test_wide_flattening_of_a_large_mesh_on_several_threads(emu, oracle, scenes)
         emu.emu_destroy(t[0])
 
 
+def test_destroying_a_container_removes_everything_in_it():
+    """DestroyEntity on a container with children (the reference's walks the child list while the children erase themselves from it,
+    scene.cpp:256-268: undefined behaviour; host/scene.cpp copies the list first).  The packed scene must equal one that never had
+    the container."""
+    from path_tracer_b200 import scene as S
+    S.ensure_spectrum_table()
+
+    def build(with_box):
+        sc = S.Scene()
+        m = sc.create_material(S.MATERIAL_BASIC_DIFFUSE, "d", BaseColor=(0.5, 0.6, 0.7))
+        sc.create_entity(S.ENTITY_PLANE, material=m)
+        box = None
+        if with_box:
+            box = sc.create_entity(S.ENTITY_CONTAINER, position=(1, 2, 3), rotation=(0.1, 0.2, 0.3), scale=(2, 2, 2))
+            sc.create_entity(S.ENTITY_SPHERE, parent=box, position=(1, 0, 0), material=m)
+            inner = sc.create_entity(S.ENTITY_CONTAINER, parent=box, position=(0, 1, 0))
+            sc.create_entity(S.ENTITY_CUBE, parent=inner, position=(0, 0, 1), material=m)
+            sc.create_entity(S.ENTITY_SPHERE, parent=inner, position=(0, 0, 2), material=m)
+            sc.create_camera((5, 5, 5), (0, 0, 0))           # a camera outside the container stays
+            cam_in = sc._L.ptbh_create_entity(sc.h, S.ENTITY_CAMERA, inner)
+            assert cam_in
+        else:
+            sc.create_camera((5, 5, 5), (0, 0, 0))
+        sc.create_entity(S.ENTITY_CUBE, position=(-3, 0, 1), material=m)
+        return sc, box
+
+    a, box = build(True)
+    a.pack()
+    assert len(a.shapes) == 5 and len(a.cameras) == 2
+    a.destroy_entity(box)
+    a.pack()
+    b, _ = build(False)
+    b.pack()
+    for name in ("shapes", "shape_nodes", "cameras", "materials"):
+        assert getattr(a, name).tobytes() == getattr(b, name).tobytes(), name
+    assert len(a.shapes) == 2 and len(a.cameras) == 1
+
+
 def test_random_scenes_scatter_like_the_oracle(emu):
     """A slice of tools/fuzz_scatter.py: random materials over their whole parameter range, nested and overlapping
     dielectrics, media, textured sky, three cameras, every flag combination, path-length limits and termination

@@ -56,8 +56,15 @@ def edit_round(sc, S, rng):
     ents = sc.__dict__.setdefault("made_entities", [])
     mats = sc.__dict__.setdefault("made_materials", [])
 
+    def is_gone(r):                                            # destroyed itself, or inside a destroyed container (any depth)
+        while r is not None:
+            if r["gone"]:
+                return True
+            r = r["owner"]
+        return False
+
     def living():
-        return [r for r in ents if not r["gone"] and not (r["owner"] is not None and r["owner"]["gone"])]
+        return [r for r in ents if not is_gone(r)]
     alive = living()
     for _ in range(int(rng.integers(1, 5))):
         what = rng.integers(0, 6)
@@ -67,6 +74,9 @@ def edit_round(sc, S, rng):
         elif what == 1 and alive:
             sc.set_active(alive[rng.integers(0, len(alive))]["handle"], bool(rng.integers(0, 2)))
         elif what == 2 and alive:
+            # Containers are left alone: the reference's DestroyEntity walks Entity->Children while every child erases itself from that
+            # very vector (scene.cpp:256-268) - undefined behaviour, a crash in this build - so a container with children cannot be
+            # destroyed through it.  host/scene.cpp copies the list first (tests/test_host_layer.py, test_destroying_a_container_removes_everything_in_it).
             leaves = [r for r in alive if r["type"] != S.ENTITY_CONTAINER]
             if leaves:
                 r = leaves[rng.integers(0, len(leaves))]
