@@ -131,6 +131,46 @@ def test_wide_flattening_of_a_large_mesh_on_several_threads(emu, oracle, scenes)
         emu.emu_destroy(t[0])
 
 
+def test_resolve_on_random_accumulators(emu, oracle, scenes):
+    """resolve_pixel (ptb_resolve.cuh, host build) against the oracle's restatement of resolve.glsl and - where it is here -
+    against the reference's own fragment stage, on accumulators nobody would render: huge, tiny, negative, zero sample counts,
+    infinities and NaNs, every tone-mapping mode, random brightness and white level.  Bit for bit (same libm)."""
+    sc = scenes("cornell")
+    w, h = 64, 48
+    e = emu.emu_create(C.addressof(sc.view), w, h)
+    emu.emu_resolve.argtypes = [C.c_void_p, C.c_float, C.c_uint32, C.c_float, C.c_void_p, C.c_void_p]
+    acc = np.frombuffer((C.c_float * (w * h * 4)).from_address(emu.emu_accum(e)), dtype=np.float32).reshape(h, w, 4)
+    try:
+        from oracle.ref import binding as R
+        ref = R if R.available() else None
+        if ref:
+            ref.lib()
+    except Exception:
+        ref = None
+    rng = np.random.default_rng(8)
+    for trial in range(24):
+        a = (rng.uniform(0, 1, size=(h, w, 4)) * 10.0 ** rng.integers(-6, 7, size=(h, w, 1))).astype(np.float32)
+        a[..., 3] = rng.integers(0, 5, size=(h, w)) * rng.choice([1.0, 1000.0])         # sample counts, zeros included
+        a[rng.random(size=(h, w)) < 0.05, :3] *= -1.0
+        for v in (np.inf, -np.inf, np.nan, 0.0, -0.0):
+            a[rng.integers(0, h), rng.integers(0, w), rng.integers(0, 4)] = v
+        acc[...] = a
+        mode = trial % 4
+        brightness, white = float(rng.choice([0.0, 0.01, 1.0, 3.7, 1e4])), float(rng.choice([0.1, 1.0, 11.2, 1e3]))
+        lin = np.zeros((h, w, 3), np.float32)
+        srgb = np.zeros((h, w, 4), np.uint8)
+        emu.emu_resolve(e, brightness, mode, white, lin.ctypes.data, srgb.ctypes.data)
+        o_lin, o_srgb = oracle.resolve(a, brightness, mode, white)
+        same = (lin.view(np.uint32) == o_lin.view(np.uint32)) | (np.isnan(lin) & np.isnan(o_lin))
+        assert same.all(), (trial, mode, np.argwhere(~same)[0], lin[~same][:3], o_lin[~same][:3])
+        assert np.array_equal(srgb, o_srgb), (trial, mode)
+        if ref:
+            r_lin = ref.resolve(a, brightness, mode, white)
+            same = (r_lin.view(np.uint32) == o_lin.view(np.uint32)) | (np.isnan(r_lin) & np.isnan(o_lin))
+            assert same.all(), ("reference", trial, mode, np.argwhere(~same)[0], r_lin[~same][:3], o_lin[~same][:3])
+    emu.emu_destroy(e)
+
+
 def test_destroying_a_container_removes_everything_in_it():
     """DestroyEntity on a container with children (the reference's walks the child list while the children erase themselves from it,
     scene.cpp:256-268: undefined behaviour; host/scene.cpp copies the list first).  The packed scene must equal one that never had
