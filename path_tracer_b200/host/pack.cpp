@@ -131,6 +131,8 @@ void pack_textures(scene* S) {
         const uint32_t ImageIndex = (uint32_t)S->Images.size();
         std::vector<texture*> Left;
         bool any = false;
+        struct job { texture const* T; uint32_t rx, ry; };
+        std::vector<job> Jobs;
         for (texture* T : Pending) {
             auto Found = Spot.find(T);
             if (Found == Spot.end()) { Left.push_back(T); continue; }
@@ -146,28 +148,50 @@ void pack_textures(scene* S) {
             K.AtlasPlacementMaximum[1] = (ry + 0.5f) / float(AH);
             K.Type = (uint32_t)T->Type;       // (left uninitialised by the reference)
             K.Flags = T->EnableNearestFiltering ? (uint32_t)TEXTURE_FLAG_FILTER_NEAREST : 0u;
-            for (uint32_t Y = 0; Y < T->Height; Y++) {
-                vec4 const* Src = T->Pixels.data() + (size_t)Y * T->Width;
-                float* Dst = Layer.data() + ((size_t)(ry + Y) * AW + rx) * 4;
-                for (uint32_t X = 0; X < T->Width; X++, Dst += 4) {
-                    vec4 V = Src[X];
-                    if (T->Type == TEXTURE_TYPE_RAW) {
-                        Dst[0] = V.x; Dst[1] = V.y; Dst[2] = V.z; Dst[3] = V.w;
-                    } else if (T->Type == TEXTURE_TYPE_REFLECTANCE_WITH_ALPHA) {       // scene.cpp:1187-1195
-                        vec3 B = GetParametricSpectrumCoefficients(S->RGBSpectrumTable, {V.x, V.y, V.z});
-                        Dst[0] = B.x; Dst[1] = B.y; Dst[2] = B.z; Dst[3] = V.w;
-                    } else {                                                            // RADIANCE, scene.cpp:1196-1211
-                        float I = 2 * std::max(std::max(V.x, V.y), V.z);
-                        if (I > 1e-6f) {
-                            vec3 B = GetParametricSpectrumCoefficients(S->RGBSpectrumTable, {V.x / I, V.y / I, V.z / I});
-                            Dst[0] = B.x; Dst[1] = B.y; Dst[2] = B.z; Dst[3] = I;
-                        } else { Dst[0] = Dst[1] = Dst[2] = Dst[3] = 0.0f; }
-                    }
-                }
-            }
+            Jobs.push_back({T, rx, ry});
             S->TexturePack.push_back(K);
         }
         if (!any) break;   // a texture larger than the atlas: dropped (the reference would loop forever)
+        // Texel conversion (scene.cpp:1179-1212): every texel is a pure function of its source texel, rows are dealt to all host threads.
+        {
+            struct rows { job const* J; uint32_t Y0, Y1; };
+            std::vector<rows> Work;
+            for (job const& J : Jobs) {
+                const uint32_t step = std::max<uint32_t>(1, 65536 / std::max<uint32_t>(1, J.T->Width));
+                for (uint32_t Y = 0; Y < J.T->Height; Y += step) Work.push_back({&J, Y, std::min(J.T->Height, Y + step)});
+            }
+            std::atomic<size_t> Next(0);
+            auto Convert = [&]() {
+                for (size_t w = Next.fetch_add(1); w < Work.size(); w = Next.fetch_add(1)) {
+                    texture const* T = Work[w].J->T;
+                    const uint32_t rx = Work[w].J->rx, ry = Work[w].J->ry;
+                    for (uint32_t Y = Work[w].Y0; Y < Work[w].Y1; Y++) {
+                        vec4 const* Src = T->Pixels.data() + (size_t)Y * T->Width;
+                        float* Dst = Layer.data() + ((size_t)(ry + Y) * AW + rx) * 4;
+                        for (uint32_t X = 0; X < T->Width; X++, Dst += 4) {
+                            vec4 V = Src[X];
+                            if (T->Type == TEXTURE_TYPE_RAW) {
+                                Dst[0] = V.x; Dst[1] = V.y; Dst[2] = V.z; Dst[3] = V.w;
+                            } else if (T->Type == TEXTURE_TYPE_REFLECTANCE_WITH_ALPHA) {       // scene.cpp:1187-1195
+                                vec3 B = GetParametricSpectrumCoefficients(S->RGBSpectrumTable, {V.x, V.y, V.z});
+                                Dst[0] = B.x; Dst[1] = B.y; Dst[2] = B.z; Dst[3] = V.w;
+                            } else {                                                            // RADIANCE, scene.cpp:1196-1211
+                                float I = 2 * std::max(std::max(V.x, V.y), V.z);
+                                if (I > 1e-6f) {
+                                    vec3 B = GetParametricSpectrumCoefficients(S->RGBSpectrumTable, {V.x / I, V.y / I, V.z / I});
+                                    Dst[0] = B.x; Dst[1] = B.y; Dst[2] = B.z; Dst[3] = I;
+                                } else { Dst[0] = Dst[1] = Dst[2] = Dst[3] = 0.0f; }
+                            }
+                        }
+                    }
+                }
+            };
+            const unsigned Threads = (unsigned)std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), std::max<size_t>(1, Work.size()));
+            std::vector<std::thread> Pool;
+            for (unsigned t = 1; t < Threads; t++) Pool.emplace_back(Convert);
+            Convert();
+            for (auto& Th : Pool) Th.join();
+        }
         S->Images.push_back(std::move(Layer));
         Pending.swap(Left);
     }
