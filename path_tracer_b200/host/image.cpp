@@ -16,8 +16,8 @@
 //          followed so that 8-bit output is identical with the reference's.
 //   * TGA (types 1/2/3 and run-length 9/10/11; 8/15/16/24/32 bits) and BMP (1/4/8-bit paletted, 16/24/32-bit, BITFIELDS; no RLE),
 //          with stb_image's conversions (5-5-5 scaling, bit-field replication, the "all alpha zero means opaque" rule).
-//   * PPM (P6) and PFM (PF) kept from round 1 (not stb formats with this contract: P6 is read as
-//          sRGB-encoded, PFM as linear float, rows bottom to top).
+//   * PGM / PPM (binary P5 / P6, 8 and 16 bit) as stb_image reads them, quirks included (see decode_pnm_stb); PFM (PF, linear float,
+//          rows bottom to top) is this repository's own addition.
 // 8-bit sources become float the way stbi_loadf does it (stb_image.h "ldr_to_hdr"): colour channels
 // pow(v / 255, 2.2), alpha v / 255.
 // Pinned against the reference's own vendored stb_image.h compiled into oracle/_ref
@@ -1181,7 +1181,67 @@ bool decode_bmp(const std::vector<u8>& f, int& W, int& H, std::vector<u8>& rgba)
     return true;
 }
 
-// ------------------------------------------------------------------ PPM / PFM (round 1)
+// ------------------------------------------------------------------ PGM / PPM as stb_image reads them, and PFM
+// stb_image.h:7491-7618.  "P5" (grey) and "P6" (RGB), binary.  Header: width, height, maximum value, separated by blanks
+// (space, \t, \n, \v, \f, \r) and comments (# to the end of the line); ONE byte after the maximum value, then the samples.
+// The maximum value only chooses the sample size (<= 255: one byte, <= 65535: two) - samples are not rescaled by it - and
+// two-byte samples are read in HOST byte order and reduced to their high byte, which on a little-endian host is the SECOND
+// byte of the big-endian pair the format prescribes.  Both quirks are stb_image's; files decode as they do in the reference.
+// PFM ("PF", little-endian, rows bottom to top, linear float) is this repository's own addition: stb_image does not read it.
+bool pnm_blank(u8 c) { return c == ' ' || c == '\t' || c == '\n' || c == '\v' || c == '\f' || c == '\r'; }
+
+bool decode_pnm_stb(const std::vector<u8>& f, int& W, int& H, std::vector<u8>& rgba) {
+    if (f.size() < 3 || f[0] != 'P' || (f[1] != '5' && f[1] != '6')) return false;
+    const int comp = f[1] == '6' ? 3 : 1;
+    size_t pos = 2;
+    auto get = [&]() -> u8 { return pos < f.size() ? f[pos++] : 0; };
+    auto at_end = [&]() { return pos >= f.size(); };
+    u8 c = get();
+    auto skip = [&]() {
+        for (;;) {
+            while (!at_end() && pnm_blank(c)) c = get();
+            if (at_end() || c != '#') break;
+            while (!at_end() && c != '\n' && c != '\r') c = get();
+        }
+    };
+    bool overflow = false;
+    auto integer = [&]() {
+        long long v = 0;
+        while (!at_end() && c >= '0' && c <= '9') {
+            v = v * 10 + (c - '0');
+            c = get();
+            if (v > 214748364 || (v == 214748364 && c > '7')) { overflow = true; return 0; }
+        }
+        return (int)v;
+    };
+    skip();
+    const int w = integer();
+    if (overflow || w == 0) return false;
+    skip();
+    const int h = integer();
+    if (overflow || h == 0) return false;
+    skip();
+    const int maxv = integer();
+    if (overflow || maxv > 65535) return false;
+    const int bytes = maxv > 255 ? 2 : 1;
+    if (w > (1 << 24) || h > (1 << 24)) return false;
+    const size_t count = (size_t)w * h * comp;
+    if (count > ((size_t)1 << 31) / bytes || pos + count * bytes > f.size()) return false;
+    rgba.resize((size_t)w * h * 4);
+    for (size_t i = 0; i < (size_t)w * h; i++) {
+        u8 v[3];
+        for (int k = 0; k < comp; k++) {
+            const size_t at = pos + (i * comp + k) * bytes;
+            if (bytes == 1) v[k] = f[at];
+            else { uint16_t native; std::memcpy(&native, &f[at], 2); v[k] = (u8)(native >> 8); }
+        }
+        if (comp == 1) v[1] = v[2] = v[0];
+        rgba[4 * i] = v[0]; rgba[4 * i + 1] = v[1]; rgba[4 * i + 2] = v[2]; rgba[4 * i + 3] = 255;
+    }
+    W = w; H = h;
+    return true;
+}
+
 bool pnm_token(const std::vector<u8>& f, size_t& pos, std::string& tok) {
     tok.clear();
     while (pos < f.size()) {
@@ -1193,38 +1253,22 @@ bool pnm_token(const std::vector<u8>& f, size_t& pos, std::string& tok) {
     return !tok.empty();
 }
 
-bool decode_pnm(const std::vector<u8>& file, int& W, int& H, std::vector<vec4>& px) {
+bool decode_pfm(const std::vector<u8>& file, int& W, int& H, std::vector<vec4>& px) {
     size_t pos = 0;
     std::string magic, a, b, c;
     if (!pnm_token(file, pos, magic) || !pnm_token(file, pos, a) || !pnm_token(file, pos, b) || !pnm_token(file, pos, c)) return false;
     const int w = std::atoi(a.c_str()), h = std::atoi(b.c_str());
-    if (w <= 0 || h <= 0) return false;
+    if (magic != "PF" || w <= 0 || h <= 0) return false;
     pos++;                                   // the single whitespace byte that ends the header
-    if (magic == "P6") {
-        const int maxv = std::atoi(c.c_str());
-        if (maxv <= 0 || maxv >= 256 || pos + (size_t)w * h * 3 > file.size()) return false;
-        px.resize((size_t)w * h);
-        for (size_t i = 0; i < px.size(); i++) {
-            float v[3];
-            for (int k = 0; k < 3; k++) {
-                const float s = file[pos + 3 * i + k] / (float)maxv;          // 8-bit PPM holds sRGB-encoded values
-                v[k] = s <= 0.04045f ? s / 12.92f : std::pow((s + 0.055f) / 1.055f, 2.4f);
-            }
-            px[i] = {v[0], v[1], v[2], 1.0f};
+    const float scale = (float)std::atof(c.c_str());
+    if (!(scale < 0) || pos + (size_t)w * h * 12 > file.size()) return false;      // little-endian only
+    px.resize((size_t)w * h);
+    for (int y = 0; y < h; y++)                                           // PFM rows run bottom to top
+        for (int x = 0; x < w; x++) {
+            float s[3];
+            std::memcpy(s, &file[pos + ((size_t)(h - 1 - y) * w + x) * 12], 12);
+            px[(size_t)y * w + x] = {s[0], s[1], s[2], 1.0f};
         }
-    } else if (magic == "PF") {
-        const float scale = (float)std::atof(c.c_str());
-        if (!(scale < 0) || pos + (size_t)w * h * 12 > file.size()) return false;      // little-endian only
-        px.resize((size_t)w * h);
-        for (int y = 0; y < h; y++)                                           // PFM rows run bottom to top
-            for (int x = 0; x < w; x++) {
-                float s[3];
-                std::memcpy(s, &file[pos + ((size_t)(h - 1 - y) * w + x) * 12], 12);
-                px[(size_t)y * w + x] = {s[0], s[1], s[2], 1.0f};
-            }
-    } else {
-        return false;
-    }
     W = w; H = h;
     return true;
 }
@@ -1247,7 +1291,12 @@ bool DecodeImageFile(char const* Path, int& Width, int& Height, std::vector<vec4
         return true;
     }
     if (file[0] == '#' && file[1] == '?') return decode_hdr(file, Width, Height, Pixels);
-    if (file[0] == 'P' && (file[1] == '6' || file[1] == 'F')) return decode_pnm(file, Width, Height, Pixels);
+    if (file[0] == 'P' && (file[1] == '5' || file[1] == '6')) {
+        if (!decode_pnm_stb(file, Width, Height, rgba)) return false;
+        ldr_to_float(rgba, Pixels);
+        return true;
+    }
+    if (file[0] == 'P' && file[1] == 'F') return decode_pfm(file, Width, Height, Pixels);
     if (file[0] == 'B' && file[1] == 'M') {
         if (!decode_bmp(file, Width, Height, rgba)) return false;
         ldr_to_float(rgba, Pixels);

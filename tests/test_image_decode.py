@@ -397,3 +397,32 @@ def test_random_valid_files_decode_like_stb_image():
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
     import fuzz_image_files
     assert fuzz_image_files.main(["--files", "300", "--seed", "5"]) == 0
+
+
+@pytest.mark.parametrize("case", ["ppm8", "pgm8", "ppm16", "pgm16", "maxval-100", "odd-blanks", "comments", "maxval-256"])
+def test_pnm_matches_stb_image(tmp_path, case):
+    """stb_image's P5 / P6 reader (stb_image.h:7491-7618): the maximum value chooses the sample size and nothing else, two-byte
+    samples are taken in host byte order and reduced to their high byte."""
+    rng = np.random.default_rng(3)
+    px = rng.integers(0, 256, size=(5, 7, 3), dtype=np.uint8)
+    px16 = rng.integers(0, 65536, size=(5, 7, 3)).astype(">u2")
+    data = {"ppm8": b"P6\n7 5\n255\n" + px.tobytes(),
+            "pgm8": b"P5\n7 5\n255\n" + px[..., 0].tobytes(),
+            "ppm16": b"P6\n7 5\n65535\n" + px16.tobytes(),
+            "pgm16": b"P5\n7 5\n65535\n" + px16[..., 0].tobytes(),
+            "maxval-100": b"P6 7 5 100\n" + (px // 3).tobytes(),
+            "odd-blanks": b"P6\n7\t5\v\f255 " + px.tobytes(),
+            "comments": b"P5#a\n# b\r7 5 # c\n255\n" + px[..., 0].tobytes(),
+            "maxval-256": b"P5\n7 5\n256\n" + px16[..., 0].tobytes()}[case]
+    f = tmp_path / "t.pnm"
+    f.write_bytes(data)
+    out = same(f)
+    if case == "ppm8":
+        assert np.allclose(out[0, 0, :3], (px[0, 0] / 255.0) ** 2.2, atol=1e-6) and out[0, 0, 3] == 1.0
+
+
+@pytest.mark.parametrize("data", [b"P6\n7 5\n255\n" + bytes(104), b"P6\n0 5\n255\n" + bytes(105), b"P6\n7 5\n70000\n" + bytes(210), b"P6\n99999999999 5\n255\n"])
+def test_pnm_refused_like_stb_image(tmp_path, data):
+    f = tmp_path / "t.pnm"
+    f.write_bytes(data)
+    assert H.stbi_loadf(str(f)) is None and S.decode_image(str(f)) is None

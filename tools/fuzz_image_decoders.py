@@ -22,7 +22,7 @@ def add(name, im, **kw):
     p=os.path.join(d,name); im.save(p,**kw); seeds.append(open(p,"rb").read())
 add("a.tga", Image.fromarray(b[...,:3])); add("b.tga", Image.fromarray(b), compression="tga_rle")
 add("c.tga", Image.fromarray(b[...,:3]).quantize(17), compression="tga_rle"); add("d.tga", Image.fromarray(b[...,[0,3]],"LA"))
-add("k.jpg", Image.fromarray(b,"CMYK"), quality=70); add("a.bmp", Image.fromarray(b[...,:3])); add("b.bmp", Image.fromarray(b)); add("c.bmp", Image.fromarray(b[...,:3]).quantize(17)); add("d.bmp", Image.fromarray(b[...,0]>128))
+add("k.jpg", Image.fromarray(b,"CMYK"), quality=70); seeds.append(b"P6\n40 30\n255\n"+b[...,:3].tobytes()); seeds.append(b"P5 40 30 65535\n"+b[...,:2].tobytes()); add("a.bmp", Image.fromarray(b[...,:3])); add("b.bmp", Image.fromarray(b)); add("c.bmp", Image.fromarray(b[...,:3]).quantize(17)); add("d.bmp", Image.fromarray(b[...,0]>128))
 files=[]
 for it in range(16000):
     s=bytearray(seeds[it%len(seeds)])

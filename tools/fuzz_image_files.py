@@ -6,7 +6,7 @@ tool writes well-formed files with random content AND random encoder settings th
 palettes of odd sizes, tRNS, interlace is not writable by Pillow and stays with the unit tests, compression levels, odd sizes),
 JPEG (quality 1-100, 4:4:4 / 4:2:2 / 4:2:0 / 4:1:1 / 4:4:0 subsampling, progressive, optimised tables, greyscale, CMYK and YCCK
 with the Adobe marker, restart intervals, sizes around the MCU edges), TGA (RLE or not, palettes, 8/24/32 bit), BMP (1/4/8/24/32
-bit) and noisy as well as smooth pictures - and demands that `stbi_loadf(path, ..., 4)` of the reference (oracle/_ref/
+bit), binary PGM / PPM (8 and 16 bit, hand-written headers) and noisy as well as smooth pictures - and demands that `stbi_loadf(path, ..., 4)` of the reference (oracle/_ref/
 libref_host.so) and DecodeImageFile return the same float pixels bit for bit.
 
     python tools/fuzz_image_files.py [--files 1500] [--seed 1]
@@ -44,7 +44,7 @@ def write_random_file(rng, d, k):
     w = int(rng.choice([1, 2, 7, 8, 9, 15, 16, 17, 31, 33, 64, 100])) if rng.random() < 0.7 else int(rng.integers(1, 200))
     h = int(rng.choice([1, 2, 7, 8, 9, 15, 16, 17, 31, 33, 64, 100])) if rng.random() < 0.7 else int(rng.integers(1, 200))
     a = random_picture(rng, w, h)
-    fmt = rng.choice(["png", "jpg", "jpg", "tga", "bmp"])
+    fmt = rng.choice(["png", "jpg", "jpg", "tga", "bmp", "pnm"])
     path = os.path.join(d, "f%05d.%s" % (k, fmt))
     if fmt == "png":
         mode = rng.choice(["L", "LA", "RGB", "RGBA", "P", "P-trns", "1", "I;16", "RGB-trns", "L-trns"])
@@ -86,6 +86,13 @@ def write_random_file(rng, d, k):
         if rng.random() < 0.5:
             kw["orientation"] = int(rng.choice([1, -1]))
         im.save(path, **kw)
+    elif fmt == "pnm":                                         # binary P5 / P6, 8 and 16 bit, header written by hand
+        grey, wide = bool(rng.integers(0, 2)), bool(rng.integers(0, 2))
+        body = (rng.integers(0, 65536, size=(h, w, 1 if grey else 3)).astype(">u2") if wide else a[..., :1] if grey else a[..., :3]).tobytes()
+        sep = [b"\n", b" ", b"\t", b"\r\n", b"\n# c\n"]
+        hdr = (b"P5" if grey else b"P6") + sep[rng.integers(0, 5)] + str(w).encode() + sep[rng.integers(0, 5)] + str(h).encode() + sep[rng.integers(0, 5)]
+        hdr += str(int(rng.integers(256, 65536)) if wide else int(rng.integers(1, 256))).encode() + sep[rng.integers(0, 3)][:1]
+        open(path, "wb").write(hdr + body)
     else:
         mode = rng.choice(["RGB", "RGBA", "L", "P", "1"])
         im = (Image.fromarray(a[..., :3]).quantize(int(rng.integers(2, 257))) if mode == "P" else Image.fromarray(a[..., 0] > 128) if mode == "1" else
