@@ -16,7 +16,7 @@
 //          followed so that 8-bit output is identical with the reference's.
 //   * TGA (types 1/2/3 and run-length 9/10/11; 8/15/16/24/32 bits) and BMP (1/4/8-bit paletted, 16/24/32-bit, BITFIELDS; no RLE),
 //          with stb_image's conversions (5-5-5 scaling, bit-field replication, the "all alpha zero means opaque" rule).
-//   * PGM / PPM (binary P5 / P6, 8 and 16 bit) as stb_image reads them, quirks included (see decode_pnm_stb); PFM (PF, linear float,
+//   * GIF (first frame, as stb_image composes it), PGM / PPM (binary P5 / P6, 8 and 16 bit) as stb_image reads them, quirks included (see decode_pnm_stb); PFM (PF, linear float,
 //          rows bottom to top) is this repository's own addition.
 // 8-bit sources become float the way stbi_loadf does it (stb_image.h "ldr_to_hdr"): colour channels
 // pow(v / 255, 2.2), alpha v / 255.
@@ -1181,6 +1181,147 @@ bool decode_bmp(const std::vector<u8>& f, int& W, int& H, std::vector<u8>& rgba)
     return true;
 }
 
+// ------------------------------------------------------------------ GIF, the first frame, as stb_image returns it
+// stb_image.h stbi__gif_load / stbi__gif_load_next / stbi__process_gif_raster.  Always four components.  What it does beyond the
+// format: pixels the frame does not draw - outside its rectangle, or drawn with the transparent index - stay (0, 0, 0, 0), unless
+// the header names a background index > 0, in which case every untouched pixel gets that palette entry COPIED AS STORED, and the
+// palette is stored blue-first (so red and blue are swapped in a background fill - a stb_image quirk files render with in the
+// reference).  The transparent index of a graphic-control extension clears the alpha of the GLOBAL palette entry; a local palette
+// gets it when it is parsed.  A stream that ends (0x3B) before any image, a raster without a leading clear code, more than 8192
+// codes, or a frame rectangle outside the screen is refused.
+bool decode_gif(const std::vector<u8>& f, int& W, int& H, std::vector<u8>& rgba) {
+    size_t pos = 0;
+    auto get8 = [&]() -> int { return pos < f.size() ? f[pos++] : 0; };
+    auto get16 = [&]() -> int { int a = get8(); return a | (get8() << 8); };
+    auto skip = [&](int n) { pos = std::min(f.size(), pos + (size_t)std::max(0, n)); };
+    if (get8() != 'G' || get8() != 'I' || get8() != 'F' || get8() != '8') return false;
+    const int version = get8();
+    if (version != '7' && version != '9') return false;
+    if (get8() != 'a') return false;
+    const int w = get16(), h = get16(), flags = get8(), bgindex = get8();
+    get8();                                                    // aspect ratio
+    if (w > (1 << 24) || h > (1 << 24)) return false;
+    u8 pal[256][4] = {}, lpal[256][4] = {};
+    auto colortable = [&](u8 (*table)[4], int entries, int transparent) {
+        for (int i = 0; i < entries; i++) {
+            table[i][2] = (u8)get8(); table[i][1] = (u8)get8(); table[i][0] = (u8)get8();     // stored blue, green, red
+            table[i][3] = transparent == i ? 0 : 255;
+        }
+    };
+    if (flags & 0x80) colortable(pal, 2 << (flags & 7), -1);
+    if ((uint64_t)w * (uint64_t)h > ((uint64_t)1 << 29)) return false;
+    const size_t pcount = (size_t)w * h;
+    std::vector<u8> out(pcount * 4, 0), history(pcount, 0);
+    int transparent = -1, eflags = 0;
+    for (;;) {
+        const int tag = get8();
+        if (tag == 0x2C) {
+            const int x = get16(), y = get16(), fw = get16(), fh = get16();
+            if (x + fw > w || y + fh > h) return false;
+            const long long line = (long long)w * 4;
+            const long long start_x = (long long)x * 4, start_y = (long long)y * line, max_x = start_x + (long long)fw * 4, max_y = start_y + (long long)fh * line;
+            long long cur_x = start_x, cur_y = fw == 0 ? max_y : start_y, step;
+            int parse;
+            const int lflags = get8();
+            if (lflags & 0x40) { step = 8 * line; parse = 3; } else { step = line; parse = 0; }
+            u8 (*table)[4];
+            if (lflags & 0x80) { colortable(lpal, 2 << (lflags & 7), (eflags & 1) ? transparent : -1); table = lpal; }
+            else if (flags & 0x80) table = pal;
+            else return false;
+            // LZW raster
+            const int lzw_cs = get8();
+            if (lzw_cs > 12) return false;
+            struct code_t { int16_t prefix; u8 first, suffix; };
+            std::vector<code_t> codes(8192);
+            const int clear = 1 << lzw_cs;
+            bool first = true;
+            int codesize = lzw_cs + 1, codemask = (1 << codesize) - 1, avail = clear + 2, oldcode = -1, len = 0, valid_bits = 0;
+            int32_t bits = 0;
+            for (int i = 0; i < clear; i++) { codes[i].prefix = -1; codes[i].first = (u8)i; codes[i].suffix = (u8)i; }
+            std::vector<u8> chain;
+            auto emit = [&](int code) {                       // the string of `code`, first symbol first
+                chain.clear();
+                for (int c = code; c >= 0; c = codes[c].prefix) chain.push_back(codes[c].suffix);
+                for (size_t k = chain.size(); k-- > 0;) {
+                    if (cur_y >= max_y) continue;
+                    const long long idx = cur_x + cur_y;
+                    u8* p = &out[(size_t)idx];
+                    history[(size_t)(idx / 4)] = 1;
+                    const u8* c = table[chain[k]];
+                    if (c[3] > 128) { p[0] = c[2]; p[1] = c[1]; p[2] = c[0]; p[3] = c[3]; }
+                    cur_x += 4;
+                    if (cur_x >= max_x) {
+                        cur_x = start_x;
+                        cur_y += step;
+                        while (cur_y >= max_y && parse > 0) {
+                            step = ((long long)1 << parse) * line;
+                            cur_y = start_y + (step >> 1);
+                            --parse;
+                        }
+                    }
+                }
+            };
+            bool done = false;
+            while (!done) {
+                if (valid_bits < codesize) {
+                    if (len == 0) {
+                        len = get8();
+                        if (len == 0) break;                   // raster ends with the blocks
+                    }
+                    --len;
+                    bits |= (int32_t)((uint32_t)get8() << valid_bits);
+                    valid_bits += 8;
+                } else {
+                    const int code = bits & codemask;
+                    bits >>= codesize;
+                    valid_bits -= codesize;
+                    if (code == clear) {
+                        codesize = lzw_cs + 1; codemask = (1 << codesize) - 1; avail = clear + 2; oldcode = -1; first = false;
+                    } else if (code == clear + 1) {
+                        skip(len);
+                        while ((len = get8()) > 0) skip(len);
+                        done = true;
+                    } else if (code <= avail) {
+                        if (first) return false;
+                        if (oldcode >= 0) {
+                            if (avail + 1 > 8192) return false;
+                            code_t& n = codes[avail++];
+                            n.prefix = (int16_t)oldcode;
+                            n.first = codes[oldcode].first;
+                            n.suffix = (code == avail) ? n.first : codes[code].first;
+                        } else if (code == avail) return false;
+                        emit(code);
+                        if ((avail & codemask) == 0 && avail <= 0x0FFF) { codesize++; codemask = (1 << codesize) - 1; }
+                        oldcode = code;
+                    } else return false;
+                }
+            }
+            if (bgindex > 0)
+                for (size_t pi = 0; pi < pcount; pi++)
+                    if (!history[pi]) { pal[bgindex][3] = 255; std::memcpy(&out[pi * 4], pal[bgindex], 4); }
+            W = w; H = h;
+            rgba.swap(out);
+            return w > 0 && h > 0;
+        } else if (tag == 0x21) {
+            const int ext = get8();
+            int len;
+            if (ext == 0xF9) {
+                len = get8();
+                if (len == 4) {
+                    eflags = get8();
+                    get16();                                   // delay
+                    if (transparent >= 0) pal[transparent][3] = 255;
+                    if (eflags & 1) { transparent = get8(); pal[transparent][3] = 0; }
+                    else { skip(1); transparent = -1; }
+                } else { skip(len); continue; }
+            }
+            while ((len = get8()) != 0) skip(len);
+        } else {
+            return false;                                      // 0x3B before any image, or an unknown block
+        }
+    }
+}
+
 // ------------------------------------------------------------------ PGM / PPM as stb_image reads them, and PFM
 // stb_image.h:7491-7618.  "P5" (grey) and "P6" (RGB), binary.  Header: width, height, maximum value, separated by blanks
 // (space, \t, \n, \v, \f, \r) and comments (# to the end of the line); ONE byte after the maximum value, then the samples.
@@ -1297,6 +1438,11 @@ bool DecodeImageFile(char const* Path, int& Width, int& Height, std::vector<vec4
         return true;
     }
     if (file[0] == 'P' && file[1] == 'F') return decode_pfm(file, Width, Height, Pixels);
+    if (file[0] == 'G' && file[1] == 'I' && file[2] == 'F' && file[3] == '8') {
+        if (!decode_gif(file, Width, Height, rgba)) return false;
+        ldr_to_float(rgba, Pixels);
+        return true;
+    }
     if (file[0] == 'B' && file[1] == 'M') {
         if (!decode_bmp(file, Width, Height, rgba)) return false;
         ldr_to_float(rgba, Pixels);

@@ -426,3 +426,71 @@ def test_pnm_refused_like_stb_image(tmp_path, data):
     f = tmp_path / "t.pnm"
     f.write_bytes(data)
     assert H.stbi_loadf(str(f)) is None and S.decode_image(str(f)) is None
+
+
+def gif_parts(data):
+    """(logical screen descriptor flags offset, global table slice, offset of the first image descriptor) of a GIF."""
+    flags = data[10]
+    table = slice(13, 13 + (3 * (2 << (flags & 7)) if flags & 0x80 else 0))
+    at = table.stop
+    while data[at] == 0x21:                                     # extensions: label, then sub-blocks
+        at += 2
+        while data[at]:
+            at += 1 + data[at]
+        at += 1
+    assert data[at] == 0x2C
+    return table, at
+
+
+@pytest.mark.parametrize("case", ["palette-17", "palette-256", "grey", "two-colours", "transparent", "interlaced", "interlaced-odd", "animated",
+                                  "bigger-screen-background", "bigger-screen-no-background", "local-palette", "local-palette-transparent",
+                                  "truncated", "ends-before-image", "gif87a"])
+def test_gif_first_frame_matches_stb_image(tmp_path, case):
+    """stbi__gif_load: the first frame composed as stb_image composes it - untouched pixels (0, 0, 0, 0) or the background entry
+    copied blue-first, transparent pixels not drawn, local palettes, interlace."""
+    a = picture(45, 30 if case != "interlaced-odd" else 29, 3)
+    f = tmp_path / "t.gif"
+    rgb = PIL.fromarray(a[..., :3])
+    if case == "palette-256":
+        rgb.quantize(256).save(f)
+    elif case == "grey":
+        PIL.fromarray(a[..., 0]).save(f)
+    elif case == "two-colours":
+        rgb.quantize(2).save(f)
+    elif case in ("transparent", "local-palette-transparent"):
+        rgb.quantize(5).save(f, transparency=2)
+    elif case in ("interlaced", "interlaced-odd"):
+        rgb.quantize(64).save(f, interlace=True)
+        assert f.read_bytes()[gif_parts(f.read_bytes())[1] + 9] & 0x40
+    elif case == "animated":
+        frames = [PIL.fromarray(picture(45, 30, k)[..., :3]).quantize(30) for k in range(3)]
+        frames[0].save(f, save_all=True, append_images=frames[1:], duration=40, loop=0)
+    else:
+        rgb.quantize(17).save(f)
+    data = bytearray(f.read_bytes())
+    if case.startswith("bigger-screen"):
+        data[6:10] = struct.pack("<HH", 45 + 6, 30 + 4)         # the frame keeps its 45 x 30 rectangle at (0, 0)
+        data[11] = 3 if case == "bigger-screen-background" else 0
+    elif case.startswith("local-palette"):
+        table, at = gif_parts(bytes(data))
+        pal = bytes(data[table])
+        size_bits = data[10] & 7
+        desc = bytearray(data[at:at + 10])
+        desc[9] |= 0x80 | size_bits
+        data = data[:10] + bytes([data[10] & 0x7F]) + data[11:13] + data[table.stop:at] + desc + pal + data[at + 10:]
+    elif case == "truncated":
+        data = data[:len(data) // 2]
+    elif case == "ends-before-image":
+        table, at = gif_parts(bytes(data))
+        data = data[:at] + b";"
+    elif case == "gif87a":
+        data[3:6] = b"87a"
+    f.write_bytes(bytes(data))
+    if case == "ends-before-image":
+        assert H.stbi_loadf(str(f)) is None and S.decode_image(str(f)) is None
+        return
+    out = same(f)
+    if case == "bigger-screen-no-background":
+        assert (out[:, 45:] == 0).all() and (out[30:] == 0).all()
+    if case == "bigger-screen-background":
+        assert (out[:, 45:, 3] == 1).all()

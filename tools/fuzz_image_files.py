@@ -6,7 +6,8 @@ tool writes well-formed files with random content AND random encoder settings th
 palettes of odd sizes, tRNS, interlace is not writable by Pillow and stays with the unit tests, compression levels, odd sizes),
 JPEG (quality 1-100, 4:4:4 / 4:2:2 / 4:2:0 / 4:1:1 / 4:4:0 subsampling, progressive, optimised tables, greyscale, CMYK and YCCK
 with the Adobe marker, restart intervals, sizes around the MCU edges), TGA (RLE or not, palettes, 8/24/32 bit), BMP (1/4/8/24/32
-bit), binary PGM / PPM (8 and 16 bit, hand-written headers) and noisy as well as smooth pictures - and demands that `stbi_loadf(path, ..., 4)` of the reference (oracle/_ref/
+bit), binary PGM / PPM (8 and 16 bit, hand-written headers), GIF (palette sizes, transparency, interlace, animation, larger
+screens with and without a background index, local palettes) and noisy as well as smooth pictures - and demands that `stbi_loadf(path, ..., 4)` of the reference (oracle/_ref/
 libref_host.so) and DecodeImageFile return the same float pixels bit for bit.
 
     python tools/fuzz_image_files.py [--files 1500] [--seed 1]
@@ -44,7 +45,7 @@ def write_random_file(rng, d, k):
     w = int(rng.choice([1, 2, 7, 8, 9, 15, 16, 17, 31, 33, 64, 100])) if rng.random() < 0.7 else int(rng.integers(1, 200))
     h = int(rng.choice([1, 2, 7, 8, 9, 15, 16, 17, 31, 33, 64, 100])) if rng.random() < 0.7 else int(rng.integers(1, 200))
     a = random_picture(rng, w, h)
-    fmt = rng.choice(["png", "jpg", "jpg", "tga", "bmp", "pnm"])
+    fmt = rng.choice(["png", "jpg", "jpg", "tga", "bmp", "pnm", "gif"])
     path = os.path.join(d, "f%05d.%s" % (k, fmt))
     if fmt == "png":
         mode = rng.choice(["L", "LA", "RGB", "RGBA", "P", "P-trns", "1", "I;16", "RGB-trns", "L-trns"])
@@ -86,6 +87,36 @@ def write_random_file(rng, d, k):
         if rng.random() < 0.5:
             kw["orientation"] = int(rng.choice([1, -1]))
         im.save(path, **kw)
+    elif fmt == "gif":                                         # first frame; sometimes a larger screen, a background index, a local palette
+        import struct
+        kw = {}
+        if rng.random() < 0.4:
+            kw["interlace"] = True
+        n = int(rng.integers(2, 257))
+        if rng.random() < 0.4:
+            kw["transparency"] = int(rng.integers(0, n))
+        im = Image.fromarray(a[..., 0]) if rng.random() < 0.2 else Image.fromarray(a[..., :3]).quantize(n)
+        if rng.random() < 0.2:
+            im.save(path, save_all=True, append_images=[Image.fromarray(random_picture(rng, w, h)[..., :3]).quantize(n)], duration=30, **kw)
+        else:
+            im.save(path, **kw)
+        data = bytearray(open(path, "rb").read())
+        if rng.random() < 0.4:
+            data[6:10] = struct.pack("<HH", w + int(rng.integers(0, 9)), h + int(rng.integers(0, 9)))
+            data[11] = int(rng.integers(0, 2 << (data[10] & 7))) if (data[10] & 0x80) and rng.random() < 0.6 else 0
+        if rng.random() < 0.3 and (data[10] & 0x80):            # move the global palette behind the image descriptor
+            table = slice(13, 13 + 3 * (2 << (data[10] & 7)))
+            at = table.stop
+            while data[at] == 0x21:
+                at += 2
+                while data[at]:
+                    at += 1 + data[at]
+                at += 1
+            if data[at] == 0x2C:
+                desc = bytearray(data[at:at + 10])
+                desc[9] |= 0x80 | (data[10] & 7)
+                data = data[:10] + bytes([data[10] & 0x7F]) + data[11:13] + data[table.stop:at] + desc + bytes(data[table]) + data[at + 10:]
+        open(path, "wb").write(bytes(data))
     elif fmt == "pnm":                                         # binary P5 / P6, 8 and 16 bit, header written by hand
         grey, wide = bool(rng.integers(0, 2)), bool(rng.integers(0, 2))
         body = (rng.integers(0, 65536, size=(h, w, 1 if grey else 3)).astype(">u2") if wide else a[..., :1] if grey else a[..., :3]).tobytes()
