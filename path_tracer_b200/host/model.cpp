@@ -38,7 +38,7 @@ namespace {
 
 struct corner { int v = -1, vt = -1, vn = -1; };
 struct obj_shape { std::string name; std::vector<corner> corners; std::vector<int> material_ids; };   // 3 corners per face
-struct obj_material { std::string name; float kd[3] = {0.6f, 0.6f, 0.6f}; float ke[3] = {0, 0, 0}; std::string map_kd, map_ke; };
+struct obj_material { std::string name; float kd[3] = {0, 0, 0}; float ke[3] = {0, 0, 0}; std::string map_kd, map_ke; };   // tinyobjloader's InitMaterial: black
 
 // Polygons become triangles the way the reference's loader makes them (tinyobjloader 2.0.0rc, "simple" method,
 // tiny_obj_loader.h:1509-1964; float arithmetic): which triangles come out decides face numbering and shading, so a fan is
@@ -133,24 +133,56 @@ std::string rest_of(std::istringstream& ss) {
     return a == std::string::npos ? std::string() : r.substr(a, b - a + 1);
 }
 
+// The file name of a `map_*` statement the way tinyobjloader finds it (ParseTextureNameAndOption, tiny_obj_loader.h): options
+// are skipped with the number of blank-separated arguments each one CONSUMES there (three for -o / -s / -t whatever they are, two
+// for -mm, one for the others), and the first thing that is not a known option starts the name, which runs to the end of the
+// line, blanks included.
+std::string texture_name_of(const std::string& rest) {
+    static const struct { const char* name; int args; } options[] = {
+        {"-blendu", 1}, {"-blendv", 1}, {"-clamp", 1}, {"-boost", 1}, {"-bm", 1}, {"-o", 3}, {"-s", 3}, {"-t", 3},
+        {"-type", 1}, {"-texres", 1}, {"-imfchan", 1}, {"-mm", 2}, {"-colorspace", 1}};
+    size_t at = 0;
+    auto blanks = [&]() { while (at < rest.size() && (rest[at] == ' ' || rest[at] == '\t')) at++; };
+    auto word = [&]() { while (at < rest.size() && rest[at] != ' ' && rest[at] != '\t' && rest[at] != '\r') at++; };
+    for (;;) {
+        blanks();
+        if (at >= rest.size()) return std::string();
+        bool option = false;
+        for (auto const& o : options) {
+            const size_t n = std::strlen(o.name);
+            if (rest.compare(at, n, o.name) == 0 && at + n < rest.size() && (rest[at + n] == ' ' || rest[at + n] == '\t')) {
+                at += n;
+                for (int k = 0; k < o.args; k++) { blanks(); word(); }
+                option = true;
+                break;
+            }
+        }
+        if (!option) return rest.substr(at);
+    }
+}
+
 bool load_mtl(const std::string& path, std::vector<obj_material>& out, std::unordered_map<std::string, int>& index) {
     std::ifstream f(path);
     if (!f) return false;
     std::string line;
     obj_material* cur = nullptr;
+    bool has_kd = false;              // tinyobjloader keeps this flag for the whole FILE (newmtl does not clear it): kept, it decides colours
     while (std::getline(f, line)) {
         std::istringstream ss(line);
         std::string key;
         if (!(ss >> key) || key[0] == '#') continue;
         if (key == "newmtl") {
-            obj_material m; m.name = rest_of(ss);
+            obj_material m;
+            ss >> m.name;                                      // parseString: the first word (a name with blanks is cut there, in `usemtl` too)
             index[m.name] = (int)out.size();
             out.push_back(m);
             cur = &out.back();
-        } else if (cur && key == "Kd") ss >> cur->kd[0] >> cur->kd[1] >> cur->kd[2];
+        } else if (cur && key == "Kd") { ss >> cur->kd[0] >> cur->kd[1] >> cur->kd[2]; has_kd = true; }
         else if (cur && key == "Ke") ss >> cur->ke[0] >> cur->ke[1] >> cur->ke[2];
-        else if (cur && key == "map_Kd") cur->map_kd = rest_of(ss);
-        else if (cur && key == "map_Ke") cur->map_ke = rest_of(ss);
+        else if (cur && key == "map_Kd") {
+            cur->map_kd = texture_name_of(rest_of(ss));
+            if (!has_kd) cur->kd[0] = cur->kd[1] = cur->kd[2] = 0.6f;          // "a decent default" when a texture comes without Kd
+        } else if (cur && key == "map_Ke") cur->map_ke = texture_name_of(rest_of(ss));
     }
     return true;
 }
@@ -255,7 +287,9 @@ prefab* LoadModelAsPrefab(scene* Scene, char const* Path, load_model_options* Op
             if (Shapes.back().corners.empty()) Shapes.back().name = name;
             else { Shapes.emplace_back(); Shapes.back().name = name; }
         } else if (key == "usemtl") {
-            auto it = MaterialIndex.find(rest_of(ss));
+            std::string name;
+            ss >> name;
+            auto it = MaterialIndex.find(name);
             CurrentMaterial = it == MaterialIndex.end() ? -1 : it->second;
         } else if (key == "mtllib") {
             load_mtl(Directory + "/" + rest_of(ss), FileMaterials, MaterialIndex);
@@ -297,6 +331,11 @@ prefab* LoadModelAsPrefab(scene* Scene, char const* Path, load_model_options* Op
                 TextureMap[FM.map_kd] = LoadTexture(Scene, (Directory + "/" + FM.map_kd).c_str(), TEXTURE_TYPE_REFLECTANCE_WITH_ALPHA, FM.map_kd.c_str());
             M->BaseTexture = TextureMap[FM.map_kd];
         }
+        // The reference loads the emission map as well (scene.cpp:703-707), as a radiance texture of its OpenPBR material.  BasicDiffuse
+        // has nowhere to attach it, but it is loaded all the same: the textures of a scene, their order and their atlas placements
+        // stay the reference's.
+        if (!FM.map_ke.empty() && !TextureMap.count(FM.map_ke))
+            TextureMap[FM.map_ke] = LoadTexture(Scene, (Directory + "/" + FM.map_ke).c_str(), TEXTURE_TYPE_RADIANCE, FM.map_ke.c_str());
         Materials.push_back(M);
     }
 

@@ -246,3 +246,35 @@ def test_scene_file_with_prefabs_and_side_files(model_dir, tmp_path):
         S.Scene.load(str(tmp_path / "bad.json"))
     a.close()
     b.close()
+
+
+def test_mtl_is_read_the_way_tinyobjloader_reads_it(tmp_path):
+    """Defaults and quirks of the reference's loader that decide what a model looks like: a material without Kd is black, unless it
+    has a map_Kd and no Kd statement has been seen IN THE FILE so far (then 0.6); options in front of a texture name are skipped by
+    argument count; a texture name runs to the end of the line; material names are one word (newmtl and usemtl alike)."""
+    from path_tracer_b200 import scene as S
+    from PIL import Image
+    S.ensure_spectrum_table()
+    Image.fromarray(np.full((2, 2, 3), 200, np.uint8)).save(tmp_path / "a b.png")
+    (tmp_path / "m.mtl").write_text("newmtl first extra words\nmap_Kd -s 2 2 1 -clamp on a b.png\n"       # no Kd seen yet: 0.6, texture found
+                                    "newmtl second\n"                                                     # nothing: black
+                                    "newmtl third\nKd 0.25 0.5 0.75\n"
+                                    "newmtl fourth\nmap_Kd a b.png\n")                                   # a Kd was seen before in the file: stays black
+    (tmp_path / "m.obj").write_text("mtllib m.mtl\nv 0 0 0\nv 1 0 0\nv 0 1 0\nv 1 1 0\nvt 0 0\nvt 1 0\nvt 0 1\n"
+                                    "usemtl first ignored\nf 1/1 2/2 3/3\nusemtl second\nf 2/1 4/2 3/3\nusemtl third\nf 1/1 2/2 4/3\nusemtl fourth\nf 1/1 4/2 3/3\n")
+    sc = S.Scene()
+    sc.set_atlas_size(64, 64)
+    prefab = sc.load_model(str(tmp_path / "m.obj"))
+    assert sc.prefab_mesh_count(prefab) == 4
+    sc.create_prefab_instance(prefab, position=(0, 0, 0))
+    sc.pack()
+    want = S.Scene()
+    want.set_atlas_size(64, 64)
+    t = want.load_texture(str(tmp_path / "a b.png"), S.TEXTURE_REFLECTANCE_WITH_ALPHA)
+    want.create_material(S.MATERIAL_BASIC_DIFFUSE, "first", BaseColor=(0.6, 0.6, 0.6), textures={"BaseTexture": t})
+    want.create_material(S.MATERIAL_BASIC_DIFFUSE, "second", BaseColor=(0, 0, 0))
+    want.create_material(S.MATERIAL_BASIC_DIFFUSE, "third", BaseColor=(0.25, 0.5, 0.75))
+    want.create_material(S.MATERIAL_BASIC_DIFFUSE, "fourth", BaseColor=(0, 0, 0), textures={"BaseTexture": t})
+    want.pack()
+    assert len(sc.textures) == 1
+    assert np.asarray(sc.materials).tobytes() == np.asarray(want.materials).tobytes()

@@ -4,7 +4,7 @@
 
 Random files: vertices with and without normals and texture coordinates (per face or not at all), triangles, quads and
 larger polygons (tinyobjloader triangulates them), absolute and negative (relative) indices, several `o` / `g` blocks,
-`usemtl` switches inside a shape, smoothing-group lines, comments, blank lines, trailing spaces, exponents and signs in
+`usemtl` switches inside a shape, MTL files with texture maps (options, blanks in names, shared and missing files, emission maps), smoothing-group lines, comments, blank lines, trailing spaces, exponents and signs in
 numbers, faces that repeat a vertex (zero-area), shapes without faces.  The same file is loaded through both host layers
 (oracle/_ref/libref_host.so is the reference's scene.cpp and tiny_obj_loader.h compiled where they lie), the prefab is
 instanced, the scene packed, and per mesh - the reference takes a shape's material groups out of a std::unordered_set, so
@@ -43,9 +43,18 @@ def write_random_obj(path, rng):
     n_mats = int(rng.integers(0, 4))
     lines = ["# fuzz"]
     if n_mats:
+        # texture statements as exporters write them: plain, with options in front (tinyobjloader skips them by argument count),
+        # a name with a blank in it, the same file under two materials, a file that is not there, emission maps
+        names = ["tex_a.png", "tex b.png", "tex_c.png", "missing.png"]
         with open(os.path.join(os.path.dirname(path), "f.mtl"), "w") as m:
             for k in range(n_mats):
-                m.write("newmtl m%d\nKd %.3f %.3f %.3f\n" % ((k,) + tuple(rng.uniform(0, 1, 3))))
+                m.write("newmtl m%d\n" % k)
+                if rng.random() < 0.8:
+                    m.write("Kd %.3f %.3f %.3f\n" % tuple(rng.uniform(0, 1, 3)))
+                for key in ("map_Kd", "map_Ke"):
+                    if rng.random() < (0.6 if key == "map_Kd" else 0.25):
+                        opts = rng.choice(["", "", "-s 2 2 1 ", "-o 0.5 0 0 -s 1 1 1 ", "-clamp on ", "-blendu off -mm 0 1 ", "-bm 0.5 ", "-colorspace sRGB "])
+                        m.write("%s %s%s%s\n" % (key, opts, names[rng.integers(0, len(names))], "  " if rng.random() < 0.2 else ""))
         lines.append("mtllib f.mtl")
     nv = nt = nn = 0
     for shape in range(int(rng.integers(1, 5))):
@@ -109,6 +118,9 @@ def main(argv=None):
     H.lib()
     Ref = H.ref_scene_class()
     d = tempfile.mkdtemp(prefix="fuzz_obj_")
+    from PIL import Image
+    for k, name in enumerate(("tex_a.png", "tex b.png", "tex_c.png")):
+        Image.fromarray(np.random.default_rng(70 + k).integers(0, 256, size=(5 + 3 * k, 9 - 2 * k, 4), dtype=np.uint8)).save(os.path.join(d, name))
     meshes = faces = refused = 0
     for k in range(args.files):
         rng = np.random.default_rng(args.seed * 100003 + k)
@@ -125,8 +137,16 @@ def main(argv=None):
             sc.create_prefab_instance(prefab, position=(0.5, 1.0, 0.25), rotation=(0.2, 0.1, 0.9), scale=(1, 1.5, 1))
             sc.create_entity(S.ENTITY_CAMERA, position=(0, -6, 2), rotation=(1.4, 0, 0))
             sc.pack()
+            tex = sc.textures
+            texels = []
+            for i in range(len(tex)):
+                layer = sc.atlas_layer(int(tex["AtlasImageIndex"][i]))
+                aw, ah = sc.view.AtlasWidth, sc.view.AtlasHeight
+                x0, x1 = int(round(float(tex["AtlasPlacementMinimum"][i][0]) * aw - 0.5)), int(round(float(tex["AtlasPlacementMaximum"][i][0]) * aw + 0.5))
+                y0, y1 = int(round(float(tex["AtlasPlacementMaximum"][i][1]) * ah - 0.5)), int(round(float(tex["AtlasPlacementMinimum"][i][1]) * ah + 0.5))
+                texels.append((x0, x1, y0, y1, int(tex["AtlasImageIndex"][i]), int(tex["Flags"][i]), layer[y0:y1, x0:x1].tobytes()))
             per_mesh = sorted((sc.source_mesh_vertices(i).tobytes(), T.mesh_faces_of(sc, i).tobytes(), sc.mesh_info(i)["nodes"]) for i in range(sc.mesh_count()))   # mesh::Depth: the reference never writes it
-            got.append((n, sc.mesh_count(), per_mesh, len(sc.shapes), len(sc.mesh_faces), len(sc.mesh_vertices), len(sc.mesh_nodes)))
+            got.append((n, sc.mesh_count(), per_mesh, len(sc.shapes), len(sc.mesh_faces), len(sc.mesh_vertices), len(sc.mesh_nodes), texels))
             sc.close()
         if got[0] is None or got[1] is None:
             if (got[0] is None) != (got[1] is None):
@@ -135,7 +155,7 @@ def main(argv=None):
             refused += 1
             continue
         if got[0] != got[1]:
-            what = [name for name, a, b in zip(("prefab meshes", "scene meshes", "per-mesh vertices / face order / nodes", "shapes", "packed faces", "packed vertices", "packed nodes"), got[0], got[1]) if a != b]
+            what = [name for name, a, b in zip(("prefab meshes", "scene meshes", "per-mesh vertices / face order / nodes", "shapes", "packed faces", "packed vertices", "packed nodes", "textures: order, atlas placement, texels"), got[0], got[1]) if a != b]
             print(path, ": DIFFERS in", what, "ours", [x for x in got[0] if not isinstance(x, list)], "reference", [x for x in got[1] if not isinstance(x, list)])
             return 1
         meshes += got[0][1]
