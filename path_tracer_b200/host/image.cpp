@@ -16,7 +16,7 @@
 //          followed so that 8-bit output is identical with the reference's.
 //   * TGA (types 1/2/3 and run-length 9/10/11; 8/15/16/24/32 bits) and BMP (1/4/8-bit paletted, 16/24/32-bit, BITFIELDS; no RLE),
 //          with stb_image's conversions (5-5-5 scaling, bit-field replication, the "all alpha zero means opaque" rule).
-//   * GIF (first frame, as stb_image composes it), PGM / PPM (binary P5 / P6, 8 and 16 bit) as stb_image reads them, quirks included (see decode_pnm_stb); PFM (PF, linear float,
+//   * GIF (first frame, as stb_image composes it), PSD (flattened RGB image, raw or PackBits), PGM / PPM (binary P5 / P6, 8 and 16 bit) as stb_image reads them, quirks included (see decode_pnm_stb); PFM (PF, linear float,
 //          rows bottom to top) is this repository's own addition.
 // 8-bit sources become float the way stbi_loadf does it (stb_image.h "ldr_to_hdr"): colour channels
 // pow(v / 255, 2.2), alpha v / 255.
@@ -1322,6 +1322,85 @@ bool decode_gif(const std::vector<u8>& f, int& W, int& H, std::vector<u8>& rgba)
     }
 }
 
+// ------------------------------------------------------------------ PSD, the flattened image, as stb_image reads it
+// stb_image.h stbi__psd_load (8-bit output).  "8BPS" version 1, RGB mode only, 8 or 16 bits per channel, raw or PackBits rows
+// (the run-length reader takes one BYTE per pixel whatever the depth, as stb_image's does), channels stored one after the other; the
+// first four are used, missing ones are 0 (colour) or 255 (alpha), 16-bit samples keep their high byte.  With an alpha channel the
+// colour is "un-matted" from white, in float: c' = c / a + 255 (1 - 1 / a) for 0 < a < 255, converted to a byte the way the
+// compiler converts it (truncation to a 32-bit integer, low byte).  Reads past the end of the file yield zeros, as in stb_image.
+bool decode_psd(const std::vector<u8>& f, int& W, int& H, std::vector<u8>& rgba) {
+    size_t pos = 0;
+    auto get8 = [&]() -> uint32_t { return pos < f.size() ? f[pos++] : 0u; };
+    auto get16 = [&]() -> uint32_t { uint32_t a = get8(); return (a << 8) | get8(); };
+    auto get32 = [&]() -> uint32_t { uint32_t a = get16(); return (a << 16) | get16(); };
+    auto skip = [&](uint32_t n) { pos = (size_t)std::min<uint64_t>(f.size(), (uint64_t)pos + n); };
+    if (get32() != 0x38425053u) return false;
+    if (get16() != 1) return false;
+    skip(6);
+    const int channels = (int)get16();
+    if (channels < 0 || channels > 16) return false;
+    const uint32_t h = get32(), w = get32();
+    if (h > (1u << 24) || w > (1u << 24)) return false;
+    const int depth = (int)get16();
+    if (depth != 8 && depth != 16) return false;
+    if (get16() != 3) return false;
+    skip(get32());
+    skip(get32());
+    skip(get32());
+    const int compression = (int)get16();
+    if (compression > 1) return false;
+    if ((uint64_t)w * h > ((uint64_t)1 << 29) || w == 0 || h == 0) return false;
+    const size_t count = (size_t)w * h;
+    rgba.assign(count * 4, 0);
+    if (compression) {
+        skip((uint32_t)std::min<uint64_t>(0xFFFFFFFFu, (uint64_t)h * channels * 2));
+        for (int c = 0; c < 4; c++) {
+            u8* p = rgba.data() + c;
+            if (c >= channels) { for (size_t i = 0; i < count; i++, p += 4) *p = c == 3 ? 255 : 0; continue; }
+            size_t done = 0;
+            while (done < count) {
+                const size_t left = count - done;
+                uint32_t len = get8();
+                if (len == 128) continue;
+                if (len < 128) {
+                    len++;
+                    if (len > left) return false;
+                    done += len;
+                    while (len--) { *p = (u8)get8(); p += 4; }
+                } else {
+                    len = 257 - len;
+                    if (len > left) return false;
+                    const u8 v = (u8)get8();
+                    done += len;
+                    while (len--) { *p = v; p += 4; }
+                }
+            }
+        }
+    } else {
+        for (int c = 0; c < 4; c++) {
+            u8* p = rgba.data() + c;
+            if (c >= channels) { for (size_t i = 0; i < count; i++, p += 4) *p = c == 3 ? 255 : 0; }
+            else if (depth == 16) { for (size_t i = 0; i < count; i++, p += 4) *p = (u8)(get16() >> 8); }
+            else { for (size_t i = 0; i < count; i++, p += 4) *p = (u8)get8(); }
+        }
+    }
+    if (channels >= 4) {
+        auto to_byte = [](float v) -> u8 {                    // (unsigned char) of a float: cvttss2si, low byte
+            const int32_t t = (v >= -2147483648.0f && v < 2147483648.0f) ? (int32_t)v : INT32_MIN;
+            return (u8)((uint32_t)t & 0xFFu);
+        };
+        for (size_t i = 0; i < count; i++) {
+            u8* px = &rgba[4 * i];
+            if (px[3] != 0 && px[3] != 255) {
+                const float a = px[3] / 255.0f, ra = 1.0f / a, inv_a = 255.0f * (1 - ra);
+                px[0] = to_byte(px[0] * ra + inv_a); px[1] = to_byte(px[1] * ra + inv_a); px[2] = to_byte(px[2] * ra + inv_a);
+            }
+        }
+    }
+    W = (int)w; H = (int)h;
+    return true;
+}
+
 // ------------------------------------------------------------------ PGM / PPM as stb_image reads them, and PFM
 // stb_image.h:7491-7618.  "P5" (grey) and "P6" (RGB), binary.  Header: width, height, maximum value, separated by blanks
 // (space, \t, \n, \v, \f, \r) and comments (# to the end of the line); ONE byte after the maximum value, then the samples.
@@ -1440,6 +1519,11 @@ bool DecodeImageFile(char const* Path, int& Width, int& Height, std::vector<vec4
     if (file[0] == 'P' && file[1] == 'F') return decode_pfm(file, Width, Height, Pixels);
     if (file[0] == 'G' && file[1] == 'I' && file[2] == 'F' && file[3] == '8') {
         if (!decode_gif(file, Width, Height, rgba)) return false;
+        ldr_to_float(rgba, Pixels);
+        return true;
+    }
+    if (file[0] == '8' && file[1] == 'B' && file[2] == 'P' && file[3] == 'S') {
+        if (!decode_psd(file, Width, Height, rgba)) return false;
         ldr_to_float(rgba, Pixels);
         return true;
     }

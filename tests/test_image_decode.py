@@ -494,3 +494,78 @@ def test_gif_first_frame_matches_stb_image(tmp_path, case):
         assert (out[:, 45:] == 0).all() and (out[30:] == 0).all()
     if case == "bigger-screen-background":
         assert (out[:, 45:, 3] == 1).all()
+
+
+def packbits(row):
+    """PackBits with literal runs only where nothing repeats (enough to exercise both packet kinds)."""
+    out, i = bytearray(), 0
+    while i < len(row):
+        j = i
+        while j + 1 < len(row) and row[j + 1] == row[i] and j - i < 127:
+            j += 1
+        if j > i:
+            out += bytes([257 - (j - i + 1), row[i]])
+            i = j + 1
+        else:
+            k = i
+            while k + 1 < len(row) and row[k + 1] != row[k] and k - i < 127:
+                k += 1
+            out += bytes([k - i]) + bytes(row[i:k + 1])
+            i = k + 1
+    return bytes(out)
+
+
+def write_psd(path, planes, depth=8, rle=False, mode=3, noop=False):
+    """planes: (channels, h, w) array of uint8 (depth 8) or uint16 (depth 16)."""
+    c, h, w = planes.shape
+    head = b"8BPS" + struct.pack(">H6xHIIHH", 1, c, h, w, depth, mode) + struct.pack(">I", 0) + struct.pack(">I", 4) + b"abcd" + struct.pack(">I", 0)
+    if rle:
+        rows = [packbits(planes[k, y].astype(np.uint8).tobytes()) for k in range(c) for y in range(h)]
+        if noop:
+            rows[0] = b"\x80" + rows[0]
+        body = struct.pack(">H", 1) + b"".join(struct.pack(">H", len(r)) for r in rows) + b"".join(rows)
+    else:
+        body = struct.pack(">H", 0) + (planes.astype(">u2") if depth == 16 else planes.astype(np.uint8)).tobytes()
+    with open(path, "wb") as f:
+        f.write(head + body)
+
+
+@pytest.mark.parametrize("channels", [1, 2, 3, 4, 5])
+@pytest.mark.parametrize("kind", ["raw8", "raw16", "rle8", "rle8-noop"])
+def test_psd_matches_stb_image(tmp_path, channels, kind):
+    """stbi__psd_load: planar channels, the first four used, missing ones filled, 16-bit samples reduced to their high byte, PackBits
+    rows, and the white un-matting of colour under partial alpha."""
+    rng = np.random.default_rng(channels)
+    h, w = 13, 21
+    if kind == "raw16":
+        planes = rng.integers(0, 65536, size=(channels, h, w)).astype(np.uint16)
+    else:
+        planes = rng.integers(0, 256, size=(channels, h, w)).astype(np.uint8)
+        planes[:, 3:6, :] = planes[:, 3:6, :1]                  # flat rows: replicate packets
+        if channels >= 4:
+            planes[3, 0, :4] = (0, 255, 1, 254)                 # alpha extremes next to the un-matting cases
+    f = tmp_path / "t.psd"
+    write_psd(f, planes, depth=16 if kind == "raw16" else 8, rle=kind.startswith("rle"), noop=kind.endswith("noop"))
+    same(f)
+
+
+@pytest.mark.parametrize("what", ["cmyk-mode", "depth-32", "version-2", "seventeen-channels", "bad-compression", "rle-overrun"])
+def test_psd_refused_like_stb_image(tmp_path, what):
+    planes = np.zeros((3, 4, 5), np.uint8)
+    f = tmp_path / "t.psd"
+    write_psd(f, planes, mode=4 if what == "cmyk-mode" else 3)
+    d = bytearray(f.read_bytes())
+    if what == "depth-32":
+        d[22:24] = struct.pack(">H", 32)
+    elif what == "version-2":
+        d[4:6] = struct.pack(">H", 2)
+    elif what == "seventeen-channels":
+        d[12:14] = struct.pack(">H", 17)
+    elif what == "bad-compression":
+        d[42:44] = struct.pack(">H", 2)
+    elif what == "rle-overrun":
+        write_psd(f, planes, rle=True)
+        d = bytearray(f.read_bytes())
+        d[44 + 2 * 12] = 100                                   # a literal packet longer than the channel
+    f.write_bytes(bytes(d))
+    assert H.stbi_loadf(str(f)) is None and S.decode_image(str(f)) is None

@@ -7,7 +7,7 @@ palettes of odd sizes, tRNS, interlace is not writable by Pillow and stays with 
 JPEG (quality 1-100, 4:4:4 / 4:2:2 / 4:2:0 / 4:1:1 / 4:4:0 subsampling, progressive, optimised tables, greyscale, CMYK and YCCK
 with the Adobe marker, restart intervals, sizes around the MCU edges), TGA (RLE or not, palettes, 8/24/32 bit), BMP (1/4/8/24/32
 bit), binary PGM / PPM (8 and 16 bit, hand-written headers), GIF (palette sizes, transparency, interlace, animation, larger
-screens with and without a background index, local palettes) and noisy as well as smooth pictures - and demands that `stbi_loadf(path, ..., 4)` of the reference (oracle/_ref/
+screens with and without a background index, local palettes), PSD (1-6 channels, 8 / 16 bit, raw / PackBits) and noisy as well as smooth pictures - and demands that `stbi_loadf(path, ..., 4)` of the reference (oracle/_ref/
 libref_host.so) and DecodeImageFile return the same float pixels bit for bit.
 
     python tools/fuzz_image_files.py [--files 1500] [--seed 1]
@@ -45,7 +45,7 @@ def write_random_file(rng, d, k):
     w = int(rng.choice([1, 2, 7, 8, 9, 15, 16, 17, 31, 33, 64, 100])) if rng.random() < 0.7 else int(rng.integers(1, 200))
     h = int(rng.choice([1, 2, 7, 8, 9, 15, 16, 17, 31, 33, 64, 100])) if rng.random() < 0.7 else int(rng.integers(1, 200))
     a = random_picture(rng, w, h)
-    fmt = rng.choice(["png", "jpg", "jpg", "tga", "bmp", "pnm", "gif"])
+    fmt = rng.choice(["png", "jpg", "jpg", "tga", "bmp", "pnm", "gif", "psd"])
     path = os.path.join(d, "f%05d.%s" % (k, fmt))
     if fmt == "png":
         mode = rng.choice(["L", "LA", "RGB", "RGBA", "P", "P-trns", "1", "I;16", "RGB-trns", "L-trns"])
@@ -117,6 +117,14 @@ def write_random_file(rng, d, k):
                 desc[9] |= 0x80 | (data[10] & 7)
                 data = data[:10] + bytes([data[10] & 0x7F]) + data[11:13] + data[table.stop:at] + desc + bytes(data[table]) + data[at + 10:]
         open(path, "wb").write(bytes(data))
+    elif fmt == "psd":                                         # flattened RGB image written by hand (tests/test_image_decode.py write_psd)
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import test_image_decode as T
+        c = int(rng.integers(1, 7))
+        deep = rng.random() < 0.3
+        planes = (rng.integers(0, 65536, size=(c, h, w)).astype(np.uint16) if deep else
+                  np.stack([random_picture(rng, w, h)[..., k % 4] for k in range(c)]).astype(np.uint8))
+        T.write_psd(path, planes, depth=16 if deep else 8, rle=(not deep) and rng.random() < 0.6, noop=rng.random() < 0.2)
     elif fmt == "pnm":                                         # binary P5 / P6, 8 and 16 bit, header written by hand
         grey, wide = bool(rng.integers(0, 2)), bool(rng.integers(0, 2))
         body = (rng.integers(0, 65536, size=(h, w, 1 if grey else 3)).astype(">u2") if wide else a[..., :1] if grey else a[..., :3]).tobytes()
