@@ -16,7 +16,7 @@
 //          followed so that 8-bit output is identical with the reference's.
 //   * TGA (types 1/2/3 and run-length 9/10/11; 8/15/16/24/32 bits) and BMP (1/4/8-bit paletted, 16/24/32-bit, BITFIELDS; no RLE),
 //          with stb_image's conversions (5-5-5 scaling, bit-field replication, the "all alpha zero means opaque" rule).
-//   * GIF (first frame, as stb_image composes it), PSD (flattened RGB image, raw or PackBits), PGM / PPM (binary P5 / P6, 8 and 16 bit) as stb_image reads them, quirks included (see decode_pnm_stb); PFM (PF, linear float,
+//   * GIF (first frame, as stb_image composes it), PSD (flattened RGB image, raw or PackBits), Softimage PIC, PGM / PPM (binary P5 / P6, 8 and 16 bit) as stb_image reads them, quirks included (see decode_pnm_stb); PFM (PF, linear float,
 //          rows bottom to top) is this repository's own addition.
 // 8-bit sources become float the way stbi_loadf does it (stb_image.h "ldr_to_hdr"): colour channels
 // pow(v / 255, 2.2), alpha v / 255.
@@ -1401,6 +1401,82 @@ bool decode_psd(const std::vector<u8>& f, int& W, int& H, std::vector<u8>& rgba)
     return true;
 }
 
+// ------------------------------------------------------------------ Softimage PIC, as stb_image reads it
+// stb_image.h stbi__pic_load / stbi__pic_load_core.  Magic 53 80 F6 34 and "PICT" at byte 88; width and height (big-endian 16 bit) at
+// byte 92; from byte 104 a chain of up to ten packets {chained, bits (8), type, channel mask: 0x80 R, 0x40 G, 0x20 B, 0x10 A}, then for
+// every row the data of every packet in turn: type 0 raw, 1 runs of {count, value}, 2 mixed (count >= 128: a run of count - 127, or of a
+// 16-bit count after 128; else count + 1 raw values).  Channels no packet carries stay 255.
+bool decode_pic(const std::vector<u8>& f, int& W, int& H, std::vector<u8>& rgba) {
+    if (f.size() < 104 || f[0] != 0x53 || f[1] != 0x80 || f[2] != 0xF6 || f[3] != 0x34 || std::memcmp(&f[88], "PICT", 4) != 0) return false;
+    size_t pos = 92;
+    auto at_end = [&]() { return pos >= f.size(); };
+    auto get8 = [&]() -> int { return pos < f.size() ? f[pos++] : 0; };
+    auto get16 = [&]() -> int { int a = get8(); return (a << 8) | get8(); };
+    const int w = get16(), h = get16();
+    if (at_end()) return false;
+    pos += 8;                                                  // ratio, fields, pad
+    struct packet { int size, type, channel; } packets[10];
+    int count = 0, chained;
+    do {
+        if (count == 10) return false;
+        packet& p = packets[count++];
+        chained = get8(); p.size = get8(); p.type = get8(); p.channel = get8();
+        if (at_end()) return false;
+        if (p.size != 8) return false;
+    } while (chained);
+    if (w == 0 || h == 0) return false;
+    rgba.assign((size_t)w * h * 4, 0xFF);
+    auto read_value = [&](int channel, u8* dest) {
+        for (int i = 0, mask = 0x80; i < 4; i++, mask >>= 1)
+            if (channel & mask) { if (at_end()) return false; dest[i] = (u8)get8(); }
+        return true;
+    };
+    auto copy_value = [](int channel, u8* dest, const u8* src) {
+        for (int i = 0, mask = 0x80; i < 4; i++, mask >>= 1) if (channel & mask) dest[i] = src[i];
+    };
+    for (int y = 0; y < h; y++)
+        for (int k = 0; k < count; k++) {
+            const packet& p = packets[k];
+            u8* dest = &rgba[(size_t)y * w * 4];
+            if (p.type == 0) {
+                for (int x = 0; x < w; x++, dest += 4) if (!read_value(p.channel, dest)) return false;
+            } else if (p.type == 1) {
+                int left = w;
+                while (left > 0) {
+                    int n = get8();
+                    if (at_end()) return false;
+                    if (n > left) n = (u8)left;
+                    u8 value[4] = {0, 0, 0, 0};
+                    if (!read_value(p.channel, value)) return false;
+                    for (int i = 0; i < n; i++, dest += 4) copy_value(p.channel, dest, value);
+                    left -= n;
+                }
+            } else if (p.type == 2) {
+                int left = w;
+                while (left > 0) {
+                    int n = get8();
+                    if (at_end()) return false;
+                    if (n >= 128) {
+                        n = n == 128 ? get16() : n - 127;
+                        if (n > left) return false;
+                        u8 value[4] = {0, 0, 0, 0};
+                        if (!read_value(p.channel, value)) return false;
+                        for (int i = 0; i < n; i++, dest += 4) copy_value(p.channel, dest, value);
+                    } else {
+                        n++;
+                        if (n > left) return false;
+                        for (int i = 0; i < n; i++, dest += 4) if (!read_value(p.channel, dest)) return false;
+                    }
+                    left -= n;
+                }
+            } else {
+                return false;
+            }
+        }
+    W = w; H = h;
+    return true;
+}
+
 // ------------------------------------------------------------------ PGM / PPM as stb_image reads them, and PFM
 // stb_image.h:7491-7618.  "P5" (grey) and "P6" (RGB), binary.  Header: width, height, maximum value, separated by blanks
 // (space, \t, \n, \v, \f, \r) and comments (# to the end of the line); ONE byte after the maximum value, then the samples.
@@ -1524,6 +1600,11 @@ bool DecodeImageFile(char const* Path, int& Width, int& Height, std::vector<vec4
     }
     if (file[0] == '8' && file[1] == 'B' && file[2] == 'P' && file[3] == 'S') {
         if (!decode_psd(file, Width, Height, rgba)) return false;
+        ldr_to_float(rgba, Pixels);
+        return true;
+    }
+    if (file.size() >= 92 && file[0] == 0x53 && file[1] == 0x80 && file[2] == 0xF6 && file[3] == 0x34 && std::memcmp(&file[88], "PICT", 4) == 0) {
+        if (!decode_pic(file, Width, Height, rgba)) return false;
         ldr_to_float(rgba, Pixels);
         return true;
     }

@@ -569,3 +569,66 @@ def test_psd_refused_like_stb_image(tmp_path, what):
         d[44 + 2 * 12] = 100                                   # a literal packet longer than the channel
     f.write_bytes(bytes(d))
     assert H.stbi_loadf(str(f)) is None and S.decode_image(str(f)) is None
+
+
+def write_pic(path, rgba, packets, rng):
+    """packets: list of (type, channel mask).  Rows are written packet by packet; type 1 / 2 with runs found in the data."""
+    h, w = rgba.shape[:2]
+    head = bytearray(104)
+    head[0:4] = b"\x53\x80\xf6\x34"
+    head[88:92] = b"PICT"
+    head[92:96] = struct.pack(">HH", w, h)
+    head[96:100] = struct.pack(">f", 1.0)
+    head[100:102] = struct.pack(">H", 3)
+    body = bytearray()
+    for k, (ptype, mask) in enumerate(packets):
+        body += bytes([1 if k + 1 < len(packets) else 0, 8, ptype, mask])
+    chans = lambda mask: [i for i in range(4) if mask & (0x80 >> i)]
+    for y in range(h):
+        for ptype, mask in packets:
+            px = [bytes(rgba[y, x, chans(mask)].tolist()) for x in range(w)]
+            x = 0
+            while x < w:
+                run = 1
+                while x + run < w and px[x + run] == px[x] and run < 200:
+                    run += 1
+                if ptype == 0:
+                    body += px[x]
+                    x += 1
+                elif ptype == 1:
+                    body += bytes([run]) + px[x]
+                    x += run
+                else:
+                    if run >= 3:
+                        if run > 128 or rng.random() < 0.2:
+                            body += bytes([128]) + struct.pack(">H", run) + px[x]
+                        else:
+                            body += bytes([run + 127]) + px[x]
+                        x += run
+                    else:
+                        n = 1
+                        while x + n < w and n < 100 and not (x + n + 2 < w and px[x + n] == px[x + n + 1] == px[x + n + 2]):
+                            n += 1
+                        body += bytes([n - 1]) + b"".join(px[x:x + n])
+                        x += n
+    with open(path, "wb") as f:
+        f.write(bytes(head) + bytes(body))
+
+
+@pytest.mark.parametrize("packets", [[(0, 0xE0)], [(1, 0xE0)], [(2, 0xE0)], [(2, 0xE0), (2, 0x10)], [(0, 0xF0)], [(1, 0x80), (2, 0x40), (0, 0x20)],
+                                     [(2, 0x10)], [(2, 0xC0), (1, 0x30)]])
+def test_pic_matches_stb_image(tmp_path, packets):
+    """stbi__pic_load: raw, pure run-length and mixed run-length packets, channels spread over packets, missing channels 255."""
+    rng = np.random.default_rng(len(packets))
+    a = picture(150, 9, 5)
+    a[2:5] = a[2:5, :1]                                        # flat rows: long runs (16-bit counts in mixed packets)
+    a[6, 10:40] = a[6, 10]
+    f = tmp_path / "t.pic"
+    write_pic(f, a, packets, rng)
+    out = same(f)
+    mask = 0
+    for _, m in packets:
+        mask |= m
+    for i in range(4):
+        if not mask & (0x80 >> i):
+            assert (out[..., i] == 1.0).all()

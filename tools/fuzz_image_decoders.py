@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Mutation fuzz of host/image.cpp (PNG / JPEG / Radiance HDR / TGA / BMP / PNM / GIF / PSD decoders) under AddressSanitizer + UBSan.  CPU only.
+"""Mutation fuzz of host/image.cpp (PNG / JPEG / Radiance HDR / TGA / BMP / PNM / GIF / PSD / PIC decoders) under AddressSanitizer + UBSan.  CPU only.
     cd path_tracer_b200/host && g++ -std=c++17 -O1 -g -fsanitize=address,undefined -I . -I ../../include -o /tmp/asan_img ../../tools/fuzz_image_decoders_main.cpp image.cpp -lz
     python tools/fuzz_image_decoders.py
 Round 2: 12 000 + 8 000 (TGA / BMP seeds) mutated files, no sanitizer report (two findings on the way, fixed: signed overflow in the IDCT on absurd
@@ -22,7 +22,7 @@ def add(name, im, **kw):
     p=os.path.join(d,name); im.save(p,**kw); seeds.append(open(p,"rb").read())
 add("a.tga", Image.fromarray(b[...,:3])); add("b.tga", Image.fromarray(b), compression="tga_rle")
 add("c.tga", Image.fromarray(b[...,:3]).quantize(17), compression="tga_rle"); add("d.tga", Image.fromarray(b[...,[0,3]],"LA"))
-T.write_psd(os.path.join(d,"p.psd"), np.ascontiguousarray(b.transpose(2,0,1)), rle=True); seeds.append(open(os.path.join(d,"p.psd"),"rb").read()); T.write_psd(os.path.join(d,"q.psd"), np.ascontiguousarray(b.transpose(2,0,1)).astype(np.uint16)*257, depth=16); seeds.append(open(os.path.join(d,"q.psd"),"rb").read()); add("k.jpg", Image.fromarray(b,"CMYK"), quality=70); add("a.gif", Image.fromarray(b[...,:3]).quantize(40)); add("b.gif", Image.fromarray(b[...,:3]).quantize(7), interlace=True, transparency=3); seeds.append(b"P6\n40 30\n255\n"+b[...,:3].tobytes()); seeds.append(b"P5 40 30 65535\n"+b[...,:2].tobytes()); add("a.bmp", Image.fromarray(b[...,:3])); add("b.bmp", Image.fromarray(b)); add("c.bmp", Image.fromarray(b[...,:3]).quantize(17)); add("d.bmp", Image.fromarray(b[...,0]>128))
+T.write_psd(os.path.join(d,"p.psd"), np.ascontiguousarray(b.transpose(2,0,1)), rle=True); seeds.append(open(os.path.join(d,"p.psd"),"rb").read()); T.write_psd(os.path.join(d,"q.psd"), np.ascontiguousarray(b.transpose(2,0,1)).astype(np.uint16)*257, depth=16); seeds.append(open(os.path.join(d,"q.psd"),"rb").read()); T.write_pic(os.path.join(d,"r.pic"), b, [(2,0xE0),(1,0x10)], rng); seeds.append(open(os.path.join(d,"r.pic"),"rb").read()); add("k.jpg", Image.fromarray(b,"CMYK"), quality=70); add("a.gif", Image.fromarray(b[...,:3]).quantize(40)); add("b.gif", Image.fromarray(b[...,:3]).quantize(7), interlace=True, transparency=3); seeds.append(b"P6\n40 30\n255\n"+b[...,:3].tobytes()); seeds.append(b"P5 40 30 65535\n"+b[...,:2].tobytes()); add("a.bmp", Image.fromarray(b[...,:3])); add("b.bmp", Image.fromarray(b)); add("c.bmp", Image.fromarray(b[...,:3]).quantize(17)); add("d.bmp", Image.fromarray(b[...,0]>128))
 files=[]
 for it in range(16000):
     s=bytearray(seeds[it%len(seeds)])

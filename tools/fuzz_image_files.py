@@ -7,7 +7,7 @@ palettes of odd sizes, tRNS, interlace is not writable by Pillow and stays with 
 JPEG (quality 1-100, 4:4:4 / 4:2:2 / 4:2:0 / 4:1:1 / 4:4:0 subsampling, progressive, optimised tables, greyscale, CMYK and YCCK
 with the Adobe marker, restart intervals, sizes around the MCU edges), TGA (RLE or not, palettes, 8/24/32 bit), BMP (1/4/8/24/32
 bit), binary PGM / PPM (8 and 16 bit, hand-written headers), GIF (palette sizes, transparency, interlace, animation, larger
-screens with and without a background index, local palettes), PSD (1-6 channels, 8 / 16 bit, raw / PackBits) and noisy as well as smooth pictures - and demands that `stbi_loadf(path, ..., 4)` of the reference (oracle/_ref/
+screens with and without a background index, local palettes), PSD (1-6 channels, 8 / 16 bit, raw / PackBits), Softimage PIC (raw / run-length / mixed packets) and noisy as well as smooth pictures - and demands that `stbi_loadf(path, ..., 4)` of the reference (oracle/_ref/
 libref_host.so) and DecodeImageFile return the same float pixels bit for bit.
 
     python tools/fuzz_image_files.py [--files 1500] [--seed 1]
@@ -45,7 +45,7 @@ def write_random_file(rng, d, k):
     w = int(rng.choice([1, 2, 7, 8, 9, 15, 16, 17, 31, 33, 64, 100])) if rng.random() < 0.7 else int(rng.integers(1, 200))
     h = int(rng.choice([1, 2, 7, 8, 9, 15, 16, 17, 31, 33, 64, 100])) if rng.random() < 0.7 else int(rng.integers(1, 200))
     a = random_picture(rng, w, h)
-    fmt = rng.choice(["png", "jpg", "jpg", "tga", "bmp", "pnm", "gif", "psd"])
+    fmt = rng.choice(["png", "jpg", "jpg", "tga", "bmp", "pnm", "gif", "psd", "pic"])
     path = os.path.join(d, "f%05d.%s" % (k, fmt))
     if fmt == "png":
         mode = rng.choice(["L", "LA", "RGB", "RGBA", "P", "P-trns", "1", "I;16", "RGB-trns", "L-trns"])
@@ -125,6 +125,11 @@ def write_random_file(rng, d, k):
         planes = (rng.integers(0, 65536, size=(c, h, w)).astype(np.uint16) if deep else
                   np.stack([random_picture(rng, w, h)[..., k % 4] for k in range(c)]).astype(np.uint8))
         T.write_psd(path, planes, depth=16 if deep else 8, rle=(not deep) and rng.random() < 0.6, noop=rng.random() < 0.2)
+    elif fmt == "pic":                                         # Softimage PIC written by hand (tests/test_image_decode.py write_pic)
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import test_image_decode as T
+        masks = [[0xE0], [0xF0], [0xE0, 0x10], [0x80, 0x40, 0x20], [0xC0, 0x30], [0x10], [0x80, 0x20]][rng.integers(0, 7)]
+        T.write_pic(path, a, [(int(rng.integers(0, 3)), m) for m in masks], rng)
     elif fmt == "pnm":                                         # binary P5 / P6, 8 and 16 bit, header written by hand
         grey, wide = bool(rng.integers(0, 2)), bool(rng.integers(0, 2))
         body = (rng.integers(0, 65536, size=(h, w, 1 if grey else 3)).astype(">u2") if wide else a[..., :1] if grey else a[..., :3]).tobytes()
