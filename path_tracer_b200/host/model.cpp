@@ -283,6 +283,9 @@ prefab* LoadModelAsPrefab(scene* Scene, char const* Path, load_model_options* Op
             triangulate(poly, Positions, S.corners);
             for (size_t k = before; k < S.corners.size(); k += 3) S.material_ids.push_back(CurrentMaterial);
         } else if (key == "o" || key == "g") {
+            // tinyobjloader takes `g` / `o` as a statement only when a blank FOLLOWS the letter: a bare "g" (or "g\r") is skipped
+            const size_t at = line.find_first_not_of(" \t");
+            if (at + 1 >= line.size() || (line[at + 1] != ' ' && line[at + 1] != '\t')) continue;
             std::string name = rest_of(ss);
             if (Shapes.back().corners.empty()) Shapes.back().name = name;
             else { Shapes.emplace_back(); Shapes.back().name = name; }

@@ -36,6 +36,21 @@ def number(rng, v):
         return "%e" % v
     if style == 3:
         return ("+" if v >= 0 else "") + "%.4f" % v
+    if rng.random() < 0.3:                                     # spellings exporters produce now and then: .5  5.  1E+2  -.25e-1  007.50
+        t = "%.4f" % v
+        neg, t = t.startswith("-"), t.lstrip("-")
+        form = rng.integers(0, 5)
+        if form == 0 and t.startswith("0."):
+            t = t[1:]
+        elif form == 1:
+            t = "%d." % int(abs(v))
+        elif form == 2:
+            t = ("%.3E" % abs(v))
+        elif form == 3:
+            t = ("%.2e" % abs(v)).replace("e-0", "e-").replace("e+0", "e+")
+        else:
+            t = "00" + t
+        return ("-" if neg else "") + t
     return "%d" % int(round(v * 4)) if rng.random() < 0.5 else "%.3f" % v
 
 
@@ -63,15 +78,19 @@ def write_random_obj(path, rng):
         has_vt, has_vn = rng.random() < 0.6, rng.random() < 0.5
         count = int(rng.integers(3, 40))
         centre = rng.normal(size=3) * 3
+        shape_colours = int(rng.choice([0, 0, 0, 1, 2]))
         for _ in range(count):
             v = centre + rng.normal(size=3)
-            lines.append("v " + " ".join(number(rng, x) for x in v) + (" " if rng.random() < 0.1 else ""))
+            extra = ""
+            if shape_colours:                                  # "v x y z r g b": vertex colours, or a weight as a fourth number
+                extra = " " + " ".join("%.3f" % c for c in rng.uniform(0, 1, 3 if shape_colours == 1 else 1))
+            lines.append("v " + " ".join(number(rng, x) for x in v) + extra + (" " if rng.random() < 0.1 else ""))
         if rng.random() < 0.15:                                # exact duplicates: welded or not, like the reference
             lines.append(lines[-1])
             count += 1
         ct = int(rng.integers(1, count + 1)) if has_vt else 0
         for _ in range(ct):
-            lines.append("vt " + " ".join(number(rng, x) for x in rng.uniform(-0.5, 1.5, 2)))
+            lines.append("vt " + " ".join(number(rng, x) for x in rng.uniform(-0.5, 1.5, 3 if rng.random() < 0.2 else 2)))
         cn = int(rng.integers(1, count + 1)) if has_vn else 0
         for _ in range(cn):
             n = rng.normal(size=3)
@@ -83,6 +102,8 @@ def write_random_obj(path, rng):
         for f in range(int(rng.integers(0, 30))):
             if n_mats and rng.random() < 0.25:
                 lines.append("usemtl m%d" % rng.integers(0, n_mats))
+            if rng.random() < 0.08:                            # statements an importer has to step over
+                lines.append(rng.choice(["l 1 2 3", "p 1", "usemap off", "mg 1 0.5", "# a comment", "bevel on", "vp 0.5 0.5", "g", "   "]))
             k = int(rng.choice([3, 3, 3, 4, 4, 5, 6]))
             vs = rng.integers(0, count, size=k) if rng.random() < 0.1 else rng.permutation(count)[:k]
             relative = rng.random() < 0.3
