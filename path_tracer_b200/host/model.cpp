@@ -295,7 +295,20 @@ prefab* LoadModelAsPrefab(scene* Scene, char const* Path, load_model_options* Op
             auto it = MaterialIndex.find(name);
             CurrentMaterial = it == MaterialIndex.end() ? -1 : it->second;
         } else if (key == "mtllib") {
-            load_mtl(Directory + "/" + rest_of(ss), FileMaterials, MaterialIndex);
+            // tinyobjloader: several file names separated by blanks (a backslash escapes one), the first that loads wins
+            const std::string all = rest_of(ss);
+            std::vector<std::string> names;
+            std::string cur_name;
+            bool escaping = false;
+            for (char ch : all) {
+                if (escaping) escaping = false;
+                else if (ch == '\\') { escaping = true; continue; }
+                else if (ch == ' ') { if (!cur_name.empty()) names.push_back(cur_name); cur_name.clear(); continue; }
+                cur_name += ch;
+            }
+            names.push_back(cur_name);
+            for (std::string const& n : names)
+                if (load_mtl(Directory + "/" + n, FileMaterials, MaterialIndex)) break;
         }
     }
 

@@ -70,7 +70,7 @@ def write_random_obj(path, rng):
                     if rng.random() < (0.6 if key == "map_Kd" else 0.25):
                         opts = rng.choice(["", "", "-s 2 2 1 ", "-o 0.5 0 0 -s 1 1 1 ", "-clamp on ", "-blendu off -mm 0 1 ", "-bm 0.5 ", "-colorspace sRGB "])
                         m.write("%s %s%s%s\n" % (key, opts, names[rng.integers(0, len(names))], "  " if rng.random() < 0.2 else ""))
-        lines.append("mtllib f.mtl")
+        lines.append("mtllib f.mtl" if rng.random() < 0.8 else "mtllib nothere.mtl f.mtl")
     nv = nt = nn = 0
     for shape in range(int(rng.integers(1, 5))):
         if rng.random() < 0.8:
@@ -101,7 +101,9 @@ def write_random_obj(path, rng):
             lines.append("")
         for f in range(int(rng.integers(0, 30))):
             if n_mats and rng.random() < 0.25:
-                lines.append("usemtl m%d" % rng.integers(0, n_mats))
+                lines.append("usemtl m%d" % rng.integers(0, n_mats + (1 if rng.random() < 0.2 else 0)))      # now and then a name the MTL does not define
+            if rng.random() < 0.03:
+                lines.append("f %d %d" % (nv + 1, nv + 2))         # a "face" of two corners: dropped
             if rng.random() < 0.08:                            # statements an importer has to step over
                 lines.append(rng.choice(["l 1 2 3", "p 1", "usemap off", "mg 1 0.5", "# a comment", "bevel on", "vp 0.5 0.5", "g", "   "]))
             k = int(rng.choice([3, 3, 3, 4, 4, 5, 6]))
@@ -122,8 +124,11 @@ def write_random_obj(path, rng):
                     toks.append("%d" % a)
             lines.append("f " + " ".join(toks))
         nv, nt, nn = nv + count, nt + ct, nn + cn
-    with open(path, "w") as o:
-        o.write("\n".join(lines) + "\n")
+    eol = "\r\n" if rng.random() < 0.25 else "\n"           # files from Windows exporters
+    if rng.random() < 0.2:
+        lines = [l.replace(" ", "\t") if l[:2] in ("v ", "f ", "vt", "vn") and rng.random() < 0.5 else l for l in lines]
+    with open(path, "w", newline="") as o:
+        o.write(eol.join(lines) + (eol if rng.random() < 0.9 else ""))
 
 
 def main(argv=None):
